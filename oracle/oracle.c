@@ -1,0 +1,871 @@
+/*
+ * oracle.c — CPU restatement of the stark-mlwe commitment hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under stark_mlwe_b200/ may include, link or
+ * call this file; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs use it, and only as the checker / CPU baseline.
+ *
+ * It follows the reference (saholmes/stark-mlwe, mounted at /root/reference, pure
+ * Rust, which cannot be compiled in this image: no cargo/rustc) function by
+ * function; each block cites the file:line it restates.  Third-party arithmetic
+ * that is not under /root/reference is restated from its published algorithm:
+ *   ark-ff 0.5.0 / ark-pallas 0.5.0 (Fp256 Montgomery, R = 2^256, `F::rand`),
+ *   ark-poly 0.5.0 (Radix2EvaluationDomain fft/ifft conventions),
+ *   blake3 1.8.2, rand 0.8.5 + rand_chacha 0.3.1 (StdRng = ChaCha12),
+ *   rand_core 0.6.4 (SeedableRng::seed_from_u64 = PCG32 expansion).
+ *
+ * Parity pin: the reference's own `crates/channel/benchmarkdata.csv` column
+ * `proof_bytes` (k = 11..18) is reproduced by orc_deep_fri_prove_size() on the
+ * bench's seeded inputs (tests/test_oracle_kat.py); see DESIGN.md "Oracle".
+ *
+ * Arithmetic here is deliberately different from the CUDA product (4x64-bit limbs,
+ * CIOS with unsigned __int128, dense matrix in every round, no lazy reduction).
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdio.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+typedef uint8_t u8;
+typedef unsigned __int128 u128;
+
+typedef struct { u64 l[4]; } fr;   /* Montgomery form, little-endian limbs: same memory as ark-ff Fp256 */
+
+/* ------------------------------------------------------------------ field --
+ * Pallas scalar field (field/src/lib.rs:13 `ark_pallas::Fr`).                */
+static const u64 P[4] = {0x8c46eb2100000001ULL, 0x224698fc0994a8ddULL, 0x0ULL, 0x4000000000000000ULL};
+static const u64 PINV = 0x8c46eb20ffffffffULL;  /* -p^-1 mod 2^64 */
+static fr FR_R, FR_R2, FR_ZERO, FR_TWO_ADIC_ROOT;
+static int g_init = 0;
+
+static inline int ge_p(const u64 a[4]) {
+    for (int i = 3; i >= 0; i--) { if (a[i] > P[i]) return 1; if (a[i] < P[i]) return 0; }
+    return 1;
+}
+static inline void sub_p(u64 a[4]) {
+    u128 b = 0;
+    for (int i = 0; i < 4; i++) { u128 d = (u128)a[i] - P[i] - (u64)b; a[i] = (u64)d; b = (d >> 64) & 1; }
+}
+static inline fr fr_add(fr a, fr b) {
+    fr r; u128 c = 0;
+    for (int i = 0; i < 4; i++) { c += (u128)a.l[i] + b.l[i]; r.l[i] = (u64)c; c >>= 64; }
+    /* p < 2^255 so no carry out of 256 bits for canonical inputs */
+    if (ge_p(r.l)) sub_p(r.l);
+    return r;
+}
+static inline fr fr_sub(fr a, fr b) {
+    fr r; u128 bw = 0;
+    for (int i = 0; i < 4; i++) { u128 d = (u128)a.l[i] - b.l[i] - (u64)bw; r.l[i] = (u64)d; bw = (d >> 64) & 1; }
+    if (bw) { u128 c = 0; for (int i = 0; i < 4; i++) { c += (u128)r.l[i] + P[i]; r.l[i] = (u64)c; c >>= 64; } }
+    return r;
+}
+/* CIOS Montgomery product, R = 2^256 */
+static inline fr fr_mul(fr a, fr b) {
+    u64 t[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < 4; i++) {
+        u128 c = 0;
+        for (int j = 0; j < 4; j++) { c += (u128)a.l[j] * b.l[i] + t[j]; t[j] = (u64)c; c >>= 64; }
+        c += t[4]; t[4] = (u64)c; t[5] = (u64)(c >> 64);
+        u64 m = t[0] * PINV;
+        c = (u128)m * P[0] + t[0]; c >>= 64;
+        for (int j = 1; j < 4; j++) { c += (u128)m * P[j] + t[j]; t[j - 1] = (u64)c; c >>= 64; }
+        c += t[4]; t[3] = (u64)c; t[4] = t[5] + (u64)(c >> 64);
+    }
+    fr r = {{t[0], t[1], t[2], t[3]}};
+    if (t[4] || ge_p(r.l)) sub_p(r.l);
+    return r;
+}
+static inline fr fr_sqr(fr a) { return fr_mul(a, a); }
+static inline int fr_eq(fr a, fr b) { return a.l[0] == b.l[0] && a.l[1] == b.l[1] && a.l[2] == b.l[2] && a.l[3] == b.l[3]; }
+static inline int fr_is_zero(fr a) { return (a.l[0] | a.l[1] | a.l[2] | a.l[3]) == 0; }
+static inline fr fr_from_canon(const u64 c[4]) { fr x = {{c[0], c[1], c[2], c[3]}}; return fr_mul(x, FR_R2); }
+static inline void fr_to_canon(fr a, u64 out[4]) { fr one = {{1, 0, 0, 0}}; fr r = fr_mul(a, one); memcpy(out, r.l, 32); }
+static inline fr fr_from_u64(u64 v) { u64 c[4] = {v, 0, 0, 0}; return fr_from_canon(c); }
+static fr fr_pow_u64(fr a, u64 e) {
+    fr r = FR_R;
+    for (int i = 63; i >= 0; i--) { r = fr_sqr(r); if ((e >> i) & 1) r = fr_mul(r, a); }
+    return r;
+}
+static fr fr_pow_limbs(fr a, const u64 e[4]) {
+    fr r = FR_R;
+    for (int i = 255; i >= 0; i--) { r = fr_sqr(r); if ((e[i / 64] >> (i % 64)) & 1) r = fr_mul(r, a); }
+    return r;
+}
+static fr fr_inv(fr a) { /* Fermat: a^(p-2) */
+    u64 e[4] = {P[0] - 2, P[1], P[2], P[3]};
+    return fr_pow_limbs(a, e);
+}
+/* ark-ff `from_le_bytes_mod_order` on <= 64 bytes: little-endian integer mod p.
+ * Horner over bytes from the most significant end. */
+static fr fr_from_le_bytes_mod_order(const u8* b, size_t n) {
+    fr acc = FR_ZERO;
+    fr c256 = fr_from_u64(256);
+    for (size_t i = n; i-- > 0;) { acc = fr_mul(acc, c256); acc = fr_add(acc, fr_from_u64(b[i])); }
+    return acc;
+}
+
+void orc_init(void) {
+    if (g_init) return;
+    memset(&FR_ZERO, 0, sizeof FR_ZERO);
+    /* R = 2^256 mod p by repeated doubling of 1 (non-Montgomery arithmetic) */
+    fr x = {{1, 0, 0, 0}};
+    fr r1 = x, r2;
+    for (int i = 0; i < 512; i++) {
+        u128 c = 0; fr d;
+        for (int j = 0; j < 4; j++) { c += (u128)x.l[j] * 2; d.l[j] = (u64)c; c >>= 64; }
+        if (c || ge_p(d.l)) sub_p(d.l);
+        x = d;
+        if (i == 255) r1 = x;
+    }
+    r2 = x;
+    FR_R = r1; FR_R2 = r2;
+    /* TWO_ADIC_ROOT_OF_UNITY = 5^((p-1)/2^32)  (ark-pallas FrConfig: GENERATOR = 5, TWO_ADICITY = 32) */
+    u64 e[4];
+    e[0] = (P[0] >> 32) | (P[1] << 32); e[1] = (P[1] >> 32) | (P[2] << 32);
+    e[2] = (P[2] >> 32) | (P[3] << 32); e[3] = P[3] >> 32;
+    g_init = 1;
+    FR_TWO_ADIC_ROOT = fr_pow_limbs(fr_from_u64(5), e);
+}
+void orc_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+int orc_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+void orc_to_mont(const u64* canon, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr r = fr_from_canon(canon + 4 * i); memcpy(out + 4 * i, r.l, 32); } }
+void orc_from_mont(const u64* mont, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr a; memcpy(a.l, mont + 4 * i, 32); fr_to_canon(a, out + 4 * i); } }
+void orc_fr_mul(const u64* a, const u64* b, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr x, y; memcpy(x.l, a + 4 * i, 32); memcpy(y.l, b + 4 * i, 32); fr r = fr_mul(x, y); memcpy(out + 4 * i, r.l, 32); } }
+void orc_fr_add(const u64* a, const u64* b, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr x, y; memcpy(x.l, a + 4 * i, 32); memcpy(y.l, b + 4 * i, 32); fr r = fr_add(x, y); memcpy(out + 4 * i, r.l, 32); } }
+void orc_fr_sub(const u64* a, const u64* b, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr x, y; memcpy(x.l, a + 4 * i, 32); memcpy(y.l, b + 4 * i, 32); fr r = fr_sub(x, y); memcpy(out + 4 * i, r.l, 32); } }
+void orc_fr_inv(const u64* a, u64* out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) { fr x; memcpy(x.l, a + 4 * i, 32); fr r = fr_inv(x); memcpy(out + 4 * i, r.l, 32); } }
+/* field/src/lib.rs:43-53 Domain::new -> F::get_root_of_unity(n): two-adic root squared (32 - log n) times */
+static fr root_of_unity(int log_n) { fr w = FR_TWO_ADIC_ROOT; for (int i = log_n; i < 32; i++) w = fr_sqr(w); return w; }
+void orc_root_of_unity(int log_n, u64* out) { orc_init(); fr w = root_of_unity(log_n); memcpy(out, w.l, 32); }
+
+/* ----------------------------------------------------------------- BLAKE3 --
+ * blake3 1.8.2, default hash mode, inputs up to one chunk (1024 bytes): every
+ * derivation input on this path is <= 58 bytes (utils/src/lib.rs:16-22).      */
+static const u32 B3_IV[8] = {0x6A09E667, 0xBB67AE85, 0x3C6EF372, 0xA54FF53A, 0x510E527F, 0x9B05688C, 0x1F83D9AB, 0x5BE0CD19};
+static const u8 B3_PERM[16] = {2, 6, 3, 10, 7, 0, 4, 13, 1, 11, 12, 5, 9, 14, 15, 8};
+static inline u32 rotr32(u32 x, int n) { return (x >> n) | (x << (32 - n)); }
+static inline void b3_g(u32* s, int a, int b, int c, int d, u32 mx, u32 my) {
+    s[a] = s[a] + s[b] + mx; s[d] = rotr32(s[d] ^ s[a], 16);
+    s[c] = s[c] + s[d];      s[b] = rotr32(s[b] ^ s[c], 12);
+    s[a] = s[a] + s[b] + my; s[d] = rotr32(s[d] ^ s[a], 8);
+    s[c] = s[c] + s[d];      s[b] = rotr32(s[b] ^ s[c], 7);
+}
+static void b3_compress(const u32 cv[8], const u32 block[16], u64 counter, u32 blen, u32 flags, u32 out[16]) {
+    u32 s[16], m[16], t[16];
+    for (int i = 0; i < 8; i++) s[i] = cv[i];
+    for (int i = 0; i < 4; i++) s[8 + i] = B3_IV[i];
+    s[12] = (u32)counter; s[13] = (u32)(counter >> 32); s[14] = blen; s[15] = flags;
+    memcpy(m, block, 64);
+    for (int r = 0; r < 7; r++) {
+        b3_g(s, 0, 4, 8, 12, m[0], m[1]);   b3_g(s, 1, 5, 9, 13, m[2], m[3]);
+        b3_g(s, 2, 6, 10, 14, m[4], m[5]);  b3_g(s, 3, 7, 11, 15, m[6], m[7]);
+        b3_g(s, 0, 5, 10, 15, m[8], m[9]);  b3_g(s, 1, 6, 11, 12, m[10], m[11]);
+        b3_g(s, 2, 7, 8, 13, m[12], m[13]); b3_g(s, 3, 4, 9, 14, m[14], m[15]);
+        for (int i = 0; i < 16; i++) t[i] = m[B3_PERM[i]];
+        memcpy(m, t, 64);
+    }
+    for (int i = 0; i < 8; i++) { out[i] = s[i] ^ s[i + 8]; out[i + 8] = s[i + 8] ^ cv[i]; }
+}
+void orc_blake3(const u8* in, size_t len, u8 out[32]) {
+    enum { CHUNK_START = 1, CHUNK_END = 2, ROOT = 8 };
+    if (len > 1024) { fprintf(stderr, "orc_blake3: input > 1 chunk unsupported\n"); abort(); }
+    u32 cv[8]; memcpy(cv, B3_IV, 32);
+    size_t nblocks = len == 0 ? 1 : (len + 63) / 64;
+    for (size_t b = 0; b < nblocks; b++) {
+        u8 blk[64]; memset(blk, 0, 64);
+        size_t off = b * 64, bl = len - off > 64 ? 64 : len - off;
+        memcpy(blk, in + off, bl);
+        u32 words[16];
+        for (int i = 0; i < 16; i++) words[i] = (u32)blk[4 * i] | ((u32)blk[4 * i + 1] << 8) | ((u32)blk[4 * i + 2] << 16) | ((u32)blk[4 * i + 3] << 24);
+        u32 flags = (b == 0 ? CHUNK_START : 0) | (b == nblocks - 1 ? (CHUNK_END | ROOT) : 0);
+        u32 o[16];
+        b3_compress(cv, words, 0, (u32)bl, flags, o);
+        memcpy(cv, o, 32);
+    }
+    for (int i = 0; i < 8; i++) { out[4 * i] = (u8)cv[i]; out[4 * i + 1] = (u8)(cv[i] >> 8); out[4 * i + 2] = (u8)(cv[i] >> 16); out[4 * i + 3] = (u8)(cv[i] >> 24); }
+}
+/* utils/src/lib.rs:7-22: fr_from_hash(tag, data) = LE(BLAKE3(tag||data)) zero-extended to 64 bytes, mod p */
+static fr fr_from_hash(const char* tag, const u8* data, size_t len) {
+    u8 buf[1024]; size_t tl = strlen(tag);
+    memcpy(buf, tag, tl); memcpy(buf + tl, data, len);
+    u8 h[64]; memset(h, 0, 64);
+    orc_blake3(buf, tl + len, h);
+    return fr_from_le_bytes_mod_order(h, 64);
+}
+void orc_fr_from_hash(const char* tag, const u8* data, size_t len, u64* out) { orc_init(); fr r = fr_from_hash(tag, data, len); memcpy(out, r.l, 32); }
+
+/* -------------------------------------------------------------------- RNG --
+ * rand 0.8.5 StdRng = rand_chacha 0.3.1 ChaCha12Rng: key = seed, 64-bit block
+ * counter (words 12,13) from 0, stream id 0; BlockRng buffers 4 blocks (64 u32);
+ * next_u64 = lo | hi << 32 from two consecutive words.                          */
+typedef struct { u32 key[8]; u64 counter; u32 buf[64]; int idx; } stdrng;
+static inline u32 rotl32(u32 x, int n) { return (x << n) | (x >> (32 - n)); }
+#define QR(a, b, c, d) a += b; d ^= a; d = rotl32(d, 16); c += d; b ^= c; b = rotl32(b, 12); a += b; d ^= a; d = rotl32(d, 8); c += d; b ^= c; b = rotl32(b, 7);
+static void chacha12_block(const u32 key[8], u64 ctr, u32 out[16]) {
+    u32 s[16] = {0x61707865, 0x3320646e, 0x79622d32, 0x6b206574, key[0], key[1], key[2], key[3], key[4], key[5], key[6], key[7], (u32)ctr, (u32)(ctr >> 32), 0, 0};
+    u32 x[16]; memcpy(x, s, 64);
+    for (int r = 0; r < 6; r++) {
+        QR(x[0], x[4], x[8], x[12]) QR(x[1], x[5], x[9], x[13]) QR(x[2], x[6], x[10], x[14]) QR(x[3], x[7], x[11], x[15])
+        QR(x[0], x[5], x[10], x[15]) QR(x[1], x[6], x[11], x[12]) QR(x[2], x[7], x[8], x[13]) QR(x[3], x[4], x[9], x[14])
+    }
+    for (int i = 0; i < 16; i++) out[i] = x[i] + s[i];
+}
+static void rng_refill(stdrng* g) { for (int b = 0; b < 4; b++) chacha12_block(g->key, g->counter + b, g->buf + 16 * b); g->counter += 4; g->idx = 0; }
+static void rng_from_seed(stdrng* g, const u8 seed[32]) {
+    for (int i = 0; i < 8; i++) g->key[i] = (u32)seed[4 * i] | ((u32)seed[4 * i + 1] << 8) | ((u32)seed[4 * i + 2] << 16) | ((u32)seed[4 * i + 3] << 24);
+    g->counter = 0; g->idx = 64;
+}
+/* rand_core 0.6.4 SeedableRng::seed_from_u64 (PCG32 expansion) */
+static void rng_seed_from_u64(stdrng* g, u64 state) {
+    const u64 MUL = 6364136223846793005ULL, INC = 11634580027462260723ULL;
+    u8 seed[32];
+    for (int i = 0; i < 8; i++) {
+        state = state * MUL + INC;
+        u32 xs = (u32)(((state >> 18) ^ state) >> 27); u32 rot = (u32)(state >> 59);
+        u32 x = (xs >> rot) | (xs << ((32 - rot) & 31));
+        seed[4 * i] = (u8)x; seed[4 * i + 1] = (u8)(x >> 8); seed[4 * i + 2] = (u8)(x >> 16); seed[4 * i + 3] = (u8)(x >> 24);
+    }
+    rng_from_seed(g, seed);
+}
+static u64 rng_next_u64(stdrng* g) {
+    /* rand_core BlockRng::next_u64 */
+    if (g->idx < 63) { u64 v = (u64)g->buf[g->idx] | ((u64)g->buf[g->idx + 1] << 32); g->idx += 2; return v; }
+    if (g->idx >= 64) { rng_refill(g); u64 v = (u64)g->buf[0] | ((u64)g->buf[1] << 32); g->idx = 2; return v; }
+    u64 lo = g->buf[63]; rng_refill(g); u64 hi = g->buf[0]; g->idx = 1; return lo | (hi << 32);
+}
+/* ark-ff 0.5.0 `impl Distribution<Fp> for Standard`: 4 u64 limbs, mask top bit(s), reject >= p;
+ * the accepted raw limbs ARE the Montgomery representation. */
+static fr rng_fr_rand(stdrng* g) {
+    for (;;) {
+        fr x; for (int i = 0; i < 4; i++) x.l[i] = rng_next_u64(g);
+        x.l[3] &= 0x7fffffffffffffffULL;
+        if (!ge_p(x.l)) return x;
+    }
+}
+void* orc_rng_seed_from_u64(u64 s) { stdrng* g = malloc(sizeof *g); rng_seed_from_u64(g, s); return g; }
+void* orc_rng_from_seed(const u8* seed) { stdrng* g = malloc(sizeof *g); rng_from_seed(g, seed); return g; }
+u64 orc_rng_next_u64(void* g) { return rng_next_u64((stdrng*)g); }
+void orc_rng_fr_rand(void* g, u64* out, size_t n) { for (size_t i = 0; i < n; i++) { fr x = rng_fr_rand((stdrng*)g); memcpy(out + 4 * i, x.l, 32); } }
+void orc_rng_free(void* g) { free(g); }
+
+/* --------------------------------------------------------------- Poseidon --
+ * poseidon/src/lib.rs:104-114 PoseidonParamsDynamic; :176-216 derive_*;
+ * :318-356 generate_params_t17_x5 (same derivation, seed supplied).            */
+typedef struct { int t, rf, rp; fr* mds; fr* rc_full; fr* rc_partial; } pparams;
+
+static void put_u64le(u8* p, u64 v) { for (int i = 0; i < 8; i++) p[i] = (u8)(v >> (8 * i)); }
+void* orc_params_new(const u8* seed, size_t seed_len, int t, int rp) {
+    orc_init();
+    pparams* pp = malloc(sizeof *pp);
+    pp->t = t; pp->rf = 8; pp->rp = rp;
+    pp->mds = malloc(sizeof(fr) * t * t); pp->rc_full = malloc(sizeof(fr) * 8 * t); pp->rc_partial = malloc(sizeof(fr) * rp);
+    u8 data[256];
+    for (int i = 0; i < t; i++) for (int j = 0; j < t; j++) {
+        put_u64le(data, i); put_u64le(data + 8, j); memcpy(data + 16, seed, seed_len);
+        pp->mds[i * t + j] = fr_from_hash("POSEIDON-MDS", data, 16 + seed_len);
+    }
+    for (int r = 0; r < 8; r++) for (int i = 0; i < t; i++) {
+        put_u64le(data, r); put_u64le(data + 8, i); memcpy(data + 16, seed, seed_len);
+        pp->rc_full[r * t + i] = fr_from_hash("POSEIDON-RC-FULL", data, 16 + seed_len);
+    }
+    for (int r = 0; r < rp; r++) {
+        put_u64le(data, r); memcpy(data + 8, seed, seed_len);
+        pp->rc_partial[r] = fr_from_hash("POSEIDON-RC-PART", data, 8 + seed_len);
+    }
+    return pp;
+}
+/* poseidon/src/lib.rs:120-146 poseidon_params_for_width; :168-174 seed_for_t */
+void* orc_params_for_width(int t) {
+    int rp;
+    switch (t) { case 9: rp = 60; break; case 17: rp = 64; break; case 33: rp = 68; break; case 65: rp = 76; break; case 129: rp = 84; break; default: return NULL; }
+    u8 seed[32]; memcpy(seed, "POSEIDON-PALLAS-T", 17); put_u64le(seed + 17, (u64)t);
+    return orc_params_new(seed, 25, t, rp);
+}
+/* poseidon/src/lib.rs:155-166 poseidon_params_for_arity */
+int orc_width_for_arity(int arity) {
+    if (arity <= 8) return 9; if (arity <= 16) return 17; if (arity <= 32) return 33; if (arity <= 64) return 65; if (arity <= 128) return 129; return -1;
+}
+void* orc_params_for_arity(int arity) { int t = orc_width_for_arity(arity); return t < 0 ? NULL : orc_params_for_width(t); }
+void orc_params_free(void* h) { pparams* p = h; if (!p) return; free(p->mds); free(p->rc_full); free(p->rc_partial); free(p); }
+int orc_params_t(void* h) { return ((pparams*)h)->t; }
+int orc_params_rp(void* h) { return ((pparams*)h)->rp; }
+void orc_params_export(void* h, u64* mds, u64* rc_full, u64* rc_partial) {
+    pparams* p = h;
+    if (mds) memcpy(mds, p->mds, sizeof(fr) * p->t * p->t);
+    if (rc_full) memcpy(rc_full, p->rc_full, sizeof(fr) * 8 * p->t);
+    if (rc_partial) memcpy(rc_partial, p->rc_partial, sizeof(fr) * p->rp);
+}
+
+static inline fr sbox5(fr x) { fr x2 = fr_sqr(x); fr x4 = fr_sqr(x2); return fr_mul(x, x4); } /* poseidon/src/lib.rs:24-29 */
+/* poseidon/src/lib.rs:260-272 mds_mul_dynamic_in_place: dense t x t in every round */
+static void mds_mul(const pparams* p, fr* s) {
+    int t = p->t; fr out[129];
+    for (int i = 0; i < t; i++) { fr acc = FR_ZERO; const fr* row = p->mds + i * t; for (int j = 0; j < t; j++) acc = fr_add(acc, fr_mul(row[j], s[j])); out[i] = acc; }
+    memcpy(s, out, sizeof(fr) * t);
+}
+/* poseidon/src/lib.rs:219-258 permute_dynamic (== :31-68 permute for t = 17) */
+static void permute(const pparams* p, fr* s) {
+    int t = p->t, half = p->rf / 2;
+    for (int r = 0; r < half; r++) { for (int i = 0; i < t; i++) s[i] = fr_add(s[i], p->rc_full[r * t + i]); for (int i = 0; i < t; i++) s[i] = sbox5(s[i]); mds_mul(p, s); }
+    for (int r = 0; r < p->rp; r++) { s[0] = fr_add(s[0], p->rc_partial[r]); s[0] = sbox5(s[0]); mds_mul(p, s); }
+    for (int r = half; r < p->rf; r++) { for (int i = 0; i < t; i++) s[i] = fr_add(s[i], p->rc_full[r * t + i]); for (int i = 0; i < t; i++) s[i] = sbox5(s[i]); mds_mul(p, s); }
+}
+void orc_permute(void* h, u64* state, size_t batch) {
+    pparams* p = h;
+#pragma omp parallel for schedule(static)
+    for (size_t b = 0; b < batch; b++) permute(p, (fr*)(state + 4 * p->t * b));
+}
+/* poseidon/src/lib.rs:276-312 absorb_one + hash_with_ds_dynamic */
+static fr hash_with_ds_dynamic(const pparams* p, const fr* ds, int nds, const fr* in, size_t n) {
+    fr s[129]; int t = p->t, rate = t - 1, cur = 0;
+    for (int i = 0; i < t; i++) s[i] = FR_ZERO;
+#define ABSORB(x) do { s[cur] = fr_add(s[cur], (x)); if (++cur == rate) { cur = 0; permute(p, s); } } while (0)
+    for (int i = 0; i < nds; i++) ABSORB(ds[i]);
+    for (size_t i = 0; i < n; i++) ABSORB(in[i]);
+    ABSORB(FR_R);
+    while (cur != 0) ABSORB(FR_ZERO);
+#undef ABSORB
+    return s[0];
+}
+void orc_hash_with_ds_dynamic(void* h, const u64* ds, int nds, const u64* in, size_t n, u64* out) {
+    fr r = hash_with_ds_dynamic(h, (const fr*)ds, nds, (const fr*)in, n); memcpy(out, r.l, 32);
+}
+/* poseidon/src/lib.rs:85-100 hash_with_ds (legacy, t = 17) */
+void orc_hash_with_ds_legacy(void* h, const u64* in, size_t n, const u64* ds_tag, u64* out) {
+    pparams* p = h; fr s[17];
+    for (int i = 0; i < 17; i++) s[i] = FR_ZERO;
+    memcpy(s[16].l, ds_tag, 32);
+    for (size_t off = 0; off < n; off += 16) { size_t c = n - off < 16 ? n - off : 16; for (size_t i = 0; i < c; i++) s[i] = fr_add(s[i], ((const fr*)in)[off + i]); permute(p, s); }
+    memcpy(out, s[0].l, 32);
+}
+
+/* ------------------------------------------------------------- Transcript --
+ * transcript/src/lib.rs:13-117                                                */
+typedef struct { fr state[17]; int pos; const pparams* p; } transcript;
+static pparams* g_tr_params = NULL;      /* transcript::default_params(), :44-46 */
+static pparams* g_commit_params = NULL;  /* commitment::default_params(), commitment/src/lib.rs:48-51 */
+static const pparams* tr_default_params(void) {
+    orc_init();
+    pparams* q;
+#pragma omp critical(orc_trp)
+    { if (!g_tr_params) g_tr_params = orc_params_new((const u8*)"POSEIDON-T17-X5-TRANSCRIPT", 26, 17, 64); q = g_tr_params; }
+    return q;
+}
+static const pparams* commit_default_params(void) {
+    orc_init();
+    pparams* q;
+#pragma omp critical(orc_cmp)
+    { if (!g_commit_params) g_commit_params = orc_params_new((const u8*)"POSEIDON-T17-X5-SEED", 20, 17, 64); q = g_commit_params; }
+    return q;
+}
+void* orc_transcript_default_params(void) { return (void*)tr_default_params(); }
+void* orc_commitment_default_params(void) { return (void*)commit_default_params(); }
+/* :13-30 domain_tag_to_field */
+static fr domain_tag_to_field(const u8* tag, size_t n) {
+    if (n <= 32) { u8 le[32]; memset(le, 0, 32); memcpy(le, tag, n); return fr_from_le_bytes_mod_order(le, 32); }
+    fr acc = FR_ZERO;
+    for (size_t off = 0; off < n; off += 32) { u8 le[32]; memset(le, 0, 32); size_t c = n - off < 32 ? n - off : 32; memcpy(le, tag + off, c); acc = fr_add(acc, fr_from_le_bytes_mod_order(le, 32)); }
+    return acc;
+}
+static void tr_absorb_field(transcript* T, fr x) { /* :79-88 */
+    if (T->pos == 16) { permute(T->p, T->state); T->pos = 0; }
+    T->state[T->pos] = fr_add(T->state[T->pos], x); T->pos++;
+}
+static void tr_absorb_bytes(transcript* T, const u8* b, size_t n) { /* :67-73 with :33-41 bytes_to_field_words */
+    tr_absorb_field(T, domain_tag_to_field((const u8*)"FSv1-ABSORB-BYTES", 17));
+    for (size_t off = 0; off < n; off += 31) { u8 le[32]; memset(le, 0, 32); size_t c = n - off < 31 ? n - off : 31; memcpy(le, b + off, c); tr_absorb_field(T, fr_from_le_bytes_mod_order(le, 32)); }
+}
+static void tr_new(transcript* T, const u8* label, size_t n, const pparams* p) { /* :55-65 */
+    for (int i = 0; i < 17; i++) T->state[i] = FR_ZERO;
+    T->pos = 0; T->p = p;
+    T->state[16] = domain_tag_to_field((const u8*)"FSv1-TRANSCRIPT-INIT", 20);
+    tr_absorb_bytes(T, label, n);
+}
+static fr tr_challenge(transcript* T, const u8* label, size_t n) { /* :92-101 */
+    tr_absorb_field(T, domain_tag_to_field((const u8*)"FSv1-CHALLENGE", 14));
+    tr_absorb_bytes(T, label, n);
+    permute(T->p, T->state); T->pos = 0;
+    return T->state[0];
+}
+void* orc_tr_new(const u8* label, size_t n, void* params) { transcript* T = malloc(sizeof *T); tr_new(T, label, n, params ? (const pparams*)params : tr_default_params()); return T; }
+void orc_tr_absorb_bytes(void* T, const u8* b, size_t n) { tr_absorb_bytes(T, b, n); }
+void orc_tr_absorb_field(void* T, const u64* x) { fr v; memcpy(v.l, x, 32); tr_absorb_field(T, v); }
+void orc_tr_challenge(void* T, const u8* label, size_t n, u64* out) { fr r = tr_challenge(T, label, n); memcpy(out, r.l, 32); }
+void orc_tr_state(void* Tv, u64* state17, int* pos) { transcript* T = Tv; memcpy(state17, T->state, sizeof(fr) * 17); *pos = T->pos; }
+void orc_tr_free(void* T) { free(T); }
+
+/* deep_ali/src/fri.rs:28-35 tr_hash_fields_tagged */
+static fr tr_hash_fields_tagged(const char* tag, const fr* xs, size_t n) {
+    transcript T; tr_new(&T, (const u8*)"FRI/FS", 6, tr_default_params());
+    tr_absorb_bytes(&T, (const u8*)tag, strlen(tag));
+    for (size_t i = 0; i < n; i++) tr_absorb_field(&T, xs[i]);
+    return tr_challenge(&T, (const u8*)"out", 3);
+}
+void orc_tr_hash_fields_tagged(const char* tag, const u64* xs, size_t n, u64* out) { fr r = tr_hash_fields_tagged(tag, (const fr*)xs, n); memcpy(out, r.l, 32); }
+/* deep_ali/src/fri.rs:38-44 hash_leaf_pair */
+static fr hash_leaf_pair(fr f, fr s) {
+    transcript T; tr_new(&T, (const u8*)"FRI/leaf/poseidon", 17, tr_default_params());
+    tr_absorb_bytes(&T, (const u8*)"FRI/leaf", 8);
+    tr_absorb_field(&T, f); tr_absorb_field(&T, s);
+    return tr_challenge(&T, (const u8*)"leaf", 4);
+}
+void orc_hash_leaf_pair(const u64* f, const u64* s, u64* out, size_t n) {
+    tr_default_params();
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; i++) { fr r = hash_leaf_pair(((const fr*)f)[i], ((const fr*)s)[i]); memcpy(out + 4 * i, r.l, 32); }
+}
+
+/* ----------------------------------------------------------------- Merkle --
+ * merkle/src/lib.rs:58-74 DsLabel, :147-193 MerkleTree::new, :380-445 new_pairs */
+typedef struct { int arity; u64 tree_label; const pparams* p; int nlevels; size_t* len; fr** lv; } mtree;
+
+static void ds_fields(int arity, u64 level, u64 position, u64 label, fr out[4]) {
+    out[0] = fr_from_u64((u64)arity); out[1] = fr_from_u64(level); out[2] = fr_from_u64(position); out[3] = fr_from_u64(label);
+}
+static mtree* tree_build(fr* level0 /* takes ownership */, size_t n, const pparams* p, int arity, u64 label) {
+    mtree* T = malloc(sizeof *T);
+    T->arity = arity; T->tree_label = label; T->p = p;
+    T->len = malloc(sizeof(size_t) * 70); T->lv = malloc(sizeof(fr*) * 70);
+    T->nlevels = 1; T->len[0] = n; T->lv[0] = level0;
+    u64 cur_level = 0;
+    while (T->len[T->nlevels - 1] > 1) {
+        size_t cn = T->len[T->nlevels - 1]; const fr* cur = T->lv[T->nlevels - 1];
+        size_t nn = (cn + arity - 1) / arity; fr* next = malloc(sizeof(fr) * nn);
+#pragma omp parallel for schedule(static)
+        for (size_t q = 0; q < nn; q++) {
+            fr ds[4]; ds_fields(arity, cur_level, q, label, ds);
+            size_t base = q * arity, c = cn - base < (size_t)arity ? cn - base : (size_t)arity;
+            next[q] = hash_with_ds_dynamic(p, ds, 4, cur + base, c);
+        }
+        T->len[T->nlevels] = nn; T->lv[T->nlevels] = next; T->nlevels++; cur_level++;
+    }
+    return T;
+}
+static int width_ok(int arity, int t) { return orc_width_for_arity(arity) == t; }
+void* orc_merkle_new(void* params, int arity, u64 label, const u64* leaves, size_t n) {
+    const pparams* p = params;
+    if (n == 0 || !width_ok(arity, p->t)) return NULL;   /* asserts at merkle/src/lib.rs:148,161 */
+    fr* l0 = malloc(sizeof(fr) * n); memcpy(l0, leaves, sizeof(fr) * n);
+    return tree_build(l0, n, p, arity, label);
+}
+void* orc_merkle_new_pairs(void* params, int arity, u64 label, const u64* f, const u64* cp, size_t n) {
+    const pparams* p = params;
+    if (n == 0 || !width_ok(arity, p->t)) return NULL;
+    fr* l0 = malloc(sizeof(fr) * n);
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; i++) { /* :382-390 encode_leaf_digest_ds, LEAF_LEVEL_DS = u32::MAX (:378) */
+        fr ds[4]; ds_fields(arity, 0xffffffffULL, i, label, ds);
+        fr pr[2] = {((const fr*)f)[i], ((const fr*)cp)[i]};
+        l0[i] = hash_with_ds_dynamic(p, ds, 4, pr, 2);
+    }
+    return tree_build(l0, n, p, arity, label);
+}
+int orc_tree_nlevels(void* t) { return ((mtree*)t)->nlevels; }
+size_t orc_tree_level_len(void* t, int l) { return ((mtree*)t)->len[l]; }
+void orc_tree_level_copy(void* t, int l, u64* out) { mtree* T = t; memcpy(out, T->lv[l], sizeof(fr) * T->len[l]); }
+void orc_tree_root(void* t, u64* out) { mtree* T = t; memcpy(out, T->lv[T->nlevels - 1], 32); }
+void orc_tree_free(void* t) { mtree* T = t; if (!T) return; for (int i = 0; i < T->nlevels; i++) free(T->lv[i]); free(T->lv); free(T->len); free(T); }
+
+/* merkle/src/lib.rs:246-315 open_union_of_paths.  Output: siblings flattened level by
+ * level, per-level sibling counts, group sizes flattened + per-level group counts. */
+typedef struct { size_t n_idx; size_t* idx; int nlev; size_t* nsib; fr** sib; size_t* ngrp; u8** grp; int arity; } mproof;
+static int cmp_sz(const void* a, const void* b) { size_t x = *(const size_t*)a, y = *(const size_t*)b; return x < y ? -1 : x > y; }
+static size_t sort_dedup(size_t* v, size_t n) { qsort(v, n, sizeof(size_t), cmp_sz); size_t k = 0; for (size_t i = 0; i < n; i++) if (k == 0 || v[k - 1] != v[i]) v[k++] = v[i]; return k; }
+void* orc_tree_open(void* t, const u64* indices, size_t n) {
+    mtree* T = t; int arity = T->arity, h = T->nlevels - 1;
+    mproof* pr = calloc(1, sizeof *pr);
+    size_t* cur = malloc(sizeof(size_t) * (n ? n : 1)); for (size_t i = 0; i < n; i++) cur[i] = (size_t)indices[i];
+    size_t nc = sort_dedup(cur, n);
+    pr->n_idx = nc; pr->idx = malloc(sizeof(size_t) * (nc ? nc : 1)); memcpy(pr->idx, cur, sizeof(size_t) * nc);
+    pr->nlev = h; pr->arity = arity;
+    pr->nsib = calloc(h + 1, sizeof(size_t)); pr->sib = calloc(h + 1, sizeof(fr*)); pr->ngrp = calloc(h + 1, sizeof(size_t)); pr->grp = calloc(h + 1, sizeof(u8*));
+    for (int lev = 0; lev < h; lev++) {
+        const fr* nodes = T->lv[lev]; size_t llen = T->len[lev];
+        fr* sib = malloc(sizeof(fr) * (nc * (size_t)arity + 1)); u8* grp = malloc(nc + 1); size_t ns = 0, ng = 0;
+        size_t i = 0;
+        while (i < nc) {           /* cur is sorted: runs with equal parent are the BTreeMap groups */
+            size_t parent = cur[i] / arity, j = i;
+            while (j < nc && cur[j] / arity == parent) j++;
+            size_t base = parent * arity, end = base + arity < llen ? base + arity : llen, cc = end - base;
+            grp[ng++] = (u8)cc;
+            size_t k = i;
+            for (size_t c = 0; c < cc; c++) { if (k < j && cur[k] % arity == c) k++; else sib[ns++] = nodes[base + c]; }
+            i = j;
+        }
+        pr->nsib[lev] = ns; pr->sib[lev] = sib; pr->ngrp[lev] = ng; pr->grp[lev] = grp;
+        for (size_t q = 0; q < nc; q++) cur[q] /= arity;
+        nc = sort_dedup(cur, nc);
+    }
+    free(cur);
+    return pr;
+}
+size_t orc_proof_total_siblings(void* p) { mproof* pr = p; size_t s = 0; for (int l = 0; l < pr->nlev; l++) s += pr->nsib[l]; return s; }
+int orc_proof_nlevels(void* p) { return ((mproof*)p)->nlev; }
+size_t orc_proof_nsib(void* p, int l) { return ((mproof*)p)->nsib[l]; }
+size_t orc_proof_ngrp(void* p, int l) { return ((mproof*)p)->ngrp[l]; }
+size_t orc_proof_nidx(void* p) { return ((mproof*)p)->n_idx; }
+void orc_proof_indices(void* p, u64* out) { mproof* pr = p; for (size_t i = 0; i < pr->n_idx; i++) out[i] = pr->idx[i]; }
+void orc_proof_level(void* p, int l, u64* sib, u8* grp) { mproof* pr = p; if (sib) memcpy(sib, pr->sib[l], sizeof(fr) * pr->nsib[l]); if (grp) memcpy(grp, pr->grp[l], pr->ngrp[l]); }
+void orc_proof_free(void* p) { mproof* pr = p; if (!pr) return; for (int l = 0; l < pr->nlev; l++) { free(pr->sib[l]); free(pr->grp[l]); } free(pr->sib); free(pr->grp); free(pr->nsib); free(pr->ngrp); free(pr->idx); free(pr); }
+
+/* merkle/src/lib.rs:587-701 verify_many_ds.  Proof passed flattened (as orc_proof_level lays it out). */
+int orc_verify_many_ds(const u64* root, const u64* indices, const u64* values, size_t n,
+                       const u64* proof_indices, size_t n_pidx, int nlev, const size_t* nsib, const u64* sib_flat,
+                       const size_t* ngrp, const u8* grp_flat, int arity, u64 tree_label, void* params) {
+    const pparams* p = params;
+    if (n == 0) return 0;
+    if (!width_ok(arity, p->t)) return 0;
+    size_t* req = malloc(sizeof(size_t) * n); for (size_t i = 0; i < n; i++) req[i] = (size_t)indices[i];
+    size_t nreq = sort_dedup(req, n);
+    int ok = (nreq == n_pidx);
+    for (size_t i = 0; ok && i < nreq; i++) ok = (req[i] == (size_t)proof_indices[i]);
+    if (!ok) { free(req); return 0; }
+    fr* vals = malloc(sizeof(fr) * nreq);
+    for (size_t i = 0; i < nreq; i++) { /* BTreeMap insert: last value for a duplicated index wins */
+        for (size_t j = 0; j < n; j++) if ((size_t)indices[j] == req[i]) memcpy(vals[i].l, values + 4 * j, 32);
+    }
+    size_t nc = nreq; size_t soff = 0, goff = 0;
+    fr* children = malloc(sizeof(fr) * arity);
+    for (int lev = 0; lev < nlev && ok; lev++) {
+        const fr* sib = (const fr*)sib_flat + soff; const u8* grp = grp_flat + goff;
+        size_t off = 0, g = 0, i = 0, nn = 0;
+        size_t* nidx = malloc(sizeof(size_t) * nc); fr* nval = malloc(sizeof(fr) * nc);
+        size_t groups = 0; { size_t a = 0; while (a < nc) { size_t par = req[a] / arity; while (a < nc && req[a] / arity == par) a++; groups++; } }
+        if (groups != ngrp[lev]) ok = 0;
+        while (ok && i < nc) {
+            size_t parent = req[i] / arity, j = i; while (j < nc && req[j] / arity == parent) j++;
+            size_t cc = grp[g++];
+            if (cc == 0 || cc > (size_t)arity) { ok = 0; break; }
+            size_t k = i;
+            for (size_t c = 0; c < cc; c++) {
+                if (k < j && req[k] % arity == c) { children[c] = vals[k]; k++; }
+                else { if (off >= nsib[lev]) { ok = 0; break; } children[c] = sib[off++]; }
+            }
+            if (!ok) break;
+            fr ds[4]; ds_fields(arity, (u64)lev, parent, tree_label, ds);
+            nidx[nn] = parent; nval[nn] = hash_with_ds_dynamic(p, ds, 4, children, cc); nn++;
+            i = j;
+        }
+        if (ok && off != nsib[lev]) ok = 0;
+        if (ok) { memcpy(req, nidx, sizeof(size_t) * nn); memcpy(vals, nval, sizeof(fr) * nn); nc = nn; }
+        free(nidx); free(nval);
+        soff += nsib[lev]; goff += ngrp[lev];
+    }
+    if (ok) { fr r; memcpy(r.l, root, 32); ok = (nc == 1) && fr_eq(vals[0], r); }
+    free(children); free(vals); free(req);
+    return ok;
+}
+
+/* -------------------------------------------------------------------- FRI --
+ * deep_ali/src/fri.rs                                                          */
+/* :59-82 fri_sample_z_ell */
+static fr fri_sample_z_ell(u64 seed_z, u64 level, u64 domain_size) {
+    fr in[3] = {fr_from_u64(seed_z), fr_from_u64(level), fr_from_u64(domain_size)};
+    fr fused = tr_hash_fields_tagged("FRI/z/l", in, 3);
+    u64 c[4]; fr_to_canon(fused, c);
+    stdrng g; rng_from_seed(&g, (const u8*)c);   /* serialize_uncompressed = canonical LE bytes (x86 is LE) */
+    for (int tries = 0; tries < 1000; tries++) {
+        fr cand = fr_from_u64(rng_next_u64(&g));
+        if (!fr_is_zero(cand) && !fr_eq(fr_pow_u64(cand, domain_size), FR_R)) return cand;
+    }
+    fr fb = fr_from_u64(seed_z + level + 7);
+    if (!fr_eq(fr_pow_u64(fb, domain_size), FR_R)) return fb;
+    return fr_from_u64(11);
+}
+void orc_fri_sample_z_ell(u64 seed_z, u64 level, u64 n, u64* out) { orc_init(); fr z = fri_sample_z_ell(seed_z, level, n); memcpy(out, z.l, 32); }
+/* :85-102 fri_fold_layer */
+static void fri_fold_layer(const fr* f, size_t n, fr z, size_t m, fr* out) {
+    fr zp[128]; fr acc = FR_R; for (size_t t = 0; t < m; t++) { zp[t] = acc; acc = fr_mul(acc, z); }
+    size_t nn = n / m;
+#pragma omp parallel for schedule(static)
+    for (size_t b = 0; b < nn; b++) { fr s = FR_ZERO; for (size_t t = 0; t < m; t++) s = fr_add(s, fr_mul(f[b * m + t], zp[t])); out[b] = s; }
+}
+int orc_fri_fold_layer(const u64* f, size_t n, const u64* z, size_t m, u64* out) {
+    if (m < 2 || m > 128 || n % m) return -1; fr zz; memcpy(zz.l, z, 32); fri_fold_layer((const fr*)f, n, zz, m, (fr*)out); return 0;
+}
+/* :123-143 compute_s_layer */
+int orc_compute_s_layer(const u64* f, size_t n, const u64* z, size_t m, u64* out) {
+    if (m < 1 || m > 128 || n % m) return -1;
+    fr zz; memcpy(zz.l, z, 32); size_t nn = n / m; fr* b = malloc(sizeof(fr) * nn);
+    fri_fold_layer((const fr*)f, n, zz, m, b);
+    for (size_t i = 0; i < n; i++) ((fr*)out)[i] = b[i / m];
+    free(b); return 0;
+}
+/* :220-229 pick_arity_for_layer */
+int orc_pick_arity_for_layer(size_t n, size_t m) {
+    if (m >= 128 && n % 128 == 0) return 128; if (m >= 64 && n % 64 == 0) return 64; if (m >= 32 && n % 32 == 0) return 32;
+    if (m >= 16 && n % 16 == 0) return 16; if (m >= 8 && n % 8 == 0) return 8; if (m >= 4 && n % 4 == 0) return 4;
+    if (n % 2 == 0) return 2; return 1;
+}
+/* :194-216 FriLayerCommitment / FriProverState, :231-312 fri_build_transcript */
+typedef struct { int L; size_t* m; size_t* n; fr** f; fr** s; int* hashed; int* arity; mtree** tree; pparams** params; fr* z; } fristate;
+static pparams* g_width_params[130];
+static const pparams* params_for_arity_cached(int arity) {
+    int t = orc_width_for_arity(arity); pparams* q;
+#pragma omp critical(orc_wp)
+    { if (!g_width_params[t]) g_width_params[t] = orc_params_for_width(t); q = g_width_params[t]; }
+    return q;
+}
+void* orc_fri_build(const u64* f0, size_t n0, const u64* schedule, int L, u64 seed_z) {
+    orc_init();
+    fristate* S = calloc(1, sizeof *S);
+    S->L = L; S->m = malloc(sizeof(size_t) * (L + 1)); S->n = malloc(sizeof(size_t) * (L + 1));
+    S->f = calloc(L + 1, sizeof(fr*)); S->s = calloc(L + 1, sizeof(fr*)); S->hashed = calloc(L + 1, sizeof(int)); S->arity = calloc(L + 1, sizeof(int));
+    S->tree = calloc(L + 1, sizeof(mtree*)); S->params = calloc(L + 1, sizeof(pparams*)); S->z = malloc(sizeof(fr) * (L + 1));
+    size_t n = n0;
+    S->f[0] = malloc(sizeof(fr) * n0); memcpy(S->f[0], f0, sizeof(fr) * n0); S->n[0] = n0;
+    for (int l = 0; l < L; l++) {
+        size_t m = (size_t)schedule[l]; S->m[l] = m;
+        if (m < 2 || n % m) { /* assert at fri.rs:86-87 */ fprintf(stderr, "orc_fri_build: bad schedule\n"); abort(); }
+        S->z[l] = fri_sample_z_ell(seed_z, (u64)l, (u64)n);
+        S->f[l + 1] = malloc(sizeof(fr) * (n / m));
+        fri_fold_layer(S->f[l], n, S->z[l], m, S->f[l + 1]);
+        n /= m; S->n[l + 1] = n;
+    }
+    S->m[L] = 1;
+    for (int l = 0; l < L; l++) { /* s layers: recomputed fold, broadcast (:259-265) — equal to f[l+1][i/m] */
+        size_t nl = S->n[l], m = S->m[l]; S->s[l] = malloc(sizeof(fr) * nl);
+        fr* b = malloc(sizeof(fr) * (nl / m)); fri_fold_layer(S->f[l], nl, S->z[l], m, b);
+        for (size_t i = 0; i < nl; i++) S->s[l][i] = b[i / m];
+        free(b);
+    }
+    S->s[L] = calloc(S->n[L], sizeof(fr));
+    for (int l = 0; l <= L; l++) {
+        size_t nl = S->n[l]; int arity = orc_pick_arity_for_layer(nl, S->m[l]);
+        int hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
+        const pparams* p = params_for_arity_cached(arity);
+        S->arity[l] = arity; S->hashed[l] = hashed;
+        if (hashed) {
+            fr* h = malloc(sizeof(fr) * nl);
+            tr_default_params();
+#pragma omp parallel for schedule(static)
+            for (size_t i = 0; i < nl; i++) h[i] = hash_leaf_pair(S->f[l][i], S->s[l][i]);
+            S->tree[l] = tree_build(h, nl, p, arity, (u64)l);
+        } else {
+            S->tree[l] = orc_merkle_new_pairs((void*)p, arity, (u64)l, (const u64*)S->f[l], (const u64*)S->s[l], nl);
+        }
+    }
+    return S;
+}
+int orc_fri_nlayers(void* s) { return ((fristate*)s)->L + 1; }
+size_t orc_fri_layer_n(void* s, int l) { return ((fristate*)s)->n[l]; }
+int orc_fri_layer_arity(void* s, int l) { return ((fristate*)s)->arity[l]; }
+int orc_fri_layer_hashed(void* s, int l) { return ((fristate*)s)->hashed[l]; }
+void orc_fri_layer_f(void* s, int l, u64* out) { fristate* S = s; memcpy(out, S->f[l], sizeof(fr) * S->n[l]); }
+void orc_fri_layer_s(void* s, int l, u64* out) { fristate* S = s; memcpy(out, S->s[l], sizeof(fr) * S->n[l]); }
+void orc_fri_layer_root(void* s, int l, u64* out) { orc_tree_root(((fristate*)s)->tree[l], out); }
+void* orc_fri_layer_tree(void* s, int l) { return ((fristate*)s)->tree[l]; }
+void orc_fri_z(void* s, int l, u64* out) { memcpy(out, ((fristate*)s)->z[l].l, 32); }
+void orc_fri_free(void* s) {
+    fristate* S = s; if (!S) return;
+    for (int l = 0; l <= S->L; l++) { free(S->f[l]); free(S->s[l]); orc_tree_free(S->tree[l]); }
+    free(S->f); free(S->s); free(S->tree); free(S->params); free(S->m); free(S->n); free(S->hashed); free(S->arity); free(S->z); free(S);
+}
+/* :178-191 index_from_seed / index_seed */
+static size_t index_from_seed(fr seed, size_t n_pow2) {
+    u64 c[4]; fr_to_canon(seed, c); stdrng g; rng_from_seed(&g, (const u8*)c);
+    return (size_t)rng_next_u64(&g) & (n_pow2 - 1);
+}
+static size_t next_pow2(size_t n) { size_t p = 1; while (p < n) p <<= 1; return p; }
+/* :355-466 fri_prove_queries (index derivation + batching) and :775-805 deep_fri_proof_size_bytes.
+ * Also returns the per-layer unique child / parent index lists when the out arrays are given. */
+size_t orc_fri_prove_size(void* s, size_t r, u64* roots_seed_out, u64* child_idx_out, size_t* child_cnt_out, u64* parent_idx_out, size_t* parent_cnt_out) {
+    fristate* S = s; int L = S->L;
+    fr* roots = malloc(sizeof(fr) * (L + 1));
+    for (int l = 0; l <= L; l++) orc_tree_root(S->tree[l], roots[l].l);
+    fr roots_seed = tr_hash_fields_tagged("FRI/seed", roots, L + 1);   /* :176 fs_seed_from_roots */
+    if (roots_seed_out) memcpy(roots_seed_out, roots_seed.l, 32);
+    size_t total = 0;
+    total += (size_t)(L + 1) * 32; total += 32; total += 8;
+    for (int l = 0; l < L; l++) {
+        size_t n = S->n[l], np2 = next_pow2(n), m = S->m[l];
+        u64* ci = malloc(sizeof(u64) * r); u64* pi = malloc(sizeof(u64) * r);
+        for (size_t q = 0; q < r; q++) {
+            fr in[3] = {roots_seed, fr_from_u64((u64)l), fr_from_u64((u64)q)};
+            fr seed = tr_hash_fields_tagged("FRI/index", in, 3);
+            size_t i0 = index_from_seed(seed, np2), i;
+            if (i0 < n) i = i0;
+            else { fr in2[2] = {seed, fr_from_u64(1)}; fr rs = tr_hash_fields_tagged("FRI/index", in2, 2); size_t i2 = index_from_seed(rs, np2); i = i2 < n ? i2 : (i2 & (n - 1)); }
+            ci[q] = i; pi[q] = i / m;
+        }
+        void* cp = orc_tree_open(S->tree[l], ci, r); void* pp = orc_tree_open(S->tree[l + 1], pi, r);
+        mproof* c = cp; mproof* p = pp;
+        total += orc_proof_total_siblings(cp) * 32 + orc_proof_total_siblings(pp) * 32;
+        total += c->n_idx * 8 + p->n_idx * 8;
+        if (child_idx_out) { for (size_t i = 0; i < c->n_idx; i++) child_idx_out[(size_t)l * r + i] = c->idx[i]; child_cnt_out[l] = c->n_idx; }
+        if (parent_idx_out) { for (size_t i = 0; i < p->n_idx; i++) parent_idx_out[(size_t)l * r + i] = p->idx[i]; parent_cnt_out[l] = p->n_idx; }
+        orc_proof_free(cp); orc_proof_free(pp); free(ci); free(pi);
+    }
+    { u64 zero = 0; void* fp = orc_tree_open(S->tree[L], &zero, 1); total += orc_proof_total_siblings(fp) * 32; orc_proof_free(fp); }
+    total += r * (8 + 64 + (size_t)L * 16 + (size_t)L * 128);
+    free(roots);
+    return total;
+}
+
+/* deep_ali/src/lib.rs:17-45 lagrange_eval_on_h (off-domain branch), :60-105 deep_ali_merge_evals[_blinded] */
+void orc_deep_ali_merge_evals(const u64* a, const u64* s, const u64* e, const u64* t, size_t n, const u64* omega_p, const u64* z_p, u64* f0_out, u64* c_star_out) {
+    orc_init();
+    fr omega, z; memcpy(omega.l, omega_p, 32); memcpy(z.l, z_p, 32);
+    fr* phi = malloc(sizeof(fr) * n);
+    for (size_t i = 0; i < n; i++) phi[i] = fr_sub(fr_add(fr_mul(((const fr*)a)[i], ((const fr*)s)[i]), ((const fr*)e)[i]), ((const fr*)t)[i]);
+    fr* wj = malloc(sizeof(fr) * n); { fr w = FR_R; for (size_t j = 0; j < n; j++) { wj[j] = w; w = fr_mul(w, omega); } }
+    if (c_star_out) {
+        fr zh = fr_sub(fr_pow_u64(z, (u64)n), FR_R);
+        fr n_inv = fr_inv(fr_from_u64((u64)n));
+        fr sum = FR_ZERO;
+        for (size_t j = 0; j < n; j++) sum = fr_add(sum, fr_mul(fr_mul(phi[j], wj[j]), fr_inv(fr_sub(z, wj[j]))));
+        fr phi_z = fr_mul(fr_mul(zh, n_inv), sum);
+        fr cs = fr_mul(phi_z, fr_inv(zh)); memcpy(c_star_out, cs.l, 32);
+    }
+#pragma omp parallel for schedule(static)
+    for (size_t j = 0; j < n; j++) ((fr*)f0_out)[j] = fr_mul(phi[j], fr_inv(fr_sub(wj[j], z)));
+    free(phi); free(wj);
+}
+/* deep_ali/src/fri.rs:508-533 ali_sample_z_beta_fs */
+static void ali_sample_z_beta_fs(const char* tag, u64 n0, fr roots_seed, fr* z, fr* beta) {
+    fr in[2] = {roots_seed, fr_from_u64(n0)};
+    fr fused = tr_hash_fields_tagged(tag, in, 2);
+    u64 c[4]; fr_to_canon(fused, c); stdrng g; rng_from_seed(&g, (const u8*)c);
+    *beta = fr_from_u64(rng_next_u64(&g));
+    for (int tries = 0; tries < 1000; tries++) {
+        fr cand = fr_from_u64(rng_next_u64(&g));
+        if (!fr_is_zero(cand) && !fr_eq(fr_pow_u64(cand, n0), FR_R)) { *z = cand; return; }
+    }
+    fr fb = fr_add(roots_seed, fr_from_u64(17));
+    if (!fr_eq(fr_pow_u64(fb, n0), FR_R)) { *z = fb; return; }
+    *z = fr_from_u64(19);
+}
+/* deep_ali/src/fri.rs:535-570 DeepAliRealBuilder::build_f0 (default: no blinding, ds_tag "ALI/DEEP") */
+void orc_deep_ali_build_f0(const u64* a, const u64* s, const u64* e, const u64* t, size_t n0, u64* f0_out, u64* z_out) {
+    orc_init();
+    fr h[5];
+    /* four independent serial sponges */
+#pragma omp parallel sections
+    {
+#pragma omp section
+        h[0] = tr_hash_fields_tagged("ALI/A", (const fr*)a, n0);
+#pragma omp section
+        h[1] = tr_hash_fields_tagged("ALI/S", (const fr*)s, n0);
+#pragma omp section
+        h[2] = tr_hash_fields_tagged("ALI/E", (const fr*)e, n0);
+#pragma omp section
+        h[3] = tr_hash_fields_tagged("ALI/T", (const fr*)t, n0);
+    }
+    h[4] = fr_from_u64((u64)n0);
+    fr seed_f = tr_hash_fields_tagged("ALI/seed", h, 5);
+    fr z, beta; ali_sample_z_beta_fs("ALI/DEEP", (u64)n0, seed_f, &z, &beta);
+    int log_n = 0; while (((size_t)1 << log_n) < n0) log_n++;
+    fr omega = root_of_unity(log_n);     /* FriDomain::new_radix2 (fri.rs:53-56) */
+    if (z_out) memcpy(z_out, z.l, 32);
+    orc_deep_ali_merge_evals(a, s, e, t, n0, omega.l, z.l, f0_out, NULL);   /* c_star discarded by build_f0 (:562-568) */
+}
+/* deep_ali/src/fri.rs:601-641 deep_fri_prove + :775-805 size.  roots_out: (L+1) x 4 u64 or NULL. */
+size_t orc_deep_fri_prove_size(const u64* a, const u64* s, const u64* e, const u64* t, size_t n0, const u64* schedule, int L, size_t r, u64 seed_z, u64* roots_out) {
+    fr* f0 = malloc(sizeof(fr) * n0);
+    orc_deep_ali_build_f0(a, s, e, t, n0, (u64*)f0, NULL);
+    void* S = orc_fri_build((const u64*)f0, n0, schedule, L, seed_z);
+    if (roots_out) for (int l = 0; l <= L; l++) orc_fri_layer_root(S, l, roots_out + 4 * l);
+    size_t sz = orc_fri_prove_size(S, r, NULL, NULL, NULL, NULL, NULL);
+    orc_fri_free(S); free(f0);
+    return sz;
+}
+
+/* -------------------------------------------------------------- NTT / LDE --
+ * fft/src/lib.rs:6-32 wraps ark-poly 0.5.0 Radix2EvaluationDomain: fft = natural-order
+ * coefficients -> natural-order evaluations P(w^i); ifft = inverse with the 1/n factor.
+ * (The fft crate is declared over BLS12-381 Fr and has no live caller; the pipeline is
+ * only well-typed over Pallas Fr — SURVEY.md D1/D2.  Parity unpinned for this block: the
+ * reference holds no NTT vector; tests pin it against a direct O(n^2) DFT instead.)      */
+static void ntt_inplace(fr* a, int log_n, int inverse) {
+    size_t n = (size_t)1 << log_n;
+    for (size_t i = 0, j = 0; i < n; i++) { if (i < j) { fr t = a[i]; a[i] = a[j]; a[j] = t; } size_t bit = n >> 1; for (; j & bit; bit >>= 1) j ^= bit; j ^= bit; }
+    fr w_n = root_of_unity(log_n); if (inverse) w_n = fr_inv(w_n);
+    fr* tw = malloc(sizeof(fr) * (n / 2 ? n / 2 : 1)); { fr w = FR_R; for (size_t i = 0; i < n / 2; i++) { tw[i] = w; w = fr_mul(w, w_n); } }
+    for (int s = 1; s <= log_n; s++) {
+        size_t len = (size_t)1 << s, half = len >> 1, step = n / len;
+#pragma omp parallel for schedule(static) if (n >= 4096)
+        for (size_t k = 0; k < n / 2; k++) {
+            size_t blk = k / half, j = k % half, i0 = blk * len + j, i1 = i0 + half;
+            fr u = a[i0], v = fr_mul(a[i1], tw[j * step]); a[i0] = fr_add(u, v); a[i1] = fr_sub(u, v);
+        }
+    }
+    if (inverse) { fr ninv = fr_inv(fr_from_u64((u64)n)); for (size_t i = 0; i < n; i++) a[i] = fr_mul(a[i], ninv); }
+    free(tw);
+}
+void orc_ntt(u64* buf, int log_n, int inverse) { orc_init(); ntt_inplace((fr*)buf, log_n, inverse); }
+/* direct O(n^2) evaluation P(w^i) for pinning the NTT */
+void orc_dft_naive(const u64* coeffs, int log_n, u64* out) {
+    orc_init(); size_t n = (size_t)1 << log_n; fr w = root_of_unity(log_n);
+    fr x = FR_R;
+    for (size_t i = 0; i < n; i++) { fr acc = FR_ZERO; for (size_t j = n; j-- > 0;) acc = fr_add(fr_mul(acc, x), ((const fr*)coeffs)[j]); ((fr*)out)[i] = acc; x = fr_mul(x, w); }
+}
+/* coset LDE: c = ifft_n(col); c[i] *= g^i; zero-pad to beta*n; fft_{beta n} */
+void orc_lde(const u64* col, int log_n, int log_blowup, const u64* shift, u64* out) {
+    orc_init(); size_t n = (size_t)1 << log_n, N = n << log_blowup;
+    fr g; memcpy(g.l, shift, 32);
+    fr* c = (fr*)out; memcpy(c, col, sizeof(fr) * n);
+    ntt_inplace(c, log_n, 1);
+    fr gp = FR_R; for (size_t i = 0; i < n; i++) { c[i] = fr_mul(c[i], gp); gp = fr_mul(gp, g); }
+    for (size_t i = n; i < N; i++) c[i] = FR_ZERO;
+    ntt_inplace(c, log_n + log_blowup, 0);
+}
+
+/* ------------------------------------------------- Merkle-folded sum-check --
+ * channel/src/lib.rs:406-416 sumcheck_round_coeffs                              */
+void orc_sumcheck_round_coeffs(const u64* layer, size_t n, u64* c0, u64* c1) {
+    fr a0 = FR_ZERO, a1 = FR_ZERO;
+    for (size_t i = 0; i < n; i += 2) { fr a = ((const fr*)layer)[i], b = ((const fr*)layer)[i + 1]; a0 = fr_add(a0, a); a1 = fr_add(a1, fr_sub(b, a)); }
+    memcpy(c0, a0.l, 32); memcpy(c1, a1.l, 32);
+}
+/* channel/src/lib.rs:592-598 mf_round_challenge_from_root (params = the channel transcript's params) */
+void orc_mf_round_challenge_from_root(u64 round_idx, const u64* prev_root, void* tr_params, u64* out) {
+    transcript T; tr_new(&T, (const u8*)"SUMCHECK-MF/ROUND-CHAL", 22, tr_params ? (const pparams*)tr_params : tr_default_params());
+    tr_absorb_bytes(&T, (const u8*)"SUMCHECK/MF/R", 13);
+    u8 le[8]; put_u64le(le, round_idx); tr_absorb_bytes(&T, le, 8);
+    fr r; memcpy(r.l, prev_root, 32); tr_absorb_field(&T, r);
+    fr c = tr_challenge(&T, (const u8*)"r_i", 3); memcpy(out, c.l, 32);
+}
+/* channel/src/lib.rs:648-655 fold: next[j] = (1 - r) * cur[2j] + r * cur[2j+1] */
+void orc_mf_fold(const u64* cur, size_t n, const u64* r_p, u64* next) {
+    fr r; memcpy(r.l, r_p, 32); fr om = fr_sub(FR_R, r);
+    for (size_t j = 0; j < n / 2; j++) ((fr*)next)[j] = fr_add(fr_mul(om, ((const fr*)cur)[2 * j]), fr_mul(r, ((const fr*)cur)[2 * j + 1]));
+}
+/* commitment/src/lib.rs:69-90 MerkleCommitment::commit: arity 16, default t=17 params (or caller's), tree_label = ds_tag */
+void* orc_commitment_commit(u64 ds_tag, void* params, const u64* leaves, size_t n) {
+    return orc_merkle_new(params ? params : (void*)commit_default_params(), 16, ds_tag, leaves, n);
+}
+/* The commit phase of channel::prove_mf (SumCheckMFProver::new + round loop, :600-657): roots of every
+ * folded layer and the r_i; query sampling/openings (:660-712) are left to the "next" tier. */
+int orc_mf_commit_phase(u64 ds_tag, const u64* table, size_t n, u64* roots_out /* (k+1) x 4 */, u64* r_out /* k x 4 */, u64* final_out) {
+    orc_init();
+    int k = 0; while (((size_t)1 << k) < n) k++;
+    fr* cur = malloc(sizeof(fr) * n); memcpy(cur, table, sizeof(fr) * n);
+    void* tr = orc_commitment_commit(ds_tag, NULL, (const u64*)cur, n); orc_tree_root(tr, roots_out); orc_tree_free(tr);
+    size_t len = n;
+    for (int i = 0; i < k; i++) {
+        fr r; orc_mf_round_challenge_from_root((u64)i, roots_out + 4 * i, NULL, r.l);
+        memcpy(r_out + 4 * i, r.l, 32);
+        fr* next = malloc(sizeof(fr) * (len / 2)); orc_mf_fold((const u64*)cur, len, r.l, (u64*)next);
+        free(cur); cur = next; len /= 2;
+        tr = orc_commitment_commit(ds_tag, NULL, (const u64*)cur, len); orc_tree_root(tr, roots_out + 4 * (i + 1)); orc_tree_free(tr);
+    }
+    if (final_out) memcpy(final_out, cur[0].l, 32);
+    free(cur); return k;
+}
