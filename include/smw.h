@@ -1,0 +1,161 @@
+/*
+ * smw.h — C ABI of libsmw.so: the B200 (sm_100a) implementation of stark-mlwe's commitment hot path.
+ *
+ * One entry point per reference function on the path; each declaration cites the
+ * reference interface it replaces (paths relative to the reference repository root).  A Rust shim
+ * binds these with `extern "C"` (INTEGRATION.md shows the stubs); no torch / C++ types cross the ABI.
+ *
+ * Conventions
+ *  - Field elements ("Fr") are 32 bytes: four little-endian u64 limbs in Montgomery form, R = 2^256,
+ *    canonical (< p) — byte-identical to ark-ff 0.5 `Fp256<MontBackend<ark_pallas::FrConfig,4>>`
+ *    (field/src/lib.rs:13), so a Rust `&[F]` can be passed without conversion.
+ *    smw_fr_from_canonical / smw_fr_to_canonical convert to/from canonical little-endian integers
+ *    (the ark-serialize wire form, field/src/lib.rs:206-215).
+ *  - `mem` says where a caller buffer lives: SMW_HOST (copied through the context's stream) or
+ *    SMW_DEVICE (a CUDA device pointer on the context's device, used in place).
+ *  - Every function returns an int32 status (SMW_OK = 0).  The reference panics on the same
+ *    conditions (file:line given per code); a shim turns non-zero into that panic.
+ *  - A context is bound to one device and one stream and is not thread-safe; use one per GPU.
+ *  - All arithmetic runs on the GPU.  There is no CPU fallback: without a CUDA device
+ *    smw_ctx_create fails with SMW_ERR_CUDA.
+ */
+#ifndef SMW_H
+#define SMW_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef struct smw_ctx smw_ctx;
+typedef struct smw_params smw_params;          /* PoseidonParamsDynamic (poseidon/src/lib.rs:104-114), device resident */
+typedef struct smw_tree smw_tree;              /* MerkleTree (merkle/src/lib.rs:114-128) */
+typedef struct smw_proof smw_proof;            /* MerkleProof (merkle/src/lib.rs:131-143) */
+typedef struct smw_transcript smw_transcript;  /* Transcript (transcript/src/lib.rs:48-52) */
+typedef struct smw_fri smw_fri;                /* FriProverState (deep_ali/src/fri.rs:210-216) */
+
+enum {
+    SMW_OK = 0,
+    SMW_ERR_CUDA = 1,              /* CUDA runtime failure; see smw_last_error */
+    SMW_ERR_EMPTY = 2,             /* "no leaves"                     merkle/src/lib.rs:148,394 */
+    SMW_ERR_ARITY_WIDTH = 3,       /* arity incompatible with width   merkle/src/lib.rs:161,413 */
+    SMW_ERR_LENGTH_MISMATCH = 4,   /* "f and cp length mismatch"      merkle/src/lib.rs:393 */
+    SMW_ERR_NOT_DIVISIBLE = 5,     /* layer size not divisible by m   deep_ali/src/fri.rs:87,124 */
+    SMW_ERR_UNSUPPORTED_WIDTH = 6, /* unsupported Poseidon width      poseidon/src/lib.rs:127 */
+    SMW_ERR_UNSUPPORTED_ARITY = 7, /* unsupported Merkle arity        poseidon/src/lib.rs:163 */
+    SMW_ERR_INVALID_ARG = 8,
+    SMW_ERR_PARAMS_SINGULAR = 9,   /* matrix has a zero pivot: the exact sparse/LU factorisation does not exist */
+    SMW_ERR_NOMEM = 10,
+    SMW_ERR_EMPTY_INDICES = 11     /* "open_many: empty indices"      merkle/src/lib.rs:247 */
+};
+enum { SMW_HOST = 0, SMW_DEVICE = 1 };
+
+/* ---- context ------------------------------------------------------------------------------ */
+int32_t smw_ctx_create(int32_t device, smw_ctx** out);
+int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** out);
+void smw_ctx_destroy(smw_ctx* ctx);
+int32_t smw_ctx_sync(smw_ctx* ctx);
+const char* smw_last_error(const smw_ctx* ctx);
+uint64_t smw_ctx_launch_count(const smw_ctx* ctx);   /* kernels launched so far through this context */
+void* smw_ctx_stream(const smw_ctx* ctx);
+
+/* ---- field (field/src/lib.rs:13,43-53,206-215; ark-ff) ------------------------------------- */
+int32_t smw_fr_from_canonical(smw_ctx* ctx, const void* canon_le32, void* out_fr, size_t n, int32_t mem);
+int32_t smw_fr_to_canonical(smw_ctx* ctx, const void* fr, void* out_canon_le32, size_t n, int32_t mem);
+int32_t smw_root_of_unity(smw_ctx* ctx, int32_t log_n, void* out_fr_host);   /* F::get_root_of_unity(2^log_n), field/src/lib.rs:46 */
+
+/* ---- Poseidon parameters (poseidon/src/lib.rs:120-216, 318-356; utils/src/lib.rs:7-22) ---- */
+int32_t smw_params_from_seed(smw_ctx* ctx, const uint8_t* seed, size_t seed_len, int32_t t, int32_t rp, smw_params** out); /* params::generate_params_t17_x5(seed) for t=17, rp=64 */
+int32_t smw_params_for_width(smw_ctx* ctx, int32_t t, smw_params** out);          /* poseidon_params_for_width; cached, owned by ctx */
+int32_t smw_params_for_arity(smw_ctx* ctx, int32_t arity, smw_params** out);      /* poseidon_params_for_arity; cached, owned by ctx */
+int32_t smw_params_commitment_default(smw_ctx* ctx, smw_params** out);            /* commitment::default_params (commitment/src/lib.rs:48-51) */
+int32_t smw_params_transcript_default(smw_ctx* ctx, smw_params** out);            /* transcript::default_params (transcript/src/lib.rs:44-46) */
+int32_t smw_params_from_tables(smw_ctx* ctx, int32_t t, int32_t rp, const void* mds, const void* rc_full, const void* rc_partial, int32_t mem, smw_params** out); /* caller-supplied PoseidonParamsDynamic */
+int32_t smw_params_export(smw_params* p, void* mds_out, void* rc_full_out, void* rc_partial_out);   /* host buffers: t*t, 8*t, rp Fr */
+int32_t smw_params_width(const smw_params* p);
+int32_t smw_params_partial_rounds(const smw_params* p);
+void smw_params_free(smw_params* p);   /* no-op for ctx-owned (cached) sets */
+
+/* ---- permutation and sponges (poseidon/src/lib.rs:31-68, 85-100, 219-312) ------------------ */
+int32_t smw_poseidon_permute(smw_ctx* ctx, const smw_params* p, void* states, size_t batch, int32_t mem);              /* permute / permute_dynamic, in place, [batch][t] Fr */
+int32_t smw_poseidon_permute_dense(smw_ctx* ctx, const smw_params* p, void* states, size_t batch, int32_t mem);        /* same result, literal round structure (test aid) */
+int32_t smw_hash_with_ds_dynamic(smw_ctx* ctx, const smw_params* p, const void* ds_fields, size_t n_ds, const void* inputs, size_t n, void* out_fr, int32_t mem);
+int32_t smw_hash_with_ds(smw_ctx* ctx, const smw_params* p, const void* inputs, size_t n, const void* ds_tag, void* out_fr, int32_t mem);   /* legacy, t = 17 */
+
+/* ---- Merkle (merkle/src/lib.rs:58-112, 147-193, 380-445) ----------------------------------- */
+int32_t smw_merkle_new(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t tree_label, const void* leaves, size_t n, int32_t mem, smw_tree** out);               /* MerkleTree::new */
+int32_t smw_merkle_new_pairs(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t tree_label, const void* f, const void* cp, size_t n_f, size_t n_cp, int32_t mem, smw_tree** out); /* MerkleTree::new_pairs */
+int32_t smw_tree_root(smw_tree* t, void* out_fr_host);          /* MerkleTree::root */
+int32_t smw_tree_num_levels(const smw_tree* t);                 /* levels.len(); level 0 = leaves */
+size_t smw_tree_level_len(const smw_tree* t, int32_t level);
+int32_t smw_tree_level(smw_tree* t, int32_t level, void* out, int32_t mem);
+int32_t smw_tree_arity(const smw_tree* t);
+void smw_tree_free(smw_tree* t);
+/* many equally sized columns at once: one tree per column, tree_label = label0 + c*label_stride; roots only
+ * (the device-side column-batched form of calling MerkleTree::new once per column) */
+int32_t smw_merkle_commit_columns(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t label0, uint64_t label_stride,
+                                  const void* cols, size_t n, int32_t n_cols, int32_t mem, void* roots_out_host);
+
+/* ---- commitment (commitment/src/lib.rs:13-27, 60-113; channel/src/lib.rs:172-179) ---------- */
+int32_t smw_commitment_commit(smw_ctx* ctx, uint64_t ds_tag, smw_params* params_or_null, const void* leaves, size_t n, int32_t mem, smw_tree** out); /* MerkleCommitment::commit: arity 16, tree_label = ds_tag */
+
+/* ---- NTT / coset LDE (fft/src/lib.rs:6-32) ---------------------------------- */
+int32_t smw_ntt(smw_ctx* ctx, void* buf, int32_t log_n, int32_t inverse, int32_t n_cols, int32_t mem);   /* fft_in_place / ifft_in_place per column, natural order in and out */
+int32_t smw_lde(smw_ctx* ctx, const void* in, int32_t log_n, int32_t log_blowup, const void* shift_fr_host, void* out, int32_t n_cols, int32_t mem);
+/* the benchmark pipeline: LDE of n_cols columns, then one arity-16 commitment-default tree per extended column */
+int32_t smw_lde_commit(smw_ctx* ctx, const void* cols, int32_t log_n, int32_t log_blowup, const void* shift_fr_host, int32_t n_cols,
+                       uint64_t label0, int32_t mem, void* roots_out_host);
+
+/* ---- transcript (transcript/src/lib.rs:55-117; deep_ali/src/fri.rs:28-44) ------------------ */
+int32_t smw_transcript_new(smw_ctx* ctx, const uint8_t* label, size_t len, smw_params* params_or_null, smw_transcript** out);
+int32_t smw_transcript_absorb_bytes(smw_transcript* t, const uint8_t* bytes, size_t len);
+int32_t smw_transcript_absorb_field(smw_transcript* t, const void* fr_host);
+int32_t smw_transcript_absorb_fields(smw_transcript* t, const void* frs, size_t n, int32_t mem);
+int32_t smw_transcript_challenge(smw_transcript* t, const uint8_t* label, size_t len, void* out_fr_host);
+int32_t smw_transcript_state(smw_transcript* t, void* out_17_fr_host, int32_t* pos_out);
+void smw_transcript_free(smw_transcript* t);
+int32_t smw_tr_hash_fields_tagged(smw_ctx* ctx, const uint8_t* tag, size_t tag_len, const void* xs, size_t n, int32_t mem, void* out_fr_host);
+int32_t smw_hash_leaf_pair(smw_ctx* ctx, const void* f, const void* s, size_t n, void* out, int32_t mem);   /* hash_leaf_pair, element-wise */
+
+/* ---- FRI-like commit phase (deep_ali/src/fri.rs:59-143, 220-312) --------------------------- */
+int32_t smw_fri_sample_z_ell(smw_ctx* ctx, uint64_t seed_z, uint64_t level, uint64_t domain_size, void* out_fr_host);
+int32_t smw_fri_fold_layer(smw_ctx* ctx, const void* f, size_t n, const void* z_fr_host, size_t m, void* out, int32_t mem);
+int32_t smw_compute_s_layer(smw_ctx* ctx, const void* f, size_t n, const void* z_fr_host, size_t m, void* out, int32_t mem);
+int32_t smw_pick_arity_for_layer(size_t n, size_t requested_m);
+int32_t smw_fri_build_transcript(smw_ctx* ctx, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, smw_fri** out);
+int32_t smw_fri_num_layers(const smw_fri* s);                                          /* L + 1 */
+int32_t smw_fri_layer_info(const smw_fri* s, int32_t l, size_t* n, size_t* m, int32_t* arity, int32_t* hashed_leaves);
+int32_t smw_fri_layer_f(smw_fri* s, int32_t l, void* out, int32_t mem);
+int32_t smw_fri_layer_s(smw_fri* s, int32_t l, void* out, int32_t mem);                /* s_l[i] = f_{l+1}[i / m]; zeros for the last layer */
+int32_t smw_fri_roots(smw_fri* s, void* out_host);                                     /* L + 1 Fr */
+int32_t smw_fri_z(smw_fri* s, void* out_host);                                         /* L Fr */
+smw_tree* smw_fri_layer_tree(smw_fri* s, int32_t l);                                   /* borrowed */
+void smw_fri_free(smw_fri* s);
+
+/* ---- Merkle-folded sum-check commit loop (channel/src/lib.rs:406-416, 592-598, 600-657) ---- */
+int32_t smw_sumcheck_round_coeffs(smw_ctx* ctx, const void* layer, size_t n, void* c0_host, void* c1_host, int32_t mem);
+int32_t smw_mf_round_challenge_from_root(smw_ctx* ctx, uint64_t round_idx, const void* prev_root_host, smw_params* tr_params_or_null, void* out_fr_host);
+int32_t smw_mf_fold(smw_ctx* ctx, const void* cur, size_t n, const void* r_fr_host, void* next, int32_t mem);
+int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host /* k+1 */, void* r_out_host /* k */, void* final_out_host);
+
+/* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */
+int32_t smw_tree_open_many(smw_tree* t, const uint64_t* indices, size_t n, smw_proof** out);   /* open_union_of_paths, merkle/src/lib.rs:246-315 */
+int32_t smw_proof_num_levels(const smw_proof* p);
+size_t smw_proof_num_indices(const smw_proof* p);
+int32_t smw_proof_indices(const smw_proof* p, uint64_t* out);
+size_t smw_proof_level_siblings(const smw_proof* p, int32_t level);
+size_t smw_proof_level_groups(const smw_proof* p, int32_t level);
+int32_t smw_proof_level(const smw_proof* p, int32_t level, void* siblings_out_host, uint8_t* group_sizes_out);
+void smw_proof_free(smw_proof* p);
+int32_t smw_deep_ali_merge_evals(smw_ctx* ctx, const void* a, const void* s, const void* e, const void* t, size_t n, const void* omega_fr_host, const void* z_fr_host, void* f0_out, int32_t mem); /* deep_ali/src/lib.rs:60-105 (f0 only; c_star is discarded by build_f0) */
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif

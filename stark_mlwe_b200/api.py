@@ -1,0 +1,660 @@
+"""Host-side mirror of the reference's Rust API for the commitment hot path, over the C ABI of libsmw.so.
+
+Names and argument meaning follow the reference crates (file:line cited per item) so the parity tests read
+like the reference's own tests; conditions on which the reference panics raise SmwError here (the C ABI
+returns a status code, include/smw.h).  Field elements travel as numpy uint64 arrays of shape (..., 4)
+(Montgomery limbs, the memory image of ark-ff's Fp256) or as torch CUDA tensors of dtype int64 with the
+same layout, which are used in place on the device.  All arithmetic happens in the CUDA library.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import HOST, DEVICE
+
+P = 0x40000000000000000000000000000000224698FC0994A8DD8C46EB2100000001
+
+
+class SmwError(RuntimeError):
+    def __init__(self, code, msg=""):
+        self.code = code
+        self.name = _lib.ERR.get(code, str(code))
+        super().__init__("%s: %s" % (self.name, msg))
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _buf(x):
+    """-> (pointer, n_fr, mem, keepalive)"""
+    if x is None:
+        return None, 0, HOST, None
+    if _is_torch(x):
+        assert x.is_cuda and x.is_contiguous() and x.element_size() == 8 and x.shape[-1] == 4
+        return C.c_void_p(x.data_ptr()), x.numel() // 4, DEVICE, x
+    a = np.ascontiguousarray(x, dtype=np.uint64)
+    assert a.shape[-1] == 4, "field arrays have shape (..., 4)"
+    return C.c_void_p(a.ctypes.data), a.size // 4, HOST, a
+
+
+def _fr1(x):
+    a = np.ascontiguousarray(x, dtype=np.uint64).reshape(4)
+    return a
+
+
+def _out(n):
+    return np.zeros((n, 4), dtype=np.uint64)
+
+
+def _bytes(b):
+    b = bytes(b)
+    return (C.c_uint8 * max(len(b), 1)).from_buffer_copy(b if b else b"\0"), len(b)
+
+
+class Context:
+    """One CUDA device + stream (smw_ctx). Not in the reference: the reference has no device."""
+
+    def __init__(self, device=0, stream=None):
+        self.L = _lib.load()
+        h = C.c_void_p()
+        rc = self.L.smw_ctx_create_on_stream(int(device), C.c_void_p(stream) if stream else None, C.byref(h))
+        if rc:
+            raise SmwError(rc, "cannot create a context on CUDA device %d (no CPU fallback exists)" % device)
+        self.h = h
+        self.device = device
+
+    def check(self, rc):
+        if rc:
+            raise SmwError(rc, (self.L.smw_last_error(self.h) or b"").decode())
+
+    def sync(self):
+        self.check(self.L.smw_ctx_sync(self.h))
+
+    def launch_count(self):
+        return int(self.L.smw_ctx_launch_count(self.h))
+
+    def stream(self):
+        return self.L.smw_ctx_stream(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.smw_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- field helpers (ark-ff / field/src/lib.rs:206-215)
+    def from_canonical(self, canon):
+        p, n, mem, _k = _buf(canon)
+        out = _out(n)
+        self.check(self.L.smw_fr_from_canonical(self.h, p, C.c_void_p(out.ctypes.data), n, HOST))
+        return out
+
+    def to_canonical(self, fr):
+        p, n, mem, _k = _buf(fr)
+        out = _out(n)
+        self.check(self.L.smw_fr_to_canonical(self.h, p, C.c_void_p(out.ctypes.data), n, HOST))
+        return out
+
+    def root_of_unity(self, log_n):
+        out = _out(1)
+        self.check(self.L.smw_root_of_unity(self.h, int(log_n), C.c_void_p(out.ctypes.data)))
+        return out[0]
+
+
+# ----------------------------------------------------------------------------- poseidon
+class PoseidonParamsDynamic:
+    """poseidon/src/lib.rs:104-114 (device resident; static t=17 `PoseidonParams` is the same object with t == 17)."""
+
+    def __init__(self, ctx, h, owned):
+        self.ctx, self.h, self.owned = ctx, h, owned
+        self.t = int(ctx.L.smw_params_width(h))
+        self.rate = self.t - 1
+        self.rounds_full = 8
+        self.rounds_partial = int(ctx.L.smw_params_partial_rounds(h))
+
+    def export(self):
+        t, rp = self.t, self.rounds_partial
+        mds, rcf, rcp = np.zeros((t, t, 4), np.uint64), np.zeros((8, t, 4), np.uint64), np.zeros((rp, 4), np.uint64)
+        self.ctx.check(self.ctx.L.smw_params_export(self.h, C.c_void_p(mds.ctypes.data), C.c_void_p(rcf.ctypes.data), C.c_void_p(rcp.ctypes.data)))
+        return mds, rcf, rcp
+
+    def __del__(self):
+        try:
+            if self.owned and self.ctx.h:
+                self.ctx.L.smw_params_free(self.h)
+        except Exception:
+            pass
+
+
+def generate_params_t17_x5(ctx, seed):
+    """poseidon::params::generate_params_t17_x5 (poseidon/src/lib.rs:318-356)"""
+    buf, n = _bytes(seed)
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_from_seed(ctx.h, buf, n, 17, 64, C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, True)
+
+
+def params_from_seed(ctx, seed, t, rp):
+    buf, n = _bytes(seed)
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_from_seed(ctx.h, buf, n, int(t), int(rp), C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, True)
+
+
+def params_from_tables(ctx, mds, rc_full, rc_partial):
+    """A caller-built PoseidonParamsDynamic (MerkleChannelCfg::with_params accepts any, merkle/src/lib.rs:91)."""
+    t, rp = np.asarray(mds).shape[0], np.asarray(rc_partial).reshape(-1, 4).shape[0]
+    a, b, c = (np.ascontiguousarray(x, dtype=np.uint64) for x in (mds, rc_full, rc_partial))
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_from_tables(ctx.h, t, rp, C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(c.ctypes.data), HOST, C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, True)
+
+
+def poseidon_params_for_width(ctx, t):
+    """poseidon/src/lib.rs:120-146; panics (SMW_ERR_UNSUPPORTED_WIDTH) outside {9,17,33,65,129}"""
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_for_width(ctx.h, int(t), C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, False)
+
+
+def poseidon_params_for_arity(ctx, arity):
+    """poseidon/src/lib.rs:155-166"""
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_for_arity(ctx.h, int(arity), C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, False)
+
+
+def commitment_default_params(ctx):
+    """commitment::default_params (commitment/src/lib.rs:48-51) == merkle::default_params (merkle/src/lib.rs:365-368)"""
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_commitment_default(ctx.h, C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, False)
+
+
+def transcript_default_params(ctx):
+    """transcript::default_params (transcript/src/lib.rs:44-46)"""
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_params_transcript_default(ctx.h, C.byref(h)))
+    return PoseidonParamsDynamic(ctx, h, False)
+
+
+def permute(ctx, state, params, dense=False):
+    """permute / permute_dynamic (poseidon/src/lib.rs:31-68, 219-258). state: (batch, t, 4) or (t, 4); returns a permuted copy
+    (torch CUDA tensors are permuted in place)."""
+    if _is_torch(state):
+        p, n, mem, _k = _buf(state)
+        fn = ctx.L.smw_poseidon_permute_dense if dense else ctx.L.smw_poseidon_permute
+        ctx.check(fn(ctx.h, params.h, p, n // params.t, DEVICE))
+        return state
+    s = np.ascontiguousarray(state, dtype=np.uint64).copy()
+    assert s.shape[-2] == params.t, "state width must equal params.t"
+    fn = ctx.L.smw_poseidon_permute_dense if dense else ctx.L.smw_poseidon_permute
+    ctx.check(fn(ctx.h, params.h, C.c_void_p(s.ctypes.data), s.size // (4 * params.t), HOST))
+    return s
+
+
+def hash_with_ds_dynamic(ctx, ds_fields, inputs, params):
+    """poseidon/src/lib.rs:288-312"""
+    ds = np.ascontiguousarray(ds_fields, dtype=np.uint64).reshape(-1, 4)
+    inp = np.ascontiguousarray(inputs, dtype=np.uint64).reshape(-1, 4)
+    out = _out(1)
+    ctx.check(ctx.L.smw_hash_with_ds_dynamic(ctx.h, params.h, C.c_void_p(ds.ctypes.data), ds.shape[0], C.c_void_p(inp.ctypes.data) if inp.size else None, inp.shape[0], C.c_void_p(out.ctypes.data), HOST))
+    return out[0]
+
+
+def hash_with_ds(ctx, inputs, ds_tag, params):
+    """legacy sponge, poseidon/src/lib.rs:85-100"""
+    inp = np.ascontiguousarray(inputs, dtype=np.uint64).reshape(-1, 4)
+    tag = _fr1(ds_tag)
+    out = _out(1)
+    ctx.check(ctx.L.smw_hash_with_ds(ctx.h, params.h, C.c_void_p(inp.ctypes.data) if inp.size else None, inp.shape[0], C.c_void_p(tag.ctypes.data), C.c_void_p(out.ctypes.data), HOST))
+    return out[0]
+
+
+# ----------------------------------------------------------------------------- merkle
+class MerkleChannelCfg:
+    """merkle/src/lib.rs:84-112"""
+
+    def __init__(self, ctx, arity, params, tree_label=0):
+        self.ctx, self.arity, self.params, self.tree_label = ctx, arity, params, tree_label
+
+    @classmethod
+    def new(cls, ctx, arity):
+        return cls(ctx, arity, poseidon_params_for_arity(ctx, arity), 0)
+
+    @classmethod
+    def with_params(cls, ctx, arity, params):
+        return cls(ctx, arity, params, 0)
+
+    def with_tree_label(self, label):
+        return MerkleChannelCfg(self.ctx, self.arity, self.params, int(label))
+
+
+class MerkleProof:
+    """merkle/src/lib.rs:131-143"""
+
+    def __init__(self, ctx, h, arity):
+        L = ctx.L
+        nl = int(L.smw_proof_num_levels(h))
+        n = int(L.smw_proof_num_indices(h))
+        idx = np.zeros(max(n, 1), dtype=np.uint64)
+        L.smw_proof_indices(h, C.c_void_p(idx.ctypes.data))
+        self.indices = [int(v) for v in idx[:n]]
+        self.siblings, self.group_sizes = [], []
+        for l in range(nl):
+            ns, ng = int(L.smw_proof_level_siblings(h, l)), int(L.smw_proof_level_groups(h, l))
+            sib, grp = np.zeros((max(ns, 1), 4), np.uint64), np.zeros(max(ng, 1), np.uint8)
+            L.smw_proof_level(h, l, C.c_void_p(sib.ctypes.data), C.c_void_p(grp.ctypes.data))
+            self.siblings.append(sib[:ns].copy())
+            self.group_sizes.append(grp[:ng].copy())
+        self.arity = arity
+        self.nlev = nl
+        L.smw_proof_free(h)
+
+
+class MerkleTree:
+    """merkle/src/lib.rs:114-128, 147-193, 392-445. `levels[0]` are the leaves."""
+
+    def __init__(self, ctx, h, cfg, owned=True):
+        self.ctx, self.h, self.cfg, self.owned = ctx, h, cfg, owned
+
+    @classmethod
+    def new(cls, leaves, cfg):
+        ctx = cfg.ctx
+        p, n, mem, _k = _buf(leaves)
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_merkle_new(ctx.h, cfg.params.h, int(cfg.arity), int(cfg.tree_label), p, n, mem, C.byref(h)))
+        return cls(ctx, h, cfg)
+
+    @classmethod
+    def new_pairs(cls, f_vals, cp_vals, cfg):
+        ctx = cfg.ctx
+        pf, nf, memf, _k1 = _buf(f_vals)
+        pc, nc, memc, _k2 = _buf(cp_vals)
+        assert memf == memc
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_merkle_new_pairs(ctx.h, cfg.params.h, int(cfg.arity), int(cfg.tree_label), pf, pc, nf, nc, memf, C.byref(h)))
+        return cls(ctx, h, cfg)
+
+    def root(self):
+        out = _out(1)
+        self.ctx.check(self.ctx.L.smw_tree_root(self.h, C.c_void_p(out.ctypes.data)))
+        return out[0]
+
+    def arity(self):
+        return int(self.ctx.L.smw_tree_arity(self.h))
+
+    def height(self):
+        return int(self.ctx.L.smw_tree_num_levels(self.h)) - 1
+
+    def level(self, l):
+        n = int(self.ctx.L.smw_tree_level_len(self.h, int(l)))
+        out = _out(n)
+        self.ctx.check(self.ctx.L.smw_tree_level(self.h, int(l), C.c_void_p(out.ctypes.data), HOST))
+        return out
+
+    @property
+    def levels(self):
+        return [self.level(l) for l in range(self.height() + 1)]
+
+    def open_many(self, indices):
+        """open_union_of_paths (merkle/src/lib.rs:246-315)"""
+        idx = np.ascontiguousarray(indices, dtype=np.uint64)
+        h = C.c_void_p()
+        self.ctx.check(self.ctx.L.smw_tree_open_many(self.h, C.c_void_p(idx.ctypes.data) if idx.size else None, idx.size, C.byref(h)))
+        return MerkleProof(self.ctx, h, self.arity())
+
+    open_many_single = open_many
+
+    def __del__(self):
+        try:
+            if self.owned and self.ctx.h:
+                self.ctx.L.smw_tree_free(self.h)
+        except Exception:
+            pass
+
+
+def merkle_commit_columns(ctx, cols, arity, params, label0=0, label_stride=1):
+    """One MerkleTree::new per column, batched on the device; returns the roots (n_cols, 4)."""
+    if _is_torch(cols):
+        n_cols, n = cols.shape[0], cols.shape[1]
+        p, mem, keep = C.c_void_p(cols.data_ptr()), DEVICE, cols
+    else:
+        keep = np.ascontiguousarray(cols, dtype=np.uint64)
+        n_cols, n = keep.shape[0], keep.shape[1]
+        p, mem = C.c_void_p(keep.ctypes.data), HOST
+    roots = _out(n_cols)
+    ctx.check(ctx.L.smw_merkle_commit_columns(ctx.h, params.h, int(arity), int(label0), int(label_stride), p, n, n_cols, mem, C.c_void_p(roots.ctypes.data)))
+    return roots
+
+
+# ----------------------------------------------------------------------------- commitment
+class MerkleConfig:
+    """commitment/src/lib.rs:31-46"""
+
+    def __init__(self, ctx, ds_tag, params):
+        self.ctx, self.ds_tag, self.params = ctx, int(ds_tag), params
+
+    @classmethod
+    def with_default_params(cls, ctx, ds_tag):
+        return cls(ctx, ds_tag, commitment_default_params(ctx))
+
+
+class MerkleAux:
+    def __init__(self, tree):
+        self.tree = tree
+
+
+class MerkleCommitment:
+    """CommitmentScheme for MerkleCommitment (commitment/src/lib.rs:60-113): arity 16, tree_label = ds_tag."""
+
+    def __init__(self, cfg):
+        self.cfg = cfg
+
+    def tree_cfg(self):
+        return MerkleChannelCfg(self.cfg.ctx, 16, self.cfg.params, self.cfg.ds_tag)
+
+    def commit(self, leaves):
+        ctx = self.cfg.ctx
+        p, n, mem, _k = _buf(leaves)
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_commitment_commit(ctx.h, self.cfg.ds_tag, self.cfg.params.h, p, n, mem, C.byref(h)))
+        tree = MerkleTree(ctx, h, self.tree_cfg())
+        return tree.root(), MerkleAux(tree)
+
+    def open(self, indices, aux):
+        return aux.tree.open_many(indices)
+
+
+# ----------------------------------------------------------------------------- NTT / LDE
+def fft(ctx, coeffs):
+    """fft::fft (fft/src/lib.rs:22-26): natural-order coefficients -> natural-order evaluations. (n,4) or (cols,n,4)."""
+    return _ntt(ctx, coeffs, 0)
+
+
+def ifft(ctx, evals):
+    """fft::ifft (fft/src/lib.rs:28-32)"""
+    return _ntt(ctx, evals, 1)
+
+
+def _ntt(ctx, a, inverse):
+    if _is_torch(a):
+        n = a.shape[-2]
+        cols = a.numel() // (4 * n)
+        ctx.check(ctx.L.smw_ntt(ctx.h, C.c_void_p(a.data_ptr()), n.bit_length() - 1, inverse, cols, DEVICE))
+        return a
+    v = np.ascontiguousarray(a, dtype=np.uint64).copy()
+    n = v.shape[-2]
+    assert n & (n - 1) == 0
+    ctx.check(ctx.L.smw_ntt(ctx.h, C.c_void_p(v.ctypes.data), n.bit_length() - 1, inverse, v.size // (4 * n), HOST))
+    return v
+
+
+def lde(ctx, cols, log_blowup, shift, out=None):
+    """coset low-degree extension. cols: (n,4) or (n_cols,n,4) -> (..., n << log_blowup, 4)"""
+    sh = _fr1(shift)
+    if _is_torch(cols):
+        n = cols.shape[-2]
+        nc = cols.numel() // (4 * n)
+        assert out is not None
+        ctx.check(ctx.L.smw_lde(ctx.h, C.c_void_p(cols.data_ptr()), n.bit_length() - 1, int(log_blowup), C.c_void_p(sh.ctypes.data), C.c_void_p(out.data_ptr()), nc, DEVICE))
+        return out
+    v = np.ascontiguousarray(cols, dtype=np.uint64)
+    n = v.shape[-2]
+    nc = v.size // (4 * n)
+    o = np.zeros(v.shape[:-2] + (n << log_blowup, 4), dtype=np.uint64)
+    ctx.check(ctx.L.smw_lde(ctx.h, C.c_void_p(v.ctypes.data), n.bit_length() - 1, int(log_blowup), C.c_void_p(sh.ctypes.data), C.c_void_p(o.ctypes.data), nc, HOST))
+    return o
+
+
+def lde_commit(ctx, cols, log_blowup, shift, label0=0):
+    """LDE of every column, then MerkleCommitment::commit of every extended column (tree_label = label0 + column). Roots only."""
+    sh = _fr1(shift)
+    if _is_torch(cols):
+        n_cols, n = cols.shape[0], cols.shape[1]
+        p, mem, keep = C.c_void_p(cols.data_ptr()), DEVICE, cols
+    else:
+        keep = np.ascontiguousarray(cols, dtype=np.uint64)
+        n_cols, n = keep.shape[0], keep.shape[1]
+        p, mem = C.c_void_p(keep.ctypes.data), HOST
+    roots = _out(n_cols)
+    ctx.check(ctx.L.smw_lde_commit(ctx.h, p, n.bit_length() - 1, int(log_blowup), C.c_void_p(sh.ctypes.data), n_cols, int(label0), mem, C.c_void_p(roots.ctypes.data)))
+    return roots
+
+
+# ----------------------------------------------------------------------------- transcript
+class Transcript:
+    """transcript/src/lib.rs:48-117; the sponge state lives on the device."""
+
+    def __init__(self, ctx, label, params=None):
+        self.ctx = ctx
+        buf, n = _bytes(label)
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_transcript_new(ctx.h, buf, n, params.h if params else None, C.byref(h)))
+        self.h = h
+        self._params = params
+
+    @classmethod
+    def new(cls, ctx, label, params=None):
+        return cls(ctx, label, params)
+
+    def absorb_bytes(self, b):
+        buf, n = _bytes(b)
+        self.ctx.check(self.ctx.L.smw_transcript_absorb_bytes(self.h, buf, n))
+
+    def absorb_field(self, x):
+        a = _fr1(x)
+        self.ctx.check(self.ctx.L.smw_transcript_absorb_field(self.h, C.c_void_p(a.ctypes.data)))
+
+    def absorb_fields(self, xs):
+        p, n, mem, _k = _buf(xs)
+        self.ctx.check(self.ctx.L.smw_transcript_absorb_fields(self.h, p, n, mem))
+
+    def challenge(self, label):
+        buf, n = _bytes(label)
+        out = _out(1)
+        self.ctx.check(self.ctx.L.smw_transcript_challenge(self.h, buf, n, C.c_void_p(out.ctypes.data)))
+        return out[0]
+
+    def challenges(self, label, n):
+        return [self.challenge(bytes(label) + int(i).to_bytes(8, "little")) for i in range(n)]
+
+    def state(self):
+        st = np.zeros((17, 4), np.uint64)
+        pos = C.c_int32(0)
+        self.ctx.check(self.ctx.L.smw_transcript_state(self.h, C.c_void_p(st.ctypes.data), C.byref(pos)))
+        return st, pos.value
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.ctx.L.smw_transcript_free(self.h)
+        except Exception:
+            pass
+
+
+def tr_hash_fields_tagged(ctx, tag, fields):
+    """deep_ali/src/fri.rs:28-35"""
+    buf, n = _bytes(tag)
+    p, nf, mem, _k = _buf(np.ascontiguousarray(fields, dtype=np.uint64).reshape(-1, 4) if not _is_torch(fields) else fields)
+    out = _out(1)
+    ctx.check(ctx.L.smw_tr_hash_fields_tagged(ctx.h, buf, n, p if nf else None, nf, mem, C.c_void_p(out.ctypes.data)))
+    return out[0]
+
+
+def hash_leaf_pair(ctx, f, s):
+    """deep_ali/src/fri.rs:38-44, element-wise over arrays"""
+    pf, n, mem, _k1 = _buf(f)
+    ps, n2, mem2, _k2 = _buf(s)
+    assert n == n2 and mem == mem2 == HOST
+    out = _out(n)
+    ctx.check(ctx.L.smw_hash_leaf_pair(ctx.h, pf, ps, n, C.c_void_p(out.ctypes.data), HOST))
+    return out
+
+
+# ----------------------------------------------------------------------------- FRI
+def fri_sample_z_ell(ctx, seed_z, level, domain_size):
+    """deep_ali/src/fri.rs:59-82"""
+    out = _out(1)
+    ctx.check(ctx.L.smw_fri_sample_z_ell(ctx.h, int(seed_z), int(level), int(domain_size), C.c_void_p(out.ctypes.data)))
+    return out[0]
+
+
+def fri_fold_layer(ctx, f_l, z_l, m):
+    """deep_ali/src/fri.rs:85-102"""
+    p, n, mem, _k = _buf(f_l)
+    z = _fr1(z_l)
+    out = _out(n // m if m else 0)
+    ctx.check(ctx.L.smw_fri_fold_layer(ctx.h, p, n, C.c_void_p(z.ctypes.data), int(m), C.c_void_p(out.ctypes.data), HOST))
+    return out
+
+
+def compute_s_layer(ctx, f_l, z_l, m):
+    """deep_ali/src/fri.rs:123-143"""
+    p, n, mem, _k = _buf(f_l)
+    z = _fr1(z_l)
+    out = _out(n)
+    ctx.check(ctx.L.smw_compute_s_layer(ctx.h, p, n, C.c_void_p(z.ctypes.data), int(m), C.c_void_p(out.ctypes.data), HOST))
+    return out
+
+
+def pick_arity_for_layer(n, requested_m):
+    """deep_ali/src/fri.rs:220-229"""
+    return int(_lib.load().smw_pick_arity_for_layer(int(n), int(requested_m)))
+
+
+class FriProverParams:
+    """deep_ali/src/fri.rs:208"""
+
+    def __init__(self, schedule, seed_z):
+        self.schedule, self.seed_z = list(schedule), int(seed_z)
+
+
+class FriLayerCommitment:
+    """deep_ali/src/fri.rs:194-204 (f, s and tree are fetched from the device on access)"""
+
+    def __init__(self, st, l):
+        self._st, self._l = st, l
+        n, m, ar, hs = C.c_size_t(), C.c_size_t(), C.c_int32(), C.c_int32()
+        st.ctx.check(st.ctx.L.smw_fri_layer_info(st.h, l, C.byref(n), C.byref(m), C.byref(ar), C.byref(hs)))
+        self.n, self.m, self.arity, self.hashed_leaves = n.value, m.value, ar.value, bool(hs.value)
+
+    @property
+    def f(self):
+        out = _out(self.n)
+        self._st.ctx.check(self._st.ctx.L.smw_fri_layer_f(self._st.h, self._l, C.c_void_p(out.ctypes.data), HOST))
+        return out
+
+    @property
+    def s(self):
+        out = _out(self.n)
+        self._st.ctx.check(self._st.ctx.L.smw_fri_layer_s(self._st.h, self._l, C.c_void_p(out.ctypes.data), HOST))
+        return out
+
+    @property
+    def tree(self):
+        ctx = self._st.ctx
+        h = C.c_void_p(ctx.L.smw_fri_layer_tree(self._st.h, self._l))
+        return MerkleTree(ctx, h, None, owned=False)
+
+    @property
+    def root(self):
+        return self.tree.root()
+
+
+class FriProverState:
+    """deep_ali/src/fri.rs:210-216"""
+
+    def __init__(self, ctx, h, schedule):
+        self.ctx, self.h = ctx, h
+        self.schedule = list(schedule)
+        self.layers = [FriLayerCommitment(self, l) for l in range(len(schedule) + 1)]
+
+    @property
+    def z_layers(self):
+        out = _out(max(len(self.schedule), 1))
+        self.ctx.check(self.ctx.L.smw_fri_z(self.h, C.c_void_p(out.ctypes.data)))
+        return out[: len(self.schedule)]
+
+    def roots(self):
+        out = _out(len(self.schedule) + 1)
+        self.ctx.check(self.ctx.L.smw_fri_roots(self.h, C.c_void_p(out.ctypes.data)))
+        return out
+
+    @property
+    def f_layers(self):
+        return [l.f for l in self.layers]
+
+    @property
+    def s_layers(self):
+        return [l.s for l in self.layers]
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.ctx.L.smw_fri_free(self.h)
+        except Exception:
+            pass
+
+
+def fri_build_transcript(ctx, f0, params):
+    """deep_ali/src/fri.rs:231-312 (the FriDomain argument only carries n0 = len(f0))"""
+    p, n, mem, _k = _buf(f0)
+    sch = np.ascontiguousarray(params.schedule, dtype=np.uint64)
+    h = C.c_void_p()
+    ctx.check(ctx.L.smw_fri_build_transcript(ctx.h, p, n, C.c_void_p(sch.ctypes.data) if sch.size else None, len(params.schedule), params.seed_z, mem, C.byref(h)))
+    return FriProverState(ctx, h, params.schedule)
+
+
+# ----------------------------------------------------------------------------- Merkle-folded sum-check
+def sumcheck_round_coeffs(ctx, layer):
+    """channel/src/lib.rs:406-416"""
+    p, n, mem, _k = _buf(layer)
+    c0, c1 = _out(1), _out(1)
+    ctx.check(ctx.L.smw_sumcheck_round_coeffs(ctx.h, p, n, C.c_void_p(c0.ctypes.data), C.c_void_p(c1.ctypes.data), mem))
+    return c0[0], c1[0]
+
+
+def mf_round_challenge_from_root(ctx, round_idx, prev_root, tr_params=None):
+    """channel/src/lib.rs:592-598"""
+    r = _fr1(prev_root)
+    out = _out(1)
+    ctx.check(ctx.L.smw_mf_round_challenge_from_root(ctx.h, int(round_idx), C.c_void_p(r.ctypes.data), tr_params.h if tr_params else None, C.c_void_p(out.ctypes.data)))
+    return out[0]
+
+
+def mf_fold(ctx, cur, r):
+    """channel/src/lib.rs:648-655"""
+    p, n, mem, _k = _buf(cur)
+    rr = _fr1(r)
+    out = _out(n // 2)
+    ctx.check(ctx.L.smw_mf_fold(ctx.h, p, n, C.c_void_p(rr.ctypes.data), C.c_void_p(out.ctypes.data), HOST))
+    return out
+
+
+def mf_commit_phase(ctx, table, ds_tag):
+    """SumCheckMFProver::new + the commit half of every round (channel/src/lib.rs:600-657): roots, r_i, final value"""
+    p, n, mem, _k = _buf(table)
+    k = n.bit_length() - 1
+    roots, rs, fin = _out(k + 1), _out(max(k, 1)), _out(1)
+    ctx.check(ctx.L.smw_mf_commit_phase(ctx.h, int(ds_tag), p, n, mem, C.c_void_p(roots.ctypes.data), C.c_void_p(rs.ctypes.data), C.c_void_p(fin.ctypes.data)))
+    return roots, rs[:k], fin[0]
+
+
+def deep_ali_merge_evals(ctx, a, s, e, t, omega, z):
+    """deep_ali/src/lib.rs:47-105, f0 only"""
+    pa, n, mem, _k1 = _buf(a)
+    ps, _, _, _k2 = _buf(s)
+    pe, _, _, _k3 = _buf(e)
+    pt, _, _, _k4 = _buf(t)
+    w, zz = _fr1(omega), _fr1(z)
+    out = _out(n)
+    ctx.check(ctx.L.smw_deep_ali_merge_evals(ctx.h, pa, ps, pe, pt, n, C.c_void_p(w.ctypes.data), C.c_void_p(zz.ctypes.data), C.c_void_p(out.ctypes.data), HOST))
+    return out

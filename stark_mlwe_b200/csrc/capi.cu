@@ -1,0 +1,784 @@
+// capi.cu — the C ABI (include/smw.h) over the CUDA kernels: handle management, host<->device staging,
+// and the orchestration of level-by-level tree builds, the FRI-like commit phase and the
+// Merkle-folded sum-check commit loop.  No field arithmetic happens on the host: byte strings are only
+// packed into 256-bit little-endian words (transcript/src/lib.rs:13-41) and reduced on the device.
+#include "smw_internal.h"
+#include <cstring>
+#include <cstdio>
+#include <algorithm>
+#include <memory>
+#include <array>
+#include <map>
+
+using namespace smw;
+
+namespace smw {
+int set_err(smw_ctx* c, int code, const char* what) { if (c) c->last_error = what ? what : ""; return code; }
+int cuda_err(smw_ctx* c, cudaError_t e, const char* what) {
+    if (c) { c->last_error = std::string(what ? what : "") + ": " + cudaGetErrorString(e); }
+    return SMW_ERR_CUDA;
+}
+} // namespace smw
+
+namespace {
+
+constexpr size_t FR = 32;
+
+// caller buffer -> device pointer (copy in when it lives on the host)
+struct In {
+    smw_ctx* c; const uint32_t* d = nullptr; uint32_t* owned = nullptr; int rc = SMW_OK;
+    In(smw_ctx* ctx, const void* p, size_t n_fr, int mem) : c(ctx) {
+        if (n_fr == 0 || p == nullptr) return;
+        if (mem == SMW_DEVICE) { d = (const uint32_t*)p; return; }
+        cudaError_t e = cudaMalloc(&owned, n_fr * FR);
+        if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(input staging)"); return; }
+        e = cudaMemcpyAsync(owned, p, n_fr * FR, cudaMemcpyHostToDevice, c->stream);
+        if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMemcpyAsync(H2D)"); return; }
+        d = owned;
+    }
+    uint32_t* release() { uint32_t* r = owned; owned = nullptr; return r; }
+    ~In() { if (owned) { cudaStreamSynchronize(c->stream); cudaFree(owned); } }
+};
+// caller output buffer: device scratch when it lives on the host, copied back by finish()
+struct Out {
+    smw_ctx* c; uint32_t* d = nullptr; void* host = nullptr; size_t n; bool owned = false; int rc = SMW_OK;
+    Out(smw_ctx* ctx, void* p, size_t n_fr, int mem) : c(ctx), n(n_fr) {
+        if (n_fr == 0) return;
+        if (mem == SMW_DEVICE) { d = (uint32_t*)p; return; }
+        host = p; owned = true;
+        cudaError_t e = cudaMalloc(&d, n_fr * FR);
+        if (e != cudaSuccess) rc = cuda_err(c, e, "cudaMalloc(output staging)");
+    }
+    int finish() {
+        if (!owned || n == 0) return SMW_OK;
+        SMW_CUDA(c, cudaMemcpyAsync(host, d, n * FR, cudaMemcpyDeviceToHost, c->stream));
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+        return SMW_OK;
+    }
+    ~Out() { if (owned && d) { cudaStreamSynchronize(c->stream); cudaFree(d); } }
+};
+int d2h(smw_ctx* c, void* host, const void* dev, size_t bytes) {
+    SMW_CUDA(c, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SMW_OK;
+}
+
+int width_for_arity(int arity) {   // poseidon/src/lib.rs:155-166
+    if (arity < 0) return -1;
+    if (arity <= 8) return 9; if (arity <= 16) return 17; if (arity <= 32) return 33; if (arity <= 64) return 65; if (arity <= 128) return 129;
+    return -1;
+}
+int rp_for_width(int t) { switch (t) { case 9: return 60; case 17: return 64; case 33: return 68; case 65: return 76; case 129: return 84; default: return -1; } }
+
+// ---- transcript byte packing (transcript/src/lib.rs:13-41): 256-bit LE words, reduced on the device
+using Word = std::array<uint32_t, 8>;
+Word word_from_bytes(const uint8_t* b, size_t n) {   // n <= 32
+    uint8_t le[32]; memset(le, 0, 32); memcpy(le, b, n);
+    Word w; for (int i = 0; i < 8; i++) w[i] = (uint32_t)le[4 * i] | ((uint32_t)le[4 * i + 1] << 8) | ((uint32_t)le[4 * i + 2] << 16) | ((uint32_t)le[4 * i + 3] << 24);
+    return w;
+}
+Word word_from_u64(uint64_t v) { Word w{}; w[0] = (uint32_t)v; w[1] = (uint32_t)(v >> 32); return w; }
+Word tag_word(const char* s) { return word_from_bytes((const uint8_t*)s, strlen(s)); }
+const char* TAG_INIT = "FSv1-TRANSCRIPT-INIT"; const char* TAG_ABSORB = "FSv1-ABSORB-BYTES"; const char* TAG_CHAL = "FSv1-CHALLENGE";
+void push_absorb_bytes(std::vector<Word>& v, const uint8_t* b, size_t n) {   // marker, then 31-byte words
+    v.push_back(tag_word(TAG_ABSORB));
+    for (size_t off = 0; off < n; off += 31) v.push_back(word_from_bytes(b + off, std::min<size_t>(31, n - off)));
+}
+void push_challenge(std::vector<Word>& v, const uint8_t* label, size_t n) { v.push_back(tag_word(TAG_CHAL)); push_absorb_bytes(v, label, n); }
+int advance_pos(int pos, size_t count) { for (size_t i = 0; i < count; i++) { if (pos == 16) pos = 0; pos++; } return pos; }
+
+int upload_words(smw_ctx* c, const std::vector<Word>& w, uint32_t** d) {
+    *d = nullptr; if (w.empty()) return SMW_OK;
+    SMW_CUDA(c, cudaMalloc(d, w.size() * FR));
+    SMW_CUDA(c, cudaMemcpyAsync(*d, w.data(), w.size() * FR, cudaMemcpyHostToDevice, c->stream));
+    return SMW_OK;
+}
+
+int get_transcript_params(smw_ctx* c, smw_params* given, smw_params** out) {
+    if (given) { if (given->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript params must have t = 17"); *out = given; return SMW_OK; }
+    return smw_params_transcript_default(c, out);
+}
+
+// one-shot transcript hash on the device: new(label0) ; absorb_bytes(tag) ; fields ; challenge(chal)
+int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t* tag, size_t tag_len, const std::vector<Word>& imm_fields,
+                 const uint32_t* d_ext, size_t n_ext, const char* chal, uint32_t* d_out) {
+    std::vector<Word> A, C;
+    A.push_back(tag_word(TAG_INIT));
+    push_absorb_bytes(A, (const uint8_t*)label0, strlen(label0));
+    push_absorb_bytes(A, tag, tag_len);
+    for (auto& w : imm_fields) A.push_back(w);
+    push_challenge(C, (const uint8_t*)chal, strlen(chal));
+    uint32_t *dA, *dC; int rc = upload_words(c, A, &dA); if (rc) return rc; rc = upload_words(c, C, &dC); if (rc) { cudaFree(dA); return rc; }
+    rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA, (int)A.size(), d_ext, n_ext, dC, (int)C.size(), 1, d_out);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(dA); cudaFree(dC);
+    return rc;
+}
+
+// level-by-level tree over a device level 0 (merkle/src/lib.rs:164-181)
+int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out) {
+    auto t = std::make_unique<smw_tree>();
+    t->ctx = c; t->params = p; t->arity = arity; t->tree_label = label;
+    t->len.push_back(n); t->lv.push_back(d_level0); t->owned.push_back(own0);
+    uint32_t level = 0;
+    while (t->len.back() > 1) {
+        size_t cn = t->len.back(), nn = (cn + arity - 1) / arity;
+        uint32_t* d_next; cudaError_t e = cudaMalloc(&d_next, nn * FR);
+        if (e != cudaSuccess) { smw_tree_free(t.release()); return cuda_err(c, e, "cudaMalloc(tree level)"); }
+        t->len.push_back(nn); t->lv.push_back(d_next); t->owned.push_back(true);
+        int rc = launch_merkle_level(c, p, t->lv[t->lv.size() - 2], cn, d_next, nn, arity, level, label, 0, 0, 1, 0, 0);
+        if (rc) { smw_tree_free(t.release()); return rc; }
+        level++;
+    }
+    *out = t.release();
+    return SMW_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------- context
+int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** out) {
+    if (!out) return SMW_ERR_INVALID_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return SMW_ERR_CUDA;      // no CPU fallback
+    if (device < 0 || device >= ndev) return SMW_ERR_INVALID_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return SMW_ERR_CUDA;
+    smw_ctx* c = new smw_ctx();
+    c->device = device;
+    if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
+    else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SMW_ERR_CUDA; } c->own_stream = true; }
+    *out = c;
+    return SMW_OK;
+}
+int32_t smw_ctx_create(int32_t device, smw_ctx** out) { return smw_ctx_create_on_stream(device, nullptr, out); }
+static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_ext); delete p; }
+void smw_ctx_destroy(smw_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_params_internal(c->commitment_default); free_params_internal(c->transcript_default);
+    for (auto& kv : c->by_width) free_params_internal(kv.second);
+    cudaFree(c->d_twiddles); cudaFree(c->d_scratch);
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+int32_t smw_ctx_sync(smw_ctx* c) { if (!c) return SMW_ERR_INVALID_ARG; SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK; }
+const char* smw_last_error(const smw_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
+uint64_t smw_ctx_launch_count(const smw_ctx* c) { return c ? c->launches : 0; }
+void* smw_ctx_stream(const smw_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+// ---------------------------------------------------------------------------------------- field
+int32_t smw_fr_from_canonical(smw_ctx* c, const void* in, void* out, size_t n, int32_t mem) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In i(c, in, n, mem); if (i.rc) return i.rc; Out o(c, out, n, mem); if (o.rc) return o.rc;
+    int rc = launch_to_mont(c, i.d, o.d, n, 0); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_fr_to_canonical(smw_ctx* c, const void* in, void* out, size_t n, int32_t mem) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In i(c, in, n, mem); if (i.rc) return i.rc; Out o(c, out, n, mem); if (o.rc) return o.rc;
+    int rc = launch_to_mont(c, i.d, o.d, n, 1); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_root_of_unity(smw_ctx* c, int32_t log_n, void* out_host) {
+    if (!c || !out_host) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    Out o(c, out_host, 1, SMW_HOST); if (o.rc) return o.rc;
+    int rc = launch_root_of_unity(c, log_n, o.d); if (rc) return rc;
+    return o.finish();
+}
+
+// ---------------------------------------------------------------------------------------- params
+int32_t smw_params_from_seed(smw_ctx* c, const uint8_t* seed, size_t seed_len, int32_t t, int32_t rp, smw_params** out) {
+    if (!c || !out || (!seed && seed_len)) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    if (rp_for_width(t) < 0) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "unsupported Poseidon width");
+    if (rp <= 0 || rp > 1024) return set_err(c, SMW_ERR_INVALID_ARG, "bad partial round count");
+    smw_params* p = new smw_params(); p->ctx = c; p->t = t; p->rp = rp;
+    int rc = launch_derive_params(c, p, seed, (int)seed_len);
+    if (rc) { free_params_internal(p); return rc; }
+    *out = p; return SMW_OK;
+}
+int32_t smw_params_for_width(smw_ctx* c, int32_t t, smw_params** out) {
+    if (!c || !out) return SMW_ERR_INVALID_ARG;
+    int rp = rp_for_width(t);
+    if (rp < 0) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "unsupported Poseidon width t; supported t in {9, 17, 33, 65, 129}");
+    auto it = c->by_width.find(t);
+    if (it != c->by_width.end()) { *out = it->second; return SMW_OK; }
+    uint8_t seed[25]; memcpy(seed, "POSEIDON-PALLAS-T", 17);                 // poseidon/src/lib.rs:168-174 seed_for_t
+    for (int i = 0; i < 8; i++) seed[17 + i] = (uint8_t)((uint64_t)t >> (8 * i));
+    smw_params* p; int rc = smw_params_from_seed(c, seed, 25, t, rp, &p); if (rc) return rc;
+    p->owned_by_ctx = true; c->by_width[t] = p; *out = p; return SMW_OK;
+}
+int32_t smw_params_for_arity(smw_ctx* c, int32_t arity, smw_params** out) {
+    if (!c || !out) return SMW_ERR_INVALID_ARG;
+    int t = width_for_arity(arity);
+    if (t < 0) return set_err(c, SMW_ERR_UNSUPPORTED_ARITY, "unsupported Merkle arity; max supported = 128");
+    return smw_params_for_width(c, t, out);
+}
+int32_t smw_params_commitment_default(smw_ctx* c, smw_params** out) {
+    if (!c || !out) return SMW_ERR_INVALID_ARG;
+    if (!c->commitment_default) {
+        smw_params* p; int rc = smw_params_from_seed(c, (const uint8_t*)"POSEIDON-T17-X5-SEED", 20, 17, 64, &p); if (rc) return rc;
+        p->owned_by_ctx = true; c->commitment_default = p;
+    }
+    *out = c->commitment_default; return SMW_OK;
+}
+int32_t smw_params_transcript_default(smw_ctx* c, smw_params** out) {
+    if (!c || !out) return SMW_ERR_INVALID_ARG;
+    if (!c->transcript_default) {
+        smw_params* p; int rc = smw_params_from_seed(c, (const uint8_t*)"POSEIDON-T17-X5-TRANSCRIPT", 26, 17, 64, &p); if (rc) return rc;
+        p->owned_by_ctx = true; c->transcript_default = p;
+    }
+    *out = c->transcript_default; return SMW_OK;
+}
+int32_t smw_params_from_tables(smw_ctx* c, int32_t t, int32_t rp, const void* mds, const void* rcf, const void* rcp, int32_t mem, smw_params** out) {
+    if (!c || !out || !mds || !rcf || !rcp) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    if (rp_for_width(t) < 0) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "unsupported Poseidon width");
+    if (rp <= 0 || rp > 1024) return set_err(c, SMW_ERR_INVALID_ARG, "bad partial round count");
+    In a(c, mds, (size_t)t * t, mem), b(c, rcf, (size_t)8 * t, mem), d(c, rcp, (size_t)rp, mem);
+    if (a.rc) return a.rc; if (b.rc) return b.rc; if (d.rc) return d.rc;
+    smw_params* p = new smw_params(); p->ctx = c; p->t = t; p->rp = rp;
+    int rc = launch_upload_params(c, p, a.d, b.d, d.d);
+    if (rc) { free_params_internal(p); return rc; }
+    *out = p; return SMW_OK;
+}
+int32_t smw_params_export(smw_params* p, void* mds, void* rcf, void* rcp) {
+    if (!p) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = p->ctx; cudaSetDevice(c->device);
+    size_t n1 = (size_t)p->t * p->t, n2 = (size_t)8 * p->t, n3 = p->rp;
+    if (mds) SMW_CUDA(c, cudaMemcpyAsync(mds, p->d_ext, n1 * FR, cudaMemcpyDeviceToHost, c->stream));
+    if (rcf) SMW_CUDA(c, cudaMemcpyAsync(rcf, p->d_ext + n1 * 8, n2 * FR, cudaMemcpyDeviceToHost, c->stream));
+    if (rcp) SMW_CUDA(c, cudaMemcpyAsync(rcp, p->d_ext + (n1 + n2) * 8, n3 * FR, cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SMW_OK;
+}
+int32_t smw_params_width(const smw_params* p) { return p ? p->t : -1; }
+int32_t smw_params_partial_rounds(const smw_params* p) { return p ? p->rp : -1; }
+void smw_params_free(smw_params* p) { if (!p || p->owned_by_ctx) return; cudaSetDevice(p->ctx->device); cudaStreamSynchronize(p->ctx->stream); free_params_internal(p); }
+
+// ---------------------------------------------------------------------------------------- permutation / sponges
+static int permute_impl(smw_ctx* c, const smw_params* p, void* states, size_t batch, int mem, bool sparse) {
+    if (!c || !p || (!states && batch)) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    size_t n = batch * p->t;
+    if (mem == SMW_DEVICE) return launch_permute_batch(c, p, (uint32_t*)states, batch, sparse);
+    In i(c, states, n, SMW_HOST); if (i.rc) return i.rc;
+    int rc = launch_permute_batch(c, p, i.owned, batch, sparse); if (rc) return rc;
+    return d2h(c, states, i.owned, n * FR);
+}
+int32_t smw_poseidon_permute(smw_ctx* c, const smw_params* p, void* states, size_t batch, int32_t mem) { return permute_impl(c, p, states, batch, mem, true); }
+int32_t smw_poseidon_permute_dense(smw_ctx* c, const smw_params* p, void* states, size_t batch, int32_t mem) { return permute_impl(c, p, states, batch, mem, false); }
+int32_t smw_hash_with_ds_dynamic(smw_ctx* c, const smw_params* p, const void* ds, size_t n_ds, const void* inputs, size_t n, void* out, int32_t mem) {
+    if (!c || !p || !out) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, ds, n_ds, mem), b(c, inputs, n, mem); if (a.rc) return a.rc; if (b.rc) return b.rc;
+    Out o(c, out, 1, mem); if (o.rc) return o.rc;
+    int rc = launch_hash_ds_single(c, p, a.d, (int)n_ds, b.d, n, o.d); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_hash_with_ds(smw_ctx* c, const smw_params* p, const void* inputs, size_t n, const void* ds_tag, void* out, int32_t mem) {
+    if (!c || !p || !out || !ds_tag) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, inputs, n, mem), b(c, ds_tag, 1, mem); if (a.rc) return a.rc; if (b.rc) return b.rc;
+    Out o(c, out, 1, mem); if (o.rc) return o.rc;
+    int rc = launch_hash_legacy_single(c, p, a.d, n, b.d, o.d); if (rc) return rc;
+    return o.finish();
+}
+
+// ---------------------------------------------------------------------------------------- Merkle
+static int check_tree_args(smw_ctx* c, smw_params* p, int arity, size_t n) {
+    if (!c || !p) return SMW_ERR_INVALID_ARG;
+    if (n == 0) return set_err(c, SMW_ERR_EMPTY, "no leaves");
+    if (arity < 1 || arity > 128) return set_err(c, SMW_ERR_UNSUPPORTED_ARITY, "unsupported Merkle arity; max supported = 128");
+    if (width_for_arity(arity) != p->t) return set_err(c, SMW_ERR_ARITY_WIDTH, "arity incompatible with Poseidon width t");
+    return SMW_OK;
+}
+int32_t smw_merkle_new(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, const void* leaves, size_t n, int32_t mem, smw_tree** out) {
+    if (!out) return SMW_ERR_INVALID_ARG;
+    int rc = check_tree_args(c, p, arity, n); if (rc) return rc;
+    if (!leaves) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    // the tree owns a copy of the leaves, as MerkleTree::new takes the Vec by value (merkle/src/lib.rs:147)
+    uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n * FR));
+    SMW_CUDA(c, cudaMemcpyAsync(d0, leaves, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    return build_tree(c, p, arity, label, d0, true, n, out);
+}
+int32_t smw_merkle_new_pairs(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, const void* f, const void* cp, size_t n_f, size_t n_cp, int32_t mem, smw_tree** out) {
+    if (!out || !c) return SMW_ERR_INVALID_ARG;
+    if (n_f != n_cp) return set_err(c, SMW_ERR_LENGTH_MISMATCH, "f and cp length mismatch");
+    int rc = check_tree_args(c, p, arity, n_f); if (rc) return rc;
+    if (!f || !cp) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, f, n_f, mem), b(c, cp, n_f, mem); if (a.rc) return a.rc; if (b.rc) return b.rc;
+    uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n_f * FR));
+    rc = launch_pair_leaves(c, p, a.d, b.d, n_f, arity, label, 0, d0, 1);
+    if (rc) { cudaFree(d0); return rc; }
+    return build_tree(c, p, arity, label, d0, true, n_f, out);
+}
+int32_t smw_tree_root(smw_tree* t, void* out_host) { if (!t || !out_host) return SMW_ERR_INVALID_ARG; cudaSetDevice(t->ctx->device); return d2h(t->ctx, out_host, t->lv.back(), FR); }
+int32_t smw_tree_num_levels(const smw_tree* t) { return t ? (int32_t)t->lv.size() : -1; }
+size_t smw_tree_level_len(const smw_tree* t, int32_t level) { return (t && level >= 0 && level < (int)t->len.size()) ? t->len[level] : 0; }
+int32_t smw_tree_level(smw_tree* t, int32_t level, void* out, int32_t mem) {
+    if (!t || !out || level < 0 || level >= (int)t->lv.size()) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = t->ctx; cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaMemcpyAsync(out, t->lv[level], t->len[level] * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SMW_OK;
+}
+int32_t smw_tree_arity(const smw_tree* t) { return t ? t->arity : -1; }
+void smw_tree_free(smw_tree* t) {
+    if (!t) return;
+    cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream);
+    for (size_t i = 0; i < t->lv.size(); i++) if (t->owned[i]) cudaFree(t->lv[i]);
+    delete t;
+}
+int32_t smw_merkle_commit_columns(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label0, uint64_t label_stride,
+                                  const void* cols, size_t n, int32_t n_cols, int32_t mem, void* roots_out_host) {
+    int rc = check_tree_args(c, p, arity, n); if (rc) return rc;
+    if (!cols || !roots_out_host || n_cols <= 0) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In in(c, cols, n * (size_t)n_cols, mem); if (in.rc) return in.rc;
+    if (n == 1) return d2h(c, roots_out_host, in.d, (size_t)n_cols * FR);   // a 1-leaf tree's root is the leaf
+    // two ping-pong buffers sized for level 1
+    size_t n1 = (n + arity - 1) / arity, n2 = (n1 + arity - 1) / arity;
+    uint32_t *bufA, *bufB = nullptr;
+    SMW_CUDA(c, cudaMalloc(&bufA, n1 * (size_t)n_cols * FR));
+    if (n1 > 1) { cudaError_t e = cudaMalloc(&bufB, n2 * (size_t)n_cols * FR); if (e != cudaSuccess) { cudaFree(bufA); return cuda_err(c, e, "cudaMalloc"); } }
+    const uint32_t* cur = in.d; size_t cn = n, cstride = n; uint32_t level = 0; uint32_t* dst = bufA;
+    while (cn > 1) {
+        size_t nn = (cn + arity - 1) / arity;
+        rc = launch_merkle_level(c, p, cur, cn, dst, nn, arity, level, label0, label_stride, 0, n_cols, cstride, nn);
+        if (rc) break;
+        cur = dst; cn = nn; cstride = nn; level++;
+        dst = (dst == bufA) ? bufB : bufA;
+    }
+    if (!rc) rc = d2h(c, roots_out_host, cur, (size_t)n_cols * FR);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(bufA); cudaFree(bufB);
+    return rc;
+}
+int32_t smw_commitment_commit(smw_ctx* c, uint64_t ds_tag, smw_params* params, const void* leaves, size_t n, int32_t mem, smw_tree** out) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    if (!params) { int rc = smw_params_commitment_default(c, &params); if (rc) return rc; }
+    return smw_merkle_new(c, params, 16, ds_tag, leaves, n, mem, out);     // commitment/src/lib.rs:69-77: arity 16, tree_label = ds_tag
+}
+
+// ---------------------------------------------------------------------------------------- NTT / LDE
+int32_t smw_ntt(smw_ctx* c, void* buf, int32_t log_n, int32_t inverse, int32_t n_cols, int32_t mem) {
+    if (!c || !buf || n_cols < 0 || log_n < 0 || log_n > 32) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    size_t n = (size_t)1 << log_n;
+    if (mem == SMW_DEVICE) return launch_ntt(c, (uint32_t*)buf, log_n, inverse, n_cols, n);
+    In i(c, buf, n * n_cols, SMW_HOST); if (i.rc) return i.rc;
+    int rc = launch_ntt(c, i.owned, log_n, inverse, n_cols, n); if (rc) return rc;
+    return d2h(c, buf, i.owned, n * n_cols * FR);
+}
+int32_t smw_lde(smw_ctx* c, const void* in, int32_t log_n, int32_t log_blowup, const void* shift_host, void* out, int32_t n_cols, int32_t mem) {
+    if (!c || !in || !out || !shift_host || n_cols < 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    size_t n = (size_t)1 << log_n, N = n << log_blowup;
+    In i(c, in, n * n_cols, mem), g(c, shift_host, 1, SMW_HOST); if (i.rc) return i.rc; if (g.rc) return g.rc;
+    Out o(c, out, N * n_cols, mem); if (o.rc) return o.rc;
+    int rc = launch_lde(c, i.d, log_n, log_blowup, g.d, o.d, n_cols); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_blowup, const void* shift_host, int32_t n_cols,
+                       uint64_t label0, int32_t mem, void* roots_out_host) {
+    if (!c || !cols || !roots_out_host || !shift_host || n_cols <= 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    size_t n = (size_t)1 << log_n, N = n << log_blowup;
+    smw_params* p; int rc = smw_params_commitment_default(c, &p); if (rc) return rc;
+    In i(c, cols, n * n_cols, mem), g(c, shift_host, 1, SMW_HOST); if (i.rc) return i.rc; if (g.rc) return g.rc;
+    uint32_t* d_ext; SMW_CUDA(c, cudaMalloc(&d_ext, N * (size_t)n_cols * FR));
+    rc = launch_lde(c, i.d, log_n, log_blowup, g.d, d_ext, n_cols);
+    if (!rc) rc = smw_merkle_commit_columns(c, p, 16, label0, 1, d_ext, N, n_cols, SMW_DEVICE, roots_out_host);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(d_ext);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------- transcript
+int32_t smw_transcript_new(smw_ctx* c, const uint8_t* label, size_t len, smw_params* params, smw_transcript** out) {
+    if (!c || !out || (!label && len)) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    smw_params* p; int rc = get_transcript_params(c, params, &p); if (rc) return rc;
+    auto t = std::make_unique<smw_transcript>(); t->ctx = c; t->params = p;
+    SMW_CUDA(c, cudaMalloc(&t->d_state, 17 * FR));
+    std::vector<Word> A; A.push_back(tag_word(TAG_INIT)); push_absorb_bytes(A, label, len);
+    uint32_t* dA; rc = upload_words(c, A, &dA); if (rc) { cudaFree(t->d_state); return rc; }
+    rc = launch_transcript_run(c, p, t->d_state, 1, 0, dA, (int)A.size(), nullptr, 0, nullptr, 0, 0, nullptr);
+    cudaStreamSynchronize(c->stream); cudaFree(dA);
+    if (rc) { cudaFree(t->d_state); return rc; }
+    t->pos = advance_pos(0, A.size() - 1);
+    *out = t.release(); return SMW_OK;
+}
+int32_t smw_transcript_absorb_bytes(smw_transcript* t, const uint8_t* bytes, size_t len) {
+    if (!t || (!bytes && len)) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = t->ctx; cudaSetDevice(c->device);
+    std::vector<Word> A; push_absorb_bytes(A, bytes, len);
+    uint32_t* dA; int rc = upload_words(c, A, &dA); if (rc) return rc;
+    rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, dA, (int)A.size(), nullptr, 0, nullptr, 0, 0, nullptr);
+    cudaStreamSynchronize(c->stream); cudaFree(dA);
+    if (!rc) t->pos = advance_pos(t->pos, A.size());
+    return rc;
+}
+int32_t smw_transcript_absorb_fields(smw_transcript* t, const void* frs, size_t n, int32_t mem) {
+    if (!t || (!frs && n)) return SMW_ERR_INVALID_ARG;
+    if (n == 0) return SMW_OK;
+    smw_ctx* c = t->ctx; cudaSetDevice(c->device);
+    In i(c, frs, n, mem); if (i.rc) return i.rc;
+    int rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, nullptr, 0, i.d, n, nullptr, 0, 0, nullptr);
+    if (!rc) t->pos = advance_pos(t->pos, n);
+    return rc;
+}
+int32_t smw_transcript_absorb_field(smw_transcript* t, const void* fr_host) { return smw_transcript_absorb_fields(t, fr_host, 1, SMW_HOST); }
+int32_t smw_transcript_challenge(smw_transcript* t, const uint8_t* label, size_t len, void* out_host) {
+    if (!t || !out_host || (!label && len)) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = t->ctx; cudaSetDevice(c->device);
+    std::vector<Word> A; push_challenge(A, label, len);
+    uint32_t *dA, *d_out; int rc = upload_words(c, A, &dA); if (rc) return rc;
+    SMW_CUDA(c, cudaMalloc(&d_out, FR));
+    rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, dA, (int)A.size(), nullptr, 0, nullptr, 0, 1, d_out);
+    if (!rc) rc = d2h(c, out_host, d_out, FR);
+    cudaStreamSynchronize(c->stream); cudaFree(dA); cudaFree(d_out);
+    if (!rc) t->pos = 0;
+    return rc;
+}
+int32_t smw_transcript_state(smw_transcript* t, void* out_17, int32_t* pos_out) {
+    if (!t || !out_17) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(t->ctx->device);
+    if (pos_out) *pos_out = t->pos;
+    return d2h(t->ctx, out_17, t->d_state, 17 * FR);
+}
+void smw_transcript_free(smw_transcript* t) { if (!t) return; cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream); cudaFree(t->d_state); delete t; }
+int32_t smw_tr_hash_fields_tagged(smw_ctx* c, const uint8_t* tag, size_t tag_len, const void* xs, size_t n, int32_t mem, void* out_host) {
+    if (!c || !out_host || (!tag && tag_len) || (!xs && n)) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
+    In i(c, xs, n, mem); if (i.rc) return i.rc;
+    Out o(c, out_host, 1, SMW_HOST); if (o.rc) return o.rc;
+    rc = oneshot_hash(c, p, "FRI/FS", tag, tag_len, {}, i.d, n, "out", o.d); if (rc) return rc;
+    return o.finish();
+}
+// the 17-lane pre-image template of hash_leaf_pair (deep_ali/src/fri.rs:38-44); returns the lanes of f and s
+static void leaf_template(std::vector<Word>& lanes, int* lane_f, int* lane_s) {
+    std::vector<Word> seq;
+    push_absorb_bytes(seq, (const uint8_t*)"FRI/leaf/poseidon", 17);
+    push_absorb_bytes(seq, (const uint8_t*)"FRI/leaf", 8);
+    *lane_f = (int)seq.size(); seq.push_back(Word{}); *lane_s = (int)seq.size(); seq.push_back(Word{});
+    push_challenge(seq, (const uint8_t*)"leaf", 4);
+    lanes.assign(17, Word{});
+    for (size_t i = 0; i < seq.size(); i++) lanes[i] = seq[i];      // 9 lanes < rate 16: no intermediate permutation
+    lanes[16] = tag_word(TAG_INIT);
+}
+static int hash_leaves_device(smw_ctx* c, const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out) {
+    smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
+    std::vector<Word> lanes; int lf, ls; leaf_template(lanes, &lf, &ls);
+    uint32_t* d_t; rc = upload_words(c, lanes, &d_t); if (rc) return rc;
+    rc = launch_fri_leaf_hashed(c, p, d_t, lf, ls, d_f, d_s, s_div, n, d_out);
+    cudaStreamSynchronize(c->stream); cudaFree(d_t);
+    return rc;
+}
+int32_t smw_hash_leaf_pair(smw_ctx* c, const void* f, const void* s, size_t n, void* out, int32_t mem) {
+    if (!c || (n && (!f || !s || !out))) return SMW_ERR_INVALID_ARG;
+    if (n == 0) return SMW_OK;
+    cudaSetDevice(c->device);
+    In a(c, f, n, mem), b(c, s, n, mem); if (a.rc) return a.rc; if (b.rc) return b.rc;
+    Out o(c, out, n, mem); if (o.rc) return o.rc;
+    int rc = hash_leaves_device(c, a.d, b.d, 1, n, o.d); if (rc) return rc;
+    return o.finish();
+}
+
+// ---------------------------------------------------------------------------------------- FRI
+int32_t smw_pick_arity_for_layer(size_t n, size_t m) {     // deep_ali/src/fri.rs:220-229
+    if (m >= 128 && n % 128 == 0) return 128; if (m >= 64 && n % 64 == 0) return 64; if (m >= 32 && n % 32 == 0) return 32;
+    if (m >= 16 && n % 16 == 0) return 16; if (m >= 8 && n % 8 == 0) return 8; if (m >= 4 && n % 4 == 0) return 4;
+    if (n % 2 == 0) return 2; return 1;
+}
+static int sample_z_device(smw_ctx* c, uint64_t seed_z, const std::vector<uint64_t>& levels, const std::vector<uint64_t>& sizes, uint32_t* d_z) {
+    smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
+    int L = (int)sizes.size(); if (L == 0) return SMW_OK;
+    std::vector<Word> all; all.reserve((size_t)L * 17);
+    for (int l = 0; l < L; l++) {
+        std::vector<Word> seq;
+        push_absorb_bytes(seq, (const uint8_t*)"FRI/FS", 6);
+        push_absorb_bytes(seq, (const uint8_t*)"FRI/z/l", 7);
+        seq.push_back(word_from_u64(seed_z)); seq.push_back(word_from_u64(levels[l])); seq.push_back(word_from_u64(sizes[l]));
+        push_challenge(seq, (const uint8_t*)"out", 3);
+        std::vector<Word> lanes(17, Word{});
+        for (size_t i = 0; i < seq.size(); i++) lanes[i] = seq[i];
+        lanes[16] = tag_word(TAG_INIT);
+        all.insert(all.end(), lanes.begin(), lanes.end());
+    }
+    uint32_t* d_t; uint64_t* d_sizes;
+    rc = upload_words(c, all, &d_t); if (rc) return rc;
+    std::vector<uint64_t> ls((size_t)2 * L);
+    for (int l = 0; l < L; l++) { ls[2 * l] = levels[l]; ls[2 * l + 1] = sizes[l]; }
+    SMW_CUDA(c, cudaMalloc(&d_sizes, (size_t)L * 16));
+    SMW_CUDA(c, cudaMemcpyAsync(d_sizes, ls.data(), (size_t)L * 16, cudaMemcpyHostToDevice, c->stream));
+    rc = launch_fri_sample_z(c, p, d_t, d_sizes, L, seed_z, d_z);
+    cudaStreamSynchronize(c->stream); cudaFree(d_t); cudaFree(d_sizes);
+    return rc;
+}
+int32_t smw_fri_sample_z_ell(smw_ctx* c, uint64_t seed_z, uint64_t level, uint64_t domain_size, void* out_host) {
+    if (!c || !out_host) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    Out o(c, out_host, 1, SMW_HOST); if (o.rc) return o.rc;
+    int rc = sample_z_device(c, seed_z, {level}, {domain_size}, o.d); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_fri_fold_layer(smw_ctx* c, const void* f, size_t n, const void* z_host, size_t m, void* out, int32_t mem) {
+    if (!c || !z_host || (n && (!f || !out))) return SMW_ERR_INVALID_ARG;
+    if (m < 2 || m > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 2..128");
+    if (n % m) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
+    cudaSetDevice(c->device);
+    In a(c, f, n, mem), z(c, z_host, 1, SMW_HOST); if (a.rc) return a.rc; if (z.rc) return z.rc;
+    Out o(c, out, n / m, mem); if (o.rc) return o.rc;
+    int rc = launch_fri_fold(c, a.d, n, z.d, m, o.d); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_compute_s_layer(smw_ctx* c, const void* f, size_t n, const void* z_host, size_t m, void* out, int32_t mem) {
+    if (!c || !z_host || (n && (!f || !out))) return SMW_ERR_INVALID_ARG;
+    if (m < 1 || m > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 1..128");
+    if (n % m) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
+    cudaSetDevice(c->device);
+    In a(c, f, n, mem), z(c, z_host, 1, SMW_HOST); if (a.rc) return a.rc; if (z.rc) return z.rc;
+    Out o(c, out, n, mem); if (o.rc) return o.rc;
+    uint32_t* d_fold; SMW_CUDA(c, cudaMalloc(&d_fold, (n / m + 1) * FR));
+    int rc = launch_fri_fold(c, a.d, n, z.d, m, d_fold);
+    if (!rc) rc = launch_broadcast_div(c, d_fold, n, m, o.d);
+    if (!rc) rc = o.finish();
+    cudaStreamSynchronize(c->stream); cudaFree(d_fold);
+    return rc;
+}
+void smw_fri_free(smw_fri* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
+    for (auto* t : s->tree) smw_tree_free(t);
+    for (auto* f : s->f) cudaFree(f);
+    cudaFree(s->d_z);
+    delete s;
+}
+int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, smw_fri** out) {
+    if (!c || !out || !f0 || L < 0 || (L && !schedule) || n0 == 0) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    // layer sizes (fri.rs:145-155) — the reference asserts divisibility level by level
+    std::vector<size_t> n(L + 1), m(L + 1); n[0] = n0;
+    for (int l = 0; l < L; l++) {
+        m[l] = (size_t)schedule[l];
+        if (m[l] < 2 || m[l] > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 2..128");
+        if (n[l] % m[l]) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
+        n[l + 1] = n[l] / m[l];
+    }
+    m[L] = 1;
+    auto s = std::make_unique<smw_fri>(); s->ctx = c; s->L = L; s->n = n; s->m = m;
+    s->arity.resize(L + 1); s->hashed.resize(L + 1); s->f.assign(L + 1, nullptr); s->tree.assign(L + 1, nullptr);
+    int rc = SMW_OK;
+    auto fail = [&](int code) { smw_fri_free(s.release()); return code; };
+    for (int l = 0; l <= L; l++) { cudaError_t e = cudaMalloc(&s->f[l], n[l] * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri layer)")); }
+    { cudaError_t e = cudaMalloc(&s->d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc")); }
+    { cudaError_t e = cudaMemcpyAsync(s->f[0], f0, n0 * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream); if (e != cudaSuccess) return fail(cuda_err(c, e, "copy f0")); }
+    // z_l depends only on public values (fri.rs:250): all levels in one launch
+    std::vector<uint64_t> levels(L), sizes(L);
+    for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
+    rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc);
+    for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); }
+    // per-layer commitment (fri.rs:267-301); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer
+    for (int l = 0; l <= L; l++) {
+        int arity = smw_pick_arity_for_layer(n[l], m[l]);
+        bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
+        s->arity[l] = arity; s->hashed[l] = hashed;
+        smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) return fail(rc);
+        uint32_t* d_leaves; { cudaError_t e = cudaMalloc(&d_leaves, n[l] * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(leaves)")); }
+        const uint32_t* d_s = (l < L) ? s->f[l + 1] : nullptr;
+        if (hashed) rc = hash_leaves_device(c, s->f[l], d_s, m[l], n[l], d_leaves);
+        else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, (uint64_t)l, 0, d_leaves, m[l]);
+        if (rc) { cudaFree(d_leaves); return fail(rc); }
+        rc = build_tree(c, p, arity, (uint64_t)l, d_leaves, true, n[l], &s->tree[l]); if (rc) return fail(rc);
+    }
+    *out = s.release();
+    return SMW_OK;
+}
+int32_t smw_fri_num_layers(const smw_fri* s) { return s ? s->L + 1 : -1; }
+int32_t smw_fri_layer_info(const smw_fri* s, int32_t l, size_t* n, size_t* m, int32_t* arity, int32_t* hashed) {
+    if (!s || l < 0 || l > s->L) return SMW_ERR_INVALID_ARG;
+    if (n) *n = s->n[l]; if (m) *m = s->m[l]; if (arity) *arity = s->arity[l]; if (hashed) *hashed = s->hashed[l];
+    return SMW_OK;
+}
+int32_t smw_fri_layer_f(smw_fri* s, int32_t l, void* out, int32_t mem) {
+    if (!s || !out || l < 0 || l > s->L) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = s->ctx; cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaMemcpyAsync(out, s->f[l], s->n[l] * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK;
+}
+int32_t smw_fri_layer_s(smw_fri* s, int32_t l, void* out, int32_t mem) {
+    if (!s || !out || l < 0 || l > s->L) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = s->ctx; cudaSetDevice(c->device);
+    Out o(c, out, s->n[l], mem); if (o.rc) return o.rc;
+    if (l == s->L) { SMW_CUDA(c, cudaMemsetAsync(o.d, 0, s->n[l] * FR, c->stream)); }
+    else { int rc = launch_broadcast_div(c, s->f[l + 1], s->n[l], s->m[l], o.d); if (rc) return rc; }
+    return o.finish();
+}
+int32_t smw_fri_roots(smw_fri* s, void* out_host) {
+    if (!s || !out_host) return SMW_ERR_INVALID_ARG;
+    for (int l = 0; l <= s->L; l++) { int rc = smw_tree_root(s->tree[l], (uint8_t*)out_host + (size_t)l * FR); if (rc) return rc; }
+    return SMW_OK;
+}
+int32_t smw_fri_z(smw_fri* s, void* out_host) { if (!s || !out_host) return SMW_ERR_INVALID_ARG; if (s->L == 0) return SMW_OK; cudaSetDevice(s->ctx->device); return d2h(s->ctx, out_host, s->d_z, (size_t)s->L * FR); }
+smw_tree* smw_fri_layer_tree(smw_fri* s, int32_t l) { return (s && l >= 0 && l <= s->L) ? s->tree[l] : nullptr; }
+
+// ---------------------------------------------------------------------------------------- MF sum-check commit loop
+int32_t smw_sumcheck_round_coeffs(smw_ctx* c, const void* layer, size_t n, void* c0_host, void* c1_host, int32_t mem) {
+    if (!c || !c0_host || !c1_host || (n && !layer) || (n & 1)) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, layer, n, mem); if (a.rc) return a.rc;
+    uint32_t* d_c; SMW_CUDA(c, cudaMalloc(&d_c, 2 * FR));
+    int rc = launch_mf_coeffs(c, a.d, n, d_c);
+    uint8_t tmp[64];
+    if (!rc) rc = d2h(c, tmp, d_c, 64);
+    if (!rc) { memcpy(c0_host, tmp, 32); memcpy(c1_host, tmp + 32, 32); }
+    cudaFree(d_c);
+    return rc;
+}
+static int mf_challenge_device(smw_ctx* c, smw_params* trp, uint64_t round_idx, const uint32_t* d_root, uint32_t* d_out) {
+    // channel/src/lib.rs:592-598: new("SUMCHECK-MF/ROUND-CHAL"); absorb_bytes("SUMCHECK/MF/R"); absorb_bytes(u64le(i)); absorb_field(root); challenge("r_i")
+    std::vector<Word> A, C;
+    A.push_back(tag_word(TAG_INIT));
+    push_absorb_bytes(A, (const uint8_t*)"SUMCHECK-MF/ROUND-CHAL", 22);
+    push_absorb_bytes(A, (const uint8_t*)"SUMCHECK/MF/R", 13);
+    uint8_t le[8]; for (int i = 0; i < 8; i++) le[i] = (uint8_t)(round_idx >> (8 * i));
+    push_absorb_bytes(A, le, 8);
+    push_challenge(C, (const uint8_t*)"r_i", 3);
+    uint32_t *dA, *dC; int rc = upload_words(c, A, &dA); if (rc) return rc; rc = upload_words(c, C, &dC); if (rc) { cudaFree(dA); return rc; }
+    rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA, (int)A.size(), d_root, 1, dC, (int)C.size(), 1, d_out);
+    cudaStreamSynchronize(c->stream); cudaFree(dA); cudaFree(dC);
+    return rc;
+}
+int32_t smw_mf_round_challenge_from_root(smw_ctx* c, uint64_t round_idx, const void* prev_root_host, smw_params* trp, void* out_host) {
+    if (!c || !prev_root_host || !out_host) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    smw_params* p; int rc = get_transcript_params(c, trp, &p); if (rc) return rc;
+    In r(c, prev_root_host, 1, SMW_HOST); if (r.rc) return r.rc;
+    Out o(c, out_host, 1, SMW_HOST); if (o.rc) return o.rc;
+    rc = mf_challenge_device(c, p, round_idx, r.d, o.d); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_mf_fold(smw_ctx* c, const void* cur, size_t n, const void* r_host, void* next, int32_t mem) {
+    if (!c || !r_host || (n & 1) || (n && (!cur || !next))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, cur, n, mem), r(c, r_host, 1, SMW_HOST); if (a.rc) return a.rc; if (r.rc) return r.rc;
+    Out o(c, next, n / 2, mem); if (o.rc) return o.rc;
+    int rc = launch_mf_fold(c, a.d, n, r.d, o.d); if (rc) return rc;
+    return o.finish();
+}
+int32_t smw_mf_commit_phase(smw_ctx* c, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host, void* r_out_host, void* final_out_host) {
+    if (!c || !table || !roots_out_host || n == 0 || (n & (n - 1))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    int k = 0; while (((size_t)1 << k) < n) k++;
+    smw_params *cp, *trp; int rc = smw_params_commitment_default(c, &cp); if (rc) return rc; rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
+    In t0(c, table, n, mem); if (t0.rc) return t0.rc;
+    uint32_t *d_roots, *d_r, *bufA = nullptr, *bufB = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_roots, (size_t)(k + 1) * FR)); SMW_CUDA(c, cudaMalloc(&d_r, (size_t)(k + 1) * FR));
+    if (k > 0) { SMW_CUDA(c, cudaMalloc(&bufA, (n / 2) * FR)); SMW_CUDA(c, cudaMalloc(&bufB, (n / 4 + 1) * FR)); }
+    const uint32_t* cur = t0.d; size_t len = n;
+    for (int i = 0; i <= k && !rc; i++) {
+        // commit the current layer (arity 16, tree_label = ds_tag); only the root is kept
+        smw_tree* tr = nullptr;
+        rc = build_tree(c, cp, 16, ds_tag, (uint32_t*)cur, false, len, &tr); if (rc) break;
+        cudaMemcpyAsync(d_roots + (size_t)i * 8, tr->lv.back(), FR, cudaMemcpyDeviceToDevice, c->stream);
+        smw_tree_free(tr);
+        if (i == k) break;
+        // r_i from (i, root_i) stays on the device and feeds the fold directly: no host round trip per round
+        rc = mf_challenge_device(c, trp, (uint64_t)i, d_roots + (size_t)i * 8, d_r + (size_t)i * 8); if (rc) break;
+        uint32_t* dst = (i % 2 == 0) ? bufA : bufB;
+        rc = launch_mf_fold(c, cur, len, d_r + (size_t)i * 8, dst); if (rc) break;
+        cur = dst; len /= 2;
+    }
+    if (!rc) rc = d2h(c, roots_out_host, d_roots, (size_t)(k + 1) * FR);
+    if (!rc && r_out_host && k > 0) rc = d2h(c, r_out_host, d_r, (size_t)k * FR);
+    if (!rc && final_out_host) rc = d2h(c, final_out_host, cur, FR);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(d_roots); cudaFree(d_r); cudaFree(bufA); cudaFree(bufB);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------- openings (merkle/src/lib.rs:246-315)
+struct smw_proof {
+    std::vector<uint64_t> indices;                       // unique, ascending
+    std::vector<std::vector<uint8_t>> siblings;          // per level, 32 bytes per sibling
+    std::vector<std::vector<uint8_t>> group_sizes;       // per level, child count of every touched parent
+    int arity = 0;
+};
+int32_t smw_tree_open_many(smw_tree* t, const uint64_t* indices, size_t n, smw_proof** out) {
+    if (!t || !out) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = t->ctx; cudaSetDevice(c->device);
+    if (n == 0 || !indices) return set_err(c, SMW_ERR_EMPTY_INDICES, "open_many: empty indices");
+    const size_t arity = (size_t)t->arity; const int height = (int)t->lv.size() - 1;
+    std::vector<uint64_t> cur(indices, indices + n);
+    std::sort(cur.begin(), cur.end()); cur.erase(std::unique(cur.begin(), cur.end()), cur.end());
+    if (cur.back() >= t->len[0]) return set_err(c, SMW_ERR_INVALID_ARG, "open_many: index out of range");
+    auto pr = std::make_unique<smw_proof>(); pr->arity = t->arity; pr->indices = cur;
+    pr->siblings.resize(height); pr->group_sizes.resize(height);
+    for (int level = 0; level < height; level++) {
+        const size_t level_len = t->len[level];
+        std::vector<uint64_t> need;                      // node indices at this level to fetch, in proof order
+        size_t i = 0;
+        while (i < cur.size()) {                         // cur is sorted: equal-parent runs are the BTreeMap groups
+            size_t parent = cur[i] / arity, j = i;
+            while (j < cur.size() && cur[j] / arity == parent) j++;
+            size_t base = parent * arity, end = std::min(base + arity, level_len), cc = end - base;
+            pr->group_sizes[level].push_back((uint8_t)cc);
+            size_t k = i;
+            for (size_t pos = 0; pos < cc; pos++) { if (k < j && cur[k] % arity == pos) k++; else need.push_back(base + pos); }
+            i = j;
+        }
+        pr->siblings[level].resize(need.size() * FR);
+        if (!need.empty()) {
+            uint64_t* d_idx; uint32_t* d_out;
+            SMW_CUDA(c, cudaMalloc(&d_idx, need.size() * 8)); SMW_CUDA(c, cudaMalloc(&d_out, need.size() * FR));
+            SMW_CUDA(c, cudaMemcpyAsync(d_idx, need.data(), need.size() * 8, cudaMemcpyHostToDevice, c->stream));
+            int rc = launch_gather(c, t->lv[level], d_idx, need.size(), d_out);
+            if (!rc) rc = d2h(c, pr->siblings[level].data(), d_out, need.size() * FR);
+            cudaStreamSynchronize(c->stream); cudaFree(d_idx); cudaFree(d_out);
+            if (rc) return rc;
+        }
+        for (auto& v : cur) v /= arity;
+        cur.erase(std::unique(cur.begin(), cur.end()), cur.end());
+    }
+    *out = pr.release();
+    return SMW_OK;
+}
+int32_t smw_proof_num_levels(const smw_proof* p) { return p ? (int32_t)p->siblings.size() : -1; }
+size_t smw_proof_num_indices(const smw_proof* p) { return p ? p->indices.size() : 0; }
+int32_t smw_proof_indices(const smw_proof* p, uint64_t* out) { if (!p || !out) return SMW_ERR_INVALID_ARG; memcpy(out, p->indices.data(), p->indices.size() * 8); return SMW_OK; }
+size_t smw_proof_level_siblings(const smw_proof* p, int32_t l) { return (p && l >= 0 && l < (int)p->siblings.size()) ? p->siblings[l].size() / FR : 0; }
+size_t smw_proof_level_groups(const smw_proof* p, int32_t l) { return (p && l >= 0 && l < (int)p->group_sizes.size()) ? p->group_sizes[l].size() : 0; }
+int32_t smw_proof_level(const smw_proof* p, int32_t l, void* sib_out, uint8_t* grp_out) {
+    if (!p || l < 0 || l >= (int)p->siblings.size()) return SMW_ERR_INVALID_ARG;
+    if (sib_out) memcpy(sib_out, p->siblings[l].data(), p->siblings[l].size());
+    if (grp_out) memcpy(grp_out, p->group_sizes[l].data(), p->group_sizes[l].size());
+    return SMW_OK;
+}
+void smw_proof_free(smw_proof* p) { delete p; }
+
+// ---------------------------------------------------------------------------------------- DEEP-ALI merge
+int32_t smw_deep_ali_merge_evals(smw_ctx* c, const void* a, const void* s, const void* e, const void* t, size_t n, const void* omega_host, const void* z_host, void* f0_out, int32_t mem) {
+    if (!c || !a || !s || !e || !t || !omega_host || !z_host || !f0_out || n < 2) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In ia(c, a, n, mem), is(c, s, n, mem), ie(c, e, n, mem), it(c, t, n, mem), iw(c, omega_host, 1, SMW_HOST), iz(c, z_host, 1, SMW_HOST);
+    if (ia.rc) return ia.rc; if (is.rc) return is.rc; if (ie.rc) return ie.rc; if (it.rc) return it.rc; if (iw.rc) return iw.rc; if (iz.rc) return iz.rc;
+    Out o(c, f0_out, n, mem); if (o.rc) return o.rc;
+    int rc = launch_deep_ali_merge(c, ia.d, is.d, ie.d, it.d, n, iw.d, iz.d, o.d); if (rc) return rc;
+    return o.finish();
+}
+
+} // extern "C"

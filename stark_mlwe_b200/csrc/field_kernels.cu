@@ -1,0 +1,138 @@
+// field_kernels.cu — element-wise and fold kernels in the external representation (fr32.cuh):
+// FRI fold (deep_ali/src/fri.rs:85-102), s-layer broadcast (:123-143), the Merkle-folded sum-check's
+// round coefficients and fold (channel/src/lib.rs:406-416, 648-655), the DEEP-ALI merge
+// (deep_ali/src/lib.rs:60-105) and the canonical <-> Montgomery conversions.  All HBM-bound.
+#include "smw_internal.h"
+#include "fr32.cuh"
+#include <algorithm>
+
+namespace smw {
+
+// out[b] = sum_{t<m} f[b*m + t] * z^t.  One thread per output; z powers are rebuilt per thread by a
+// running product (m <= 128 multiplies, against the m loads it needs anyway).
+__global__ void k_fri_fold(const uint32_t* __restrict__ f, size_t n_out, const uint32_t* __restrict__ z, size_t m, uint32_t* __restrict__ out) {
+    size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_out) return;
+    Fr zz = fr_ldg(z), zp = fr_const(C_R32), acc = fr_zero();
+    const uint32_t* src = f + b * m * 8;
+    for (size_t t = 0; t < m; t++) {
+        Fr x = fr_load(src + t * 8);
+        acc = fr_add(acc, t == 0 ? x : fr_mul(x, zp));
+        zp = (t == 0) ? zz : fr_mul(zp, zz);
+    }
+    fr_store(out + b * 8, acc);
+}
+__global__ void k_broadcast_div(const uint32_t* __restrict__ src, size_t n, size_t m, uint32_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    fr_store(out + i * 8, fr_load(src + (i / m) * 8));
+}
+__global__ void k_to_mont(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n, int inverse) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr x = fr_load(in + i * 8);
+    fr_store(out + i * 8, inverse ? fr_to_canonical(x) : fr_from_canonical(x));
+}
+// c0 = sum a, c1 = sum (b - a) over pairs (a, b) = (layer[2j], layer[2j+1]); block tree reduction, then a
+// second launch over the per-block partials (exact field sums, so the order does not matter)
+__global__ void __launch_bounds__(256) k_mf_coeffs(const uint32_t* __restrict__ layer, size_t n_pairs, uint32_t* __restrict__ partial, int pairs_are_c0c1) {
+    __shared__ uint32_t sh[2][256][8];
+    Fr c0 = fr_zero(), c1 = fr_zero();
+    for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_pairs; j += (size_t)gridDim.x * blockDim.x) {
+        Fr a = fr_load(layer + (2 * j) * 8), b = fr_load(layer + (2 * j + 1) * 8);
+        if (pairs_are_c0c1) { c0 = fr_add(c0, a); c1 = fr_add(c1, b); }
+        else { c0 = fr_add(c0, a); c1 = fr_add(c1, fr_sub(b, a)); }
+    }
+    for (int k = 0; k < 8; k++) { sh[0][threadIdx.x][k] = c0.v[k]; sh[1][threadIdx.x][k] = c1.v[k]; }
+    __syncthreads();
+    for (int stride = 128; stride > 0; stride >>= 1) {
+        if ((int)threadIdx.x < stride) {
+            for (int w = 0; w < 2; w++) {
+                Fr x, y;
+                for (int k = 0; k < 8; k++) { x.v[k] = sh[w][threadIdx.x][k]; y.v[k] = sh[w][threadIdx.x + stride][k]; }
+                x = fr_add(x, y);
+                for (int k = 0; k < 8; k++) sh[w][threadIdx.x][k] = x.v[k];
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) for (int w = 0; w < 2; w++) for (int k = 0; k < 8; k++) partial[((size_t)blockIdx.x * 2 + w) * 8 + k] = sh[w][0][k];
+}
+// next[j] = (1 - r) * cur[2j] + r * cur[2j+1]
+__global__ void k_mf_fold(const uint32_t* __restrict__ cur, size_t n_out, const uint32_t* __restrict__ r, uint32_t* __restrict__ next) {
+    size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_out) return;
+    Fr rr = fr_ldg(r), om = fr_sub(fr_const(C_R32), rr);
+    Fr a = fr_load(cur + (2 * j) * 8), b = fr_load(cur + (2 * j + 1) * 8);
+    fr_store(next + j * 8, fr_add(fr_mul(om, a), fr_mul(rr, b)));
+}
+// DEEP-ALI merge, f0 only: f0[j] = (a*s + e - t)[j] / (w^j - z).  Batch inversion per thread over a strip of
+// CH consecutive j (Montgomery's trick: one field inversion per CH elements instead of one per element).
+template <int CH> __global__ void k_deep_ali_merge(const uint32_t* __restrict__ a, const uint32_t* __restrict__ s, const uint32_t* __restrict__ e, const uint32_t* __restrict__ t,
+                                                   size_t n, const uint32_t* __restrict__ omega, const uint32_t* __restrict__ z, uint32_t* __restrict__ f0) {
+    size_t strip = (size_t)blockIdx.x * blockDim.x + threadIdx.x, j0 = strip * CH;
+    if (j0 >= n) return;
+    Fr w = fr_ldg(omega), zz = fr_ldg(z);
+    Fr wj = fr_pow_u64(w, j0);
+    Fr d[CH], pre[CH];
+    Fr run = fr_const(C_R32);
+    int cnt = 0;
+    for (int k = 0; k < CH && j0 + k < n; k++, cnt++) { d[k] = fr_sub(wj, zz); pre[k] = run; run = fr_mul(run, d[k]); wj = fr_mul(wj, w); }
+    Fr inv = fr_inv(run);
+    for (int k = cnt - 1; k >= 0; k--) {
+        Fr dinv = fr_mul(inv, pre[k]); inv = fr_mul(inv, d[k]);
+        size_t j = j0 + k;
+        Fr phi = fr_sub(fr_add(fr_mul(fr_load(a + j * 8), fr_load(s + j * 8)), fr_load(e + j * 8)), fr_load(t + j * 8));
+        fr_store(f0 + j * 8, fr_mul(phi, dinv));
+    }
+}
+
+__global__ void k_gather(const uint32_t* __restrict__ src, const uint64_t* __restrict__ idx, size_t n, uint32_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    fr_store(out + i * 8, fr_load(src + idx[i] * 8));
+}
+int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size_t n, uint32_t* d_out) {
+    if (n == 0) return SMW_OK;
+    k_gather<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_src, d_idx, n, d_out); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+int launch_fri_fold(smw_ctx* c, const uint32_t* d_f, size_t n, const uint32_t* d_z, size_t m, uint32_t* d_out) {
+    size_t n_out = n / m; if (n_out == 0) return SMW_OK;
+    k_fri_fold<<<(unsigned)((n_out + 127) / 128), 128, 0, c->stream>>>(d_f, n_out, d_z, m, d_out); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+int launch_broadcast_div(smw_ctx* c, const uint32_t* d_src, size_t n, size_t m, uint32_t* d_out) {
+    if (n == 0) return SMW_OK;
+    k_broadcast_div<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_src, n, m, d_out); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+int launch_to_mont(smw_ctx* c, const uint32_t* d_in, uint32_t* d_out, size_t n, int inverse) {
+    if (n == 0) return SMW_OK;
+    k_to_mont<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_in, d_out, n, inverse); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+int launch_mf_coeffs(smw_ctx* c, const uint32_t* d_layer, size_t n, uint32_t* d_c0c1) {
+    size_t pairs = n / 2;
+    unsigned blocks = (unsigned)std::min<size_t>((pairs + 255) / 256, 1024); if (blocks == 0) blocks = 1;
+    uint32_t* d_part; SMW_CUDA(c, cudaMalloc(&d_part, (size_t)blocks * 2 * 32));
+    k_mf_coeffs<<<blocks, 256, 0, c->stream>>>(d_layer, pairs, d_part, 0);
+    k_mf_coeffs<<<1, 256, 0, c->stream>>>(d_part, blocks, d_c0c1, 1);
+    c->launches += 2;
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(d_part);
+    return SMW_OK;
+}
+int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* d_r, uint32_t* d_next) {
+    size_t n_out = n / 2; if (n_out == 0) return SMW_OK;
+    k_mf_fold<<<(unsigned)((n_out + 255) / 256), 256, 0, c->stream>>>(d_cur, n_out, d_r, d_next); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0) {
+    constexpr int CH = 8;
+    size_t strips = (n + CH - 1) / CH; if (strips == 0) return SMW_OK;
+    k_deep_ali_merge<CH><<<(unsigned)((strips + 127) / 128), 128, 0, c->stream>>>(a, s, e, t, n, d_omega, d_z, d_f0); c->launches++;
+    SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+
+} // namespace smw

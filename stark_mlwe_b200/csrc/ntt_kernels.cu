@@ -1,0 +1,248 @@
+// ntt_kernels.cu — radix-2 NTT / inverse NTT / coset LDE over Pallas Fr.
+//
+// Convention (fft/src/lib.rs:6-32 -> ark-poly 0.5 Radix2EvaluationDomain): fft takes coefficients in
+// natural order and returns evals[i] = P(w^i) in natural order; ifft is its inverse including 1/n.
+// LDE: c = ifft_n(col); c[i] *= g^i; zero-pad to beta*n; fft_{beta n}.
+//
+// Structure: a size-2^L transform is split into passes of <= 8 butterfly stages; a CTA stages a tile
+// of 1024 elements (32 KB) in shared memory, gathered from global memory in runs of 2^c contiguous
+// elements (>= 128 B) and runs its stages there.  The inverse transform is decimation-in-frequency
+// (natural in, bit-reversed out) and the forward one decimation-in-time (bit-reversed in, natural
+// out), so the LDE needs no bit-reversal pass at all: the coset scaling is applied in bit-reversed
+// index space and the zero padding becomes a stride.  Only the stand-alone smw_ntt API pays for a
+// bit-reversal permutation.  Twiddles w_N^i (i < N/2) are precomputed once per context.
+#include "smw_internal.h"
+#include "fr32.cuh"
+#include <algorithm>
+#include <vector>
+
+namespace smw {
+
+constexpr int TILE_LOG = 10;
+
+// pow2[k] = primitive 2^k-th root of unity, k = 0..32 (ark-pallas FrConfig: generator 5, two-adicity 32)
+__global__ void k_pow2_roots(uint32_t* pow2) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // (p - 1) / 2^32
+    const uint32_t e[7] = {0x8c46eb21u, 0x0994a8ddu, 0x224698fcu, 0u, 0u, 0u, 0x40000000u};
+    Fr g = fr_from_u64(5), r = fr_const(C_R32);
+    for (int k = 6; k >= 0; k--) for (int b = 31; b >= 0; b--) { r = fr_sqr(r); if ((e[k] >> b) & 1u) r = fr_mul(r, g); }
+    for (int k = 32; k >= 0; k--) { fr_store(pow2 + k * 8, r); r = fr_sqr(r); }
+}
+// tw[i] = w_N^i, i < N/2
+__global__ void k_twiddles(uint32_t* tw, int log_n, const uint32_t* pow2) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t half = (size_t)1 << (log_n - 1);
+    if (i >= half) return;
+    Fr r = fr_const(C_R32);
+    for (int b = 0; b < log_n - 1; b++) if ((i >> b) & 1) r = fr_mul(r, fr_load(pow2 + (log_n - b) * 8));
+    fr_store(tw + i * 8, r);
+}
+
+struct PassArgs {
+    int L;            // transform size 2^L
+    int lo;           // lowest global bit covered by the tile's x field
+    int span;         // number of x bits held in the tile
+    int c;            // contiguous low bits held in the tile (0 when lo == 0)
+    int s_begin, s_end;   // butterfly stages [s_begin, s_end) as global bit positions
+    int tile_log;     // log2(elements per tile) = span + c
+    int tw_shift;     // table index scale: log2(N_table / N)
+    int inverse;      // use w^-1
+    size_t col_stride;
+};
+SMW_DEV size_t tile_global(const PassArgs& a, size_t tile, int local) {
+    int y = local & ((1 << a.c) - 1), x = local >> a.c;
+    int lo_bits = a.lo - a.c;                       // tile bits that sit between y and x
+    size_t t_lo = tile & (((size_t)1 << lo_bits) - 1), t_hi = tile >> lo_bits;
+    return (t_hi << (a.lo + a.span)) | ((size_t)x << a.lo) | (t_lo << a.c) | (size_t)y;
+}
+SMW_DEV Fr twiddle(const uint32_t* tw, const PassArgs& a, size_t e /* exponent of w_N, < N/2 */) {
+    size_t half = (size_t)1 << (a.L - 1);
+    if (!a.inverse) return fr_ldg(tw + ((e << a.tw_shift) * 8));
+    if (e == 0) return fr_const(C_R32);
+    return fr_neg(fr_ldg(tw + (((half - e) << a.tw_shift) * 8)));     // w^-e = -w^(N/2 - e)
+}
+// DIF = true : stages run from s_end-1 down to s_begin, butterfly (u+v, (u-v)*w)
+// DIF = false: stages run from s_begin up to s_end-1,   butterfly (u+v*w, u-v*w)
+template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass(uint32_t* data, const uint32_t* tw, PassArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint4* s_lo = reinterpret_cast<uint4*>(smem_raw);
+    uint4* s_hi = s_lo + (1 << a.tile_log);
+    uint32_t* col = data + (size_t)blockIdx.y * a.col_stride * 8;
+    const int tile_elems = 1 << a.tile_log, nthr = blockDim.x;
+    const size_t tile = blockIdx.x;
+    for (int l = threadIdx.x; l < tile_elems; l += nthr) {
+        const uint4* g = reinterpret_cast<const uint4*>(col + tile_global(a, tile, l) * 8);
+        s_lo[l] = g[0]; s_hi[l] = g[1];
+    }
+    __syncthreads();
+    const int nstages = a.s_end - a.s_begin;
+    for (int st = 0; st < nstages; st++) {
+        const int s = DIF ? (a.s_end - 1 - st) : (a.s_begin + st);
+        const int lb = s - a.lo + a.c;                 // local bit position of global bit s
+        for (int b = threadIdx.x; b < tile_elems / 2; b += nthr) {
+            int i0 = ((b >> lb) << (lb + 1)) | (b & ((1 << lb) - 1)), i1 = i0 | (1 << lb);
+            size_t gi = tile_global(a, tile, i0);
+            size_t e = (gi & (((size_t)1 << s) - 1)) << (a.L - 1 - s);
+            Fr w = twiddle(tw, a, e);
+            uint4 a0 = s_lo[i0], a1 = s_hi[i0], b0 = s_lo[i1], b1 = s_hi[i1];
+            Fr u, v;
+            u.v[0] = a0.x; u.v[1] = a0.y; u.v[2] = a0.z; u.v[3] = a0.w; u.v[4] = a1.x; u.v[5] = a1.y; u.v[6] = a1.z; u.v[7] = a1.w;
+            v.v[0] = b0.x; v.v[1] = b0.y; v.v[2] = b0.z; v.v[3] = b0.w; v.v[4] = b1.x; v.v[5] = b1.y; v.v[6] = b1.z; v.v[7] = b1.w;
+            Fr x, y;
+            if (DIF) { x = fr_add(u, v); y = fr_mul(fr_sub(u, v), w); }
+            else { Fr vw = fr_mul(v, w); x = fr_add(u, vw); y = fr_sub(u, vw); }
+            s_lo[i0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]); s_hi[i0] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+            s_lo[i1] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]); s_hi[i1] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
+        }
+        __syncthreads();
+    }
+    for (int l = threadIdx.x; l < tile_elems; l += nthr) {
+        uint4* g = reinterpret_cast<uint4*>(col + tile_global(a, tile, l) * 8);
+        g[0] = s_lo[l]; g[1] = s_hi[l];
+    }
+}
+SMW_DEV size_t bitrev(size_t x, int bits) { return bits == 0 ? 0 : (size_t)(__brevll((unsigned long long)x) >> (64 - bits)); }
+// in-place bit-reversal permutation, optionally scaled (scale == nullptr: none)
+__global__ void k_bitrev_scale(uint32_t* data, int L, const uint32_t* scale, size_t col_stride) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, n = (size_t)1 << L;
+    if (i >= n) return;
+    uint32_t* col = data + (size_t)blockIdx.y * col_stride * 8;
+    size_t j = bitrev(i, L);
+    if (j < i) return;
+    Fr a = fr_load(col + i * 8), b = fr_load(col + j * 8);
+    if (scale) { Fr s = fr_load(scale); a = fr_mul(a, s); b = fr_mul(b, s); }
+    fr_store(col + i * 8, b);
+    if (j != i) fr_store(col + j * 8, a);
+}
+// g-power tables for the coset scaling: lo[i] = g^i / n (i < 1024), hi[j] = g^(1024 j) (j < n / 1024)
+__global__ void k_gpow_tables(const uint32_t* shift, int log_n, uint32_t* lo, uint32_t* hi, size_t n_hi) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    Fr g = fr_load(shift);
+    if (i < 1024) {
+        Fr ninv = fr_inv(fr_from_u64(1ull << log_n));
+        fr_store(lo + i * 8, fr_mul(fr_pow_u64(g, i), ninv));
+    }
+    if (i < n_hi) fr_store(hi + i * 8, fr_pow_u64(g, i << 10));
+}
+// coefficients (bit-reversed order, unscaled) of size n -> DIT input of size n << lb after its first lb stages:
+// out[(i << lb) + r] = c_br[i] * g^bitrev(i) / n   for r < 2^lb
+__global__ void k_lde_expand(const uint32_t* coef, int log_n, int lb, const uint32_t* gl, const uint32_t* gh, uint32_t* out,
+                             size_t in_stride, size_t out_stride) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, n = (size_t)1 << log_n;
+    if (i >= n) return;
+    const uint32_t* src = coef + (size_t)blockIdx.y * in_stride * 8;
+    uint32_t* dst = out + (size_t)blockIdx.y * out_stride * 8;
+    size_t k = bitrev(i, log_n);
+    Fr s = fr_mul(fr_ldg(gl + (k & 1023) * 8), fr_ldg(gh + (k >> 10) * 8));
+    Fr v = fr_mul(fr_load(src + i * 8), s);
+    for (size_t r = 0; r < ((size_t)1 << lb); r++) fr_store(dst + ((i << lb) + r) * 8, v);
+}
+__global__ void k_copy_cols(const uint32_t* in, uint32_t* out, size_t n, size_t in_stride, size_t out_stride) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* s = reinterpret_cast<const uint4*>(in + ((size_t)blockIdx.y * in_stride + i) * 8);
+    uint4* d = reinterpret_cast<uint4*>(out + ((size_t)blockIdx.y * out_stride + i) * 8);
+    d[0] = s[0]; d[1] = s[1];
+}
+
+int ensure_twiddles(smw_ctx* c, int log_n) {
+    if (log_n < 1) log_n = 1;
+    if (c->d_twiddles && c->twiddle_log_n >= log_n) return SMW_OK;
+    if (log_n > 32) return set_err(c, SMW_ERR_INVALID_ARG, "NTT size exceeds the field's two-adicity (2^32)");
+    if (c->d_twiddles) { cudaStreamSynchronize(c->stream); cudaFree(c->d_twiddles); c->d_twiddles = nullptr; }
+    size_t half = (size_t)1 << (log_n - 1);
+    uint32_t* pow2;
+    SMW_CUDA(c, cudaMalloc(&pow2, 33 * 32));
+    SMW_CUDA(c, cudaMalloc(&c->d_twiddles, half * 32));
+    k_pow2_roots<<<1, 32, 0, c->stream>>>(pow2);
+    k_twiddles<<<(unsigned)((half + 255) / 256), 256, 0, c->stream>>>(c->d_twiddles, log_n, pow2);
+    c->launches += 2;
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(pow2);
+    c->twiddle_log_n = log_n;
+    return SMW_OK;
+}
+int launch_root_of_unity(smw_ctx* c, int log_n, uint32_t* d_out) {
+    if (log_n < 0 || log_n > 32) return set_err(c, SMW_ERR_INVALID_ARG, "no root of unity of that order");
+    uint32_t* pow2;
+    SMW_CUDA(c, cudaMalloc(&pow2, 33 * 32));
+    k_pow2_roots<<<1, 32, 0, c->stream>>>(pow2); c->launches++;
+    SMW_CUDA(c, cudaMemcpyAsync(d_out, pow2 + log_n * 8, 32, cudaMemcpyDeviceToDevice, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(pow2);
+    return SMW_OK;
+}
+
+// run butterfly stages [s_from, L) (DIT, ascending) or all stages L-1..0 (DIF, descending) as tiled passes
+static int run_passes(smw_ctx* c, uint32_t* d, int L, bool dif, int inverse, int s_from, int n_cols, size_t col_stride) {
+    if (L == 0) return SMW_OK;
+    int rc = ensure_twiddles(c, L); if (rc) return rc;
+    // split bit positions [0, L) into passes: the lowest pass takes <= 10 bits with contiguous tiles, the others <= 8 bits + contiguous runs
+    std::vector<std::pair<int, int>> ranges;   // [lo, hi)
+    if (L <= TILE_LOG) ranges.push_back({0, L});
+    else {
+        int np = (L + 7) / 8, base = L / np, extra = L % np, lo = 0;
+        for (int i = 0; i < np; i++) { int k = base + (i < extra ? 1 : 0); ranges.push_back({lo, lo + k}); lo += k; }
+    }
+    if (dif) std::reverse(ranges.begin(), ranges.end());
+    for (auto& r : ranges) {
+        PassArgs a; a.L = L; a.inverse = inverse; a.col_stride = col_stride; a.tw_shift = c->twiddle_log_n - L;
+        a.s_begin = r.first; a.s_end = r.second;
+        if (!dif) { if (a.s_end <= s_from) continue; if (a.s_begin < s_from) a.s_begin = s_from; }
+        if (r.first == 0) { a.lo = 0; a.c = 0; a.span = L < TILE_LOG ? L : TILE_LOG; }
+        else { a.lo = r.first; a.span = r.second - r.first; a.c = TILE_LOG - a.span; if (a.c > a.lo) a.c = a.lo; }
+        a.tile_log = a.span + a.c;
+        size_t tiles = ((size_t)1 << L) >> a.tile_log;
+        int threads = (1 << a.tile_log) / 2; if (threads < 32) threads = 32; if (threads > 512) threads = 512;
+        dim3 grid((unsigned)tiles, (unsigned)n_cols);
+        size_t sm = (size_t)32 << a.tile_log;
+        if (dif) k_ntt_pass<true><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+        else k_ntt_pass<false><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+        c->launches++;
+    }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+
+int launch_ntt(smw_ctx* c, uint32_t* d_buf, int log_n, int inverse, int n_cols, size_t col_stride) {
+    if (log_n < 0 || log_n > 32) return set_err(c, SMW_ERR_INVALID_ARG, "bad NTT size");
+    if (log_n == 0 || n_cols == 0) return SMW_OK;
+    int rc = run_passes(c, d_buf, log_n, true, inverse, 0, n_cols, col_stride); if (rc) return rc;
+    const size_t n = (size_t)1 << log_n;
+    uint32_t *d_scale = nullptr, *pow2 = nullptr;
+    if (inverse) {   // 1/n: the g-power table kernel with g = pow2[0] = 1 gives lo[0] = 1/n
+        SMW_CUDA(c, cudaMalloc(&pow2, 33 * 32)); SMW_CUDA(c, cudaMalloc(&d_scale, 1025 * 32));
+        k_pow2_roots<<<1, 32, 0, c->stream>>>(pow2);
+        k_gpow_tables<<<4, 256, 0, c->stream>>>(pow2, log_n, d_scale, d_scale + 8 * 1024, 1);
+        c->launches += 2;
+    }
+    k_bitrev_scale<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_buf, log_n, d_scale, col_stride);
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    if (inverse) { SMW_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(pow2); cudaFree(d_scale); }
+    return SMW_OK;
+}
+
+int launch_lde(smw_ctx* c, const uint32_t* d_in, int log_n, int log_blowup, const uint32_t* d_shift, uint32_t* d_out, int n_cols) {
+    if (log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return set_err(c, SMW_ERR_INVALID_ARG, "bad LDE size");
+    if (n_cols == 0) return SMW_OK;
+    const size_t n = (size_t)1 << log_n, N = n << log_blowup;
+    int rc = ensure_twiddles(c, log_n + log_blowup); if (rc) return rc;
+    // 1. coefficients: inverse DIF in a scratch copy (bit-reversed, unscaled)
+    uint32_t* d_coef; SMW_CUDA(c, cudaMalloc(&d_coef, (size_t)n_cols * n * 32));
+    k_copy_cols<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_in, d_coef, n, n, n); c->launches++;
+    rc = run_passes(c, d_coef, log_n, true, 1, 0, n_cols, n); if (rc) { cudaFree(d_coef); return rc; }
+    // 2. coset scaling (g^k / n) + zero-pad-as-stride expansion
+    size_t n_hi = (n + 1023) >> 10;
+    uint32_t* d_g; SMW_CUDA(c, cudaMalloc(&d_g, (1024 + n_hi) * 32));
+    k_gpow_tables<<<(unsigned)((std::max<size_t>(1024, n_hi) + 255) / 256), 256, 0, c->stream>>>(d_shift, log_n, d_g, d_g + 8 * 1024, n_hi); c->launches++;
+    k_lde_expand<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_coef, log_n, log_blowup, d_g, d_g + 8 * 1024, d_out, n, N); c->launches++;
+    // 3. forward DIT, skipping the log_blowup stages already folded into the expansion
+    rc = run_passes(c, d_out, log_n + log_blowup, false, 0, log_blowup, n_cols, N);
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(d_coef); cudaFree(d_g);
+    return rc;
+}
+
+} // namespace smw

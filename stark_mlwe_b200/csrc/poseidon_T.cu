@@ -1,0 +1,197 @@
+// poseidon_T.cu — compiled once per Poseidon width (-DSMW_T=9|17|33|65|129) so the widths build in
+// parallel.  Holds the launchers for the width-templated kernels; the t = 17 unit also holds the
+// transcript / FRI-leaf kernels, which are fixed at t = 17 (transcript/src/lib.rs:3).
+#include "poseidon_kernels.cuh"
+#include "chacha.cuh"
+#ifndef SMW_T
+#error "compile with -DSMW_T=<width>"
+#endif
+
+namespace smw {
+
+constexpr int T = SMW_T;
+
+template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* p, uint32_t* d_states, size_t batch, bool sparse) {
+    PoseidonDev P = dev_view(p);
+    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
+    if (sparse) { int rc = set_smem(c, k_permute_batch<T, true>, sm); if (rc) return rc; k_permute_batch<T, true><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
+    else { int rc = set_smem(c, k_permute_batch<T, false>, sm); if (rc) return rc; k_permute_batch<T, false><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* p, const uint32_t* d_children, size_t n_children, uint32_t* d_parents, size_t n_parents,
+                                  int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
+                                  int n_cols, size_t child_col_stride, size_t parent_col_stride) {
+    PoseidonDev P = dev_view(p);
+    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
+    int rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
+    dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
+    k_merkle_level<T><<<grid, nt, sm, c->stream>>>(d_children, n_children, d_parents, n_parents, arity, level, label0, label_stride, pos_offset,
+                                                   child_col_stride, parent_col_stride, P);
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
+                                 uint32_t* d_out, size_t cp_div) {
+    PoseidonDev P = dev_view(p);
+    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
+    int rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
+    k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, P);
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+template <> int hash_ds_single_T<T>(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out) {
+    size_t sm = state_smem_bytes<T>(1) + 64;
+    int rc = set_smem(c, k_hash_ds_single<T>, sm); if (rc) return rc;
+    k_hash_ds_single<T><<<1, 32, sm, c->stream>>>(d_ds, nds, d_in, n, d_out, dev_view(p));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+
+#if SMW_T == 17
+// legacy sponge (poseidon/src/lib.rs:85-100): state[16] = ds_tag, 16-chunks, no padding; t = 17
+__global__ void k_hash_legacy_single(const uint32_t* in, size_t n, const uint32_t* tag, uint32_t* out, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    StateRef S = state_ref<17>(smem, 1, 0);
+    uint32_t w[8];
+    for (int i = 0; i < 16; i++) S.store(i, f29_zero());
+    load_ext(tag, w); S.store(16, f29_from_ext(w));
+    for (size_t off = 0; off < n; off += 16) {
+        size_t c = n - off < 16 ? n - off : 16;
+        for (size_t i = 0; i < c; i++) { load_ext(in + (off + i) * 8, w); S.store((int)i, f29_add(S.load((int)i), f29_from_ext(w))); }
+        permute<17, true>(S, P);
+    }
+    f29_to_ext(S.load(0), w); store_ext(out, w);
+}
+
+// ------------------------------------------------------------------ transcript (transcript/src/lib.rs:55-101), t = 17
+// One launch runs a whole absorb program on the device-resident state:
+//   [fresh: state = 0, lane 16 = INIT tag (immA[0])] ; absorb immA[fresh..nA) ; absorb extB[0..nB) ; absorb immC[0..nC) ; [final permute]
+// Immediates are 256-bit little-endian integers (tags, 31-byte words, small integers), reduced mod p here.
+SMW_DEV void tr_absorb(const StateRef& S, const PoseidonDev& P, int& pos, const F29& x) {
+    if (pos == 16) { permute<17, true>(S, P); pos = 0; }
+    S.store(pos, f29_add(S.load(pos), x)); pos++;
+}
+__global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint32_t* immA, int nA, const uint32_t* extB, size_t nB,
+                                 const uint32_t* immC, int nC, int final_permute, uint32_t* out, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    StateRef S = state_ref<17>(smem, 1, 0);
+    uint32_t w[8];
+    int a0 = 0;
+    if (fresh) {
+        for (int i = 0; i < 16; i++) S.store(i, f29_zero());
+        load_ext(immA, w); S.store(16, f29_from_le256(w)); a0 = 1; pos = 0;
+    } else {
+        for (int i = 0; i < 17; i++) { load_ext(state + i * 8, w); S.store(i, f29_from_ext(w)); }
+    }
+    for (int i = a0; i < nA; i++) { load_ext(immA + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
+    for (size_t i = 0; i < nB; i++) { load_ext(extB + i * 8, w); tr_absorb(S, P, pos, f29_from_ext(w)); }
+    for (int i = 0; i < nC; i++) { load_ext(immC + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
+    if (final_permute) permute<17, true>(S, P);
+    if (state) for (int i = 0; i < 17; i++) { f29_to_ext(S.load(i), w); store_ext(state + i * 8, w); }
+    if (out) { f29_to_ext(S.load(0), w); store_ext(out, w); }
+}
+
+// FRI hashed leaves (deep_ali/src/fri.rs:38-44 hash_leaf_pair): the pre-image is a fixed 17-lane template
+// (tags and label words; transcript/src/lib.rs absorbs 9 lanes, no intermediate permutation) with f and s
+// dropped into two lanes: exactly one permutation per leaf.  s_i = s[i / s_div] (or 0 when s == nullptr).
+__global__ void __launch_bounds__(Cfg<17>::NT, Cfg<17>::MINB)
+k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, int lane_f, int lane_s, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
+                  size_t s_div, size_t n, uint32_t* __restrict__ out, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
+    uint32_t w[8];
+#pragma unroll 1
+    for (int j = 0; j < 17; j++) {
+        F29 x;
+        if (j == lane_f) { load_ext(f + i * 8, w); x = f29_from_ext(w); }
+        else if (j == lane_s) { if (s) { load_ext(s + (i / s_div) * 8, w); x = f29_from_ext(w); } else x = f29_zero(); }
+        else { load_ext(tmpl_le256 + j * 8, w); x = f29_from_le256(w); }
+        S.store(j, x);
+    }
+    permute<17, true>(S, P);
+    f29_to_ext(S.load(0), w); store_ext(out + i * 8, w);
+}
+
+// fri_sample_z_ell (deep_ali/src/fri.rs:59-82) for all L levels at once: thread l hashes its template
+// (one permutation), seeds ChaCha12 with the canonical bytes of the digest, and takes the first u64 c with
+// c != 0 and c^n != 1.
+__global__ void k_fri_sample_z(const uint32_t* tmpl_le256, const uint64_t* level_size /* L x (level, size) */, int L, uint64_t seed_z, uint32_t* z_out, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= L) return;
+    StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
+    uint32_t w[8];
+    for (int j = 0; j < 17; j++) { load_ext(tmpl_le256 + ((size_t)l * 17 + j) * 8, w); S.store(j, f29_from_le256(w)); }
+    permute<17, true>(S, P);
+    // canonical integer of the digest: x*2^261 -> x
+    F29 one_int = f29_zero(); one_int.v[0] = 1;
+    F29 d = f29_canonicalize(f29_mul(S.load(0), one_int));
+    uint32_t key[8]; f29_repack_to32(d, key);
+    const uint64_t level = level_size[2 * l], n = level_size[2 * l + 1];
+    ChaChaRng rng; chacha_init(rng, key);
+    F29 z = f29_zero(); bool found = false;
+    for (int tries = 0; tries < 1000 && !found; tries++) {
+        uint64_t c = chacha_next_u64(rng);
+        if (c == 0) continue;
+        F29 cand = f29_from_u64(c);
+        F29 pw = f29_const(C_ONE29);                 // cand^n by square-and-multiply over the bits of n
+        for (int b = 63; b >= 0; b--) { pw = f29_sqr(pw); if ((n >> b) & 1ull) pw = f29_mul(pw, cand); }
+        F29 diff = f29_sub_canon(f29_full_reduce(pw), f29_const(C_ONE29));
+        if (!f29_is_zero_canon(diff)) { z = cand; found = true; }
+    }
+    if (!found) {   // fallbacks of fri.rs:75-79
+        F29 fb = f29_from_u64(seed_z + level + 7ull);
+        F29 pw = f29_const(C_ONE29);
+        for (int b = 63; b >= 0; b--) { pw = f29_sqr(pw); if ((n >> b) & 1ull) pw = f29_mul(pw, fb); }
+        F29 diff = f29_sub_canon(f29_full_reduce(pw), f29_const(C_ONE29));
+        z = f29_is_zero_canon(diff) ? f29_from_u64(11) : fb;
+    }
+    f29_to_ext(z, w); store_ext(z_out + (size_t)l * 8, w);
+}
+
+
+int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out) {
+    if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "legacy hash_with_ds is fixed at t = 17");
+    k_hash_legacy_single<<<1, 32, state_smem_bytes<17>(1) + 64, c->stream>>>(d_in, n, d_tag, d_out, dev_view(p));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
+                          const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute, uint32_t* d_out) {
+    if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
+    k_transcript_run<<<1, 32, state_smem_bytes<17>(1) + 64, c->stream>>>(d_state, fresh, pos, d_immA, nA, d_extB, nB, d_immC, nC, final_permute, d_out, dev_view(p));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, int lane_f, int lane_s,
+                           const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out) {
+    if (n == 0) return SMW_OK;
+    const int nt = Cfg<17>::NT; size_t sm = state_smem_bytes<17>(nt);
+    int rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
+    k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, lane_f, lane_s, d_f, d_s, s_div, n, d_out, dev_view(trp));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_fri_sample_z(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, const uint64_t* d_sizes, int L, uint64_t seed_z, uint32_t* d_z) {
+    if (L <= 0) return SMW_OK;
+    const int nt = 32; size_t sm = state_smem_bytes<17>(nt);
+    k_fri_sample_z<<<(L + nt - 1) / nt, nt, sm, c->stream>>>(d_tmpl, d_sizes, L, seed_z, d_z, dev_view(trp));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+#endif
+
+} // namespace smw

@@ -1,0 +1,120 @@
+// smw_internal.h — host-side structures behind the opaque C-ABI handles, and the launchers the ABI
+// layer calls.  Everything here is product code: no oracle, no CPU arithmetic on field elements.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstddef>
+#include <string>
+#include <vector>
+#include <map>
+#include <mutex>
+#include "../../include/smw.h"
+
+namespace smw {
+struct PoseidonDev;
+}
+
+struct smw_params {
+    smw_ctx* ctx = nullptr;
+    int t = 0, rp = 0;
+    uint32_t* d_tables = nullptr;     // one allocation holding every internal-form table
+    uint32_t* d_ext = nullptr;        // external-form copies (mds, rc_full, rc_partial) for export
+    // device views (pointers into d_tables)
+    const uint32_t *lu_full = nullptr, *rc_full = nullptr, *rc_part = nullptr, *sp_row = nullptr, *sp_col = nullptr, *lu_post = nullptr;
+    bool owned_by_ctx = false;
+};
+
+struct smw_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    std::string last_error;
+    smw_params* commitment_default = nullptr;    // "POSEIDON-T17-X5-SEED"
+    smw_params* transcript_default = nullptr;    // "POSEIDON-T17-X5-TRANSCRIPT"
+    std::map<int, smw_params*> by_width;         // poseidon_params_for_width cache
+    uint32_t* d_twiddles = nullptr;              // w_N^i, i < N/2, external Montgomery form
+    int twiddle_log_n = 0;
+    uint32_t* d_scratch = nullptr; size_t scratch_bytes = 0;
+    void* h_pinned = nullptr; size_t pinned_bytes = 0;
+    uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
+};
+
+struct smw_tree {
+    smw_ctx* ctx = nullptr;
+    smw_params* params = nullptr;
+    int arity = 0;
+    uint64_t tree_label = 0;
+    std::vector<size_t> len;          // level 0 = leaves
+    std::vector<uint32_t*> lv;        // device pointers, external form
+    std::vector<bool> owned;
+};
+
+struct smw_transcript {
+    smw_ctx* ctx = nullptr;
+    smw_params* params = nullptr;
+    uint32_t* d_state = nullptr;      // 17 elements, external form
+    int pos = 0;                      // rate cursor: a function of the call sequence only, so tracked on the host
+};
+
+struct smw_fri {
+    smw_ctx* ctx = nullptr;
+    int L = 0;
+    std::vector<size_t> n, m;
+    std::vector<int> arity, hashed;
+    std::vector<uint32_t*> f;         // device, external form
+    uint32_t* d_z = nullptr;          // L elements
+    std::vector<smw_tree*> tree;
+};
+
+namespace smw {
+
+// status helpers
+int set_err(smw_ctx* c, int code, const char* what);
+int cuda_err(smw_ctx* c, cudaError_t e, const char* what);
+#define SMW_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return smw::cuda_err((ctx), e__, #call); } while (0)
+
+// launchers (poseidon_kernels.cu)
+int launch_derive_params(smw_ctx* c, smw_params* p, const unsigned char* seed, int seed_len);            // BLAKE3 -> tables
+int launch_upload_params(smw_ctx* c, smw_params* p, const uint32_t* d_mds, const uint32_t* d_rcf, const uint32_t* d_rcp); // device ext tables -> internal
+int launch_permute_batch(smw_ctx* c, const smw_params* p, uint32_t* d_states, size_t batch, bool sparse);
+int launch_merkle_level(smw_ctx* c, const smw_params* p, const uint32_t* d_children, size_t n_children, uint32_t* d_parents, size_t n_parents,
+                        int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
+                        int n_cols, size_t child_col_stride, size_t parent_col_stride);
+int launch_pair_leaves(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
+                       uint32_t* d_out, size_t cp_div);
+int launch_hash_ds_single(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
+int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
+// transcript program: state' = run(state, pos; immediates A, ext elements B, immediates C, optional final permute)
+int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
+                          const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute,
+                          uint32_t* d_out /* optional: state[0] after the run */);
+int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_template_le256 /* 17 x 8 words */, int lane_f, int lane_s,
+                           const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out);
+int launch_fri_sample_z(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_templates_le256 /* L x 17 x 8 */, const uint64_t* d_level_size /* L x 2 */, int L,
+                        uint64_t seed_z, uint32_t* d_z);
+
+// per-width launchers (poseidon_T.cu, one translation unit per width)
+template <int T> int permute_batch_T(smw_ctx* c, const smw_params* p, uint32_t* d_states, size_t batch, bool sparse);
+template <int T> int merkle_level_T(smw_ctx* c, const smw_params* p, const uint32_t* d_children, size_t n_children, uint32_t* d_parents, size_t n_parents,
+                                    int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
+                                    int n_cols, size_t child_col_stride, size_t parent_col_stride);
+template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
+                                   uint32_t* d_out, size_t cp_div);
+template <int T> int hash_ds_single_T(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
+
+// field_kernels.cu
+int launch_fri_fold(smw_ctx* c, const uint32_t* d_f, size_t n, const uint32_t* d_z, size_t m, uint32_t* d_out);
+int launch_broadcast_div(smw_ctx* c, const uint32_t* d_src, size_t n, size_t m, uint32_t* d_out);   // out[i] = src[i / m]
+int launch_to_mont(smw_ctx* c, const uint32_t* d_in, uint32_t* d_out, size_t n, int inverse);
+int launch_mf_coeffs(smw_ctx* c, const uint32_t* d_layer, size_t n, uint32_t* d_c0c1);
+int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* d_r, uint32_t* d_next);
+int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size_t n, uint32_t* d_out);   // out[i] = src[idx[i]]
+int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0);
+
+// ntt_kernels.cu
+int ensure_twiddles(smw_ctx* c, int log_n);
+int launch_ntt(smw_ctx* c, uint32_t* d_buf, int log_n, int inverse, int n_cols, size_t col_stride);
+int launch_lde(smw_ctx* c, const uint32_t* d_in, int log_n, int log_blowup, const uint32_t* d_shift, uint32_t* d_out, int n_cols);
+int launch_root_of_unity(smw_ctx* c, int log_n, uint32_t* d_out);
+
+} // namespace smw
