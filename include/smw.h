@@ -61,6 +61,12 @@ int32_t smw_ctx_sync(smw_ctx* ctx);
 const char* smw_last_error(const smw_ctx* ctx);
 uint64_t smw_ctx_launch_count(const smw_ctx* ctx);   /* kernels launched so far through this context */
 void* smw_ctx_stream(const smw_ctx* ctx);
+/* measurement aids (no reference counterpart): per-kernel-class device time from CUDA events on the context's
+ * stream — classes: 0 merkle_level, 1 pair_leaves, 2 fri_leaf, 3 permute, 4 ntt_pass, 5 lde_aux, 6 fold, 7 misc —
+ * and the measured 32x32+64->64 multiply-accumulate (IMAD.WIDE.U32) issue rate that the roofline fractions use */
+int32_t smw_ctx_profile_enable(smw_ctx* ctx, int32_t on);
+int32_t smw_ctx_profile_read(smw_ctx* ctx, double* ms_out, uint64_t* launches_out, int32_t n_classes);   /* syncs, sums, resets */
+int32_t smw_diag_mac_rate(smw_ctx* ctx, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 
 /* ---- field (field/src/lib.rs:13,43-53,206-215; ark-ff) ------------------------------------- */
 int32_t smw_fr_from_canonical(smw_ctx* ctx, const void* canon_le32, void* out_fr, size_t n, int32_t mem);

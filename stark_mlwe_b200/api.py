@@ -78,6 +78,25 @@ class Context:
     def stream(self):
         return self.L.smw_ctx_stream(self.h)
 
+    KERNEL_CLASSES = ("merkle_level", "pair_leaves", "fri_leaf", "permute", "ntt_pass", "lde_aux", "fold", "misc")
+
+    def profile(self, on=True):
+        """per-kernel-class device timing (CUDA events on the context's stream); a measurement aid, not in the reference"""
+        self.check(self.L.smw_ctx_profile_enable(self.h, 1 if on else 0))
+
+    def profile_read(self):
+        """-> {class: (ms, launches)} since the last read; synchronises the stream"""
+        n = len(self.KERNEL_CLASSES)
+        ms, cnt = (C.c_double * n)(), (C.c_uint64 * n)()
+        self.check(self.L.smw_ctx_profile_read(self.h, ms, cnt, n))
+        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+
+    def mac_rate(self):
+        """measured IMAD.WIDE.U32 rate: (32x32+64 multiply-accumulates per second, warp instructions per clock per SM)"""
+        a, b = C.c_double(), C.c_double()
+        self.check(self.L.smw_diag_mac_rate(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def close(self):
         if self.h:
             self.L.smw_ctx_destroy(self.h)

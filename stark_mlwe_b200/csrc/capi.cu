@@ -162,6 +162,8 @@ void smw_ctx_destroy(smw_ctx* c) {
     cudaStreamSynchronize(c->stream);
     free_params_internal(c->commitment_default); free_params_internal(c->transcript_default);
     for (auto& kv : c->by_width) free_params_internal(kv.second);
+    for (auto& r : c->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (auto e : c->prof_pool) cudaEventDestroy(e);
     cudaFree(c->d_twiddles); cudaFree(c->d_scratch);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -171,6 +173,33 @@ int32_t smw_ctx_sync(smw_ctx* c) { if (!c) return SMW_ERR_INVALID_ARG; SMW_CUDA(
 const char* smw_last_error(const smw_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
 uint64_t smw_ctx_launch_count(const smw_ctx* c) { return c ? c->launches : 0; }
 void* smw_ctx_stream(const smw_ctx* c) { return c ? (void*)c->stream : nullptr; }
+int32_t smw_ctx_profile_enable(smw_ctx* c, int32_t on) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (auto& r : c->prof) { c->prof_pool.push_back(r.a); c->prof_pool.push_back(r.b); }
+    c->prof.clear();
+    c->prof_on = on != 0;
+    return SMW_OK;
+}
+int32_t smw_ctx_profile_read(smw_ctx* c, double* ms_out, uint64_t* launches_out, int32_t n_classes) {
+    if (!c || n_classes < 0) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < n_classes; i++) { if (ms_out) ms_out[i] = 0; if (launches_out) launches_out[i] = 0; }
+    for (auto& r : c->prof) {
+        float ms = 0; cudaEventElapsedTime(&ms, r.a, r.b);
+        if (r.cls < n_classes) { if (ms_out) ms_out[r.cls] += ms; if (launches_out) launches_out[r.cls]++; }
+        c->prof_pool.push_back(r.a); c->prof_pool.push_back(r.b);
+    }
+    c->prof.clear();
+    return SMW_OK;
+}
+int32_t smw_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    return launch_diag_mac_rate(c, mac_per_s, warp_instr_per_clk_per_sm);
+}
 
 // ---------------------------------------------------------------------------------------- field
 int32_t smw_fr_from_canonical(smw_ctx* c, const void* in, void* out, size_t n, int32_t mem) {

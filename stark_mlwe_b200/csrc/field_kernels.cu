@@ -5,6 +5,7 @@
 #include "smw_internal.h"
 #include "fr32.cuh"
 #include <algorithm>
+#include <vector>
 
 namespace smw {
 
@@ -99,7 +100,7 @@ int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size
 }
 int launch_fri_fold(smw_ctx* c, const uint32_t* d_f, size_t n, const uint32_t* d_z, size_t m, uint32_t* d_out) {
     size_t n_out = n / m; if (n_out == 0) return SMW_OK;
-    k_fri_fold<<<(unsigned)((n_out + 127) / 128), 128, 0, c->stream>>>(d_f, n_out, d_z, m, d_out); c->launches++;
+    { LaunchScope ls(c, KC_FOLD); k_fri_fold<<<(unsigned)((n_out + 127) / 128), 128, 0, c->stream>>>(d_f, n_out, d_z, m, d_out); }
     SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
 }
 int launch_broadcast_div(smw_ctx* c, const uint32_t* d_src, size_t n, size_t m, uint32_t* d_out) {
@@ -125,7 +126,7 @@ int launch_mf_coeffs(smw_ctx* c, const uint32_t* d_layer, size_t n, uint32_t* d_
 }
 int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* d_r, uint32_t* d_next) {
     size_t n_out = n / 2; if (n_out == 0) return SMW_OK;
-    k_mf_fold<<<(unsigned)((n_out + 255) / 256), 256, 0, c->stream>>>(d_cur, n_out, d_r, d_next); c->launches++;
+    { LaunchScope ls(c, KC_FOLD); k_mf_fold<<<(unsigned)((n_out + 255) / 256), 256, 0, c->stream>>>(d_cur, n_out, d_r, d_next); }
     SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
 }
 int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0) {
@@ -133,6 +134,53 @@ int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, cons
     size_t strips = (n + CH - 1) / CH; if (strips == 0) return SMW_OK;
     k_deep_ali_merge<CH><<<(unsigned)((strips + 127) / 128), 128, 0, c->stream>>>(a, s, e, t, n, d_omega, d_z, d_f0); c->launches++;
     SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
+}
+
+
+// ---- integer-pipe micro-benchmark: IMAD.WIDE.U32 issue rate, 8 independent chains per thread, 8 x 256 threads per SM.
+// Its result is the denominator of the "fraction of the integer-multiply roofline" figures (tools/imad_peak.cu is the
+// stand-alone, wider version of the same measurement).
+__global__ void __launch_bounds__(256) k_diag_mac(uint32_t* out, uint32_t seed, long long* cyc, int iters) {
+    uint32_t b = seed ^ threadIdx.x, c2 = seed * 3 + threadIdx.x;
+    uint64_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = (uint64_t)(seed + i * 7 + threadIdx.x) * 0x9E3779B97F4A7C15ull;
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(b), "r"(c2));
+    }
+    long long t1 = clock64();
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r ^= (uint32_t)w[i] ^ (uint32_t)(w[i] >> 32);
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) {
+    cudaDeviceProp prop; SMW_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
+    const int nsm = prop.multiProcessorCount, per_sm = 8, block = 256, iters = 8192, grid = nsm * per_sm;
+    uint32_t* out; long long* cyc;
+    SMW_CUDA(c, cudaMalloc(&out, (size_t)grid * block * 4)); SMW_CUDA(c, cudaMalloc(&cyc, (size_t)grid * 8));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double best = 0, best_w = 0;
+    std::vector<long long> h(grid);
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(e0, c->stream);
+        k_diag_mac<<<grid, block, 0, c->stream>>>(out, 12345u + rep, cyc, iters); c->launches++;
+        cudaEventRecord(e1, c->stream);
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        cudaMemcpy(h.data(), cyc, (size_t)grid * 8, cudaMemcpyDeviceToHost);
+        double avg = 0; for (int i = 0; i < grid; i++) avg += (double)h[i]; avg /= grid;
+        double rate = (double)grid * block * (double)iters * 8 / (ms * 1e-3);
+        if (rep > 0 && rate > best) { best = rate; best_w = per_sm * (block / 32.0) * (double)iters * 8 / avg; }
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out); cudaFree(cyc);
+    if (mac_per_s) *mac_per_s = best;
+    if (winstr) *winstr = best_w;
+    return SMW_OK;
 }
 
 } // namespace smw

@@ -197,9 +197,9 @@ static int run_passes(smw_ctx* c, uint32_t* d, int L, bool dif, int inverse, int
         int threads = (1 << a.tile_log) / 2; if (threads < 32) threads = 32; if (threads > 512) threads = 512;
         dim3 grid((unsigned)tiles, (unsigned)n_cols);
         size_t sm = (size_t)32 << a.tile_log;
+        LaunchScope ls(c, KC_NTT_PASS);
         if (dif) k_ntt_pass<true><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
         else k_ntt_pass<false><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
-        c->launches++;
     }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
@@ -231,13 +231,13 @@ int launch_lde(smw_ctx* c, const uint32_t* d_in, int log_n, int log_blowup, cons
     int rc = ensure_twiddles(c, log_n + log_blowup); if (rc) return rc;
     // 1. coefficients: inverse DIF in a scratch copy (bit-reversed, unscaled)
     uint32_t* d_coef; SMW_CUDA(c, cudaMalloc(&d_coef, (size_t)n_cols * n * 32));
-    k_copy_cols<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_in, d_coef, n, n, n); c->launches++;
+    { LaunchScope ls(c, KC_LDE_AUX); k_copy_cols<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_in, d_coef, n, n, n); }
     rc = run_passes(c, d_coef, log_n, true, 1, 0, n_cols, n); if (rc) { cudaFree(d_coef); return rc; }
     // 2. coset scaling (g^k / n) + zero-pad-as-stride expansion
     size_t n_hi = (n + 1023) >> 10;
     uint32_t* d_g; SMW_CUDA(c, cudaMalloc(&d_g, (1024 + n_hi) * 32));
     k_gpow_tables<<<(unsigned)((std::max<size_t>(1024, n_hi) + 255) / 256), 256, 0, c->stream>>>(d_shift, log_n, d_g, d_g + 8 * 1024, n_hi); c->launches++;
-    k_lde_expand<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_coef, log_n, log_blowup, d_g, d_g + 8 * 1024, d_out, n, N); c->launches++;
+    { LaunchScope ls(c, KC_LDE_AUX); k_lde_expand<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_coef, log_n, log_blowup, d_g, d_g + 8 * 1024, d_out, n, N); }
     // 3. forward DIT, skipping the log_blowup stages already folded into the expansion
     rc = run_passes(c, d_out, log_n + log_blowup, false, 0, log_blowup, n_cols, N);
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));

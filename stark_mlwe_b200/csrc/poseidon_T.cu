@@ -14,9 +14,8 @@ constexpr int T = SMW_T;
 template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* p, uint32_t* d_states, size_t batch, bool sparse) {
     PoseidonDev P = dev_view(p);
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
-    if (sparse) { int rc = set_smem(c, k_permute_batch<T, true>, sm); if (rc) return rc; k_permute_batch<T, true><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
-    else { int rc = set_smem(c, k_permute_batch<T, false>, sm); if (rc) return rc; k_permute_batch<T, false><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
-    c->launches++;
+    if (sparse) { int rc = set_smem(c, k_permute_batch<T, true>, sm); if (rc) return rc; LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T, true><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
+    else { int rc = set_smem(c, k_permute_batch<T, false>, sm); if (rc) return rc; LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T, false><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
@@ -27,9 +26,9 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* p, const uint32_
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
     int rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
     dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
-    k_merkle_level<T><<<grid, nt, sm, c->stream>>>(d_children, n_children, d_parents, n_parents, arity, level, label0, label_stride, pos_offset,
-                                                   child_col_stride, parent_col_stride, P);
-    c->launches++;
+    { LaunchScope ls(c, KC_MERKLE_LEVEL);
+      k_merkle_level<T><<<grid, nt, sm, c->stream>>>(d_children, n_children, d_parents, n_parents, arity, level, label0, label_stride, pos_offset,
+                                                     child_col_stride, parent_col_stride, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
@@ -38,8 +37,8 @@ template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* p, const uint32_t
     PoseidonDev P = dev_view(p);
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
     int rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
-    k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, P);
-    c->launches++;
+    { LaunchScope ls(c, KC_PAIR_LEAVES);
+      k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
@@ -179,8 +178,8 @@ int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* trp, const uint32_t* d_
     if (n == 0) return SMW_OK;
     const int nt = Cfg<17>::NT; size_t sm = state_smem_bytes<17>(nt);
     int rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
-    k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, lane_f, lane_s, d_f, d_s, s_div, n, d_out, dev_view(trp));
-    c->launches++;
+    { LaunchScope ls(c, KC_FRI_LEAF);
+      k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, lane_f, lane_s, d_f, d_s, s_div, n, d_out, dev_view(trp)); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }

@@ -37,6 +37,11 @@ struct smw_ctx {
     uint32_t* d_scratch = nullptr; size_t scratch_bytes = 0;
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
+    // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
+    bool prof_on = false;
+    struct ProfRec { int cls; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof;
+    std::vector<cudaEvent_t> prof_pool;
 };
 
 struct smw_tree {
@@ -67,6 +72,23 @@ struct smw_fri {
 };
 
 namespace smw {
+
+// kernel classes for the optional device-side timing (smw_ctx_profile_*)
+enum { KC_MERKLE_LEVEL = 0, KC_PAIR_LEAVES, KC_FRI_LEAF, KC_PERMUTE, KC_NTT_PASS, KC_LDE_AUX, KC_FOLD, KC_MISC, KC_COUNT };
+// counts one launch; when profiling is on, brackets it with two events on the context's stream
+struct LaunchScope {
+    smw_ctx* c; cudaEvent_t b = nullptr;
+    LaunchScope(smw_ctx* ctx, int cls) : c(ctx) {
+        c->launches++;
+        if (!c->prof_on) return;
+        cudaEvent_t a;
+        if (c->prof_pool.size() >= 2) { a = c->prof_pool.back(); c->prof_pool.pop_back(); b = c->prof_pool.back(); c->prof_pool.pop_back(); }
+        else { cudaEventCreate(&a); cudaEventCreate(&b); }
+        cudaEventRecord(a, c->stream);
+        c->prof.push_back({cls, a, b});
+    }
+    ~LaunchScope() { if (b) cudaEventRecord(b, c->stream); }
+};
 
 // status helpers
 int set_err(smw_ctx* c, int code, const char* what);
@@ -110,6 +132,8 @@ int launch_mf_coeffs(smw_ctx* c, const uint32_t* d_layer, size_t n, uint32_t* d_
 int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* d_r, uint32_t* d_next);
 int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size_t n, uint32_t* d_out);   // out[i] = src[idx[i]]
 int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0);
+
+int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 
 // ntt_kernels.cu
 int ensure_twiddles(smw_ctx* c, int log_n);
