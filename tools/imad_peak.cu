@@ -63,6 +63,44 @@ template<int MODE> __global__ void __launch_bounds__(256) k(uint32_t* out, uint3
       asm volatile("add.cc.u32 %0, %0, %8; addc.cc.u32 %1, %1, %8; addc.cc.u32 %2, %2, %8; addc.cc.u32 %3, %3, %8;"
                    "addc.cc.u32 %4, %4, %8; addc.cc.u32 %5, %5, %8; addc.cc.u32 %6, %6, %8; addc.u32 %7, %7, %8;"
                    : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]) : "r"(b));
+    } else if (MODE == 9) { // what ptxas makes of the 29-bit column sums: IMAD.WIDE.U32 with RZ accumulate + 3-input IADD3 / IADD3.X
+      #pragma unroll
+      for (int i = 0; i < 4; i++) {
+        uint64_t p0, p1;
+        asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"(b + i), "r"(c));
+        asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(p1) : "r"(c + i), "r"(b));
+        w[i] += p0 + p1;
+      }
+    } else if (MODE == 10) { // products only (RZ accumulate), folded with LOP3 so they stay live
+      #pragma unroll
+      for (int i = 0; i < 8; i++) {
+        uint64_t p0;
+        asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"(b + i), "r"(c));
+        w[i] ^= p0;
+      }
+    } else if (MODE == 11) { // DFMA, 8 independent chains
+      double* d = (double*)w; double x = __longlong_as_double(0x3ff0000000000001ll + b), y = 1e-9 * c;
+      #pragma unroll
+      for (int i = 0; i < 8; i++) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[i]) : "d"(x), "d"(y));
+    } else if (MODE == 12) { // 4 DFMA + 8 IMAD.WIDE: do the FP64 and integer-multiply pipes overlap?
+      double* d = (double*)(w + 4); double x = __longlong_as_double(0x3ff0000000000001ll + b), y = 1e-9 * c;
+      #pragma unroll
+      for (int i = 0; i < 4; i++) {
+        asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[i]) : "d"(x), "d"(y));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(b), "r"(c));
+        asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(c), "r"(b));
+      }
+    } else if (MODE == 13) { // IMAD.WIDE with accumulate, distinct operand registers per chain (no operand-reuse cache help)
+      #pragma unroll
+      for (int i = 0; i < 8; i++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(a[i]), "r"(a[(i + 3) & 7]));
+    } else if (MODE == 14) { // 16 products per 8 accumulators, RZ form + adds, distinct operands (closest to acc_mac)
+      #pragma unroll
+      for (int i = 0; i < 8; i++) {
+        uint64_t p0, p1;
+        asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(p0) : "r"(a[i]), "r"(a[(i + 3) & 7]));
+        asm volatile("mul.wide.u32 %0, %1, %2;" : "=l"(p1) : "r"(a[(i + 1) & 7]), "r"(a[(i + 5) & 7]));
+        w[i] += p0 + p1;
+      }
     } else if (MODE == 8) { // 8 IMAD.WIDE + 16 IADD3
       uint32_t* q = (uint32_t*)(w + 4);
       #pragma unroll
@@ -106,11 +144,13 @@ template<int MODE> int run(const char* name, int instr_per_iter, int mul_per_ite
 int main() {
   cudaDeviceProp p; CHK(cudaGetDeviceProperties(&p, 0));
   int nsm = p.multiProcessorCount; printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_khz\": %d}\n", p.name, nsm, p.clockRate);
-  for (int c = 2; c <= 8; c *= 2) {
+  for (int c = 1; c <= 8; c *= 2) {
     run<0>("imad_lo", 8, 8, c, nsm); run<1>("imad_hi", 8, 8, c, nsm); run<2>("imad_wide", 8, 8, c, nsm);
     run<3>("imad_wide_carry_rows", 8, 8, c, nsm); run<4>("iadd3", 8, 0, c, nsm);
     run<5>("imad_wide8+iadd8", 16, 8, c, nsm); run<6>("imad_wide8+iadd4", 12, 8, c, nsm); run<7>("iadd3x_chain", 8, 0, c, nsm);
     run<8>("imad_wide8+iadd16", 24, 8, c, nsm);
+    run<9>("imad_wide_rz8+iadd3x4pairs", 16, 8, c, nsm); run<10>("imad_wide_rz8+lop", 24, 8, c, nsm); run<11>("dfma8", 8, 8, c, nsm);
+    run<12>("dfma4+imad_wide8", 12, 8, c, nsm); run<13>("imad_wide_acc_distinct_ops", 8, 8, c, nsm); run<14>("imad_wide_rz16+iadd3x8pairs", 32, 16, c, nsm);
   }
   return 0;
 }
