@@ -155,7 +155,7 @@ int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** ou
     return SMW_OK;
 }
 int32_t smw_ctx_create(int32_t device, smw_ctx** out) { return smw_ctx_create_on_stream(device, nullptr, out); }
-static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_ext); delete p; }
+static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_ext); cudaFree(p->d_prog); delete p; }
 void smw_ctx_destroy(smw_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);

@@ -25,6 +25,9 @@ constexpr uint32_t M29 = 0x1fffffffu;
 // p = 2^254 + c in radix 2^29: limbs 5..7 are zero, limb 0 is 1, limb 8 is 2^22; -p^-1 mod 2^29 = 2^29-1
 constexpr uint32_t P29_1 = 0x02375908u, P29_2 = 0x052a3763u, P29_3 = 0x0d31f813u, P29_4 = 0x00000224u, P29_8 = 0x00400000u;
 
+// external form (8 x u32, Montgomery R = 2^256) of 1: 2^256 mod p
+__device__ __constant__ const uint32_t C_R32W[8] = {0xfffffffdu, 0x5b2b3e9cu, 0xe3420567u, 0x992c350bu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0x3fffffffu};
+
 struct F29 { uint32_t v[9]; };
 struct Acc { uint64_t c[17]; };
 
@@ -34,10 +37,17 @@ __device__ __constant__ const uint32_t C_KIN29[9]  = {0x1ffff001u, 0x0ca6d907u, 
 __device__ __constant__ const uint32_t C_KOUT29[9] = {0x1ffffffdu, 0x1959f4e7u, 0x108159d6u, 0x186a17c6u, 0x1ffff992u, 0x1fffffffu, 0x1fffffffu, 0x1fffffffu, 0x003fffffu}; // 2^256 mod p
 __device__ __constant__ const uint32_t C_P29[9]    = {0x00000001u, 0x02375908u, 0x052a3763u, 0x0d31f813u, 0x00000224u, 0x00000000u, 0x00000000u, 0x00000000u, 0x00400000u};
 
+// Written as plain C on purpose: ptxas turns `mul.wide.u32 + add.s64` into ONE accumulating IMAD.WIDE.U32, whereas the
+// PTX `mad.wide.u32` spelled through inline asm is split into IMAD.WIDE.U32 (RZ addend) + IADD3 + IADD3.X, which makes
+// the ALU pipe, not the multiplier, the bottleneck of every dot product (profiles/r01b_sass_mac_forms.md).
 SMW_DEV uint64_t madw(uint32_t a, uint32_t b, uint64_t c) {
+#ifdef SMW_MADW_ASM
     uint64_t r;
     asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
     return r;
+#else
+    return (uint64_t)a * b + c;
+#endif
 }
 
 SMW_DEV F29 f29_const(const uint32_t* c) { F29 r;

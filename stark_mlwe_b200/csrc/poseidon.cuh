@@ -1,35 +1,68 @@
 // poseidon.cuh — device-side Poseidon permutation and sponges over fr29.
 //
 // Mapping to the SM: ONE THREAD PER PERMUTATION, state resident in shared memory in a
-// word-interleaved layout ([element][chunk][thread], conflict-free LDS.128), constants read as
-// warp-uniform loads from a global table (L1/L2 resident, 48-byte aligned elements).  The dense
-// t x t matrix is applied IN PLACE through its LU factors (same multiply count as the dense product,
-// no second state buffer, so 2x the resident threads per SM); the RP partial rounds use the exact
-// sparse factorisation (row + rank-1 update per round, one dense (t-1)x(t-1) matrix at the end).
-// Every dot product is accumulated lazily (fr29.cuh) and reduced once.
+// word-interleaved layout ([lane][chunk][thread], conflict-free LDS.128), constants read as
+// warp-uniform loads from one global table (L1/L2 resident, 48-byte aligned elements).
+//
+// The permutation is not written out as code: it is a PROGRAM of "row operations" built once per
+// parameter set on the host (poseidon_prog.cu) and run by one small interpreter loop (run_ops below).
+// A row operation is
+//        x = sum_{j < n} A_j * B_j            lazily accumulated (fr29.cuh), ONE Montgomery reduction
+//        x += S[dst]   (optional)             unit diagonal of L / rank-1 update of a sparse partial round
+//        x += rc       (optional)             the NEXT round's round constant, folded into the producer
+//        S[dst] = x
+// with A_j a state lane (or an external input element) and B_j a table entry (or a state lane, for the
+// S-box multiplications).  Why an interpreter: round 1a inlined the rounds as straight-line code, 360 KB of
+// SASS for the Merkle kernel; with ten warps per SM in different phases the instruction cache thrashed and
+// "no instruction" was the top stall (profiles/r01a_ncu_full_merkle_level17_details.csv: 6.2 of 10.6 cycles per
+// issue).  Here every warp executes the same ~8 KB loop whose body is one 81-multiply block, so the hot
+// code stays in the L0/L1 instruction caches whatever the phase of each warp.
+//
+// The dense t x t matrix is applied IN PLACE through its LU factors (same multiply count as the dense
+// product, no second state buffer); the RP partial rounds use the exact sparse factorisation (one row
+// dot product + rank-1 update per round, one dense (t-1)x(t-1) matrix at the end).  These are exact
+// identities over the field, so outputs are bit-identical to the reference's dense rounds.
 //
 // Reference semantics: poseidon/src/lib.rs:219-258 permute_dynamic (== :31-68 permute for t = 17),
 // :260-272 dense mat-vec in every round, :276-312 absorb_one / hash_with_ds_dynamic.
-// The factorisations are exact identities over the field, so outputs are bit-identical.
 #pragma once
+#include "smw_internal.h"
 #include "fr29.cuh"
 
 namespace smw {
 
 constexpr int EL = 12;   // table element stride in 32-bit words (9 used; 48 B keeps 16-byte alignment)
 
-// Device view of one parameter set (all tables in internal form: x * 2^261 mod p, canonical limbs)
+// row-operation flags (bits 24..31 of Op.y)
+enum : uint32_t {
+    OPF_BSTATE  = 1,    // B operand is state lane Op.x (S-box multiplications) instead of table element Op.x
+    OPF_ADDSELF = 2,    // add the old S[dst] to the reduced result
+    OPF_ADDRC   = 4,    // add table element Op.z (round constant / padding one)
+    OPF_LOAD    = 8,    // no products: x = S[Op.w]
+    OPF_SQR     = 16,   // x = S[j0]^2 (45 multiplies instead of 81)
+    OPF_AEXT    = 32    // A operand is external input element Op.w (raw 29-bit repack; the B operand carries the
+                        // conversion constant), single term
+};
+// Op = uint4 { x: B offset (table element index, or state lane), y: j0 | n << 8 | dst << 16 | flags << 24,
+//              z: table element index of the constant to add, w: source lane (LOAD) / input index (AEXT) }
+__host__ __device__ inline uint4 make_op(uint32_t b_off, int j0, int n, int dst, uint32_t flags, uint32_t rc_off = 0, uint32_t aux = 0) {
+    uint4 o; o.x = b_off; o.y = (uint32_t)j0 | ((uint32_t)n << 8) | ((uint32_t)dst << 16) | (flags << 24); o.z = rc_off; o.w = aux; return o;
+}
+
+// Segs (smw_internal.h): up to 8 (first, count) ranges of the op array, run in order, e.g.
+// [absorb block 0][permutation][absorb block 1][permutation]
+
+// Device view of one parameter set
 struct PoseidonDev {
     int t, rp;
-    const uint32_t* lu_full;   // [t][t]      : U on and above the diagonal, unit-L strictly below   (M = L*U)
-    const uint32_t* rc_full;   // [8][t]
-    const uint32_t* rc_part;   // [rp]
-    const uint32_t* sp_row;    // [rp][t]     : (M00, v^T * Mh^k)            -> new lane 0
-    const uint32_t* sp_col;    // [rp][t-1]   : Mh^-(k+1) * w                -> rank-1 update of lanes 1..
-    const uint32_t* lu_post;   // [t-1][t-1]  : LU of Mh^rp, applied to lanes 1.. after the partial rounds
+    const uint32_t* tbl;     // every table in internal form (x * 2^261 mod p, canonical limbs), EL words per element
+    const uint4* prog;       // row operations
+    int perm_first, perm_count;       // the production permutation (sparse partial rounds)
+    int dense_first, dense_count;     // the literal round structure (dense matrix in every partial round): test aid
+    uint32_t k_in, k_out, k_rr, k_one;   // table indices of 2^266, 2^256, 2^522, 2^261 (mod p)
 };
 
-SMW_DEV F29 tbl_load(const uint32_t* base, int idx) {
+SMW_DEV F29 tbl_load(const uint32_t* base, uint32_t idx) {
     const uint4* q = reinterpret_cast<const uint4*>(base + (size_t)idx * EL);
     uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
     F29 r;
@@ -37,10 +70,10 @@ SMW_DEV F29 tbl_load(const uint32_t* base, int idx) {
     return r;
 }
 
-// Per-thread state in shared memory: element j = two uint4 (limbs 0-3, 4-7) + one word (limb 8)
+// Per-thread state in shared memory: lane j = two uint4 (limbs 0-3, 4-7) + one word (limb 8); T + 1 lanes (lane T is scratch)
 struct StateRef {
-    uint4* q;       // [T][2][NT]
-    uint32_t* w;    // [T][NT]
+    uint4* q;       // [T+1][2][NT]
+    uint32_t* w;    // [T+1][NT]
     int nt, tid;
     SMW_DEV F29 load(int j) const {
         uint4 a = q[(2 * j) * nt + tid], b = q[(2 * j + 1) * nt + tid];
@@ -55,95 +88,9 @@ struct StateRef {
     }
 };
 template <int T> SMW_DEV StateRef state_ref(unsigned char* smem, int nt, int tid) {
-    StateRef S; S.q = reinterpret_cast<uint4*>(smem); S.w = reinterpret_cast<uint32_t*>(smem + (size_t)T * 2 * nt * 16); S.nt = nt; S.tid = tid; return S;
+    StateRef S; S.q = reinterpret_cast<uint4*>(smem); S.w = reinterpret_cast<uint32_t*>(smem + (size_t)(T + 1) * 2 * nt * 16); S.nt = nt; S.tid = tid; return S;
 }
-template <int T> __host__ __device__ constexpr size_t state_smem_bytes(int nt) { return (size_t)T * nt * 36; }
-
-// s[off .. off+n) <- (L*U) * s[off .. off+n), in place.  lu is an n x n table.
-SMW_DEV void matvec_lu_inplace(const StateRef& S, const uint32_t* lu, int n, int off) {
-    // U sweep, ascending rows: row i reads lanes >= i only
-#pragma unroll 1
-    for (int i = 0; i < n; i++) {
-        Acc A; acc_zero(A); int c = 0;
-        const uint32_t* row = lu + (size_t)i * n * EL;
-#pragma unroll 1
-        for (int j = i; j < n; j++) {
-            acc_mac(A, S.load(off + j), tbl_load(row, j));
-            if (++c == 6) { acc_normalize(A); c = 0; }
-        }
-        S.store(off + i, acc_reduce(A));
-    }
-    // L sweep (unit diagonal), descending rows: row i reads lanes <= i only
-#pragma unroll 1
-    for (int i = n - 1; i >= 1; i--) {
-        Acc A; acc_zero(A); int c = 0;
-        const uint32_t* row = lu + (size_t)i * n * EL;
-#pragma unroll 1
-        for (int j = 0; j < i; j++) {
-            acc_mac(A, S.load(off + j), tbl_load(row, j));
-            if (++c == 6) { acc_normalize(A); c = 0; }
-        }
-        S.store(off + i, acc_reduce_add(A, S.load(off + i)));
-    }
-}
-
-template <int T> SMW_DEV void full_round(const StateRef& S, const PoseidonDev& P, int r) {
-#pragma unroll 1
-    for (int i = 0; i < T; i++) S.store(i, f29_sbox5(f29_add(S.load(i), tbl_load(P.rc_full, r * T + i))));
-    matvec_lu_inplace(S, P.lu_full, T, 0);
-}
-
-// The permutation.  SPARSE = false keeps the reference's round structure literally (dense matrix in
-// every partial round); SPARSE = true is the production path.  Both are tested against the oracle.
-template <int T, bool SPARSE> SMW_DEV void permute(const StateRef& S, const PoseidonDev& P) {
-#pragma unroll 1
-    for (int r = 0; r < 4; r++) full_round<T>(S, P, r);
-    if (SPARSE) {
-#pragma unroll 1
-        for (int k = 0; k < P.rp; k++) {
-            F29 x0 = f29_sbox5(f29_add(S.load(0), tbl_load(P.rc_part, k)));
-            const uint32_t* row = P.sp_row + (size_t)k * T * EL;
-            const uint32_t* col = P.sp_col + (size_t)k * (T - 1) * EL;
-            Acc A; acc_zero(A); acc_mac(A, x0, tbl_load(row, 0)); int c = 1;
-#pragma unroll 1
-            for (int i = 1; i < T; i++) {
-                F29 si = S.load(i);
-                acc_mac(A, si, tbl_load(row, i));
-                if (++c == 6) { acc_normalize(A); c = 0; }
-                Acc B; acc_zero(B); acc_mac(B, x0, tbl_load(col, i - 1));
-                S.store(i, acc_reduce_add(B, si));
-            }
-            S.store(0, acc_reduce(A));
-        }
-        matvec_lu_inplace(S, P.lu_post, T - 1, 1);
-    } else {
-#pragma unroll 1
-        for (int k = 0; k < P.rp; k++) {
-            S.store(0, f29_sbox5(f29_add(S.load(0), tbl_load(P.rc_part, k))));
-            matvec_lu_inplace(S, P.lu_full, T, 0);
-        }
-    }
-#pragma unroll 1
-    for (int r = 4; r < 8; r++) full_round<T>(S, P, r);
-}
-
-// DS sponge (poseidon/src/lib.rs:276-312): rate T-1, additive absorb, pad with 1 then zeros.
-template <int T, bool SPARSE> struct Sponge {
-    StateRef S; const PoseidonDev& P; int cursor;
-    SMW_DEV Sponge(const StateRef& s, const PoseidonDev& p) : S(s), P(p), cursor(0) {
-#pragma unroll 1
-        for (int i = 0; i < T; i++) S.store(i, f29_zero());
-    }
-    SMW_DEV void absorb(const F29& x) {
-        S.store(cursor, f29_add(S.load(cursor), x));
-        if (++cursor == T - 1) { cursor = 0; permute<T, SPARSE>(S, P); }
-    }
-    SMW_DEV F29 finish() {
-        absorb(f29_const(C_ONE29));
-        if (cursor != 0) { cursor = 0; permute<T, SPARSE>(S, P); }   // absorbing zeros only advances the cursor
-        return S.load(0);
-    }
-};
+template <int T> __host__ __device__ constexpr size_t state_smem_bytes(int nt) { return (size_t)(T + 1) * nt * 36; }
 
 SMW_DEV void load_ext(const uint32_t* p, uint32_t w[8]) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
@@ -153,6 +100,63 @@ SMW_DEV void load_ext(const uint32_t* p, uint32_t w[8]) {
 SMW_DEV void store_ext(uint32_t* p, const uint32_t w[8]) {
     uint4* q = reinterpret_cast<uint4*>(p);
     q[0] = make_uint4(w[0], w[1], w[2], w[3]); q[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+
+// "no external inputs" functor for programs without OPF_AEXT operations
+struct NoInput { SMW_DEV F29 operator()(uint32_t) const { return f29_zero(); } };
+
+// The interpreter.  One copy per kernel (noinline: the sponges call it once per segment list), a few hundred
+// instructions; all warps of the SM loop over the same code.
+template <class In>
+__device__ __noinline__ void run_ops(StateRef S, const uint32_t* __restrict__ tbl, const uint4* __restrict__ prog, int first, int count, In in) {
+    uint4 d = __ldg(prog + first);
+#pragma unroll 1
+    for (int k = 0; k < count; k++) {
+        const uint4 dn = __ldg(prog + first + k + 1);        // every program is followed by one padding op
+        const uint32_t fl = d.y >> 24;
+        const int j0 = d.y & 255, n = (d.y >> 8) & 255, dst = (d.y >> 16) & 255;
+        F29 x;
+        if (fl & OPF_LOAD) {
+            x = S.load((int)d.w);
+        } else {
+            Acc A; acc_zero(A);
+            if (fl & OPF_SQR) {
+                acc_sqr(A, S.load(j0));
+            } else {
+                F29 a = (fl & OPF_AEXT) ? in(d.w) : S.load(j0);
+                F29 b = (fl & OPF_BSTATE) ? S.load((int)d.x) : tbl_load(tbl, d.x);
+                int c = 0;
+#pragma unroll 1
+                for (int j = 1; j <= n; j++) {
+                    F29 an = a, bn = b;
+                    if (j < n) { an = S.load(j0 + j); bn = tbl_load(tbl, d.x + j); }   // next term's operands, in flight during this term's 81 multiplies
+                    if (c == 6) { acc_normalize(A); c = 0; }
+                    acc_mac(A, a, b); c++;
+                    a = an; b = bn;
+                }
+            }
+            if (fl & OPF_ADDSELF) {
+                F29 s = S.load(dst);
+#pragma unroll
+                for (int i = 0; i < 8; i++) A.c[9 + i] += s.v[i];
+                x = acc_reduce(A);
+                x.v[8] += s.v[8];
+            } else {
+                x = acc_reduce(A);
+            }
+        }
+        if (fl & OPF_ADDRC) x = f29_add(x, tbl_load(tbl, d.z));
+        S.store(dst, x);
+        d = dn;
+    }
+}
+template <class In>
+SMW_DEV void run_segs(const StateRef& S, const PoseidonDev& P, const Segs& sg, const In& in) {
+#pragma unroll 1
+    for (int s = 0; s < sg.n; s++) run_ops(S, P.tbl, P.prog, sg.first[s], sg.count[s], in);
+}
+SMW_DEV void run_perm(const StateRef& S, const PoseidonDev& P, bool sparse = true) {
+    run_ops(S, P.tbl, P.prog, sparse ? P.perm_first : P.dense_first, sparse ? P.perm_count : P.dense_count, NoInput());
 }
 
 } // namespace smw

@@ -11,34 +11,56 @@ namespace smw {
 
 constexpr int T = SMW_T;
 
-template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* p, uint32_t* d_states, size_t batch, bool sparse) {
+// segment list [load lanes][permutation][lanes -> external scale] of the batched permutation
+static int io_segs(smw_ctx* c, smw_params* p, bool sparse, Segs* sg) {
+    Segs io; int rc = get_sponge_segs(c, p, -1, 0, &io); if (rc) return rc;      // key (-1, 0): first[0] = load ops, first[1] = output ops
+    sg->n = 3;
+    sg->first[0] = io.first[0]; sg->count[0] = p->t;
+    sg->first[1] = sparse ? p->perm_first : p->dense_first; sg->count[1] = sparse ? p->perm_count : p->dense_count;
+    sg->first[2] = io.first[1]; sg->count[2] = p->t;
+    return SMW_OK;
+}
+static int out_first_op(smw_ctx* c, smw_params* p, int* out_first) {
+    Segs io; int rc = get_sponge_segs(c, p, -1, 0, &io); if (rc) return rc;
+    *out_first = io.first[1]; return SMW_OK;
+}
+
+template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* cp, uint32_t* d_states, size_t batch, bool sparse) {
+    smw_params* p = const_cast<smw_params*>(cp);
+    Segs sg; int rc = io_segs(c, p, sparse, &sg); if (rc) return rc;
     PoseidonDev P = dev_view(p);
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
-    if (sparse) { int rc = set_smem(c, k_permute_batch<T, true>, sm); if (rc) return rc; LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T, true><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
-    else { int rc = set_smem(c, k_permute_batch<T, false>, sm); if (rc) return rc; LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T, false><<<grid, nt, sm, c->stream>>>(d_states, batch, P); }
+    rc = set_smem(c, k_permute_batch<T>, sm); if (rc) return rc;
+    { LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T><<<grid, nt, sm, c->stream>>>(d_states, batch, sg, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
-template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* p, const uint32_t* d_children, size_t n_children, uint32_t* d_parents, size_t n_parents,
+template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32_t* d_children, size_t n_children, uint32_t* d_parents, size_t n_parents,
                                   int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
                                   int n_cols, size_t child_col_stride, size_t parent_col_stride) {
+    smw_params* p = const_cast<smw_params*>(cp);
+    Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
+    int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
-    int rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
+    rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
     dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
     { LaunchScope ls(c, KC_MERKLE_LEVEL);
       k_merkle_level<T><<<grid, nt, sm, c->stream>>>(d_children, n_children, d_parents, n_parents, arity, level, label0, label_stride, pos_offset,
-                                                     child_col_stride, parent_col_stride, P); }
+                                                     child_col_stride, parent_col_stride, sg, out_first, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
-template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
+template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
                                  uint32_t* d_out, size_t cp_div) {
+    smw_params* p = const_cast<smw_params*>(cp);
+    Segs sg; int rc = get_sponge_segs(c, p, 4, 2, &sg); if (rc) return rc;
+    int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
-    int rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
+    rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_PAIR_LEAVES);
-      k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, P); }
+      k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, sg, out_first, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
@@ -63,7 +85,7 @@ __global__ void k_hash_legacy_single(const uint32_t* in, size_t n, const uint32_
     for (size_t off = 0; off < n; off += 16) {
         size_t c = n - off < 16 ? n - off : 16;
         for (size_t i = 0; i < c; i++) { load_ext(in + (off + i) * 8, w); S.store((int)i, f29_add(S.load((int)i), f29_from_ext(w))); }
-        permute<17, true>(S, P);
+        run_perm(S, P);
     }
     f29_to_ext(S.load(0), w); store_ext(out, w);
 }
@@ -73,7 +95,7 @@ __global__ void k_hash_legacy_single(const uint32_t* in, size_t n, const uint32_
 //   [fresh: state = 0, lane 16 = INIT tag (immA[0])] ; absorb immA[fresh..nA) ; absorb extB[0..nB) ; absorb immC[0..nC) ; [final permute]
 // Immediates are 256-bit little-endian integers (tags, 31-byte words, small integers), reduced mod p here.
 SMW_DEV void tr_absorb(const StateRef& S, const PoseidonDev& P, int& pos, const F29& x) {
-    if (pos == 16) { permute<17, true>(S, P); pos = 0; }
+    if (pos == 16) { run_perm(S, P); pos = 0; }
     S.store(pos, f29_add(S.load(pos), x)); pos++;
 }
 __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint32_t* immA, int nA, const uint32_t* extB, size_t nB,
@@ -92,7 +114,7 @@ __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint
     for (int i = a0; i < nA; i++) { load_ext(immA + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
     for (size_t i = 0; i < nB; i++) { load_ext(extB + i * 8, w); tr_absorb(S, P, pos, f29_from_ext(w)); }
     for (int i = 0; i < nC; i++) { load_ext(immC + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
-    if (final_permute) permute<17, true>(S, P);
+    if (final_permute) run_perm(S, P);
     if (state) for (int i = 0; i < 17; i++) { f29_to_ext(S.load(i), w); store_ext(state + i * 8, w); }
     if (out) { f29_to_ext(S.load(0), w); store_ext(out, w); }
 }
@@ -100,24 +122,25 @@ __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint
 // FRI hashed leaves (deep_ali/src/fri.rs:38-44 hash_leaf_pair): the pre-image is a fixed 17-lane template
 // (tags and label words; transcript/src/lib.rs absorbs 9 lanes, no intermediate permutation) with f and s
 // dropped into two lanes: exactly one permutation per leaf.  s_i = s[i / s_div] (or 0 when s == nullptr).
+struct InFriLeaf {
+    const uint32_t* f; const uint32_t* s; const uint32_t* tmpl;
+    SMW_DEV F29 operator()(uint32_t idx) const {
+        if (idx == 0) return raw_ext(f);
+        if (idx == 1) return s ? raw_ext(s) : f29_zero();
+        return raw_ext(tmpl + (size_t)(idx - 2) * 8);          // template lane idx-2: a 256-bit little-endian integer (tag / label word)
+    }
+};
 __global__ void __launch_bounds__(Cfg<17>::NT, Cfg<17>::MINB)
-k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, int lane_f, int lane_s, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
-                  size_t s_div, size_t n, uint32_t* __restrict__ out, PoseidonDev P) {
+k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
+                  size_t s_div, size_t n, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
-    uint32_t w[8];
-#pragma unroll 1
-    for (int j = 0; j < 17; j++) {
-        F29 x;
-        if (j == lane_f) { load_ext(f + i * 8, w); x = f29_from_ext(w); }
-        else if (j == lane_s) { if (s) { load_ext(s + (i / s_div) * 8, w); x = f29_from_ext(w); } else x = f29_zero(); }
-        else { load_ext(tmpl_le256 + j * 8, w); x = f29_from_le256(w); }
-        S.store(j, x);
-    }
-    permute<17, true>(S, P);
-    f29_to_ext(S.load(0), w); store_ext(out + i * 8, w);
+    InFriLeaf in{f + i * 8, s ? s + (i / s_div) * 8 : nullptr, tmpl_le256};
+    run_segs(S, P, sg, in);                       // [17 lane loads][permutation]
+    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    emit_ext(S.load(0), out + i * 8);
 }
 
 // fri_sample_z_ell (deep_ali/src/fri.rs:59-82) for all L levels at once: thread l hashes its template
@@ -130,7 +153,7 @@ __global__ void k_fri_sample_z(const uint32_t* tmpl_le256, const uint64_t* level
     StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
     uint32_t w[8];
     for (int j = 0; j < 17; j++) { load_ext(tmpl_le256 + ((size_t)l * 17 + j) * 8, w); S.store(j, f29_from_le256(w)); }
-    permute<17, true>(S, P);
+    run_perm(S, P);
     // canonical integer of the digest: x*2^261 -> x
     F29 one_int = f29_zero(); one_int.v[0] = 1;
     F29 d = f29_canonicalize(f29_mul(S.load(0), one_int));
@@ -173,13 +196,16 @@ int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, in
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
-int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, int lane_f, int lane_s,
+int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* ctrp, const uint32_t* d_tmpl, int lane_f, int lane_s,
                            const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out) {
     if (n == 0) return SMW_OK;
+    smw_params* trp = const_cast<smw_params*>(ctrp);
+    Segs sg; int rc = get_sponge_segs(c, trp, -2, lane_f * 256 + lane_s, &sg); if (rc) return rc;
+    int out_first; rc = out_first_op(c, trp, &out_first); if (rc) return rc;
     const int nt = Cfg<17>::NT; size_t sm = state_smem_bytes<17>(nt);
-    int rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
+    rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_FRI_LEAF);
-      k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, lane_f, lane_s, d_f, d_s, s_div, n, d_out, dev_view(trp)); }
+      k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, d_f, d_s, s_div, n, d_out, sg, out_first, dev_view(trp)); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }

@@ -1,12 +1,16 @@
 // poseidon_kernels.cuh — kernel templates shared by the per-width translation units.
+// Every kernel is: a short prologue (zero the lanes, write the raw DS integers), ONE interpreter (run_ops) fed with
+// segment lists built on the host, and a short epilogue (canonicalise + repack the digest).
 #pragma once
 #include "smw_internal.h"
 #include "poseidon.cuh"
+#include <vector>
+#include <algorithm>
 
 namespace smw {
 
-// launch shape per width: threads per CTA and CTAs per SM so that the per-thread state (T * 36 B)
-// fills shared memory: t=9 -> 2 x 256, t=17 -> 2 x 160 (196 KB), larger widths 1 CTA.
+// launch shape per width: threads per CTA and CTAs per SM so that the per-thread state ((T + 1) * 36 B)
+// fills shared memory: t=9 -> 2 x 256, t=17 -> 2 x 160 (207 KB), larger widths 1 CTA.
 template <int T> struct Cfg;
 template <> struct Cfg<9>   { static constexpr int NT = 256, MINB = 2; };
 template <> struct Cfg<17>  { static constexpr int NT = 160, MINB = 2; };
@@ -15,8 +19,10 @@ template <> struct Cfg<65>  { static constexpr int NT = 96,  MINB = 1; };
 template <> struct Cfg<129> { static constexpr int NT = 32,  MINB = 1; };
 
 static PoseidonDev dev_view(const smw_params* p) {
-    PoseidonDev d; d.t = p->t; d.rp = p->rp; d.lu_full = p->lu_full; d.rc_full = p->rc_full; d.rc_part = p->rc_part;
-    d.sp_row = p->sp_row; d.sp_col = p->sp_col; d.lu_post = p->lu_post; return d;
+    PoseidonDev d; d.t = p->t; d.rp = p->rp; d.tbl = p->d_tables; d.prog = p->d_prog;
+    d.perm_first = p->perm_first; d.perm_count = p->perm_count; d.dense_first = p->dense_first; d.dense_count = p->dense_count;
+    d.k_in = p->layout.k_in; d.k_out = p->layout.k_out; d.k_rr = p->layout.k_rr; d.k_one = p->layout.k_one;
+    return d;
 }
 
 // ------------------------------------------------------------------ plain (non-__ldg) table access
@@ -33,69 +39,114 @@ SMW_DEV F29 mulc(const F29& a, const F29& b) { return f29_canonicalize(f29_mul(a
 // 256-bit little-endian integer (any value < 2^256) -> internal form, canonical
 SMW_DEV F29 f29_from_le256(const uint32_t w[8]) { return f29_canonicalize(f29_mul(f29_repack_from32(w), f29_const(C_RR29))); }
 
+SMW_DEV F29 raw_ext(const uint32_t* p) { uint32_t w[8]; load_ext(p, w); return f29_repack_from32(w); }
+SMW_DEV F29 raw_one_ext() { uint32_t w[8];           // external form of 1 (= 2^256 mod p), repacked; constant-folded
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = C_R32W[i];
+    return f29_repack_from32(w); }
+SMW_DEV F29 raw_u64(uint64_t x) { F29 a = f29_zero(); a.v[0] = (uint32_t)x & M29; a.v[1] = (uint32_t)(x >> 29) & M29; a.v[2] = (uint32_t)(x >> 58); return a; }
+// lane value after the k_out multiplication (< 2p) -> canonical external words
+SMW_DEV void emit_ext(const F29& x, uint32_t* dst) { uint32_t w[8]; f29_repack_to32(f29_canonicalize(x), w); store_ext(dst, w); }
+SMW_DEV void zero_lanes(const StateRef& S, int n) {
+#pragma unroll 1
+    for (int i = 0; i < n; i++) S.store(i, f29_zero());
+}
+
 // ------------------------------------------------------------------ batched permutation
-template <int T, bool SPARSE> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
-k_permute_batch(uint32_t* states, size_t batch, PoseidonDev P) {
+struct InStates { const uint32_t* st; SMW_DEV F29 operator()(uint32_t idx) const { return raw_ext(st + (size_t)idx * 8); } };
+template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
+k_permute_batch(uint32_t* states, size_t batch, Segs sg, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= batch) return;
     StateRef S = state_ref<T>(smem, blockDim.x, threadIdx.x);
     uint32_t* st = states + b * T * 8;
+    InStates in{st};
+    run_segs(S, P, sg, in);                      // [load lanes][permutation][lanes * 2^256 / 2^261]
 #pragma unroll 1
-    for (int i = 0; i < T; i++) { uint32_t w[8]; load_ext(st + i * 8, w); S.store(i, f29_from_ext(w)); }
-    permute<T, SPARSE>(S, P);
-#pragma unroll 1
-    for (int i = 0; i < T; i++) { uint32_t w[8]; f29_to_ext(S.load(i), w); store_ext(st + i * 8, w); }
+    for (int i = 0; i < T; i++) emit_ext(S.load(i), st + i * 8);
 }
 
 // ------------------------------------------------------------------ Merkle level (merkle/src/lib.rs:164-179)
 // thread q of column c: parents[c][q] = hash_with_ds_dynamic([arity, level, q + pos_offset, label_c], children[c][q*arity ..])
+struct InChildren {
+    const uint32_t* src; int cnt;
+    SMW_DEV F29 operator()(uint32_t idx) const {
+        if ((int)idx < cnt) return raw_ext(src + (size_t)idx * 8);
+        return (int)idx == cnt ? raw_one_ext() : f29_zero();
+    }
+};
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
 k_merkle_level(const uint32_t* __restrict__ children, size_t n_children, uint32_t* __restrict__ parents, size_t n_parents,
                int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
-               size_t child_col_stride, size_t parent_col_stride, PoseidonDev P) {
+               size_t child_col_stride, size_t parent_col_stride, Segs sg, int out_first, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n_parents) return;
     const int col = blockIdx.y;
     StateRef S = state_ref<T>(smem, blockDim.x, threadIdx.x);
-    Sponge<T, true> sp(S, P);
-    sp.absorb(f29_from_u64((uint64_t)arity)); sp.absorb(f29_from_u64(level));
-    sp.absorb(f29_from_u64(q + pos_offset)); sp.absorb(f29_from_u64(label0 + label_stride * col));
+    zero_lanes(S, T);
+    S.store(0, raw_u64((uint64_t)arity)); S.store(1, raw_u64(level)); S.store(2, raw_u64(q + pos_offset)); S.store(3, raw_u64(label0 + label_stride * col));
     size_t base = q * (size_t)arity;
-    int cnt = (int)((n_children - base < (size_t)arity) ? (n_children - base) : (size_t)arity);
-    const uint32_t* src = children + ((size_t)col * child_col_stride + base) * 8;
+    InChildren in;
+    in.cnt = (int)((n_children - base < (size_t)arity) ? (n_children - base) : (size_t)arity);
+    in.src = children + ((size_t)col * child_col_stride + base) * 8;
+    const int my_seg = 2 * ((4 + in.cnt + 1 + (T - 2)) / (T - 1)) - 1;     // the permutation after which this node's digest is state[0]
+    F29 out = f29_zero();
 #pragma unroll 1
-    for (int j = 0; j < cnt; j++) { uint32_t w[8]; load_ext(src + j * 8, w); sp.absorb(f29_from_ext(w)); }
-    uint32_t w[8]; f29_to_ext(sp.finish(), w);
-    store_ext(parents + ((size_t)col * parent_col_stride + q) * 8, w);
+    for (int s = 0; s < sg.n; s++) {
+        run_ops(S, P.tbl, P.prog, sg.first[s], sg.count[s], in);
+        if (s == my_seg) out = S.load(0);
+    }
+    S.store(0, out);
+    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    emit_ext(S.load(0), parents + ((size_t)col * parent_col_stride + q) * 8);
 }
 // pair leaves (merkle/src/lib.rs:382-400): leaf i = H(DS(arity, u32::MAX, i, label), [f_i, cp_{i / cp_div}])
+struct InPair {
+    const uint32_t* f; const uint32_t* cp;
+    SMW_DEV F29 operator()(uint32_t idx) const {
+        if (idx == 0) return raw_ext(f);
+        if (idx == 1) return cp ? raw_ext(cp) : f29_zero();
+        return idx == 2 ? raw_one_ext() : f29_zero();
+    }
+};
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
 k_pair_leaves(const uint32_t* __restrict__ f, const uint32_t* __restrict__ cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
-              uint32_t* __restrict__ out, size_t cp_div, PoseidonDev P) {
+              uint32_t* __restrict__ out, size_t cp_div, Segs sg, int out_first, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     StateRef S = state_ref<T>(smem, blockDim.x, threadIdx.x);
-    Sponge<T, true> sp(S, P);
-    sp.absorb(f29_from_u64((uint64_t)arity)); sp.absorb(f29_from_u64(0xffffffffull));
-    sp.absorb(f29_from_u64(i + pos_offset)); sp.absorb(f29_from_u64(label));
-    uint32_t w[8];
-    load_ext(f + i * 8, w); sp.absorb(f29_from_ext(w));
-    if (cp) { load_ext(cp + (i / cp_div) * 8, w); sp.absorb(f29_from_ext(w)); } else sp.absorb(f29_zero());
-    f29_to_ext(sp.finish(), w); store_ext(out + i * 8, w);
+    zero_lanes(S, T);
+    S.store(0, raw_u64((uint64_t)arity)); S.store(1, raw_u64(0xffffffffull)); S.store(2, raw_u64(i + pos_offset)); S.store(3, raw_u64(label));
+    InPair in{f + i * 8, cp ? cp + (i / cp_div) * 8 : nullptr};
+    run_segs(S, P, sg, in);                       // 4 + 2 + 1 absorbed lanes <= rate for every width: one permutation
+    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    emit_ext(S.load(0), out + i * 8);
 }
-// one hash with arbitrary input length (poseidon/src/lib.rs:288-312), single thread
+// one hash with arbitrary input length (poseidon/src/lib.rs:288-312), single thread: latency only
 template <int T> __global__ void k_hash_ds_single(const uint32_t* ds, int nds, const uint32_t* in, size_t n, uint32_t* out, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     StateRef S = state_ref<T>(smem, 1, 0);
-    Sponge<T, true> sp(S, P);
-    uint32_t w[8];
-    for (int i = 0; i < nds; i++) { load_ext(ds + i * 8, w); sp.absorb(f29_from_ext(w)); }
-    for (size_t i = 0; i < n; i++) { load_ext(in + i * 8, w); sp.absorb(f29_from_ext(w)); }
-    f29_to_ext(sp.finish(), w); store_ext(out, w);
+    zero_lanes(S, T);
+    int cursor = 0;
+    const size_t total = (size_t)nds + n + 1;
+#pragma unroll 1
+    for (size_t k = 0; k < total; k++) {
+        uint32_t w[8];
+        if (k < (size_t)nds) load_ext(ds + k * 8, w);
+        else if (k < (size_t)nds + n) load_ext(in + (k - nds) * 8, w);
+        else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) w[i] = C_R32W[i];
+        }
+        S.store(cursor, f29_add(S.load(cursor), f29_from_ext(w)));
+        if (++cursor == T - 1) { cursor = 0; run_perm(S, P); }
+    }
+    if (cursor != 0) run_perm(S, P);              // absorbing zeros only advances the cursor
+    uint32_t w[8]; f29_to_ext(S.load(0), w); store_ext(out, w);
 }
 
 template <typename K> static int set_smem(smw_ctx* c, K kernel, size_t bytes) {

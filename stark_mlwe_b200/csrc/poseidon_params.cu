@@ -154,23 +154,83 @@ __global__ void __launch_bounds__(256) k_derive_factor(DeriveArgs a) {
     lu_inplace(a.lu_post, n, a.status, &sh_inv);
 }
 
-static size_t tables_words(int t, int rp) { return (size_t)EL * ((size_t)t * t + 8 * t + rp + (size_t)rp * t + (size_t)rp * (t - 1) + (size_t)(t - 1) * (t - 1) + (size_t)t * t); }
+__global__ void k_store_consts(uint32_t* tbl, TableLayout L) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    gs(tbl, L.k_in, f29_const(C_KIN29)); gs(tbl, L.k_out, f29_const(C_KOUT29)); gs(tbl, L.k_rr, f29_const(C_RR29)); gs(tbl, L.k_one, f29_const(C_ONE29));
+}
+static const uint4 PAD_OP = make_op(0, 0, 0, 0, OPF_LOAD, 0, 0);
+
+int upload_programs(smw_ctx* c, smw_params* p) {
+    size_t n = p->h_prog.size();
+    if (n > p->d_prog_cap) {
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));          // kernels in flight still read the old copy
+        if (p->d_prog) cudaFree(p->d_prog);
+        p->d_prog_cap = n + 4096;
+        SMW_CUDA(c, cudaMalloc(&p->d_prog, p->d_prog_cap * sizeof(uint4)));
+    }
+    // the host vector only ever grows at the end, so in-flight kernels read unchanged ops
+    SMW_CUDA(c, cudaMemcpyAsync(p->d_prog, p->h_prog.data(), n * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));               // h_prog may be re-allocated by the next append
+    return SMW_OK;
+}
+// Cached segment lists.  n_ds >= 0: DS sponge with n_ds integer DS fields and up to max_inputs elements.
+// n_ds == -1: first[0] = "load lane i from external element i" ops, first[1] = "lane i -> external scale" ops (t each).
+// n_ds == -2: FRI hashed-leaf pre-image (max_inputs = lane_f * 256 + lane_s): [17 lane loads][permutation].
+int get_sponge_segs(smw_ctx* c, smw_params* p, int n_ds, int max_inputs, Segs* out) {
+    auto key = std::make_pair(n_ds, max_inputs);
+    auto it = p->sponge_cache.find(key);
+    if (it != p->sponge_cache.end()) { *out = it->second; return SMW_OK; }
+    const int t = p->t; const TableLayout& L = p->layout;
+    Segs sg; sg.n = 0;
+    if (n_ds >= 0) {
+        if (n_ds > t - 1 || (n_ds + max_inputs + 1 + (t - 2)) / (t - 1) > 4) return set_err(c, SMW_ERR_INVALID_ARG, "sponge program too long");
+        sg = build_sponge_program(p->h_prog, t, p->rp, n_ds, max_inputs, p->perm_first, p->perm_count);
+    } else if (n_ds == -1) {
+        sg.n = 2;
+        sg.first[0] = (int)p->h_prog.size(); sg.count[0] = t;
+        for (int i = 0; i < t; i++) p->h_prog.push_back(make_op(L.k_in, 0, 1, i, OPF_AEXT, 0, (uint32_t)i));
+        p->h_prog.push_back(PAD_OP);
+        sg.first[1] = (int)p->h_prog.size(); sg.count[1] = t;
+        for (int i = 0; i < t; i++) p->h_prog.push_back(make_op(L.k_out, i, 1, i, 0));
+        p->h_prog.push_back(PAD_OP);
+    } else {
+        const int lane_f = max_inputs / 256, lane_s = max_inputs % 256;
+        sg.n = 2;
+        sg.first[0] = (int)p->h_prog.size(); sg.count[0] = t;
+        for (int j = 0; j < t; j++) {
+            if (j == lane_f) p->h_prog.push_back(make_op(L.k_in, 0, 1, j, OPF_AEXT, 0, 0));
+            else if (j == lane_s) p->h_prog.push_back(make_op(L.k_in, 0, 1, j, OPF_AEXT, 0, 1));
+            else p->h_prog.push_back(make_op(L.k_rr, 0, 1, j, OPF_AEXT, 0, (uint32_t)(2 + j)));
+        }
+        p->h_prog.push_back(PAD_OP);
+        sg.first[1] = p->perm_first; sg.count[1] = p->perm_count;
+    }
+    int rc = upload_programs(c, p); if (rc) return rc;
+    p->sponge_cache[key] = sg;
+    *out = sg;
+    return SMW_OK;
+}
+
+static size_t tables_words(int t, int rp) { return (size_t)EL * table_layout(t, rp).total; }
 
 // allocate tables; returns pointer to the raw (un-factored) matrix slot
 static int alloc_tables(smw_ctx* c, smw_params* p, uint32_t** mds_internal) {
     int t = p->t, rp = p->rp;
+    p->layout = table_layout(t, rp);
+    const TableLayout& L = p->layout;
     SMW_CUDA(c, cudaMalloc(&p->d_tables, tables_words(t, rp) * 4));
     SMW_CUDA(c, cudaMemsetAsync(p->d_tables, 0, tables_words(t, rp) * 4, c->stream));
     uint32_t* q = p->d_tables;
-    p->lu_full = q; q += (size_t)EL * t * t;
-    p->rc_full = q; q += (size_t)EL * 8 * t;
-    p->rc_part = q; q += (size_t)EL * rp;
-    p->sp_row = q; q += (size_t)EL * rp * t;
-    p->sp_col = q; q += (size_t)EL * rp * (t - 1);
-    p->lu_post = q; q += (size_t)EL * (t - 1) * (t - 1);
-    *mds_internal = q;
+    p->lu_full = q + (size_t)EL * L.lu_full; p->rc_full = q + (size_t)EL * L.rc_full; p->rc_part = q + (size_t)EL * L.rc_part;
+    p->sp_row = q + (size_t)EL * L.sp_row; p->sp_col = q + (size_t)EL * L.sp_col; p->lu_post = q + (size_t)EL * L.lu_post;
+    *mds_internal = q + (size_t)EL * L.mds;
+    k_store_consts<<<1, 32, 0, c->stream>>>(p->d_tables, L); c->launches++;
     SMW_CUDA(c, cudaMalloc(&p->d_ext, ((size_t)t * t + 8 * t + rp) * 32));
-    return SMW_OK;
+    // the permutation programs (indices only; the tables they point into are filled below)
+    p->h_prog.clear();
+    p->perm_first = 0; build_perm_program(p->h_prog, t, rp, true); p->perm_count = (int)p->h_prog.size(); p->h_prog.push_back(PAD_OP);
+    p->dense_first = (int)p->h_prog.size(); build_perm_program(p->h_prog, t, rp, false); p->dense_count = (int)p->h_prog.size() - p->dense_first; p->h_prog.push_back(PAD_OP);
+    return upload_programs(c, p);
 }
 static int finish_params(smw_ctx* c, smw_params* p, uint32_t* mds_internal) {
     int t = p->t, rp = p->rp, n = t - 1;

@@ -12,6 +12,9 @@
 
 namespace smw {
 struct PoseidonDev;
+// element indices (EL-word elements) of the tables inside smw_params::d_tables
+struct TableLayout { uint32_t lu_full, rc_full, rc_part, sp_row, sp_col, lu_post, mds, k_in, k_out, k_rr, k_one, total; };
+struct Segs { int n; int first[8]; int count[8]; };   // (first, count) ranges of the op array, run in order
 }
 
 struct smw_params {
@@ -21,6 +24,11 @@ struct smw_params {
     uint32_t* d_ext = nullptr;        // external-form copies (mds, rc_full, rc_partial) for export
     // device views (pointers into d_tables)
     const uint32_t *lu_full = nullptr, *rc_full = nullptr, *rc_part = nullptr, *sp_row = nullptr, *sp_col = nullptr, *lu_post = nullptr;
+    smw::TableLayout layout{};
+    // row-operation programs run by the interpreter in poseidon.cuh (built on the host by poseidon_prog.cu)
+    std::vector<uint4> h_prog; uint4* d_prog = nullptr; size_t d_prog_cap = 0;
+    int perm_first = 0, perm_count = 0, dense_first = 0, dense_count = 0;
+    std::map<std::pair<int, int>, smw::Segs> sponge_cache;     // (n_ds, max_inputs) -> segments
     bool owned_by_ctx = false;
 };
 
@@ -94,6 +102,13 @@ struct LaunchScope {
 int set_err(smw_ctx* c, int code, const char* what);
 int cuda_err(smw_ctx* c, cudaError_t e, const char* what);
 #define SMW_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return smw::cuda_err((ctx), e__, #call); } while (0)
+
+// programs (poseidon_prog.cu)
+TableLayout table_layout(int t, int rp);
+void build_perm_program(std::vector<uint4>& ops, int t, int rp, bool sparse);
+Segs build_sponge_program(std::vector<uint4>& ops, int t, int rp, int n_ds, int max_inputs, int perm_first, int perm_count);
+int upload_programs(smw_ctx* c, smw_params* p);                                   // h_prog -> d_prog (re-allocates when it grew)
+int get_sponge_segs(smw_ctx* c, smw_params* p, int n_ds, int max_inputs, Segs* out); // cached per parameter set
 
 // launchers (poseidon_kernels.cu)
 int launch_derive_params(smw_ctx* c, smw_params* p, const unsigned char* seed, int seed_len);            // BLAKE3 -> tables

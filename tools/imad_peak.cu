@@ -4,12 +4,13 @@
 // The best 32x32->64 multiply-accumulate rate measured here is the denominator of every
 // "fraction of the integer-multiply roofline" figure in bench.py / DESIGN.md.
 #include <cstdio>
+#include <cstdlib>
 #include <cstdint>
 #include <cuda_runtime.h>
-#define ITERS 4096
+static int ITERS = 4096;   // argv[1] overrides (longer runs show the sustained clock)
 #define CHK(x) do{cudaError_t e=(x); if(e!=cudaSuccess){printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); return 1;}}while(0)
 
-template<int MODE> __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed, long long* cyc) {
+template<int MODE> __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed, long long* cyc, int ITERS) {
   uint32_t a[8], b = seed ^ threadIdx.x, c = seed * 3 + threadIdx.x;
   #pragma unroll
   for (int i = 0; i < 8; i++) a[i] = seed + i * 7 + threadIdx.x;
@@ -127,9 +128,9 @@ template<int MODE> int run(const char* name, int instr_per_iter, int mul_per_ite
   uint32_t* out; long long* cyc;
   CHK(cudaMalloc(&out, (size_t)grid * block * 4)); CHK(cudaMalloc(&cyc, grid * 8));
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-  k<MODE><<<grid, block>>>(out, 12345u, cyc); CHK(cudaDeviceSynchronize());
+  k<MODE><<<grid, block>>>(out, 12345u, cyc, ITERS); CHK(cudaDeviceSynchronize());
   CHK(cudaEventRecord(e0));
-  k<MODE><<<grid, block>>>(out, 12345u, cyc);
+  k<MODE><<<grid, block>>>(out, 12345u, cyc, ITERS);
   CHK(cudaEventRecord(e1)); CHK(cudaDeviceSynchronize());
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   long long* h = (long long*)malloc(grid * 8); cudaMemcpy(h, cyc, grid * 8, cudaMemcpyDeviceToHost);
@@ -141,7 +142,8 @@ template<int MODE> int run(const char* name, int instr_per_iter, int mul_per_ite
          name, ctas_per_sm, winstr_per_clk_sm, winstr_per_clk_sm * 32, total_mul / (ms * 1e-3), ms, avg / (ms * 1e-3) / 1e6);
   cudaFree(out); cudaFree(cyc); free(h); return 0;
 }
-int main() {
+int main(int argc, char** argv) {
+  if (argc > 1) ITERS = atoi(argv[1]);
   cudaDeviceProp p; CHK(cudaGetDeviceProperties(&p, 0));
   int nsm = p.multiProcessorCount; printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_khz\": %d}\n", p.name, nsm, p.clockRate);
   for (int c = 1; c <= 8; c *= 2) {
