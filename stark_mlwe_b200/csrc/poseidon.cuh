@@ -105,11 +105,19 @@ SMW_DEV void store_ext(uint32_t* p, const uint32_t w[8]) {
 // "no external inputs" functor for programs without OPF_AEXT operations
 struct NoInput { SMW_DEV F29 operator()(uint32_t) const { return f29_zero(); } };
 
-// The interpreter.  One copy per kernel (noinline: the sponges call it once per segment list), a few hundred
-// instructions; all warps of the SM loop over the same code.
-template <class In>
-__device__ __noinline__ void run_ops(StateRef S, const uint32_t* __restrict__ tbl, const uint4* __restrict__ prog, int first, int count, In in) {
+// The interpreter.  One copy per kernel (noinline: the sponges call it once per segment list), about a thousand
+// instructions; all warps of the SM loop over the same code.  The state lives in the CTA's dynamic shared memory and is
+// re-derived from `smem` here (not passed as pointers) so that the compiler keeps LDS/STS addressing.
+//   * the term loop is unrolled by two with ping-pong operand registers: the next term's operands are in flight during
+//     the current term's 81 multiplies and no register moves are needed;
+//   * the next operation's descriptor and its first table operand are fetched one operation ahead (table loads mostly
+//     miss the small L1 left beside 207 KB of shared memory, and go to L2).
+template <int T, class In>
+__device__ __noinline__ void run_ops(int nt, const uint32_t* __restrict__ tbl, const uint4* __restrict__ prog, int first, int count, In in) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const StateRef S = state_ref<T>(smem, nt, threadIdx.x);
     uint4 d = __ldg(prog + first);
+    F29 bpre = ((d.y >> 24) & (OPF_BSTATE | OPF_LOAD | OPF_SQR)) ? f29_zero() : tbl_load(tbl, d.x);
 #pragma unroll 1
     for (int k = 0; k < count; k++) {
         const uint4 dn = __ldg(prog + first + k + 1);        // every program is followed by one padding op
@@ -123,40 +131,45 @@ __device__ __noinline__ void run_ops(StateRef S, const uint32_t* __restrict__ tb
             if (fl & OPF_SQR) {
                 acc_sqr(A, S.load(j0));
             } else {
-                F29 a = (fl & OPF_AEXT) ? in(d.w) : S.load(j0);
-                F29 b = (fl & OPF_BSTATE) ? S.load((int)d.x) : tbl_load(tbl, d.x);
-                int c = 0;
+                F29 a0 = (fl & OPF_AEXT) ? in(d.w) : S.load(j0);
+                F29 b0 = (fl & OPF_BSTATE) ? S.load((int)d.x) : bpre;
+                F29 a1 = a0, b1 = b0;
+                int c = 0, j = 1;
 #pragma unroll 1
-                for (int j = 1; j <= n; j++) {
-                    F29 an = a, bn = b;
-                    if (j < n) { an = S.load(j0 + j); bn = tbl_load(tbl, d.x + j); }   // next term's operands, in flight during this term's 81 multiplies
+                while (true) {
+                    if (j < n) { a1 = S.load(j0 + j); b1 = tbl_load(tbl, d.x + j); }
                     if (c == 6) { acc_normalize(A); c = 0; }
-                    acc_mac(A, a, b); c++;
-                    a = an; b = bn;
+                    acc_mac(A, a0, b0); c++;
+                    if (j >= n) break;
+                    j++;
+                    if (j < n) { a0 = S.load(j0 + j); b0 = tbl_load(tbl, d.x + j); }
+                    if (c == 6) { acc_normalize(A); c = 0; }
+                    acc_mac(A, a1, b1); c++;
+                    if (j >= n) break;
+                    j++;
                 }
             }
-            if (fl & OPF_ADDSELF) {
-                F29 s = S.load(dst);
+            if (!((dn.y >> 24) & (OPF_BSTATE | OPF_LOAD | OPF_SQR))) bpre = tbl_load(tbl, dn.x);   // in flight during the reduction
+            F29 s = f29_zero();                                   // one copy of the reduction for both cases
+            if (fl & OPF_ADDSELF) s = S.load(dst);
 #pragma unroll
-                for (int i = 0; i < 8; i++) A.c[9 + i] += s.v[i];
-                x = acc_reduce(A);
-                x.v[8] += s.v[8];
-            } else {
-                x = acc_reduce(A);
-            }
+            for (int i = 0; i < 8; i++) A.c[9 + i] += s.v[i];
+            x = acc_reduce(A);
+            x.v[8] += s.v[8];
         }
         if (fl & OPF_ADDRC) x = f29_add(x, tbl_load(tbl, d.z));
         S.store(dst, x);
         d = dn;
     }
 }
-template <class In>
-SMW_DEV void run_segs(const StateRef& S, const PoseidonDev& P, const Segs& sg, const In& in) {
+template <int T, class In>
+SMW_DEV void run_segs(int nt, const PoseidonDev& P, const Segs& sg, const In& in) {
 #pragma unroll 1
-    for (int s = 0; s < sg.n; s++) run_ops(S, P.tbl, P.prog, sg.first[s], sg.count[s], in);
+    for (int s = 0; s < sg.n; s++) run_ops<T>(nt, P.tbl, P.prog, sg.first[s], sg.count[s], in);
 }
-SMW_DEV void run_perm(const StateRef& S, const PoseidonDev& P, bool sparse = true) {
-    run_ops(S, P.tbl, P.prog, sparse ? P.perm_first : P.dense_first, sparse ? P.perm_count : P.dense_count, NoInput());
+template <int T>
+SMW_DEV void run_perm(int nt, const PoseidonDev& P, bool sparse = true) {
+    run_ops<T>(nt, P.tbl, P.prog, sparse ? P.perm_first : P.dense_first, sparse ? P.perm_count : P.dense_count, NoInput());
 }
 
 } // namespace smw

@@ -85,7 +85,7 @@ __global__ void k_hash_legacy_single(const uint32_t* in, size_t n, const uint32_
     for (size_t off = 0; off < n; off += 16) {
         size_t c = n - off < 16 ? n - off : 16;
         for (size_t i = 0; i < c; i++) { load_ext(in + (off + i) * 8, w); S.store((int)i, f29_add(S.load((int)i), f29_from_ext(w))); }
-        run_perm(S, P);
+        run_perm<17>(S.nt, P);
     }
     f29_to_ext(S.load(0), w); store_ext(out, w);
 }
@@ -95,7 +95,7 @@ __global__ void k_hash_legacy_single(const uint32_t* in, size_t n, const uint32_
 //   [fresh: state = 0, lane 16 = INIT tag (immA[0])] ; absorb immA[fresh..nA) ; absorb extB[0..nB) ; absorb immC[0..nC) ; [final permute]
 // Immediates are 256-bit little-endian integers (tags, 31-byte words, small integers), reduced mod p here.
 SMW_DEV void tr_absorb(const StateRef& S, const PoseidonDev& P, int& pos, const F29& x) {
-    if (pos == 16) { run_perm(S, P); pos = 0; }
+    if (pos == 16) { run_perm<17>(S.nt, P); pos = 0; }
     S.store(pos, f29_add(S.load(pos), x)); pos++;
 }
 __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint32_t* immA, int nA, const uint32_t* extB, size_t nB,
@@ -114,7 +114,7 @@ __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint
     for (int i = a0; i < nA; i++) { load_ext(immA + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
     for (size_t i = 0; i < nB; i++) { load_ext(extB + i * 8, w); tr_absorb(S, P, pos, f29_from_ext(w)); }
     for (int i = 0; i < nC; i++) { load_ext(immC + i * 8, w); tr_absorb(S, P, pos, f29_from_le256(w)); }
-    if (final_permute) run_perm(S, P);
+    if (final_permute) run_perm<17>(S.nt, P);
     if (state) for (int i = 0; i < 17; i++) { f29_to_ext(S.load(i), w); store_ext(state + i * 8, w); }
     if (out) { f29_to_ext(S.load(0), w); store_ext(out, w); }
 }
@@ -138,8 +138,8 @@ k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __res
     if (i >= n) return;
     StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
     InFriLeaf in{f + i * 8, s ? s + (i / s_div) * 8 : nullptr, tmpl_le256};
-    run_segs(S, P, sg, in);                       // [17 lane loads][permutation]
-    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    run_segs<17>(blockDim.x, P, sg, in);         // [17 lane loads][permutation]
+    run_ops<17>(blockDim.x, P.tbl, P.prog, out_first, 1, in);
     emit_ext(S.load(0), out + i * 8);
 }
 
@@ -153,7 +153,7 @@ __global__ void k_fri_sample_z(const uint32_t* tmpl_le256, const uint64_t* level
     StateRef S = state_ref<17>(smem, blockDim.x, threadIdx.x);
     uint32_t w[8];
     for (int j = 0; j < 17; j++) { load_ext(tmpl_le256 + ((size_t)l * 17 + j) * 8, w); S.store(j, f29_from_le256(w)); }
-    run_perm(S, P);
+    run_perm<17>(S.nt, P);
     // canonical integer of the digest: x*2^261 -> x
     F29 one_int = f29_zero(); one_int.v[0] = 1;
     F29 d = f29_canonicalize(f29_mul(S.load(0), one_int));

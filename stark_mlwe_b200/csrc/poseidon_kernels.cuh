@@ -62,7 +62,7 @@ k_permute_batch(uint32_t* states, size_t batch, Segs sg, PoseidonDev P) {
     StateRef S = state_ref<T>(smem, blockDim.x, threadIdx.x);
     uint32_t* st = states + b * T * 8;
     InStates in{st};
-    run_segs(S, P, sg, in);                      // [load lanes][permutation][lanes * 2^256 / 2^261]
+    run_segs<T>(blockDim.x, P, sg, in);         // [load lanes][permutation][lanes * 2^256 / 2^261]
 #pragma unroll 1
     for (int i = 0; i < T; i++) emit_ext(S.load(i), st + i * 8);
 }
@@ -95,11 +95,11 @@ k_merkle_level(const uint32_t* __restrict__ children, size_t n_children, uint32_
     F29 out = f29_zero();
 #pragma unroll 1
     for (int s = 0; s < sg.n; s++) {
-        run_ops(S, P.tbl, P.prog, sg.first[s], sg.count[s], in);
+        run_ops<T>(blockDim.x, P.tbl, P.prog, sg.first[s], sg.count[s], in);
         if (s == my_seg) out = S.load(0);
     }
     S.store(0, out);
-    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    run_ops<T>(blockDim.x, P.tbl, P.prog, out_first, 1, in);
     emit_ext(S.load(0), parents + ((size_t)col * parent_col_stride + q) * 8);
 }
 // pair leaves (merkle/src/lib.rs:382-400): leaf i = H(DS(arity, u32::MAX, i, label), [f_i, cp_{i / cp_div}])
@@ -121,8 +121,8 @@ k_pair_leaves(const uint32_t* __restrict__ f, const uint32_t* __restrict__ cp, s
     zero_lanes(S, T);
     S.store(0, raw_u64((uint64_t)arity)); S.store(1, raw_u64(0xffffffffull)); S.store(2, raw_u64(i + pos_offset)); S.store(3, raw_u64(label));
     InPair in{f + i * 8, cp ? cp + (i / cp_div) * 8 : nullptr};
-    run_segs(S, P, sg, in);                       // 4 + 2 + 1 absorbed lanes <= rate for every width: one permutation
-    run_ops(S, P.tbl, P.prog, out_first, 1, in);
+    run_segs<T>(blockDim.x, P, sg, in);          // 4 + 2 + 1 absorbed lanes <= rate for every width: one permutation
+    run_ops<T>(blockDim.x, P.tbl, P.prog, out_first, 1, in);
     emit_ext(S.load(0), out + i * 8);
 }
 // one hash with arbitrary input length (poseidon/src/lib.rs:288-312), single thread: latency only
@@ -143,9 +143,9 @@ template <int T> __global__ void k_hash_ds_single(const uint32_t* ds, int nds, c
             for (int i = 0; i < 8; i++) w[i] = C_R32W[i];
         }
         S.store(cursor, f29_add(S.load(cursor), f29_from_ext(w)));
-        if (++cursor == T - 1) { cursor = 0; run_perm(S, P); }
+        if (++cursor == T - 1) { cursor = 0; run_perm<T>(1, P); }
     }
-    if (cursor != 0) run_perm(S, P);              // absorbing zeros only advances the cursor
+    if (cursor != 0) run_perm<T>(1, P);              // absorbing zeros only advances the cursor
     uint32_t w[8]; f29_to_ext(S.load(0), w); store_ext(out, w);
 }
 
