@@ -59,8 +59,9 @@ def gen_columns(seed, col0, n_cols, n_rows, out=None):
 
 
 def executed_mac_per_perm(t, rp):
-    """32x32+64 multiply-accumulates the production permutation executes (poseidon.cuh: lazy radix-2^29 dot products,
-    LU in-place mat-vec, sparse partial rounds): mac = 81, square = 45, Montgomery reduction = 45."""
+    """32x32+64 multiply-accumulates the production permutation executes (poseidon_prog.cu: lazy radix-2^29 dot products,
+    LU in-place mat-vec, sparse partial rounds): mac = 81, square = 45, Montgomery reduction = 45.  (ncu counts 504 k
+    IMAD.WIDE per permutation in k_merkle_level<17>, profiles/r01d_*: this formula gives 502.5 k.)"""
     mac, sqr, red = 81, 45, 45
     sbox = 2 * sqr + mac + 3 * red
     full = t * sbox + t * t * mac + (2 * t - 1) * red
@@ -181,7 +182,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from stark_mlwe_b200 import api as smw
+    from stark_mlwe_b200 import api as smw, shard
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: the product has no CPU path"
     torch.cuda.set_device(local)
     if world > 1:
@@ -192,20 +193,18 @@ def main():
     n, nc, lb = 1 << args.log_n, args.cols, args.log_blowup
     N = n << lb
     committed_per_rank = nc * N
-    col0 = rank * nc
+    col0 = shard.column_range(rank, world, world * nc)[0]
 
     # ---- inputs: pinned host buffer (e2e leg) and a resident device copy (value leg)
     host = torch.empty((nc, n, 4), dtype=torch.int64).pin_memory()
     gen_columns(SEED, col0, nc, n, out=host.numpy().view(np.uint64))
     dev = host.to("cuda", non_blocking=False)
     shift = ctx.from_canonical(np.array([[SHIFT, 0, 0, 0]], dtype=np.uint64))[0]
-    roots_all = torch.zeros((world, nc, 4), dtype=torch.int64, device="cuda")
 
     def step(src):
-        roots = smw.lde_commit(ctx, src, lb, shift, label0=col0)          # (nc, 4) uint64 on the host
+        roots = smw.lde_commit(ctx, src, lb, shift, label0=col0)          # (nc, 4) uint64 on the host; tree_label = global column index
         if world > 1:
-            mine = torch.from_numpy(roots.view(np.int64)).to("cuda")
-            dist.all_gather_into_tensor(roots_all.view(-1), mine.view(-1))
+            shard.gather_roots(roots, world * nc, device="cuda")            # the only collective: 32 B x columns over NCCL
         return roots
 
     def barrier():
@@ -272,7 +271,8 @@ def main():
             "achieved": alg_mac / ml_s / 1e12, "peak": mac_peak / 1e12, "unit": "T mac32/s (32x32+64 multiply-accumulates; algorithmic = dense reference count)",
             "frac": alg_mac / ml_s / mac_peak,
             "executed": {"achieved": exe_mac / ml_s / 1e12, "frac": exe_mac / ml_s / mac_peak, "mac_per_permutation": executed_mac_per_perm(17, 64)},
-            "peak_source": "measured live: IMAD.WIDE.U32, 8 chains x 2048 threads/SM (smw_diag_mac_rate), %.2f warp-instr/clk/SM" % winstr,
+            "peak_source": "measured live in this run: accumulating IMAD.WIDE.U32 (32x32+64->64), 16 chains x 512 threads/SM, ~40 ms per repetition (smw_diag_mac_rate; SASS-verified loop), %.2f warp-instr/clk/SM" % winstr,
+            "frac_executed": exe_mac / ml_s / mac_peak,
             "traffic": None,
             "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps, "permutations_per_step": perms,
             "permutations_per_s": perms / ml_s,

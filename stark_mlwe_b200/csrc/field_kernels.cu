@@ -137,47 +137,59 @@ int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, cons
 }
 
 
-// ---- integer-pipe micro-benchmark: IMAD.WIDE.U32 issue rate, 8 independent chains per thread, 8 x 256 threads per SM.
-// Its result is the denominator of the "fraction of the integer-multiply roofline" figures (tools/imad_peak.cu is the
-// stand-alone, wider version of the same measurement).
-__global__ void __launch_bounds__(256) k_diag_mac(uint32_t* out, uint32_t seed, long long* cyc, int iters) {
-    uint32_t b = seed ^ threadIdx.x, c2 = seed * 3 + threadIdx.x;
-    uint64_t w[8];
+// ---- integer-pipe micro-benchmark: the issue rate of the accumulating IMAD.WIDE.U32 (32x32+64 -> 64), 16 independent
+// chains per thread, 8 x 256 threads per SM.  Its result is the denominator of the "fraction of the integer-multiply
+// roofline" figures.  Four of the operands change every iteration (a LOP3 each, on the other pipe) so that ptxas can
+// neither hoist the products out of the loop nor split the instruction into IMAD.WIDE (RZ) + IADD3 pairs — round 1a's
+// version had loop-invariant operands and measured 64-bit ADDS instead (tools/imad_peak2.cu is the stand-alone, wider
+// version of this measurement; tools/check_imad_sass.py prints the SASS mix of each timed loop).
+__global__ void __launch_bounds__(256) k_diag_mac(uint32_t* out, const uint32_t* in, long long* cyc, int iters) {
+    uint64_t w[16]; uint32_t a[4], b[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) w[i] = (uint64_t)(seed + i * 7 + threadIdx.x) * 0x9E3779B97F4A7C15ull;
+    for (int i = 0; i < 16; i++) w[i] = reinterpret_cast<const uint64_t*>(in)[(threadIdx.x + 31 * i) & 511];
+#pragma unroll
+    for (int i = 0; i < 4; i++) a[i] = in[(threadIdx.x + 40 + i) & 1023] & 0x1fffffffu;
+#pragma unroll
+    for (int i = 0; i < 8; i++) b[i] = in[(threadIdx.x + 80 + i) & 1023] & 0x1fffffffu;
     long long t0 = clock64();
 #pragma unroll 1
     for (int it = 0; it < iters; it++) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(w[i]) : "r"(b), "r"(c2));
+        for (int i = 0; i < 16; i++) w[i] += (uint64_t)a[i & 3] * b[i >> 2 | (i & 3) << 1];
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i] ^= it;
     }
     long long t1 = clock64();
     uint32_t r = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) r ^= (uint32_t)w[i] ^ (uint32_t)(w[i] >> 32);
+    for (int i = 0; i < 16; i++) r ^= (uint32_t)w[i] ^ (uint32_t)(w[i] >> 32);
     out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) {
     cudaDeviceProp prop; SMW_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
-    const int nsm = prop.multiProcessorCount, per_sm = 8, block = 256, iters = 8192, grid = nsm * per_sm;
-    uint32_t* out; long long* cyc;
-    SMW_CUDA(c, cudaMalloc(&out, (size_t)grid * block * 4)); SMW_CUDA(c, cudaMalloc(&cyc, (size_t)grid * 8));
+    // 2 CTAs x 256 threads per SM (all resident, so the in-kernel clock and the event clock agree); ~40 ms per repetition
+    // so that the clocks settle under this load
+    const int nsm = prop.multiProcessorCount, per_sm = 2, block = 256, iters = 1 << 19, grid = nsm * per_sm;
+    uint32_t *out, *in; long long* cyc;
+    SMW_CUDA(c, cudaMalloc(&out, (size_t)grid * block * 4)); SMW_CUDA(c, cudaMalloc(&cyc, (size_t)grid * 8)); SMW_CUDA(c, cudaMalloc(&in, 4096 * 4));
+    std::vector<uint32_t> hin(4096); for (int i = 0; i < 4096; i++) hin[i] = 0x9E3779B9u * (uint32_t)(i + 1) ^ ((uint32_t)i << 7);
+    SMW_CUDA(c, cudaMemcpyAsync(in, hin.data(), 4096 * 4, cudaMemcpyHostToDevice, c->stream));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     double best = 0, best_w = 0;
     std::vector<long long> h(grid);
     for (int rep = 0; rep < 4; rep++) {
         cudaEventRecord(e0, c->stream);
-        k_diag_mac<<<grid, block, 0, c->stream>>>(out, 12345u + rep, cyc, iters); c->launches++;
+        k_diag_mac<<<grid, block, 0, c->stream>>>(out, in, cyc, iters); c->launches++;
         cudaEventRecord(e1, c->stream);
         SMW_CUDA(c, cudaStreamSynchronize(c->stream));
         float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
         cudaMemcpy(h.data(), cyc, (size_t)grid * 8, cudaMemcpyDeviceToHost);
         double avg = 0; for (int i = 0; i < grid; i++) avg += (double)h[i]; avg /= grid;
-        double rate = (double)grid * block * (double)iters * 8 / (ms * 1e-3);
-        if (rep > 0 && rate > best) { best = rate; best_w = per_sm * (block / 32.0) * (double)iters * 8 / avg; }
+        double rate = (double)grid * block * (double)iters * 16 / (ms * 1e-3);
+        if (rep > 0 && rate > best) { best = rate; best_w = per_sm * (block / 32.0) * (double)iters * 16 / avg; }
     }
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out); cudaFree(cyc);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out); cudaFree(cyc); cudaFree(in);
     if (mac_per_s) *mac_per_s = best;
     if (winstr) *winstr = best_w;
     return SMW_OK;

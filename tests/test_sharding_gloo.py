@@ -1,0 +1,65 @@
+"""World-size-2 (and 3) CPU test of the multi-GPU host logic (stark_mlwe_b200/shard.py) over gloo: column partition, global
+tree labels, and the root all-gather.  Each rank "commits" its columns with the CPU oracle standing in for the device
+(test infrastructure); the gathered roots must equal the single-process result in column order."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from stark_mlwe_b200 import shard
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, n_cols, log_n, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import oracle as O
+    from bench import gen_columns, SEED, SHIFT
+    O.lib(); O.set_threads(1)
+    c0, c1 = shard.column_range(rank, world, n_cols)
+    cols = gen_columns(SEED, c0, c1 - c0, 1 << log_n)
+    shift = O.to_mont([SHIFT])[0]
+    mine = np.zeros((c1 - c0, 4), dtype=np.uint64)
+    for c in range(c1 - c0):
+        mine[c] = O.commitment_commit(O.lde(cols[c], 2, shift), c0 + c).root()      # tree_label = global column index
+    allr = shard.gather_roots(mine, n_cols)
+    if rank == 0:
+        q.put(allr)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_cols", [(2, 4), (3, 5)])
+def test_column_sharded_commit_matches_single_process(O, world, n_cols):
+    from bench import gen_columns, SEED, SHIFT
+    log_n = 4
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_cols, log_n, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    cols = gen_columns(SEED, 0, n_cols, 1 << log_n)
+    shift = O.to_mont([SHIFT])[0]
+    want = np.stack([O.commitment_commit(O.lde(cols[c], 2, shift), c).root() for c in range(n_cols)])
+    assert np.array_equal(got, want)
+
+
+def test_ranges():
+    assert [shard.column_range(r, 4, 10) for r in range(4)] == [(0, 3), (3, 6), (6, 8), (8, 10)]
+    assert [shard.column_range(r, 8, 256) for r in range(8)] == [(32 * r, 32 * r + 32) for r in range(8)]
+    assert [shard.column_range(r, 3, 2) for r in range(3)] == [(0, 1), (1, 2), (2, 2)]
+    # a 2^22-leaf layer, fold 2 x arity 2 -> aligned to 4; ranges tile the layer exactly
+    rs = [shard.leaf_range(r, 8, 1 << 22, 4) for r in range(8)]
+    assert rs[0][0] == 0 and rs[-1][1] == 1 << 22 and all(a[1] == b[0] for a, b in zip(rs, rs[1:])) and all(a % 4 == 0 for a, _ in rs)
+    assert shard.leaf_range(5, 8, 8, 4) == (8, 8)       # fewer blocks than ranks: empty tail ranges
