@@ -60,14 +60,15 @@ def gen_columns(seed, col0, n_cols, n_rows, out=None):
 
 def executed_mac_per_perm(t, rp):
     """32x32+64 multiply-accumulates the production permutation executes (poseidon_prog.cu: lazy radix-2^29 dot products,
-    LU in-place mat-vec, sparse partial rounds): mac = 81, square = 45, Montgomery reduction = 45.  (ncu counts 504 k
-    IMAD.WIDE per permutation in k_merkle_level<17>, profiles/r01d_*: this formula gives 502.5 k.)"""
+    LU in-place mat-vec, sparse partial rounds): mac = 81, square = 45, Montgomery reduction = 45.  (t = 17: 482.1 k; ncu's IMAD.WIDE count per
+    permutation in k_merkle_level<17> is within 1 % of it, profiles/r01g_*.)"""
     mac, sqr, red = 81, 45, 45
     sbox = 2 * sqr + mac + 3 * red
     full = t * sbox + t * t * mac + (2 * t - 1) * red
-    part = sbox + t * mac + (t - 1) * mac + t * red
+    # two partial rounds per block: 2 S-boxes, a t-term and a (t+1)-term row product, one 2-term update per lane
+    block = 2 * sbox + (2 * t + 1) * mac + 2 * red + (t - 1) * (2 * mac + red)
     post = (t - 1) * (t - 1) * mac + (2 * (t - 1) - 1) * red
-    return 8 * full + rp * part + post
+    return 8 * full + (rp // 2) * block + post
 
 
 class ClockSampler:

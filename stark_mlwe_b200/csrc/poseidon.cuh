@@ -44,8 +44,9 @@ enum : uint32_t {
                         // conversion constant), single term
 };
 // Op = uint4 { x: B offset (table element index, or state lane), y: j0 | n << 8 | dst << 16 | flags << 24,
-//              z: table element index of the constant to add, w: source lane (LOAD) / input index (AEXT) }
+//              z: table element index of the constant to add, w: source lane (LOAD) / input index (AEXT) / A-lane stride (else) }
 __host__ __device__ inline uint4 make_op(uint32_t b_off, int j0, int n, int dst, uint32_t flags, uint32_t rc_off = 0, uint32_t aux = 0) {
+    if (!(flags & (OPF_LOAD | OPF_AEXT)) && aux == 0) aux = 1;          // A-lane stride defaults to 1
     uint4 o; o.x = b_off; o.y = (uint32_t)j0 | ((uint32_t)n << 8) | ((uint32_t)dst << 16) | (flags << 24); o.z = rc_off; o.w = aux; return o;
 }
 
@@ -70,10 +71,10 @@ SMW_DEV F29 tbl_load(const uint32_t* base, uint32_t idx) {
     return r;
 }
 
-// Per-thread state in shared memory: lane j = two uint4 (limbs 0-3, 4-7) + one word (limb 8); T + 1 lanes (lane T is scratch)
+// Per-thread state in shared memory: lane j = two uint4 (limbs 0-3, 4-7) + one word (limb 8); T + 2 lanes (lanes T, T + 1 are scratch)
 struct StateRef {
-    uint4* q;       // [T+1][2][NT]
-    uint32_t* w;    // [T+1][NT]
+    uint4* q;       // [T+2][2][NT]
+    uint32_t* w;    // [T+2][NT]
     int nt, tid;
     SMW_DEV F29 load(int j) const {
         uint4 a = q[(2 * j) * nt + tid], b = q[(2 * j + 1) * nt + tid];
@@ -88,9 +89,9 @@ struct StateRef {
     }
 };
 template <int T> SMW_DEV StateRef state_ref(unsigned char* smem, int nt, int tid) {
-    StateRef S; S.q = reinterpret_cast<uint4*>(smem); S.w = reinterpret_cast<uint32_t*>(smem + (size_t)(T + 1) * 2 * nt * 16); S.nt = nt; S.tid = tid; return S;
+    StateRef S; S.q = reinterpret_cast<uint4*>(smem); S.w = reinterpret_cast<uint32_t*>(smem + (size_t)(T + 2) * 2 * nt * 16); S.nt = nt; S.tid = tid; return S;
 }
-template <int T> __host__ __device__ constexpr size_t state_smem_bytes(int nt) { return (size_t)(T + 1) * nt * 36; }
+template <int T> __host__ __device__ constexpr size_t state_smem_bytes(int nt) { return (size_t)(T + 2) * nt * 36; }
 
 SMW_DEV void load_ext(const uint32_t* p, uint32_t w[8]) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
@@ -134,15 +135,16 @@ __device__ __noinline__ void run_ops(int nt, const uint32_t* __restrict__ tbl, c
                 F29 a0 = (fl & OPF_AEXT) ? in(d.w) : S.load(j0);
                 F29 b0 = (fl & OPF_BSTATE) ? S.load((int)d.x) : bpre;
                 F29 a1 = a0, b1 = b0;
+                const int st = (fl & OPF_AEXT) ? 1 : (int)d.w;              // A-lane stride (1 except the two-S-box lane updates)
                 int c = 0, j = 1;
 #pragma unroll 1
                 while (true) {
-                    if (j < n) { a1 = S.load(j0 + j); b1 = tbl_load(tbl, d.x + j); }
+                    if (j < n) { a1 = S.load(j0 + j * st); b1 = tbl_load(tbl, d.x + j); }
                     if (c == 6) { acc_normalize(A); c = 0; }
                     acc_mac(A, a0, b0); c++;
                     if (j >= n) break;
                     j++;
-                    if (j < n) { a0 = S.load(j0 + j); b0 = tbl_load(tbl, d.x + j); }
+                    if (j < n) { a0 = S.load(j0 + j * st); b0 = tbl_load(tbl, d.x + j); }
                     if (c == 6) { acc_normalize(A); c = 0; }
                     acc_mac(A, a1, b1); c++;
                     if (j >= n) break;

@@ -128,8 +128,21 @@ __global__ void __launch_bounds__(256) k_derive_factor(DeriveArgs a) {
     }
     __syncthreads();
     for (int k = 0; k < rp; k++) {
-        if (threadIdx.x == 0) gs(a.sp_row, (size_t)k * t, gl(a.mds, 0));
-        for (int j = threadIdx.x; j < n; j += blockDim.x) { gs(a.sp_row, (size_t)k * t + 1 + j, gl(a.vk, j)); gs(a.sp_col, (size_t)k * n + j, gl(a.wk, j)); }
+        // layout (TableLayout, poseidon_prog.cu): sp_row has t + 1 slots per round — even k: [M00, row_k[1..]], odd k:
+        // [G, row_k[1..], M00] with G = sum_i row_k[i] * col_{k-1}[i-1] (two partial rounds run as one block);
+        // sp_col interleaves the column vectors of rounds 2b and 2b + 1
+        const int tp = t + 1;
+        if (threadIdx.x == 0) gs(a.sp_row, (size_t)k * tp + ((k & 1) ? t : 0), gl(a.mds, 0));
+        for (int j = threadIdx.x; j < n; j += blockDim.x) {
+            gs(a.sp_row, (size_t)k * tp + 1 + j, gl(a.vk, j));
+            gs(a.sp_col, (size_t)(k >> 1) * 2 * n + 2 * j + (k & 1), gl(a.wk, j));
+        }
+        __syncthreads();
+        if ((k & 1) && threadIdx.x == 0) {
+            Acc acc; acc_zero(acc); int c = 0;
+            for (int j = 0; j < n; j++) { acc_mac(acc, gl(a.vk, j), gl(a.sp_col, (size_t)(k >> 1) * 2 * n + 2 * j)); if (++c == 6) { acc_normalize(acc); c = 0; } }
+            gs(a.sp_row, (size_t)k * tp, f29_canonicalize(acc_reduce(acc)));
+        }
         __syncthreads();
         // vk <- vk^T * Mh ; wk <- Mh^-1 * wk   (through tmp / vt)
         for (int j = threadIdx.x; j < n; j += blockDim.x) {

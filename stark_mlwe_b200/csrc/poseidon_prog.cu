@@ -14,7 +14,7 @@ TableLayout table_layout(int t, int rp) {
     L.lu_full = q; q += (uint32_t)t * t;
     L.rc_full = q; q += 8u * t;
     L.rc_part = q; q += (uint32_t)rp;
-    L.sp_row = q; q += (uint32_t)rp * t;
+    L.sp_row = q; q += (uint32_t)rp * (t + 1);
     L.sp_col = q; q += (uint32_t)rp * (t - 1);
     L.lu_post = q; q += (uint32_t)(t - 1) * (t - 1);
     L.mds = q; q += (uint32_t)t * t;
@@ -32,11 +32,11 @@ struct Builder {
         ops.push_back(make_op(0, TMP, 1, TMP, OPF_SQR));
         ops.push_back(make_op((uint32_t)TMP, lane, 1, lane, OPF_BSTATE));
     }
-    // x^5 of the value held in TMP, result in lane 0 (lane 0 doubles as scratch): the sparse partial rounds
-    void sbox_tmp_to_lane0() {
-        ops.push_back(make_op(0, TMP, 1, 0, OPF_SQR));
-        ops.push_back(make_op(0, 0, 1, 0, OPF_SQR));
-        ops.push_back(make_op(0u, TMP, 1, 0, OPF_BSTATE));
+    // x^5 of the value held in TMP, result in lane `out` (which doubles as scratch): the sparse partial rounds
+    void sbox_tmp_to(int out) {
+        ops.push_back(make_op(0, TMP, 1, out, OPF_SQR));
+        ops.push_back(make_op(0, out, 1, out, OPF_SQR));
+        ops.push_back(make_op((uint32_t)out, TMP, 1, out, OPF_BSTATE));
     }
     // lanes [off, off + n) <- (L*U) * lanes, in place, lu = n x n table at element index `lu`.
     // rc_of(lane) >= 0: table index of the constant added to that lane's final value (next round's ARK); lane `off`
@@ -55,7 +55,7 @@ struct Builder {
 
 // Appends the permutation program; lanes 0..t-1 in, lanes 0..t-1 out, lane t scratch.
 void build_perm_program(std::vector<uint4>& ops, int t, int rp, bool sparse) {
-    Builder B{ops, t, rp, table_layout(t, rp), t};
+    Builder B{ops, t, rp, table_layout(t, rp), t + 1};      // lane t = X (second S-box output of a partial-round block), lane t + 1 = TMP
     const TableLayout& L = B.L;
     auto rcf = [&](int r, int lane) { return (long)(L.rc_full + (uint32_t)r * t + lane); };
     auto rcp = [&](int k) { return (long)(L.rc_part + (uint32_t)k); };
@@ -76,12 +76,20 @@ void build_perm_program(std::vector<uint4>& ops, int t, int rp, bool sparse) {
         }
     }
     if (sparse) {
-        for (int k = 0; k < rp; k++) {
-            B.sbox_tmp_to_lane0();                                                    // lane 0 = x0 = (lane0 + c_k)^5
-            long next = (k + 1 < rp) ? rcp(k + 1) : rcf(4, 0);
-            ops.push_back(make_op(L.sp_row + (uint32_t)k * t, 0, t, B.TMP, OPF_ADDRC, (uint32_t)next));          // new lane 0 (+ next constant) -> TMP
-            for (int i = 1; i < t; i++)                                               // lane i += col_k[i-1] * x0
-                ops.push_back(make_op(L.sp_col + (uint32_t)k * (t - 1) + (i - 1), 0, 1, i, OPF_ADDSELF));
+        // Two partial rounds per block (rp is even for every supported width).  With x = S-box output of round k and
+        // y = that of round k + 1, the lanes 1.. are only updated once per block:
+        //   TMP  = row_k . (x, u_1 ..)                 + c_{k+1}
+        //   TMP' = (G, row_{k+1}[1..], M00) . (x, u_1 .., y) + c_{k+2}      G = sum_i row_{k+1}[i] col_k[i-1]
+        //   u_i += col_k[i-1] x + col_{k+1}[i-1] y     (one 2-term operation per lane instead of two 1-term ones)
+        const int X = t;
+        for (int k = 0; k < rp; k += 2) {
+            B.sbox_tmp_to(0);                                                          // lane 0 = x
+            ops.push_back(make_op(L.sp_row + (uint32_t)k * (t + 1), 0, t, B.TMP, OPF_ADDRC, (uint32_t)rcp(k + 1), 1));
+            B.sbox_tmp_to(X);                                                          // lane X = y
+            long next = (k + 2 < rp) ? rcp(k + 2) : rcf(4, 0);
+            ops.push_back(make_op(L.sp_row + (uint32_t)(k + 1) * (t + 1), 0, t + 1, B.TMP, OPF_ADDRC, (uint32_t)next, 1));
+            for (int i = 1; i < t; i++)                                               // A lanes 0 and X: stride t
+                ops.push_back(make_op(L.sp_col + (uint32_t)(k / 2) * 2 * (t - 1) + 2 * (i - 1), 0, 2, i, OPF_ADDSELF, 0, (uint32_t)X));
         }
         // the deferred dense (t-1)x(t-1) matrix on lanes 1.., then ARK of full round 4
         B.matvec_lu(L.lu_post, t - 1, 1, [&](int lane) { return rcf(4, lane); });
