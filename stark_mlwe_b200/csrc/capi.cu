@@ -4,6 +4,7 @@
 // packed into 256-bit little-endian words (transcript/src/lib.rs:13-41) and reduced on the device.
 #include "smw_internal.h"
 #include <cstring>
+#include <cstdlib>
 #include <cstdio>
 #include <algorithm>
 #include <memory>
@@ -17,6 +18,17 @@ int set_err(smw_ctx* c, int code, const char* what) { if (c) c->last_error = wha
 int cuda_err(smw_ctx* c, cudaError_t e, const char* what) {
     if (c) { c->last_error = std::string(what ? what : "") + ": " + cudaGetErrorString(e); }
     return SMW_ERR_CUDA;
+}
+int ctx_scratch(smw_ctx* c, int slot, size_t bytes, void** out) {
+    if (bytes > c->slot_bytes[slot]) {
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->slot_ptr[slot]) cudaFree(c->slot_ptr[slot]);
+        c->slot_ptr[slot] = nullptr; c->slot_bytes[slot] = 0;
+        SMW_CUDA(c, cudaMalloc(&c->slot_ptr[slot], bytes));
+        c->slot_bytes[slot] = bytes;
+    }
+    *out = c->slot_ptr[slot];
+    return SMW_OK;
 }
 } // namespace smw
 
@@ -164,7 +176,7 @@ void smw_ctx_destroy(smw_ctx* c) {
     for (auto& kv : c->by_width) free_params_internal(kv.second);
     for (auto& r : c->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : c->prof_pool) cudaEventDestroy(e);
-    cudaFree(c->d_twiddles); cudaFree(c->d_scratch);
+    cudaFree(c->d_twiddles); for (int i = 0; i < smw_ctx::N_SLOTS; i++) cudaFree(c->slot_ptr[i]);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -377,11 +389,12 @@ int32_t smw_merkle_commit_columns(smw_ctx* c, smw_params* p, int32_t arity, uint
     cudaSetDevice(c->device);
     In in(c, cols, n * (size_t)n_cols, mem); if (in.rc) return in.rc;
     if (n == 1) return d2h(c, roots_out_host, in.d, (size_t)n_cols * FR);   // a 1-leaf tree's root is the leaf
-    // two ping-pong buffers sized for level 1
+    // two ping-pong buffers sized for level 1 (context scratch slots: no allocation in steady state)
     size_t n1 = (n + arity - 1) / arity, n2 = (n1 + arity - 1) / arity;
-    uint32_t *bufA, *bufB = nullptr;
-    SMW_CUDA(c, cudaMalloc(&bufA, n1 * (size_t)n_cols * FR));
-    if (n1 > 1) { cudaError_t e = cudaMalloc(&bufB, n2 * (size_t)n_cols * FR); if (e != cudaSuccess) { cudaFree(bufA); return cuda_err(c, e, "cudaMalloc"); } }
+    void *pa, *pb = nullptr;
+    rc = ctx_scratch(c, smw_ctx::SLOT_TREE_A, n1 * (size_t)n_cols * FR, &pa); if (rc) return rc;
+    if (n1 > 1) { rc = ctx_scratch(c, smw_ctx::SLOT_TREE_B, n2 * (size_t)n_cols * FR, &pb); if (rc) return rc; }
+    uint32_t *bufA = (uint32_t*)pa, *bufB = (uint32_t*)pb;
     const uint32_t* cur = in.d; size_t cn = n, cstride = n; uint32_t level = 0; uint32_t* dst = bufA;
     while (cn > 1) {
         size_t nn = (cn + arity - 1) / arity;
@@ -391,8 +404,6 @@ int32_t smw_merkle_commit_columns(smw_ctx* c, smw_params* p, int32_t arity, uint
         dst = (dst == bufA) ? bufB : bufA;
     }
     if (!rc) rc = d2h(c, roots_out_host, cur, (size_t)n_cols * FR);
-    cudaStreamSynchronize(c->stream);
-    cudaFree(bufA); cudaFree(bufB);
     return rc;
 }
 int32_t smw_commitment_commit(smw_ctx* c, uint64_t ds_tag, smw_params* params, const void* leaves, size_t n, int32_t mem, smw_tree** out) {
@@ -420,18 +431,59 @@ int32_t smw_lde(smw_ctx* c, const void* in, int32_t log_n, int32_t log_blowup, c
     int rc = launch_lde(c, i.d, log_n, log_blowup, g.d, o.d, n_cols); if (rc) return rc;
     return o.finish();
 }
+// Streams the columns through the device in chunks whose extended form fits `SMW_LDE_CHUNK_BYTES` (default 16 GiB; every chunk pays ~20 ms of latency-bound top-of-tree levels, so chunks are kept large):
+// cfg4-sized inputs (2^24 rows x 32 columns per GPU, blow-up 8 = 137 GB extended) never exist in full, only the roots do.
+// With host input the H2D copy of chunk i+1 runs on a second stream while chunk i is extended and committed.
 int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_blowup, const void* shift_host, int32_t n_cols,
                        uint64_t label0, int32_t mem, void* roots_out_host) {
     if (!c || !cols || !roots_out_host || !shift_host || n_cols <= 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
-    size_t n = (size_t)1 << log_n, N = n << log_blowup;
+    const size_t n = (size_t)1 << log_n, N = n << log_blowup;
     smw_params* p; int rc = smw_params_commitment_default(c, &p); if (rc) return rc;
-    In i(c, cols, n * n_cols, mem), g(c, shift_host, 1, SMW_HOST); if (i.rc) return i.rc; if (g.rc) return g.rc;
-    uint32_t* d_ext; SMW_CUDA(c, cudaMalloc(&d_ext, N * (size_t)n_cols * FR));
-    rc = launch_lde(c, i.d, log_n, log_blowup, g.d, d_ext, n_cols);
-    if (!rc) rc = smw_merkle_commit_columns(c, p, 16, label0, 1, d_ext, N, n_cols, SMW_DEVICE, roots_out_host);
-    cudaStreamSynchronize(c->stream);
-    cudaFree(d_ext);
+    In g(c, shift_host, 1, SMW_HOST); if (g.rc) return g.rc;
+    size_t budget = (size_t)16 << 30;
+    if (const char* e = getenv("SMW_LDE_CHUNK_BYTES")) { size_t v = strtoull(e, nullptr, 10); if (v) budget = v; }
+    const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_cols, budget / (N * FR)));
+    uint32_t* d_ext = nullptr; uint32_t* d_in[2] = {nullptr, nullptr};
+    cudaStream_t copy = nullptr; cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(c->stream);
+        if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
+        for (int i = 0; i < 2; i++) { if (copied[i]) cudaEventDestroy(copied[i]); if (consumed[i]) cudaEventDestroy(consumed[i]); }
+    };
+    { void* q; rc = ctx_scratch(c, smw_ctx::SLOT_EXT, N * (size_t)chunk * FR, &q); if (rc) return rc; d_ext = (uint32_t*)q; }
+    cudaError_t e = cudaSuccess;
+    const bool host = (mem == SMW_HOST);
+    const int n_chunks = (n_cols + chunk - 1) / chunk;
+    if (host) {
+        e = cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking);
+        for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+            if (i < n_chunks) { void* q; if (ctx_scratch(c, smw_ctx::SLOT_IN0 + i, n * (size_t)chunk * FR, &q)) e = cudaErrorMemoryAllocation; d_in[i] = (uint32_t*)q; }
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming);
+        }
+        if (e != cudaSuccess) { cleanup(); return cuda_err(c, e, "smw_lde_commit staging"); }
+    }
+    auto enqueue_copy = [&](int ci) {      // host columns of chunk ci -> d_in[ci & 1] on the copy stream
+        const int c0 = ci * chunk, nc = std::min(chunk, n_cols - c0);
+        if (ci >= 2) cudaStreamWaitEvent(copy, consumed[ci & 1], 0);
+        cudaMemcpyAsync(d_in[ci & 1], (const uint8_t*)cols + (size_t)c0 * n * FR, (size_t)nc * n * FR, cudaMemcpyHostToDevice, copy);
+        cudaEventRecord(copied[ci & 1], copy);
+    };
+    if (host) enqueue_copy(0);
+    for (int ci = 0; ci < n_chunks && !rc; ci++) {
+        const int c0 = ci * chunk, nc = std::min(chunk, n_cols - c0);
+        const uint32_t* src;
+        if (host) {
+            if (ci + 1 < n_chunks) enqueue_copy(ci + 1);
+            cudaStreamWaitEvent(c->stream, copied[ci & 1], 0);
+            src = d_in[ci & 1];
+        } else src = (const uint32_t*)cols + (size_t)c0 * n * 8;
+        rc = launch_lde(c, src, log_n, log_blowup, g.d, d_ext, nc);
+        if (host) cudaEventRecord(consumed[ci & 1], c->stream);
+        if (!rc) rc = smw_merkle_commit_columns(c, p, 16, label0 + (uint64_t)c0, 1, d_ext, N, nc, SMW_DEVICE, (uint8_t*)roots_out_host + (size_t)c0 * FR);
+    }
+    cleanup();
     return rc;
 }
 

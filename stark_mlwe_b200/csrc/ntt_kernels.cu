@@ -230,18 +230,16 @@ int launch_lde(smw_ctx* c, const uint32_t* d_in, int log_n, int log_blowup, cons
     const size_t n = (size_t)1 << log_n, N = n << log_blowup;
     int rc = ensure_twiddles(c, log_n + log_blowup); if (rc) return rc;
     // 1. coefficients: inverse DIF in a scratch copy (bit-reversed, unscaled)
-    uint32_t* d_coef; SMW_CUDA(c, cudaMalloc(&d_coef, (size_t)n_cols * n * 32));
+    uint32_t* d_coef; { void* q; int r0 = ctx_scratch(c, smw_ctx::SLOT_LDE_COEF, (size_t)n_cols * n * 32, &q); if (r0) return r0; d_coef = (uint32_t*)q; }
     { LaunchScope ls(c, KC_LDE_AUX); k_copy_cols<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_in, d_coef, n, n, n); }
-    rc = run_passes(c, d_coef, log_n, true, 1, 0, n_cols, n); if (rc) { cudaFree(d_coef); return rc; }
+    rc = run_passes(c, d_coef, log_n, true, 1, 0, n_cols, n); if (rc) return rc;
     // 2. coset scaling (g^k / n) + zero-pad-as-stride expansion
     size_t n_hi = (n + 1023) >> 10;
-    uint32_t* d_g; SMW_CUDA(c, cudaMalloc(&d_g, (1024 + n_hi) * 32));
+    uint32_t* d_g; { void* q; int r0 = ctx_scratch(c, smw_ctx::SLOT_LDE_G, (1024 + n_hi) * 32, &q); if (r0) return r0; d_g = (uint32_t*)q; }
     k_gpow_tables<<<(unsigned)((std::max<size_t>(1024, n_hi) + 255) / 256), 256, 0, c->stream>>>(d_shift, log_n, d_g, d_g + 8 * 1024, n_hi); c->launches++;
     { LaunchScope ls(c, KC_LDE_AUX); k_lde_expand<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_coef, log_n, log_blowup, d_g, d_g + 8 * 1024, d_out, n, N); }
     // 3. forward DIT, skipping the log_blowup stages already folded into the expansion
     rc = run_passes(c, d_out, log_n + log_blowup, false, 0, log_blowup, n_cols, N);
-    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
-    cudaFree(d_coef); cudaFree(d_g);
     return rc;
 }
 

@@ -42,7 +42,9 @@ struct smw_ctx {
     std::map<int, smw_params*> by_width;         // poseidon_params_for_width cache
     uint32_t* d_twiddles = nullptr;              // w_N^i, i < N/2, external Montgomery form
     int twiddle_log_n = 0;
-    uint32_t* d_scratch = nullptr; size_t scratch_bytes = 0;
+    // grow-only device scratch slots reused across calls (cudaMalloc/cudaFree of GB-sized buffers cost ~100 ms per chunk)
+    enum { SLOT_LDE_COEF = 0, SLOT_LDE_G, SLOT_TREE_A, SLOT_TREE_B, SLOT_EXT, SLOT_IN0, SLOT_IN1, N_SLOTS };
+    void* slot_ptr[N_SLOTS] = {}; size_t slot_bytes[N_SLOTS] = {};
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
@@ -97,6 +99,9 @@ struct LaunchScope {
     }
     ~LaunchScope() { if (b) cudaEventRecord(b, c->stream); }
 };
+
+// returns a device buffer of at least `bytes` for `slot` (valid until the next request for the same slot on this context)
+int ctx_scratch(smw_ctx* c, int slot, size_t bytes, void** out);
 
 // status helpers
 int set_err(smw_ctx* c, int code, const char* what);

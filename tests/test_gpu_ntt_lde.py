@@ -89,3 +89,17 @@ def test_full_size_properties_2p20(ctx, smw, O, rnd):
 def test_bad_sizes(ctx, smw, O, rnd):
     with pytest.raises(smw.SmwError):
         smw.lde(ctx, rnd(3, 4), 31, O.to_mont([5])[0])     # 2^2 << 31 exceeds the two-adicity 32
+
+
+def test_lde_commit_streams_in_chunks(ctx, smw, O, rnd, monkeypatch):
+    """smw_lde_commit streams the columns in chunks (double-buffered H2D for host input): forcing 1-, 2- and 3-column chunks
+    gives the same roots as one chunk, for host and for device-resident input"""
+    import torch
+    cols = rnd(77, 5 << 8).reshape(5, 1 << 8, 4)
+    shift = O.to_mont([5])[0]
+    want = np.stack([O.commitment_commit(O.lde(cols[c], 2, shift), 100 + c).root() for c in range(5)])
+    dev = torch.from_numpy(cols.view(np.int64)).cuda()
+    for ncols_per_chunk in (1, 2, 3, 64):
+        monkeypatch.setenv("SMW_LDE_CHUNK_BYTES", str(ncols_per_chunk * (1 << 10) * 32))
+        assert eq(smw.lde_commit(ctx, cols, 2, shift, label0=100), want)
+        assert eq(smw.lde_commit(ctx, dev, 2, shift, label0=100), want)
