@@ -13,3 +13,7 @@ CMD="python bench.py --steps 1 --warmup 1 --log-n 16 --cols 16 --no-cpu --no-e2e
 $CMD > gpurun_out/h_ncu_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/h_launches.csv $CMD > gpurun_out/h_ncu_l.log 2>&1
 tail -n 3 gpurun_out/h_ncu_l.log
+ncu --set full --clock-control none --import-source on -k regex:k_merkle_level -s 5 -c 1 -o gpurun_out/h_merkle_level -f $CMD > gpurun_out/h_ncu_f.log 2>&1
+tail -n 3 gpurun_out/h_ncu_f.log
+ncu --set full --clock-control none --import-source on -k regex:k_ntt -s 2 -c 3 -o gpurun_out/h_ntt -f $CMD > gpurun_out/h_ncu_n.log 2>&1
+tail -n 3 gpurun_out/h_ncu_n.log
