@@ -32,6 +32,10 @@ UNIT = "Fr elems/s"
 SEED = 0x5EED0002
 SHIFT = 5                    # coset shift g = field generator
 MM_PERM_T17 = 21408          # dense Fr multiplications per t = 17 permutation, as the reference computes
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_merkle_level<17> launch from the committed ncu --set full capture
+# (profiles/r01h_ncu_merkle_level17_stalls_pipes_mix.json: level 0 of 16 columns x 2^18 leaves, whose algorithmic bytes are
+# 16 * 2^18 * 32 * (1 + 1/16) = 142 606 336): the kernel moves what it must and nothing else; it is multiplier-bound.
+TRAFFIC_NCU = 136739584 + 6227712
 MAC_PER_MM = 136             # 32x32->64 multiply-accumulates per 8-limb CIOS Montgomery multiplication
 
 
@@ -56,19 +60,6 @@ def gen_columns(seed, col0, n_cols, n_rows, out=None):
             v[:, 3] &= np.uint64((1 << 62) - 1)
             out[c] = v
     return out
-
-
-def executed_mac_per_perm(t, rp):
-    """32x32+64 multiply-accumulates the production permutation executes (poseidon_prog.cu: lazy radix-2^29 dot products,
-    LU in-place mat-vec, sparse partial rounds): mac = 81, square = 45, Montgomery reduction = 45.  (t = 17: 482.1 k; ncu's IMAD.WIDE count per
-    permutation in k_merkle_level<17> is within 1 % of it, profiles/r01g_*.)"""
-    mac, sqr, red = 81, 45, 45
-    sbox = 2 * sqr + mac + 3 * red
-    full = t * sbox + t * t * mac + (2 * t - 1) * red
-    # two partial rounds per block: 2 S-boxes, a t-term and a (t+1)-term row product, one 2-term update per lane
-    block = 2 * sbox + (2 * t + 1) * mac + 2 * red + (t - 1) * (2 * mac + red)
-    post = (t - 1) * (t - 1) * mac + (2 * (t - 1) - 1) * red
-    return 8 * full + (rp // 2) * block + post
 
 
 class ClockSampler:
@@ -265,16 +256,17 @@ def main():
             cn = nn
         ml_s = ml_ms * 1e-3 / args.steps        # seconds per step inside the Merkle-level kernel (all levels)
         alg_mac = perms * MM_PERM_T17 * MAC_PER_MM
-        exe_mac = perms * executed_mac_per_perm(17, 64)
+        mac_perm = smw.commitment_default_params(ctx).executed_macs()    # counted from the device program (81 per term, 45 per reduction)
+        exe_mac = perms * mac_perm
         alg_bytes = nc * (N * 32 + sum_levels_bytes(N))
         roofline = {
             "bound": "imad", "kernel": "k_merkle_level<17>",
             "achieved": alg_mac / ml_s / 1e12, "peak": mac_peak / 1e12, "unit": "T mac32/s (32x32+64 multiply-accumulates; algorithmic = dense reference count)",
             "frac": alg_mac / ml_s / mac_peak,
-            "executed": {"achieved": exe_mac / ml_s / 1e12, "frac": exe_mac / ml_s / mac_peak, "mac_per_permutation": executed_mac_per_perm(17, 64)},
+            "executed": {"achieved": exe_mac / ml_s / 1e12, "frac": exe_mac / ml_s / mac_peak, "mac_per_permutation": mac_perm},
             "peak_source": "measured live in this run: accumulating IMAD.WIDE.U32 (32x32+64->64), 16 chains x 512 threads/SM, ~40 ms per repetition (smw_diag_mac_rate; SASS-verified loop), %.2f warp-instr/clk/SM" % winstr,
             "frac_executed": exe_mac / ml_s / mac_peak,
-            "traffic": None,
+            "traffic": TRAFFIC_NCU, "traffic_launch": "ncu capture of level 0, 16 columns x 2^18 leaves: algorithmic bytes 142606336",
             "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps, "permutations_per_step": perms,
             "permutations_per_s": perms / ml_s,
             "hbm": {"achieved": alg_bytes / ml_s / 1e9, "peak": peak_hbm(), "unit": "GB/s", "frac": alg_bytes / ml_s / 1e9 / peak_hbm()},

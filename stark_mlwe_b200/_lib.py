@@ -46,7 +46,7 @@ def load():
     A = {
         "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp],
         "smw_last_error": [vp], "smw_ctx_launch_count": [vp], "smw_ctx_stream": [vp],
-        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp],
+        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_perm_macs": [vp, vp],
         "smw_fr_from_canonical": [vp, vp, vp, sz, i32], "smw_fr_to_canonical": [vp, vp, vp, sz, i32], "smw_root_of_unity": [vp, i32, vp],
         "smw_params_from_seed": [vp, vp, sz, i32, i32, vp], "smw_params_for_width": [vp, i32, vp], "smw_params_for_arity": [vp, i32, vp],
         "smw_params_commitment_default": [vp, vp], "smw_params_transcript_default": [vp, vp],

@@ -138,6 +138,12 @@ class PoseidonParamsDynamic:
         self.rounds_full = 8
         self.rounds_partial = int(ctx.L.smw_params_partial_rounds(h))
 
+    def executed_macs(self):
+        """32x32+64 multiply-accumulates one production permutation executes (counted from the device program)"""
+        m = C.c_uint64()
+        self.ctx.check(self.ctx.L.smw_diag_perm_macs(self.h, C.byref(m)))
+        return int(m.value)
+
     def export(self):
         t, rp = self.t, self.rounds_partial
         mds, rcf, rcp = np.zeros((t, t, 4), np.uint64), np.zeros((8, t, 4), np.uint64), np.zeros((rp, 4), np.uint64)

@@ -213,6 +213,12 @@ int32_t smw_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_
     return launch_diag_mac_rate(c, mac_per_s, warp_instr_per_clk_per_sm);
 }
 
+int32_t smw_diag_perm_macs(const smw_params* p, uint64_t* macs_out) {
+    if (!p || !macs_out) return SMW_ERR_INVALID_ARG;
+    *macs_out = count_macs(p->h_prog, p->perm_first, p->perm_count);
+    return SMW_OK;
+}
+
 // ---------------------------------------------------------------------------------------- field
 int32_t smw_fr_from_canonical(smw_ctx* c, const void* in, void* out, size_t n, int32_t mem) {
     if (!c) return SMW_ERR_INVALID_ARG;

@@ -70,6 +70,16 @@ SMW_DEV void acc_mac(Acc& A, const F29& a, const F29& b) {
 #pragma unroll
         for (int j = 0; j < 9; j++) A.c[i + j] = madw(a.v[i], b.v[j], A.c[i + j]);
 }
+// A = a * b : the same 81 products without a prior value (a column's first product is an IMAD.WIDE with RZ addend)
+SMW_DEV void acc_mul(Acc& A, const F29& a, const F29& b) {
+#pragma unroll
+    for (int i = 0; i < 9; i++)
+#pragma unroll
+        for (int j = 0; j < 9; j++) {
+            if (i == 0 || j == 8) A.c[i + j] = (uint64_t)a.v[i] * b.v[j];
+            else A.c[i + j] = madw(a.v[i], b.v[j], A.c[i + j]);
+        }
+}
 // A += a * a : 45 IMAD.WIDE (off-diagonal terms use the doubled operand, < 2^30)
 SMW_DEV void acc_sqr(Acc& A, const F29& a) {
     uint32_t d[9];
@@ -125,6 +135,14 @@ SMW_DEV F29 acc_reduce_add(Acc& A, const F29& s) {
     for (int i = 0; i < 8; i++) A.c[9 + i] += s.v[i];
     F29 r = acc_reduce(A);
     r.v[8] += s.v[8];
+    return r;
+}
+// same with two addends (old lane + round constant)
+SMW_DEV F29 acc_reduce_add2(Acc& A, const F29& s, const F29& t) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) A.c[9 + i] += (uint64_t)(s.v[i] + t.v[i]);
+    F29 r = acc_reduce(A);
+    r.v[8] += s.v[8] + t.v[8];
     return r;
 }
 SMW_DEV F29 f29_mul(const F29& a, const F29& b) { Acc A; acc_zero(A); acc_mac(A, a, b); return acc_reduce(A); }

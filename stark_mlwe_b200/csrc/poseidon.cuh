@@ -11,12 +11,19 @@
 //        x += S[dst]   (optional)             unit diagonal of L / rank-1 update of a sparse partial round
 //        x += rc       (optional)             the NEXT round's round constant, folded into the producer
 //        S[dst] = x
-// with A_j a state lane (or an external input element) and B_j a table entry (or a state lane, for the
-// S-box multiplications).  Why an interpreter: round 1a inlined the rounds as straight-line code, 360 KB of
-// SASS for the Merkle kernel; with ten warps per SM in different phases the instruction cache thrashed and
-// "no instruction" was the top stall (profiles/r01a_ncu_full_merkle_level17_details.csv: 6.2 of 10.6 cycles per
-// issue).  Here every warp executes the same ~8 KB loop whose body is one 81-multiply block, so the hot
-// code stays in the L0/L1 instruction caches whatever the phase of each warp.
+// with A_j state lanes j0, j0+1, .. (or an external input element) and B_j consecutive table entries (or a
+// state lane, for the S-box multiplications).
+//
+// Why an interpreter: round 1a inlined the rounds as straight-line code, 360 KB of SASS for the Merkle kernel; with
+// ten warps per SM in different phases the instruction cache thrashed (profiles/r01a_*).  Why a SOFTWARE-PIPELINED
+// interpreter (v3): the smem-resident state limits an SM to ten warps (2.5 per scheduler), and in v2 a warp spent more
+// than half of its instructions outside the multiply block (Montgomery reduction, carry chains, stores: 58 % of the
+// executed SASS, profiles/r01h_ncu_merkle_level17_stalls_pipes_mix.json), during which it issued nothing to the
+// multiplier; the fmaheavy pipe idled 34 % of the time with "wait" as the top stall.  Here the reduction + store of
+// operation k and the first 81 multiplies of operation k+1 sit in ONE basic block on two accumulator sets (A/B,
+// alternating roles in a loop unrolled by two, so no register moves), and ptxas interleaves the dependent ALU chain of
+// the reduction with the independent IMAD.WIDE stream.  An operation whose first-term operands are the result of its
+// predecessor (OPF_DEP, set by mark_deps() in poseidon_prog.cu) cannot overlap and takes the plain path.
 //
 // The dense t x t matrix is applied IN PLACE through its LU factors (same multiply count as the dense
 // product, no second state buffer); the RP partial rounds use the exact sparse factorisation (one row
@@ -35,20 +42,21 @@ constexpr int EL = 12;   // table element stride in 32-bit words (9 used; 48 B k
 
 // row-operation flags (bits 24..31 of Op.y)
 enum : uint32_t {
-    OPF_BSTATE  = 1,    // B operand is state lane Op.x (S-box multiplications) instead of table element Op.x
+    OPF_BSTATE  = 1,    // B operand of the (single) term is state lane Op.x (S-box multiplications) instead of a table element
     OPF_ADDSELF = 2,    // add the old S[dst] to the reduced result
     OPF_ADDRC   = 4,    // add table element Op.z (round constant / padding one)
-    OPF_LOAD    = 8,    // no products: x = S[Op.w]
-    OPF_SQR     = 16,   // x = S[j0]^2 (45 multiplies instead of 81)
+    OPF_DEP     = 8,    // the first term reads the lane its predecessor writes: no overlap (set by mark_deps, never by builders)
+    OPF_SQR     = 16,   // x = S[j0]^2 (always with OPF_BSTATE and Op.x = j0; the plain path spends 45 multiplies instead of 81)
     OPF_AEXT    = 32    // A operand is external input element Op.w (raw 29-bit repack; the B operand carries the
                         // conversion constant), single term
 };
 // Op = uint4 { x: B offset (table element index, or state lane), y: j0 | n << 8 | dst << 16 | flags << 24,
-//              z: table element index of the constant to add, w: source lane (LOAD) / input index (AEXT) / A-lane stride (else) }
+//              z: table element index of the constant to add, w: input index (AEXT) }
 __host__ __device__ inline uint4 make_op(uint32_t b_off, int j0, int n, int dst, uint32_t flags, uint32_t rc_off = 0, uint32_t aux = 0) {
-    if (!(flags & (OPF_LOAD | OPF_AEXT)) && aux == 0) aux = 1;          // A-lane stride defaults to 1
     uint4 o; o.x = b_off; o.y = (uint32_t)j0 | ((uint32_t)n << 8) | ((uint32_t)dst << 16) | (flags << 24); o.z = rc_off; o.w = aux; return o;
 }
+__host__ __device__ inline uint4 pad_op() { return make_op(0, 0, 1, 0, 0); }     // lane 0 * table element 0: loads only, never stored
+__host__ __device__ inline uint4 make_sqr(int lane, int dst) { return make_op((uint32_t)lane, lane, 1, dst, OPF_SQR | OPF_BSTATE); }
 
 // Segs (smw_internal.h): up to 8 (first, count) ranges of the op array, run in order, e.g.
 // [absorb block 0][permutation][absorb block 1][permutation]
@@ -106,62 +114,63 @@ SMW_DEV void store_ext(uint32_t* p, const uint32_t w[8]) {
 // "no external inputs" functor for programs without OPF_AEXT operations
 struct NoInput { SMW_DEV F29 operator()(uint32_t) const { return f29_zero(); } };
 
-// The interpreter.  One copy per kernel (noinline: the sponges call it once per segment list), about a thousand
-// instructions; all warps of the SM loop over the same code.  The state lives in the CTA's dynamic shared memory and is
-// re-derived from `smem` here (not passed as pointers) so that the compiler keeps LDS/STS addressing.
-//   * the term loop is unrolled by two with ping-pong operand registers: the next term's operands are in flight during
-//     the current term's 81 multiplies and no register moves are needed;
-//   * the next operation's descriptor and its first table operand are fetched one operation ahead (table loads mostly
-//     miss the small L1 left beside 207 KB of shared memory, and go to L2).
+// The interpreter.  One copy per kernel (noinline: the sponges call it once per segment list); all warps of the SM loop
+// over the same code.  The state lives in the CTA's dynamic shared memory and is re-derived from `smem` here (not passed
+// as pointers) so that the compiler keeps LDS/STS addressing.  Runs operations [first, first + count); the operation
+// at first + count must exist (every program is followed by one padding operation): it is started and never finished.
+// Each iteration finishes the pending operation `pd` (accumulators P: reduce, add, store) while starting operation `nd`
+// (accumulators Q).  The initial pending operation is a zero accumulator stored to scratch lane T + 1, which is dead at
+// every segment start.  Table operands mostly miss the small L1 left beside 214 KB of shared memory and come from L2,
+// so they are always requested an operation (first term) or a term (the others) ahead.
 template <int T, class In>
 __device__ __noinline__ void run_ops(int nt, const uint32_t* __restrict__ tbl, const uint4* __restrict__ prog, int first, int count, In in) {
     extern __shared__ __align__(16) unsigned char smem[];
     const StateRef S = state_ref<T>(smem, nt, threadIdx.x);
-    uint4 d = __ldg(prog + first);
-    F29 bpre = ((d.y >> 24) & (OPF_BSTATE | OPF_LOAD | OPF_SQR)) ? f29_zero() : tbl_load(tbl, d.x);
+    Acc P; acc_zero(P);
+    uint4 pd = make_op(0, 0, 1, T + 1, 0);
+    uint4 nd = __ldg(prog + first);
+    F29 nb = f29_zero(), prc = f29_zero();                    // nd's first table operand; pd's constant (both fetched one operation ahead)
+    if (!((nd.y >> 24) & OPF_BSTATE)) nb = tbl_load(tbl, nd.x);
 #pragma unroll 1
-    for (int k = 0; k < count; k++) {
-        const uint4 dn = __ldg(prog + first + k + 1);        // every program is followed by one padding op
-        const uint32_t fl = d.y >> 24;
-        const int j0 = d.y & 255, n = (d.y >> 8) & 255, dst = (d.y >> 16) & 255;
-        F29 x;
-        if (fl & OPF_LOAD) {
-            x = S.load((int)d.w);
+    for (int k = 0; k <= count; k++) {
+        uint4 nn = nd; if (k < count) nn = __ldg(prog + first + k + 1);
+        const uint32_t pfl = pd.y >> 24; const int pdst = (pd.y >> 16) & 255;
+        const uint32_t fl = nd.y >> 24; const int j0 = nd.y & 255, n = (nd.y >> 8) & 255;
+        F29 sr = f29_zero();                                   // what is added on top of the reduced value: old lane + constant
+        if (pfl & OPF_ADDSELF) sr = S.load(pdst);
+        const F29 rc = prc;
+        prc = f29_zero();
+        if (fl & OPF_ADDRC) prc = tbl_load(tbl, nd.z);          // lands during this operation's multiplies, consumed by the next iteration
+        F29 b1 = f29_zero();                                   // table operand of term 1 (tables are immutable: no hazard with the pending store)
+        if (n > 1) b1 = tbl_load(tbl, nd.x + 1);
+        Acc Q;
+        if (!(fl & OPF_DEP)) {
+            F29 a0, b0 = nb;
+            if (fl & OPF_AEXT) a0 = in(nd.w); else a0 = S.load(j0);
+            if (fl & OPF_BSTATE) b0 = S.load((int)nd.x);
+            // ---- the fused block: 81 independent multiplies of the new operation + the dependent chain of the old one
+            acc_mul(Q, a0, b0);
+            S.store(pdst, acc_reduce_add2(P, sr, rc));
         } else {
-            Acc A; acc_zero(A);
-            if (fl & OPF_SQR) {
-                acc_sqr(A, S.load(j0));
-            } else {
-                F29 a0 = (fl & OPF_AEXT) ? in(d.w) : S.load(j0);
-                F29 b0 = (fl & OPF_BSTATE) ? S.load((int)d.x) : bpre;
-                F29 a1 = a0, b1 = b0;
-                const int st = (fl & OPF_AEXT) ? 1 : (int)d.w;              // A-lane stride (1 except the two-S-box lane updates)
-                int c = 0, j = 1;
-#pragma unroll 1
-                while (true) {
-                    if (j < n) { a1 = S.load(j0 + j * st); b1 = tbl_load(tbl, d.x + j); }
-                    if (c == 6) { acc_normalize(A); c = 0; }
-                    acc_mac(A, a0, b0); c++;
-                    if (j >= n) break;
-                    j++;
-                    if (j < n) { a0 = S.load(j0 + j * st); b0 = tbl_load(tbl, d.x + j); }
-                    if (c == 6) { acc_normalize(A); c = 0; }
-                    acc_mac(A, a1, b1); c++;
-                    if (j >= n) break;
-                    j++;
-                }
-            }
-            if (!((dn.y >> 24) & (OPF_BSTATE | OPF_LOAD | OPF_SQR))) bpre = tbl_load(tbl, dn.x);   // in flight during the reduction
-            F29 s = f29_zero();                                   // one copy of the reduction for both cases
-            if (fl & OPF_ADDSELF) s = S.load(dst);
-#pragma unroll
-            for (int i = 0; i < 8; i++) A.c[9 + i] += s.v[i];
-            x = acc_reduce(A);
-            x.v[8] += s.v[8];
+            S.store(pdst, acc_reduce_add2(P, sr, rc));
+            F29 a0;
+            if (fl & OPF_AEXT) a0 = in(nd.w); else a0 = S.load(j0);
+            if (fl & OPF_SQR) { acc_zero(Q); acc_sqr(Q, a0); }
+            else { F29 b0 = nb; if (fl & OPF_BSTATE) b0 = S.load((int)nd.x); acc_mul(Q, a0, b0); }
         }
-        if (fl & OPF_ADDRC) x = f29_add(x, tbl_load(tbl, d.z));
-        S.store(dst, x);
-        d = dn;
+        if (k < count && !((nn.y >> 24) & OPF_BSTATE)) nb = tbl_load(tbl, nn.x);
+        // remaining terms, two per iteration with alternating operand registers (the next term's are in flight during the multiplies)
+        {
+            int c = 1;
+#pragma unroll 1
+            for (int j = 1; j < n; j++) {
+                F29 a1 = S.load(j0 + j), bb = b1;
+                if (j + 1 < n) b1 = tbl_load(tbl, nd.x + j + 1);
+                if (c == 6) { acc_normalize(Q); c = 0; }
+                acc_mac(Q, a1, bb); c++;
+            }
+        }
+        P = Q; pd = nd; nd = nn;
     }
 }
 template <int T, class In>

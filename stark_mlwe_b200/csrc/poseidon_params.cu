@@ -128,20 +128,20 @@ __global__ void __launch_bounds__(256) k_derive_factor(DeriveArgs a) {
     }
     __syncthreads();
     for (int k = 0; k < rp; k++) {
-        // layout (TableLayout, poseidon_prog.cu): sp_row has t + 1 slots per round — even k: [M00, row_k[1..]], odd k:
-        // [G, row_k[1..], M00] with G = sum_i row_k[i] * col_{k-1}[i-1] (two partial rounds run as one block);
-        // sp_col interleaves the column vectors of rounds 2b and 2b + 1
+        // layout (TableLayout, poseidon_prog.cu): sp_row has t + 1 slots per round — even k: [row_k[1..], M00], odd k:
+        // [row_k[1..], G, M00] with G = sum_i row_k[i] * col_{k-1}[i-1] (two partial rounds run as one block over the
+        // lanes u_1 .., x, y); sp_col interleaves the column vectors of rounds 2b and 2b + 1
         const int tp = t + 1;
-        if (threadIdx.x == 0) gs(a.sp_row, (size_t)k * tp + ((k & 1) ? t : 0), gl(a.mds, 0));
+        if (threadIdx.x == 0) gs(a.sp_row, (size_t)k * tp + n + (k & 1), gl(a.mds, 0));
         for (int j = threadIdx.x; j < n; j += blockDim.x) {
-            gs(a.sp_row, (size_t)k * tp + 1 + j, gl(a.vk, j));
+            gs(a.sp_row, (size_t)k * tp + j, gl(a.vk, j));
             gs(a.sp_col, (size_t)(k >> 1) * 2 * n + 2 * j + (k & 1), gl(a.wk, j));
         }
         __syncthreads();
         if ((k & 1) && threadIdx.x == 0) {
             Acc acc; acc_zero(acc); int c = 0;
             for (int j = 0; j < n; j++) { acc_mac(acc, gl(a.vk, j), gl(a.sp_col, (size_t)(k >> 1) * 2 * n + 2 * j)); if (++c == 6) { acc_normalize(acc); c = 0; } }
-            gs(a.sp_row, (size_t)k * tp, f29_canonicalize(acc_reduce(acc)));
+            gs(a.sp_row, (size_t)k * tp + n, f29_canonicalize(acc_reduce(acc)));
         }
         __syncthreads();
         // vk <- vk^T * Mh ; wk <- Mh^-1 * wk   (through tmp / vt)
@@ -171,10 +171,11 @@ __global__ void k_store_consts(uint32_t* tbl, TableLayout L) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     gs(tbl, L.k_in, f29_const(C_KIN29)); gs(tbl, L.k_out, f29_const(C_KOUT29)); gs(tbl, L.k_rr, f29_const(C_RR29)); gs(tbl, L.k_one, f29_const(C_ONE29));
 }
-static const uint4 PAD_OP = make_op(0, 0, 0, 0, OPF_LOAD, 0, 0);
+static const uint4 PAD_OP = pad_op();
 
 int upload_programs(smw_ctx* c, smw_params* p) {
     size_t n = p->h_prog.size();
+    mark_deps(p->h_prog, 0);        // idempotent: an operation's flag depends only on itself and its array predecessor
     if (n > p->d_prog_cap) {
         SMW_CUDA(c, cudaStreamSynchronize(c->stream));          // kernels in flight still read the old copy
         if (p->d_prog) cudaFree(p->d_prog);

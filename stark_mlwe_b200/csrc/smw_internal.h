@@ -111,6 +111,8 @@ int cuda_err(smw_ctx* c, cudaError_t e, const char* what);
 // programs (poseidon_prog.cu)
 TableLayout table_layout(int t, int rp);
 void build_perm_program(std::vector<uint4>& ops, int t, int rp, bool sparse);
+void mark_deps(std::vector<uint4>& ops, size_t from);                             // sets OPF_DEP (poseidon.cuh) on ops[from..]
+uint64_t count_macs(const std::vector<uint4>& ops, int first, int count);         // executed 32x32+64 multiply-accumulates
 Segs build_sponge_program(std::vector<uint4>& ops, int t, int rp, int n_ds, int max_inputs, int perm_first, int perm_count);
 int upload_programs(smw_ctx* c, smw_params* p);                                   // h_prog -> d_prog (re-allocates when it grew)
 int get_sponge_segs(smw_ctx* c, smw_params* p, int n_ds, int max_inputs, Segs* out); // cached per parameter set
