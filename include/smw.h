@@ -142,6 +142,24 @@ int32_t smw_fri_roots(smw_fri* s, void* out_host);                              
 int32_t smw_fri_z(smw_fri* s, void* out_host);                                         /* L Fr */
 smw_tree* smw_fri_layer_tree(smw_fri* s, int32_t l);                                   /* borrowed */
 void smw_fri_free(smw_fri* s);
+/* layers level0.. of a larger instance: tree_label and the z_l level index start at level0 (fri.rs:250,284-289) */
+int32_t smw_fri_build_transcript_from(smw_ctx* ctx, const void* f, size_t n, const uint64_t* schedule, int32_t L, uint64_t seed_z, uint64_t level0, int32_t mem, smw_fri** out);
+
+/* ---- range-sharded commit phase of ONE large polynomial (no reference counterpart: the reference is
+ * single-process).  Rank g passes f0[first_index, first_index + n_local) with n_local = n0 / G; folds (fri.rs:95-100),
+ * leaf hashes (fri.rs:38-44, merkle/src/lib.rs:382-400) and subtrees (merkle/src/lib.rs:164-181, DS positions offset by the
+ * slice start) are local; the host all-gathers each layer's cap nodes and finishes the roots. */
+typedef struct smw_fri_shard smw_fri_shard;
+int32_t smw_fri_shard_build(smw_ctx* ctx, const void* f0_slice, size_t n_local, size_t n0, size_t first_index, const uint64_t* schedule, int32_t L,
+                            uint64_t seed_z, int32_t mem, smw_fri_shard** out);
+int32_t smw_fri_shard_num_local_layers(const smw_fri_shard* s);      /* K: layers [0, K) are committed from slices */
+int32_t smw_fri_shard_cap_info(const smw_fri_shard* s, int32_t l, size_t* n_nodes_local, int32_t* cap_level, int32_t* arity);
+int32_t smw_fri_shard_cap(smw_fri_shard* s, int32_t l, void* out, int32_t mem);   /* this rank's nodes of the cap level of layer l */
+size_t smw_fri_shard_tail_len(const smw_fri_shard* s);               /* length of this rank's slice of f_K (0 if every layer was local) */
+int32_t smw_fri_shard_tail(smw_fri_shard* s, void* out, int32_t mem);
+void smw_fri_shard_free(smw_fri_shard* s);
+/* root of the tree whose level-`level` nodes are given (level 0 = leaves / leaf digests): finishes a gathered cap */
+int32_t smw_merkle_root_from_level(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t tree_label, int32_t level, const void* nodes, size_t n, int32_t mem, void* root_out_fr_host);
 
 /* ---- Merkle-folded sum-check commit loop (channel/src/lib.rs:406-416, 592-598, 600-657) ---- */
 int32_t smw_sumcheck_round_coeffs(smw_ctx* ctx, const void* layer, size_t n, void* c0_host, void* c1_host, int32_t mem);

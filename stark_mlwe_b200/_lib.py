@@ -37,16 +37,21 @@ def load():
     L.smw_last_error.restype = C.c_char_p
     L.smw_ctx_launch_count.restype = u64
     L.smw_ctx_stream.restype = vp
-    for n in ("smw_tree_level_len", "smw_proof_num_indices", "smw_proof_level_siblings", "smw_proof_level_groups"):
+    for n in ("smw_tree_level_len", "smw_fri_shard_tail_len", "smw_proof_num_indices", "smw_proof_level_siblings", "smw_proof_level_groups"):
         getattr(L, n).restype = sz
     L.smw_fri_layer_tree.restype = vp
-    for n in ("smw_ctx_destroy", "smw_params_free", "smw_tree_free", "smw_transcript_free", "smw_fri_free", "smw_proof_free"):
+    for n in ("smw_ctx_destroy", "smw_params_free", "smw_tree_free", "smw_transcript_free", "smw_fri_free", "smw_fri_shard_free", "smw_proof_free"):
         getattr(L, n).restype = None
     # argument types: every pointer is passed as c_void_p, sizes as size_t, labels/seeds as uint64
     A = {
         "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp],
         "smw_last_error": [vp], "smw_ctx_launch_count": [vp], "smw_ctx_stream": [vp],
-        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_perm_macs": [vp, vp],
+        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp],
+        "smw_fri_build_transcript_from": [vp, vp, sz, vp, i32, u64, u64, i32, vp],
+        "smw_fri_shard_build": [vp, vp, sz, sz, sz, vp, i32, u64, i32, vp], "smw_fri_shard_num_local_layers": [vp],
+        "smw_fri_shard_cap_info": [vp, i32, vp, vp, vp], "smw_fri_shard_cap": [vp, i32, vp, i32], "smw_fri_shard_tail_len": [vp],
+        "smw_fri_shard_tail": [vp, vp, i32], "smw_fri_shard_free": [vp],
+        "smw_merkle_root_from_level": [vp, vp, i32, u64, i32, vp, sz, i32, vp], "smw_diag_perm_macs": [vp, vp],
         "smw_fr_from_canonical": [vp, vp, vp, sz, i32], "smw_fr_to_canonical": [vp, vp, vp, sz, i32], "smw_root_of_unity": [vp, i32, vp],
         "smw_params_from_seed": [vp, vp, sz, i32, i32, vp], "smw_params_for_width": [vp, i32, vp], "smw_params_for_arity": [vp, i32, vp],
         "smw_params_commitment_default": [vp, vp], "smw_params_transcript_default": [vp, vp],

@@ -629,13 +629,60 @@ class FriProverState:
             pass
 
 
-def fri_build_transcript(ctx, f0, params):
-    """deep_ali/src/fri.rs:231-312 (the FriDomain argument only carries n0 = len(f0))"""
+def fri_build_transcript(ctx, f0, params, level0=0):
+    """deep_ali/src/fri.rs:231-312 (the FriDomain argument only carries n0 = len(f0)).  level0 > 0: f0 is layer `level0`
+    of a larger instance (tree labels and z_l level indices start there) — used by the range-sharded commit phase."""
     p, n, mem, _k = _buf(f0)
     sch = np.ascontiguousarray(params.schedule, dtype=np.uint64)
     h = C.c_void_p()
-    ctx.check(ctx.L.smw_fri_build_transcript(ctx.h, p, n, C.c_void_p(sch.ctypes.data) if sch.size else None, len(params.schedule), params.seed_z, mem, C.byref(h)))
+    ctx.check(ctx.L.smw_fri_build_transcript_from(ctx.h, p, n, C.c_void_p(sch.ctypes.data) if sch.size else None, len(params.schedule), params.seed_z,
+                                                  int(level0), mem, C.byref(h)))
     return FriProverState(ctx, h, params.schedule)
+
+
+class FriShard:
+    """One rank's part of the range-sharded commit phase of a single large polynomial: local folds, leaf
+    hashes and subtrees of f0[first_index, first_index + len(f0_slice)); `caps` are gathered and finished by shard.py."""
+
+    def __init__(self, ctx, f0_slice, n0, first_index, params):
+        self.ctx = ctx
+        p, n, mem, _k = _buf(f0_slice)
+        sch = np.ascontiguousarray(params.schedule, dtype=np.uint64)
+        self.h = C.c_void_p()
+        ctx.check(ctx.L.smw_fri_shard_build(ctx.h, p, n, int(n0), int(first_index), C.c_void_p(sch.ctypes.data) if sch.size else None,
+                                            len(params.schedule), params.seed_z, mem, C.byref(self.h)))
+        self.num_local_layers = int(ctx.L.smw_fri_shard_num_local_layers(self.h))
+
+    def cap(self, l):
+        """(nodes (k, 4) uint64, DS level of the parents of these nodes, tree arity) of layer l"""
+        n, lev, ar = C.c_size_t(), C.c_int32(), C.c_int32()
+        self.ctx.check(self.ctx.L.smw_fri_shard_cap_info(self.h, l, C.byref(n), C.byref(lev), C.byref(ar)))
+        out = _out(n.value)
+        self.ctx.check(self.ctx.L.smw_fri_shard_cap(self.h, l, C.c_void_p(out.ctypes.data), HOST))
+        return out, lev.value, ar.value
+
+    def tail(self):
+        """this rank's slice of the first layer that is too small to split (empty when every layer was local)"""
+        n = int(self.ctx.L.smw_fri_shard_tail_len(self.h))
+        out = _out(n)
+        if n:
+            self.ctx.check(self.ctx.L.smw_fri_shard_tail(self.h, C.c_void_p(out.ctypes.data), HOST))
+        return out
+
+    def __del__(self):
+        try:
+            if self.ctx.h and self.h:
+                self.ctx.L.smw_fri_shard_free(self.h)
+        except Exception:
+            pass
+
+
+def merkle_root_from_level(ctx, nodes, level, arity, params, tree_label):
+    """root of the tree whose level-`level` nodes are `nodes` (level 0 = leaves / leaf digests), merkle/src/lib.rs:164-181"""
+    p, n, mem, _k = _buf(nodes)
+    out = _out(1)
+    ctx.check(ctx.L.smw_merkle_root_from_level(ctx.h, params.h, int(arity), int(tree_label), int(level), p, n, mem, C.c_void_p(out.ctypes.data)))
+    return out[0]
 
 
 # ----------------------------------------------------------------------------- Merkle-folded sum-check

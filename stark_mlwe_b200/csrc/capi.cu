@@ -128,11 +128,11 @@ int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t*
 }
 
 // level-by-level tree over a device level 0 (merkle/src/lib.rs:164-181)
-int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out) {
+int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out, uint32_t first_ds_level = 0) {
     auto t = std::make_unique<smw_tree>();
     t->ctx = c; t->params = p; t->arity = arity; t->tree_label = label;
     t->len.push_back(n); t->lv.push_back(d_level0); t->owned.push_back(own0);
-    uint32_t level = 0;
+    uint32_t level = first_ds_level;          // DS level of the parents of d_level0 (0 = parents of the leaves)
     while (t->len.back() > 1) {
         size_t cn = t->len.back(), nn = (cn + arity - 1) / arity;
         uint32_t* d_next; cudaError_t e = cudaMalloc(&d_next, nn * FR);
@@ -656,6 +656,9 @@ void smw_fri_free(smw_fri* s) {
     delete s;
 }
 int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, smw_fri** out) {
+    return smw_fri_build_transcript_from(c, f0, n0, schedule, L, seed_z, 0, mem, out);
+}
+int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, uint64_t level0, int32_t mem, smw_fri** out) {
     if (!c || !out || !f0 || L < 0 || (L && !schedule) || n0 == 0) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     // layer sizes (fri.rs:145-155) — the reference asserts divisibility level by level
@@ -676,7 +679,7 @@ int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const ui
     { cudaError_t e = cudaMemcpyAsync(s->f[0], f0, n0 * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream); if (e != cudaSuccess) return fail(cuda_err(c, e, "copy f0")); }
     // z_l depends only on public values (fri.rs:250): all levels in one launch
     std::vector<uint64_t> levels(L), sizes(L);
-    for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
+    for (int l = 0; l < L; l++) { levels[l] = level0 + (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
     rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc);
     for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); }
     // per-layer commitment (fri.rs:267-301); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer
@@ -688,9 +691,9 @@ int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const ui
         uint32_t* d_leaves; { cudaError_t e = cudaMalloc(&d_leaves, n[l] * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(leaves)")); }
         const uint32_t* d_s = (l < L) ? s->f[l + 1] : nullptr;
         if (hashed) rc = hash_leaves_device(c, s->f[l], d_s, m[l], n[l], d_leaves);
-        else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, (uint64_t)l, 0, d_leaves, m[l]);
+        else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, level0 + (uint64_t)l, 0, d_leaves, m[l]);
         if (rc) { cudaFree(d_leaves); return fail(rc); }
-        rc = build_tree(c, p, arity, (uint64_t)l, d_leaves, true, n[l], &s->tree[l]); if (rc) return fail(rc);
+        rc = build_tree(c, p, arity, level0 + (uint64_t)l, d_leaves, true, n[l], &s->tree[l]); if (rc) return fail(rc);
     }
     *out = s.release();
     return SMW_OK;
@@ -722,6 +725,116 @@ int32_t smw_fri_roots(smw_fri* s, void* out_host) {
 }
 int32_t smw_fri_z(smw_fri* s, void* out_host) { if (!s || !out_host) return SMW_ERR_INVALID_ARG; if (s->L == 0) return SMW_OK; cudaSetDevice(s->ctx->device); return d2h(s->ctx, out_host, s->d_z, (size_t)s->L * FR); }
 smw_tree* smw_fri_layer_tree(smw_fri* s, int32_t l) { return (s && l >= 0 && l <= s->L) ? s->tree[l] : nullptr; }
+
+// ---------------------------------------------------------------------------------------- range-sharded FRI commit phase
+// the fold is over contiguous blocks (fri.rs:95-100) and z_l is public (fri.rs:250), so the rank that holds
+// f_0[first, first + n_local) folds its own slice through every layer with no exchange, hashes its own leaves and builds its
+// own subtree with DS positions offset by the slice start (merkle/src/lib.rs:168-173) up to the last level whose nodes
+// are complete inside the slice (the "cap").  The host all-gathers the caps (<= a few KB per layer) and every rank
+// finishes the tree tops with smw_merkle_root_from_level; layers too small to split are rebuilt by every rank from the
+// gathered slice of the first such layer with smw_fri_build_transcript_from.
+struct smw_fri_shard {
+    smw_ctx* ctx = nullptr;
+    int K = 0;                                   // layers [0, K) are committed from local slices
+    std::vector<uint32_t*> cap; std::vector<size_t> cap_n; std::vector<int> cap_level, arity;
+    uint32_t* tail = nullptr; size_t tail_n = 0;  // local slice of f_K (empty when every layer was local)
+};
+void smw_fri_shard_free(smw_fri_shard* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
+    for (auto* q : s->cap) cudaFree(q);
+    cudaFree(s->tail);
+    delete s;
+}
+int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, size_t n0, size_t first_index, const uint64_t* schedule, int32_t L,
+                            uint64_t seed_z, int32_t mem, smw_fri_shard** out) {
+    if (!c || !out || !f0_slice || L < 0 || (L && !schedule) || n0 == 0 || n_local == 0 || n0 % n_local || first_index % n_local || first_index >= n0)
+        return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    const size_t G = n0 / n_local;               // number of equal slices
+    std::vector<size_t> n(L + 1), m(L + 1); n[0] = n0;
+    for (int l = 0; l < L; l++) {
+        m[l] = (size_t)schedule[l];
+        if (m[l] < 2 || m[l] > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 2..128");
+        if (n[l] % m[l]) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
+        n[l + 1] = n[l] / m[l];
+    }
+    m[L] = 1;
+    // layer l is local while the slice of f_l folds into a whole slice of f_{l+1} (the last layer needs no fold)
+    int K = 0;
+    while (K <= L && n[K] % G == 0 && (K == L || (n[K] / G) % m[K] == 0)) K++;
+    auto s = std::make_unique<smw_fri_shard>(); s->ctx = c; s->K = K;
+    auto fail = [&](int code) { smw_fri_shard_free(s.release()); return code; };
+    std::vector<uint32_t*> f(K + 1, nullptr);     // local slices of f_0 .. f_K (f_K only when K <= L)
+    auto free_f = [&]() { cudaStreamSynchronize(c->stream); for (auto* q : f) if (q && q != s->tail) cudaFree(q); };
+    const int n_f = (K <= L) ? K + 1 : K;
+    for (int l = 0; l < n_f; l++) { cudaError_t e = cudaMalloc(&f[l], (n[l] / G) * FR); if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "cudaMalloc(fri slice)")); } }
+    { cudaError_t e = cudaMemcpyAsync(f[0], f0_slice, n_local * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
+      if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "copy f0 slice")); } }
+    uint32_t* d_z = nullptr; { cudaError_t e = cudaMalloc(&d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "cudaMalloc")); } }
+    std::vector<uint64_t> levels(L), sizes(L);
+    for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }     // GLOBAL sizes: z_l is the same on every rank
+    int rc = sample_z_device(c, seed_z, levels, sizes, d_z);
+    for (int l = 0; !rc && l + 1 < n_f; l++) rc = launch_fri_fold(c, f[l], n[l] / G, d_z + (size_t)l * 8, m[l], f[l + 1]);
+    for (int l = 0; !rc && l < K; l++) {
+        const size_t nl = n[l] / G, first_l = first_index / (n0 / n[l]);      // slice of layer l: [first_l, first_l + nl)
+        int arity = smw_pick_arity_for_layer(n[l], m[l]);                      // chosen from the GLOBAL layer size
+        bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
+        smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) break;
+        uint32_t* cur; { cudaError_t e = cudaMalloc(&cur, nl * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(leaves)"); break; } }
+        const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
+        if (hashed) rc = hash_leaves_device(c, f[l], d_s, m[l], nl, cur);
+        else rc = launch_pair_leaves(c, p, f[l], d_s, nl, arity, (uint64_t)l, first_l, cur, m[l]);
+        size_t cn = nl, first_c = first_l; int level = 0;
+        while (!rc && arity >= 2 && cn >= (size_t)arity && cn % arity == 0) {    // whole nodes only: the ragged top belongs to the finisher
+            size_t nn = cn / arity; uint32_t* nxt;
+            cudaError_t e = cudaMalloc(&nxt, nn * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(tree level)"); break; }
+            rc = launch_merkle_level(c, p, cur, cn, nxt, nn, arity, (uint32_t)level, (uint64_t)l, 0, first_c / arity, 1, 0, 0);
+            cudaStreamSynchronize(c->stream); cudaFree(cur);
+            cur = nxt; cn = nn; first_c /= arity; level++;
+        }
+        s->cap.push_back(cur); s->cap_n.push_back(cn); s->cap_level.push_back(level); s->arity.push_back(arity);
+    }
+    if (!rc && K <= L) { s->tail = f[K]; s->tail_n = n[K] / G; }
+    free_f(); cudaFree(d_z);
+    if (rc) return fail(rc);
+    *out = s.release();
+    return SMW_OK;
+}
+int32_t smw_fri_shard_num_local_layers(const smw_fri_shard* s) { return s ? s->K : -1; }
+int32_t smw_fri_shard_cap_info(const smw_fri_shard* s, int32_t l, size_t* n_nodes, int32_t* cap_level, int32_t* arity) {
+    if (!s || l < 0 || l >= s->K) return SMW_ERR_INVALID_ARG;
+    if (n_nodes) *n_nodes = s->cap_n[l]; if (cap_level) *cap_level = s->cap_level[l]; if (arity) *arity = s->arity[l];
+    return SMW_OK;
+}
+int32_t smw_fri_shard_cap(smw_fri_shard* s, int32_t l, void* out, int32_t mem) {
+    if (!s || !out || l < 0 || l >= s->K) return SMW_ERR_INVALID_ARG;
+    smw_ctx* c = s->ctx; cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaMemcpyAsync(out, s->cap[l], s->cap_n[l] * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK;
+}
+size_t smw_fri_shard_tail_len(const smw_fri_shard* s) { return s ? s->tail_n : 0; }
+int32_t smw_fri_shard_tail(smw_fri_shard* s, void* out, int32_t mem) {
+    if (!s || (s->tail_n && !out)) return SMW_ERR_INVALID_ARG;
+    if (s->tail_n == 0) return SMW_OK;
+    smw_ctx* c = s->ctx; cudaSetDevice(c->device);
+    SMW_CUDA(c, cudaMemcpyAsync(out, s->tail, s->tail_n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK;
+}
+// root of the tree whose DS-level-`level` children are `nodes` (level 0: the leaves / leaf digests themselves)
+int32_t smw_merkle_root_from_level(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, int32_t level, const void* nodes, size_t n, int32_t mem, void* root_out_host) {
+    if (!root_out_host || level < 0) return SMW_ERR_INVALID_ARG;
+    int rc = check_tree_args(c, p, arity, n); if (rc) return rc;
+    if (!nodes) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n * FR));
+    SMW_CUDA(c, cudaMemcpyAsync(d0, nodes, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    smw_tree* t = nullptr;
+    rc = build_tree(c, p, arity, label, d0, true, n, &t, (uint32_t)level); if (rc) return rc;
+    rc = smw_tree_root(t, root_out_host);
+    smw_tree_free(t);
+    return rc;
+}
 
 // ---------------------------------------------------------------------------------------- MF sum-check commit loop
 int32_t smw_sumcheck_round_coeffs(smw_ctx* c, const void* layer, size_t n, void* c0_host, void* c1_host, int32_t mem) {

@@ -49,3 +49,75 @@ def gather_roots(local_roots, n_cols, device=None):
         a, b = column_range(r, world, n_cols)
         parts.append(host[r, : b - a])
     return np.concatenate(parts, axis=0)
+
+
+# ----------------------------------------------------------------------------- one large polynomial, sharded by ranges
+def fri_shard_plan(n0, schedule, world):
+    """Which layers of the FRI-like commit phase (deep_ali/src/fri.rs:231-312) a rank can commit from its own slice when
+    f0 is split into `world` equal contiguous slices: layer l is local while n_l / world is a whole number of fold blocks
+    (so the slice of f_l folds into exactly the slice of f_{l+1}; the last layer needs no fold).  Returns
+    (K, sizes): layers [0, K) are local, sizes[l] = global n_l.  Mirrors smw_fri_shard_build (csrc/capi.cu)."""
+    n = [int(n0)]
+    for m in schedule:
+        assert n[-1] % m == 0, "layer size must be divisible by m"
+        n.append(n[-1] // m)
+    ms = list(schedule) + [1]
+    L, K = len(schedule), 0
+    while K <= L and n[K] % world == 0 and (K == L or (n[K] // world) % ms[K] == 0):
+        K += 1
+    return K, n
+
+
+def all_gather_rows(local, group=None, device=None):
+    """all-gather of equally sized (k, 4) uint64 blocks in rank order -> (world * k, 4); one small collective."""
+    import torch
+    import torch.distributed as dist
+    local = np.ascontiguousarray(local, dtype=np.uint64).reshape(-1, 4)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local.copy()
+    world = dist.get_world_size(group)
+    mine = torch.from_numpy(local.view(np.int64).copy())
+    if device is not None:
+        mine = mine.to(device)
+    out = torch.empty((world,) + tuple(mine.shape), dtype=torch.int64, device=mine.device)
+    dist.all_gather_into_tensor(out.view(-1), mine.view(-1), group=group)
+    return out.cpu().numpy().view(np.uint64).reshape(-1, 4)
+
+
+class GpuFriBackend:
+    """the product path: every step is a C-ABI call into libsmw.so on this rank's GPU"""
+
+    def __init__(self, ctx):
+        from . import api
+        self.ctx, self.api = ctx, api
+
+    def shard(self, f0_slice, n0, first_index, schedule, seed_z):
+        return self.api.FriShard(self.ctx, f0_slice, n0, first_index, self.api.FriProverParams(schedule, seed_z))
+
+    def root_from_level(self, nodes, level, arity, label):
+        return self.api.merkle_root_from_level(self.ctx, nodes, level, arity, self.api.poseidon_params_for_arity(self.ctx, arity), label)
+
+    def build_from(self, f, schedule, seed_z, level0):
+        return self.api.fri_build_transcript(self.ctx, f, self.api.FriProverParams(schedule, seed_z), level0=level0).roots()
+
+
+def fri_roots_sharded(backend, f0_slice, n0, rank, world, schedule, seed_z, gather=all_gather_rows):
+    """Layer roots of fri_build_transcript (deep_ali/src/fri.rs:231-312) for ONE polynomial of n0 evaluations held as `world`
+    contiguous slices, one per rank.  No exchange for the folds; per layer one all-gather of the cap nodes
+    (the highest tree level that is complete inside a slice), every rank finishes the tree tops redundantly; the layers that
+    are too small to split are rebuilt by every rank from one all-gather of the first such layer.  Returns (L + 1, 4) uint64,
+    identical on every rank and to the single-process result."""
+    n_local = len(f0_slice)
+    assert n_local * world == n0, "equal contiguous slices only"
+    K, sizes = fri_shard_plan(n0, schedule, world)
+    sh = backend.shard(f0_slice, n0, rank * n_local, schedule, seed_z)
+    assert sh.num_local_layers == K, "device and host disagree on the shard plan"
+    roots = []
+    for l in range(K):
+        nodes, level, arity = sh.cap(l)
+        roots.append(backend.root_from_level(gather(nodes), level, arity, l))
+    if K <= len(schedule):
+        f_k = gather(sh.tail())
+        assert f_k.shape[0] == sizes[K]
+        roots.extend(list(backend.build_from(f_k, list(schedule[K:]), seed_z, K)))
+    return np.stack([np.asarray(r, dtype=np.uint64).reshape(4) for r in roots])

@@ -63,3 +63,48 @@ def test_ranges():
     rs = [shard.leaf_range(r, 8, 1 << 22, 4) for r in range(8)]
     assert rs[0][0] == 0 and rs[-1][1] == 1 << 22 and all(a[1] == b[0] for a, b in zip(rs, rs[1:])) and all(a % 4 == 0 for a, _ in rs)
     assert shard.leaf_range(5, 8, 8, 4) == (8, 8)       # fewer blocks than ranks: empty tail ranges
+
+
+# ----------------------------------------------------------------------------- one polynomial, range-sharded FRI commit phase
+def _fri_worker(rank, world, port, n0, schedule, seed_z, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle import oracle as O
+    from oracle_shard_backend import OracleFriBackend
+    O.lib(); O.set_threads(1)
+    f0 = O.StdRng.seed_from_u64(n0).fr_rand(n0)                 # every rank derives the same polynomial, keeps its slice only
+    k = n0 // world
+    roots = shard.fri_roots_sharded(OracleFriBackend(), f0[rank * k:(rank + 1) * k], n0, rank, world, schedule, seed_z)
+    q.put((rank, roots))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n0,schedule", [(2, 64, [2] * 6), (2, 512, [8, 8]), (4, 256, [4, 2, 2])])
+def test_range_sharded_fri_roots_match_single_process(O, world, n0, schedule):
+    seed_z = 0xDEEFBAAD
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fri_worker, args=(r, world, port, n0, schedule, seed_z, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = O.FriProverState(O.StdRng.seed_from_u64(n0).fr_rand(n0), schedule, seed_z).roots()
+    for r in range(world):
+        assert np.array_equal(got[r], want), "rank %d" % r
+
+
+def test_fri_shard_plan():
+    # cfg3 at 8 GPUs: 2^22, fold 2: slices of 2^19 fold locally down to one element per rank (layer 19); layers 19..22 are the tail
+    K, n = shard.fri_shard_plan(1 << 22, [2] * 22, 8)
+    assert K == 19 and n[19] == 8
+    # [16, 16, 8] on 2^22 at 8 GPUs: 2^19 -> 2^15 -> 2^11 -> 2^8 per rank: every layer (and the final one) is local
+    K, n = shard.fri_shard_plan(1 << 22, [16, 16, 8], 8)
+    assert K == 4 and n[3] == 1 << 11
+    assert shard.fri_shard_plan(64, [2] * 6, 1)[0] == 7
