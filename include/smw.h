@@ -112,6 +112,10 @@ int32_t smw_commitment_commit(smw_ctx* ctx, uint64_t ds_tag, smw_params* params_
 
 /* ---- NTT / coset LDE (fft/src/lib.rs:6-32) ---------------------------------- */
 int32_t smw_ntt(smw_ctx* ctx, void* buf, int32_t log_n, int32_t inverse, int32_t n_cols, int32_t mem);   /* fft_in_place / ifft_in_place per column, natural order in and out */
+/* building blocks of the cross-GPU four-step NTT (no reference counterpart): buf[i] *= g^i, and an in-place
+ * DFT of length 2^log_g (<= 16) across stride-spaced elements for every offset j < count */
+int32_t smw_scale_powers(smw_ctx* ctx, void* buf, size_t n, const void* g_fr_host, int32_t mem);
+int32_t smw_dft_strided(smw_ctx* ctx, void* buf, int32_t log_g, size_t stride, size_t count, int32_t mem);
 int32_t smw_lde(smw_ctx* ctx, const void* in, int32_t log_n, int32_t log_blowup, const void* shift_fr_host, void* out, int32_t n_cols, int32_t mem);
 /* the benchmark pipeline: LDE of n_cols columns, then one arity-16 commitment-default tree per extended column */
 int32_t smw_lde_commit(smw_ctx* ctx, const void* cols, int32_t log_n, int32_t log_blowup, const void* shift_fr_host, int32_t n_cols,

@@ -422,6 +422,22 @@ def _ntt(ctx, a, inverse):
     return v
 
 
+def scale_powers(ctx, buf, g):
+    """buf[i] *= g^i in place (host numpy (n, 4) uint64 or a CUDA torch tensor): twiddle step of the four-step NTT, coset scaling"""
+    p, n, mem, _k = _buf(buf)
+    gg = _fr1(g)
+    ctx.check(ctx.L.smw_scale_powers(ctx.h, p, n, C.c_void_p(gg.ctypes.data), mem))
+    return _k
+
+
+def dft_strided(ctx, buf, log_g, stride, count):
+    """in place: for every j < count, (buf[a * stride + j])_{a < 2^log_g} -> its DFT with the order-2^log_g root of unity"""
+    p, n, mem, _k = _buf(buf)
+    assert n >= ((1 << log_g) - 1) * stride + count
+    ctx.check(ctx.L.smw_dft_strided(ctx.h, p, int(log_g), int(stride), int(count), mem))
+    return _k
+
+
 def lde(ctx, cols, log_blowup, shift, out=None):
     """coset low-degree extension. cols: (n,4) or (n_cols,n,4) -> (..., n << log_blowup, 4)"""
     sh = _fr1(shift)

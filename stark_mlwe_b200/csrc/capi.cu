@@ -428,6 +428,39 @@ int32_t smw_ntt(smw_ctx* c, void* buf, int32_t log_n, int32_t inverse, int32_t n
     int rc = launch_ntt(c, i.owned, log_n, inverse, n_cols, n); if (rc) return rc;
     return d2h(c, buf, i.owned, n * n_cols * FR);
 }
+// ---- building blocks of the cross-GPU four-step NTT; host orchestration in stark_mlwe_b200/shard.py
+int32_t smw_scale_powers(smw_ctx* c, void* buf, size_t n, const void* g_host, int32_t mem) {
+    if (!c || (n && !buf) || !g_host) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In g(c, g_host, 1, SMW_HOST); if (g.rc) return g.rc;
+    if (mem == SMW_DEVICE) { int rc = launch_scale_powers(c, (uint32_t*)buf, n, g.d); if (rc) return rc; SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK; }
+    In i(c, buf, n, SMW_HOST); if (i.rc) return i.rc;
+    int rc = launch_scale_powers(c, i.owned, n, g.d); if (rc) return rc;
+    return d2h(c, buf, i.owned, n * FR);
+}
+int32_t smw_dft_strided(smw_ctx* c, void* buf, int32_t log_g, size_t stride, size_t count, int32_t mem) {
+    if (!c || !buf || log_g < 0 || log_g > 4 || count > stride) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    const size_t G = (size_t)1 << log_g, total = (G - 1) * stride + count;
+    int rc = SMW_OK;
+    uint32_t* d_w; SMW_CUDA(c, cudaMalloc(&d_w, G * FR));
+    {   // wpow[i] = w_G^i, i < G: a vector of ones scaled by the powers of the order-G root
+        uint32_t* d_root; SMW_CUDA(c, cudaMalloc(&d_root, FR));
+        rc = launch_root_of_unity(c, log_g, d_root);
+        if (!rc) { uint32_t* d_one; cudaMalloc(&d_one, FR); rc = launch_root_of_unity(c, 0, d_one);
+                   for (size_t i = 0; !rc && i < G; i++) cudaMemcpyAsync(d_w + i * 8, d_one, FR, cudaMemcpyDeviceToDevice, c->stream);
+                   if (!rc) rc = launch_scale_powers(c, d_w, G, d_root);
+                   cudaStreamSynchronize(c->stream); cudaFree(d_one); }
+        cudaFree(d_root);
+        if (rc) { cudaFree(d_w); return rc; }
+    }
+    if (mem == SMW_DEVICE) { rc = launch_dft_strided(c, (uint32_t*)buf, log_g, stride, count, d_w); cudaStreamSynchronize(c->stream); cudaFree(d_w); return rc; }
+    In i(c, buf, total, SMW_HOST); if (i.rc) { cudaFree(d_w); return i.rc; }
+    rc = launch_dft_strided(c, i.owned, log_g, stride, count, d_w);
+    if (!rc) rc = d2h(c, buf, i.owned, total * FR);
+    cudaStreamSynchronize(c->stream); cudaFree(d_w);
+    return rc;
+}
 int32_t smw_lde(smw_ctx* c, const void* in, int32_t log_n, int32_t log_blowup, const void* shift_host, void* out, int32_t n_cols, int32_t mem) {
     if (!c || !in || !out || !shift_host || n_cols < 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);

@@ -93,6 +93,63 @@ __global__ void k_gather(const uint32_t* __restrict__ src, const uint64_t* __res
     if (i >= n) return;
     fr_store(out + i * 8, fr_load(src + idx[i] * 8));
 }
+// data[i] *= g^i: two-level power tables (lo[i] = g^i, i < 1024; hi[j] = g^(1024 j)) built per call, then one pass.
+// The twiddle step of the cross-GPU four-step NTT (g = w_N^rank) and any coset scaling.
+__global__ void k_pow_tables(const uint32_t* __restrict__ g, uint32_t* __restrict__ lo, uint32_t* __restrict__ hi, size_t n_hi) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    Fr gg = fr_ldg(g);
+    if (i < 1024) fr_store(lo + i * 8, fr_pow_u64(gg, i));
+    if (i < n_hi) fr_store(hi + i * 8, fr_pow_u64(gg, i << 10));
+}
+__global__ void k_scale_powers(uint32_t* __restrict__ data, size_t n, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr s = fr_mul(fr_ldg(lo + (i & 1023) * 8), fr_ldg(hi + (i >> 10) * 8));
+    fr_store(data + i * 8, fr_mul(fr_load(data + i * 8), s));
+}
+// in-place DFT of length G = 2^LG across `stride`-spaced elements, one thread per offset j < count:
+// (data[a * stride + j])_a  ->  (sum_a data[a * stride + j] * w_G^(a k))_k.  G <= 16: the cross-rank step of the four-step NTT.
+template <int LG> __global__ void k_dft_strided(uint32_t* __restrict__ data, size_t stride, size_t count, const uint32_t* __restrict__ wpow /* w_G^i, i < G */) {
+    constexpr int G = 1 << LG;
+    size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    Fr x[G];
+#pragma unroll
+    for (int a = 0; a < G; a++) x[a] = fr_load(data + ((size_t)a * stride + j) * 8);
+#pragma unroll 1
+    for (int k = 0; k < G; k++) {
+        Fr acc = x[0];
+#pragma unroll
+        for (int a = 1; a < G; a++) {
+            int e = (a * k) & (G - 1);
+            acc = fr_add(acc, e == 0 ? x[a] : fr_mul(x[a], fr_ldg(wpow + e * 8)));
+        }
+        fr_store(data + ((size_t)k * stride + j) * 8, acc);      // safe: every input of this thread is already in registers
+    }
+}
+int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* d_g) {
+    if (n == 0) return SMW_OK;
+    size_t n_hi = (n + 1023) >> 10;
+    uint32_t* d_t; { void* q; int rc = ctx_scratch(c, smw_ctx::SLOT_LDE_G, (1024 + n_hi) * 32, &q); if (rc) return rc; d_t = (uint32_t*)q; }
+    k_pow_tables<<<(unsigned)((std::max<size_t>(1024, n_hi) + 255) / 256), 256, 0, c->stream>>>(d_g, d_t, d_t + 8 * 1024, n_hi); c->launches++;
+    { LaunchScope ls(c, KC_LDE_AUX); k_scale_powers<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_data, n, d_t, d_t + 8 * 1024); }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow) {
+    if (count == 0 || log_g == 0) return SMW_OK;
+    unsigned grid = (unsigned)((count + 127) / 128);
+    LaunchScope ls(c, KC_NTT_PASS);
+    switch (log_g) {
+        case 1: k_dft_strided<1><<<grid, 128, 0, c->stream>>>(d_data, stride, count, d_wpow); break;
+        case 2: k_dft_strided<2><<<grid, 128, 0, c->stream>>>(d_data, stride, count, d_wpow); break;
+        case 3: k_dft_strided<3><<<grid, 128, 0, c->stream>>>(d_data, stride, count, d_wpow); break;
+        case 4: k_dft_strided<4><<<grid, 128, 0, c->stream>>>(d_data, stride, count, d_wpow); break;
+        default: return set_err(c, SMW_ERR_INVALID_ARG, "strided DFT length must be 2..16");
+    }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
 int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size_t n, uint32_t* d_out) {
     if (n == 0) return SMW_OK;
     k_gather<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_src, d_idx, n, d_out); c->launches++;

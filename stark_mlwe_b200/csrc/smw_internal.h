@@ -155,6 +155,8 @@ int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* 
 int launch_gather(smw_ctx* c, const uint32_t* d_src, const uint64_t* d_idx, size_t n, uint32_t* d_out);   // out[i] = src[idx[i]]
 int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0);
 
+int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* d_g);                     // data[i] *= g^i
+int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow);
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 
 // ntt_kernels.cu

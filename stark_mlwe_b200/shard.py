@@ -121,3 +121,97 @@ def fri_roots_sharded(backend, f0_slice, n0, rank, world, schedule, seed_z, gath
         assert f_k.shape[0] == sizes[K]
         roots.extend(list(backend.build_from(f_k, list(schedule[K:]), seed_z, K)))
     return np.stack([np.asarray(r, dtype=np.uint64).reshape(4) for r in roots])
+
+
+# ----------------------------------------------------------------------------- one NTT across all ranks (four-step, one all-to-all)
+def all_to_all_rows(pieces, group=None):
+    """pieces: (world, k, 4) — piece r goes to rank r; returns (world, k, 4) with piece a received from rank a.  A CUDA
+    torch tensor stays on the device (NCCL); numpy goes through a CPU tensor (gloo in the tests)."""
+    import torch
+    import torch.distributed as dist
+    is_t = type(pieces).__module__.startswith("torch")
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return pieces.clone() if is_t else np.array(pieces, dtype=np.uint64, copy=True)
+    src = pieces.contiguous() if is_t else torch.from_numpy(np.ascontiguousarray(pieces, dtype=np.uint64).view(np.int64).copy())
+    out = torch.empty_like(src)
+    try:
+        dist.all_to_all_single(out.view(-1), src.view(-1), group=group)
+    except RuntimeError:                                   # a backend without all-to-all: gather everything, keep my column
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        full = torch.empty((world,) + tuple(src.shape), dtype=src.dtype, device=src.device)
+        dist.all_gather_into_tensor(full.view(-1), src.view(-1), group=group)
+        out = full[:, rank].contiguous()
+    return out if is_t else out.numpy().view(np.uint64)
+
+
+class GpuNttBackend:
+    """device steps of the distributed NTT: C-ABI calls on this rank's GPU; CUDA torch tensors are transformed in place"""
+
+    def __init__(self, ctx):
+        from . import api
+        self.ctx, self.api = ctx, api
+
+    def root_of_unity(self, log_n):
+        return self.ctx.root_of_unity(log_n)
+
+    def ntt(self, a):
+        return self.api._ntt(self.ctx, a, 0)
+
+    def scale_powers(self, a, g):
+        return self.api.scale_powers(self.ctx, a, g)
+
+    def dft_strided(self, a, log_g, stride, count):
+        return self.api.dft_strided(self.ctx, a, log_g, stride, count)
+
+
+def ntt_cyclic_to_chunks(backend, x_local, log_n, rank, world, all_to_all=all_to_all_rows):
+    """Forward NTT of ONE vector of N = 2^log_n elements spread over `world` = G ranks, convention of
+    fft/src/lib.rs:6-12 (X[k] = sum_n x[n] w_N^(n k), natural order).  Input is CYCLIC: x_local[j] = x[rank + G j], j < M = N / G.
+    With n = rank + G j and k = M k1 + k2:   X[M k1 + k2] = sum_rank w_G^(rank k1) * [ w_N^(rank k2) * NTT_M(x_local)[k2] ],
+    so the steps are: local NTT of length M, local twiddle by the powers of w_N^rank, ONE all-to-all that hands rank r the k2-range
+    [r M / G, (r+1) M / G) of every rank, and a length-G DFT across the received pieces.  Output: (G, M / G, 4) with
+    out[k1][j] = X[M k1 + r M / G + j] — G contiguous chunks per rank ("block-cyclic"), which is what the range-sharded FRI
+    commit phase takes as G slices per rank (fri_roots_sharded_chunks)."""
+    G = int(world)
+    log_g = G.bit_length() - 1
+    assert 1 << log_g == G, "the number of ranks must be a power of two"
+    M = (1 << log_n) // G
+    assert x_local.shape[0] == M and M % G == 0
+    y = backend.ntt(x_local)
+    if G == 1:
+        return y.reshape(1, M, 4)
+    w = backend.root_of_unity(log_n)
+    ones = np.tile(np.asarray(backend.root_of_unity(0), dtype=np.uint64).reshape(1, 4), (G, 1))
+    w_rank = np.asarray(backend.scale_powers(ones, w))[rank]                   # w_N^rank
+    y = backend.scale_powers(y, w_rank)
+    t = all_to_all(y.reshape(G, M // G, 4))
+    t = backend.dft_strided(t.reshape(M, 4), log_g, M // G, M // G)
+    return t.reshape(G, M // G, 4)
+
+
+def fri_roots_sharded_chunks(backend, chunks, first_indices, n0, world, schedule, seed_z, gather=all_gather_rows):
+    """fri_roots_sharded for a rank that holds SEVERAL equal contiguous chunks of f0 (chunks[c] starts at first_indices[c]), as
+    the distributed NTT leaves them.  Every (rank, chunk) pair is a slice of the plan with world * len(chunks) slices; caps
+    are gathered rank-major and put back in global order by the gathered start indices."""
+    C = len(chunks)
+    k = len(chunks[0])
+    V = world * C
+    assert k * V == n0
+    K, sizes = fri_shard_plan(n0, schedule, V)
+    shs = [backend.shard(chunks[c], n0, int(first_indices[c]), schedule, seed_z) for c in range(C)]
+    assert all(s.num_local_layers == K for s in shs)
+    starts = gather(np.array([[int(fi), 0, 0, 0] for fi in first_indices], dtype=np.uint64))[:, 0].astype(np.int64)
+    order = np.argsort(starts, kind="stable")                                      # position in the gathered array -> global slice order
+    roots = []
+    for l in range(K):
+        caps = [shs[c].cap(l) for c in range(C)]
+        per = caps[0][0].shape[0]
+        g = gather(np.concatenate([cp[0] for cp in caps])).reshape(V, per, 4)[order].reshape(-1, 4)
+        roots.append(backend.root_from_level(g, caps[0][1], caps[0][2], l))
+    if K <= len(schedule):
+        tails = np.concatenate([s.tail() for s in shs])
+        per = tails.shape[0] // C
+        f_k = gather(tails).reshape(V, per, 4)[order].reshape(-1, 4)
+        assert f_k.shape[0] == sizes[K]
+        roots.extend(list(backend.build_from(f_k, list(schedule[K:]), seed_z, K)))
+    return np.stack([np.asarray(r, dtype=np.uint64).reshape(4) for r in roots])

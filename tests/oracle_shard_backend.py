@@ -82,3 +82,33 @@ class OracleFriBackend:
             top, _ = _levels_up(params, arity, level0 + l, dig, 0, 0, False)
             roots.append(top[0])
         return roots
+
+
+class OracleNttBackend:
+    """CPU stand-in for the device steps of the distributed NTT (shard.ntt_cyclic_to_chunks): oracle NTT and field ops"""
+
+    def root_of_unity(self, log_n):
+        return O.root_of_unity(log_n)
+
+    def ntt(self, a):
+        return O.ntt(a)
+
+    def scale_powers(self, a, g):
+        a = np.asarray(a, dtype=np.uint64).reshape(-1, 4)
+        out, p, g = a.copy(), O.root_of_unity(0).reshape(1, 4), np.asarray(g, dtype=np.uint64).reshape(1, 4)
+        for i in range(len(a)):
+            out[i] = O.fr_mul(a[i:i + 1], p)[0]
+            p = O.fr_mul(p, g)
+        return out
+
+    def dft_strided(self, a, log_g, stride, count):
+        G = 1 << log_g
+        a = np.asarray(a, dtype=np.uint64).reshape(-1, 4)
+        out = a.copy()
+        wp = self.scale_powers(np.tile(O.root_of_unity(0).reshape(1, 4), (G, 1)), O.root_of_unity(log_g))
+        for k in range(G):
+            acc = np.zeros((count, 4), np.uint64)
+            for q in range(G):
+                acc = O.fr_add(acc, O.fr_mul(a[q * stride:q * stride + count], np.tile(wp[(q * k) % G].reshape(1, 4), (count, 1))))
+            out[k * stride:k * stride + count] = acc
+        return out

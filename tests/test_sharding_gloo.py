@@ -108,3 +108,49 @@ def test_fri_shard_plan():
     K, n = shard.fri_shard_plan(1 << 22, [16, 16, 8], 8)
     assert K == 4 and n[3] == 1 << 11
     assert shard.fri_shard_plan(64, [2] * 6, 1)[0] == 7
+
+
+# ----------------------------------------------------------------------------- one NTT across ranks (four-step), then FRI on its chunks
+def _ntt_worker(rank, world, port, log_n, schedule, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle import oracle as O
+    from oracle_shard_backend import OracleFriBackend, OracleNttBackend
+    O.lib(); O.set_threads(1)
+    N = 1 << log_n
+    M = N // world
+    x = O.StdRng.seed_from_u64(log_n).fr_rand(N)
+    chunks = shard.ntt_cyclic_to_chunks(OracleNttBackend(), x[rank::world].copy(), log_n, rank, world)     # cyclic in
+    firsts = [M * k1 + rank * (M // world) for k1 in range(world)]
+    roots = shard.fri_roots_sharded_chunks(OracleFriBackend(), [chunks[c] for c in range(world)], firsts, N, world, schedule, 0xDEEFBAAD)
+    q.put((rank, np.asarray(chunks), roots))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,log_n,schedule", [(2, 6, [2] * 6), (2, 7, [8, 4])])
+def test_distributed_ntt_then_sharded_fri(O, world, log_n, schedule):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ntt_worker, args=(r, world, port, log_n, schedule, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        r, ch, roots = q.get(timeout=240)
+        got[r] = (ch, roots)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    N = 1 << log_n
+    M = N // world
+    X = O.ntt(O.StdRng.seed_from_u64(log_n).fr_rand(N))                           # fft/src/lib.rs:6-12 convention, natural order
+    want_roots = O.FriProverState(X, schedule, 0xDEEFBAAD).roots()
+    for r in range(world):
+        for k1 in range(world):
+            lo = M * k1 + r * (M // world)
+            assert np.array_equal(got[r][0][k1], X[lo:lo + M // world]), "rank %d chunk %d" % (r, k1)
+        assert np.array_equal(got[r][1], want_roots)
