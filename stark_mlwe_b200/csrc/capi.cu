@@ -127,6 +127,28 @@ int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t*
     return rc;
 }
 
+// Runs independent chains of launches on side streams of the context and joins them back into its main stream.  The layers of
+// a FRI commit phase are independent trees whose upper levels (< 148 CTAs) are latency-bound single-wave launches (~0.3-1 ms
+// each, ~16 per layer): on one stream cfg3 spent a third of its time there; on eight streams they overlap the next layers' wide levels.
+struct StreamFan {
+    smw_ctx* c; cudaStream_t main; int K; std::vector<char> used;
+    StreamFan(smw_ctx* ctx, int k) : c(ctx), main(ctx->stream), K(k), used(k, 0) {
+        while ((int)c->side.size() < K) {
+            cudaStream_t s; cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking); c->side.push_back(s);
+            cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming); c->side_ev.push_back(e);
+        }
+        if (!c->fan_ev) cudaEventCreateWithFlags(&c->fan_ev, cudaEventDisableTiming);
+        cudaEventRecord(c->fan_ev, main);
+    }
+    void enter(int i) { int k = i % K; if (!used[k]) { cudaStreamWaitEvent(c->side[k], c->fan_ev, 0); used[k] = 1; } c->stream = c->side[k]; }
+    void leave() { c->stream = main; }
+    ~StreamFan() {
+        c->stream = main;
+        for (int k = 0; k < K; k++) if (used[k]) { cudaEventRecord(c->side_ev[k], c->side[k]); cudaStreamWaitEvent(main, c->side_ev[k], 0); }
+    }
+};
+constexpr int FAN_STREAMS = 8;
+
 // level-by-level tree over a device level 0 (merkle/src/lib.rs:164-181)
 int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out, uint32_t first_ds_level = 0) {
     auto t = std::make_unique<smw_tree>();
@@ -178,6 +200,9 @@ void smw_ctx_destroy(smw_ctx* c) {
     for (auto e : c->prof_pool) cudaEventDestroy(e);
     cudaFree(c->d_twiddles); for (int i = 0; i < smw_ctx::N_SLOTS; i++) cudaFree(c->slot_ptr[i]);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    for (auto st : c->side) cudaStreamDestroy(st);
+    for (auto e : c->side_ev) cudaEventDestroy(e);
+    if (c->fan_ev) cudaEventDestroy(c->fan_ev);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -600,10 +625,16 @@ static void leaf_template(std::vector<Word>& lanes, int* lane_f, int* lane_s) {
     for (size_t i = 0; i < seq.size(); i++) lanes[i] = seq[i];      // 9 lanes < rate 16: no intermediate permutation
     lanes[16] = tag_word(TAG_INIT);
 }
-static int hash_leaves_device(smw_ctx* c, const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out) {
+// d_tmpl: the 17-lane pre-image template already on the device (upload_leaf_template), or nullptr to upload it for this call
+static int upload_leaf_template(smw_ctx* c, uint32_t** d_t, int* lf, int* ls) {
+    std::vector<Word> lanes; leaf_template(lanes, lf, ls);
+    return upload_words(c, lanes, d_t);
+}
+static int hash_leaves_device(smw_ctx* c, const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out, const uint32_t* d_tmpl = nullptr) {
     smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
-    std::vector<Word> lanes; int lf, ls; leaf_template(lanes, &lf, &ls);
-    uint32_t* d_t; rc = upload_words(c, lanes, &d_t); if (rc) return rc;
+    int lf, ls;
+    if (d_tmpl) { std::vector<Word> lanes; leaf_template(lanes, &lf, &ls); return launch_fri_leaf_hashed(c, p, d_tmpl, lf, ls, d_f, d_s, s_div, n, d_out); }
+    uint32_t* d_t; rc = upload_leaf_template(c, &d_t, &lf, &ls); if (rc) return rc;
     rc = launch_fri_leaf_hashed(c, p, d_t, lf, ls, d_f, d_s, s_div, n, d_out);
     cudaStreamSynchronize(c->stream); cudaFree(d_t);
     return rc;
@@ -715,19 +746,32 @@ int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, con
     for (int l = 0; l < L; l++) { levels[l] = level0 + (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
     rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc);
     for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); }
-    // per-layer commitment (fri.rs:267-301); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer
-    for (int l = 0; l <= L; l++) {
-        int arity = smw_pick_arity_for_layer(n[l], m[l]);
-        bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
-        s->arity[l] = arity; s->hashed[l] = hashed;
-        smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) return fail(rc);
-        uint32_t* d_leaves; { cudaError_t e = cudaMalloc(&d_leaves, n[l] * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(leaves)")); }
-        const uint32_t* d_s = (l < L) ? s->f[l + 1] : nullptr;
-        if (hashed) rc = hash_leaves_device(c, s->f[l], d_s, m[l], n[l], d_leaves);
-        else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, level0 + (uint64_t)l, 0, d_leaves, m[l]);
-        if (rc) { cudaFree(d_leaves); return fail(rc); }
-        rc = build_tree(c, p, arity, level0 + (uint64_t)l, d_leaves, true, n[l], &s->tree[l]); if (rc) return fail(rc);
+    // per-layer commitment (fri.rs:267-301); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer.
+    // The layers are independent trees: each one is a chain of launches on its own side stream (StreamFan).
+    uint32_t* d_tmpl = nullptr; { int lf, ls; rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); if (rc) return fail(rc); }
+    for (int l = 0; l <= L; l++) { smw_params* p; rc = smw_params_for_arity(c, smw_pick_arity_for_layer(n[l], m[l]), &p); if (rc) { cudaFree(d_tmpl); return fail(rc); } }   // derive parameter sets before fanning out
+    {
+        StreamFan fan(c, FAN_STREAMS);
+        for (int l = 0; l <= L && !rc; l++) {
+            fan.enter(l);
+            int arity = smw_pick_arity_for_layer(n[l], m[l]);
+            bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
+            s->arity[l] = arity; s->hashed[l] = hashed;
+            smw_params* p; rc = smw_params_for_arity(c, arity, &p);
+            uint32_t* d_leaves = nullptr;
+            if (!rc) { cudaError_t e = cudaMalloc(&d_leaves, n[l] * FR); if (e != cudaSuccess) rc = cuda_err(c, e, "cudaMalloc(leaves)"); }
+            const uint32_t* d_s = (l < L) ? s->f[l + 1] : nullptr;
+            if (!rc) {
+                if (hashed) rc = hash_leaves_device(c, s->f[l], d_s, m[l], n[l], d_leaves, d_tmpl);
+                else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, level0 + (uint64_t)l, 0, d_leaves, m[l]);
+                if (rc) cudaFree(d_leaves);
+            }
+            if (!rc) rc = build_tree(c, p, arity, level0 + (uint64_t)l, d_leaves, true, n[l], &s->tree[l]);
+            fan.leave();
+        }
     }
+    cudaStreamSynchronize(c->stream); cudaFree(d_tmpl);
+    if (rc) return fail(rc);
     *out = s.release();
     return SMW_OK;
 }
@@ -809,25 +853,36 @@ int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, si
     for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }     // GLOBAL sizes: z_l is the same on every rank
     int rc = sample_z_device(c, seed_z, levels, sizes, d_z);
     for (int l = 0; !rc && l + 1 < n_f; l++) rc = launch_fri_fold(c, f[l], n[l] / G, d_z + (size_t)l * 8, m[l], f[l + 1]);
-    for (int l = 0; !rc && l < K; l++) {
-        const size_t nl = n[l] / G, first_l = first_index / (n0 / n[l]);      // slice of layer l: [first_l, first_l + nl)
-        int arity = smw_pick_arity_for_layer(n[l], m[l]);                      // chosen from the GLOBAL layer size
-        bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
-        smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) break;
-        uint32_t* cur; { cudaError_t e = cudaMalloc(&cur, nl * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(leaves)"); break; } }
-        const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
-        if (hashed) rc = hash_leaves_device(c, f[l], d_s, m[l], nl, cur);
-        else rc = launch_pair_leaves(c, p, f[l], d_s, nl, arity, (uint64_t)l, first_l, cur, m[l]);
-        size_t cn = nl, first_c = first_l; int level = 0;
-        while (!rc && arity >= 2 && cn >= (size_t)arity && cn % arity == 0) {    // whole nodes only: the ragged top belongs to the finisher
-            size_t nn = cn / arity; uint32_t* nxt;
-            cudaError_t e = cudaMalloc(&nxt, nn * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(tree level)"); break; }
-            rc = launch_merkle_level(c, p, cur, cn, nxt, nn, arity, (uint32_t)level, (uint64_t)l, 0, first_c / arity, 1, 0, 0);
-            cudaStreamSynchronize(c->stream); cudaFree(cur);
-            cur = nxt; cn = nn; first_c /= arity; level++;
+    uint32_t* d_tmpl = nullptr; if (!rc) { int lf, ls; rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); }
+    for (int l = 0; !rc && l < K; l++) { smw_params* p; rc = smw_params_for_arity(c, smw_pick_arity_for_layer(n[l], m[l]), &p); }
+    std::vector<uint32_t*> spent;                  // intermediate levels, freed after the join (cudaFree would serialise the streams)
+    if (!rc) {
+        StreamFan fan(c, FAN_STREAMS);
+        for (int l = 0; !rc && l < K; l++) {
+            fan.enter(l);
+            const size_t nl = n[l] / G, first_l = first_index / (n0 / n[l]);      // slice of layer l: [first_l, first_l + nl)
+            int arity = smw_pick_arity_for_layer(n[l], m[l]);                      // chosen from the GLOBAL layer size
+            bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
+            smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) { fan.leave(); break; }
+            uint32_t* cur; { cudaError_t e = cudaMalloc(&cur, nl * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(leaves)"); fan.leave(); break; } }
+            const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
+            if (hashed) rc = hash_leaves_device(c, f[l], d_s, m[l], nl, cur, d_tmpl);
+            else rc = launch_pair_leaves(c, p, f[l], d_s, nl, arity, (uint64_t)l, first_l, cur, m[l]);
+            size_t cn = nl, first_c = first_l; int level = 0;
+            while (!rc && arity >= 2 && cn >= (size_t)arity && cn % arity == 0) {    // whole nodes only: the ragged top belongs to the finisher
+                size_t nn = cn / arity; uint32_t* nxt;
+                cudaError_t e = cudaMalloc(&nxt, nn * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(tree level)"); break; }
+                rc = launch_merkle_level(c, p, cur, cn, nxt, nn, arity, (uint32_t)level, (uint64_t)l, 0, first_c / arity, 1, 0, 0);
+                spent.push_back(cur);
+                cur = nxt; cn = nn; first_c /= arity; level++;
+            }
+            s->cap.push_back(cur); s->cap_n.push_back(cn); s->cap_level.push_back(level); s->arity.push_back(arity);
+            fan.leave();
         }
-        s->cap.push_back(cur); s->cap_n.push_back(cn); s->cap_level.push_back(level); s->arity.push_back(arity);
     }
+    cudaStreamSynchronize(c->stream);
+    for (auto* q : spent) cudaFree(q);
+    cudaFree(d_tmpl);
     if (!rc && K <= L) { s->tail = f[K]; s->tail_n = n[K] / G; }
     free_f(); cudaFree(d_z);
     if (rc) return fail(rc);

@@ -46,6 +46,8 @@ struct smw_ctx {
     enum { SLOT_LDE_COEF = 0, SLOT_LDE_G, SLOT_TREE_A, SLOT_TREE_B, SLOT_EXT, SLOT_IN0, SLOT_IN1, N_SLOTS };
     void* slot_ptr[N_SLOTS] = {}; size_t slot_bytes[N_SLOTS] = {};
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
+    // side streams for independent launch chains (the per-layer trees of a FRI commit phase), joined back into `stream`
+    std::vector<cudaStream_t> side; std::vector<cudaEvent_t> side_ev; cudaEvent_t fan_ev = nullptr;
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
     bool prof_on = false;
