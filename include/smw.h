@@ -172,6 +172,8 @@ int32_t smw_mf_fold(smw_ctx* ctx, const void* cur, size_t n, const void* r_fr_ho
 int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host /* k+1 */, void* r_out_host /* k */, void* final_out_host);
 
 /* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */
+int32_t smw_index_from_seed(smw_ctx* ctx, const void* seeds_fr, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem);   /* index_from_seed, deep_ali/src/fri.rs:178-183, element-wise */
+int32_t smw_ali_sample_z_beta(smw_ctx* ctx, const void* fused_fr_host, const void* roots_seed_fr_host, uint64_t n0, void* z_out_fr_host, void* beta_out_fr_host); /* the ChaCha12 part of ali_sample_z_beta_fs, fri.rs:515-533 */
 int32_t smw_tree_open_many(smw_tree* t, const uint64_t* indices, size_t n, smw_proof** out);   /* open_union_of_paths, merkle/src/lib.rs:246-315 */
 int32_t smw_proof_num_levels(const smw_proof* p);
 size_t smw_proof_num_indices(const smw_proof* p);

@@ -746,3 +746,91 @@ def deep_ali_merge_evals(ctx, a, s, e, t, omega, z):
     out = _out(n)
     ctx.check(ctx.L.smw_deep_ali_merge_evals(ctx.h, pa, ps, pe, pt, n, C.c_void_p(w.ctypes.data), C.c_void_p(zz.ctypes.data), C.c_void_p(out.ctypes.data), HOST))
     return out
+
+
+# ----------------------------------------------------------------------------- query phase + DEEP-FRI prover ("next" tier)
+def _fr_from_u64(ctx, v):
+    c = np.zeros((1, 4), dtype=np.uint64)
+    c[0, 0] = int(v)
+    return ctx.from_canonical(c)[0]
+
+
+def index_from_seed(ctx, seeds, n_pow2):
+    """deep_ali/src/fri.rs:178-183, element-wise: StdRng::from_seed(canonical bytes).next_u64() & (n_pow2 - 1)"""
+    p, n, mem, _k = _buf(seeds)
+    out = np.zeros(max(n, 1), dtype=np.uint64)
+    ctx.check(ctx.L.smw_index_from_seed(ctx.h, p, n, int(n_pow2), C.c_void_p(out.ctypes.data), mem))
+    return [int(v) for v in out[:n]]
+
+
+def ali_sample_z_beta_fs(ctx, tag, n0, roots_seed):
+    """deep_ali/src/fri.rs:508-533 -> (z, beta)"""
+    fused = tr_hash_fields_tagged(ctx, tag, np.stack([np.asarray(roots_seed, dtype=np.uint64).reshape(4), _fr_from_u64(ctx, n0)]))
+    z, beta, rs = _out(1), _out(1), _fr1(roots_seed)
+    ctx.check(ctx.L.smw_ali_sample_z_beta(ctx.h, C.c_void_p(fused.ctypes.data), C.c_void_p(rs.ctypes.data), int(n0),
+                                          C.c_void_p(z.ctypes.data), C.c_void_p(beta.ctypes.data)))
+    return z[0], beta[0]
+
+
+def deep_ali_build_f0(ctx, a, s, e, t):
+    """DeepAliRealBuilder::default().build_f0 (deep_ali/src/fri.rs:535-570): no blinding, tag "ALI/DEEP" -> (f0, z)"""
+    n0 = len(a)
+    h = [tr_hash_fields_tagged(ctx, tag, x) for tag, x in ((b"ALI/A", a), (b"ALI/S", s), (b"ALI/E", e), (b"ALI/T", t))]
+    seed_f = tr_hash_fields_tagged(ctx, b"ALI/seed", np.stack(h + [_fr_from_u64(ctx, n0)]))
+    z, _beta = ali_sample_z_beta_fs(ctx, b"ALI/DEEP", n0, seed_f)
+    omega = ctx.root_of_unity(n0.bit_length() - 1)                      # FriDomain::new_radix2 (fri.rs:53-56)
+    return deep_ali_merge_evals(ctx, a, s, e, t, omega, z), z
+
+
+class FriQueryProofs:
+    """what fri_prove_queries (deep_ali/src/fri.rs:355-466) hands to the verifier, as far as proof size goes: the roots seed,
+    per layer the sampled child / parent indices and the two batched multiproofs, and the opening of the final layer"""
+
+    def __init__(self, roots_seed, child_idx, parent_idx, child_proofs, parent_proofs, final_proof, r, L):
+        self.roots_seed, self.child_idx, self.parent_idx = roots_seed, child_idx, parent_idx
+        self.child_proofs, self.parent_proofs, self.final_proof, self.r, self.L = child_proofs, parent_proofs, final_proof, r, L
+
+    def size_bytes(self):
+        """deep_fri_proof_size_bytes (deep_ali/src/fri.rs:775-805)"""
+        nsib = lambda pr: sum(len(x) for x in pr.siblings)       # noqa: E731
+        total = (self.L + 1) * 32 + 32 + 8
+        for c, p in zip(self.child_proofs, self.parent_proofs):
+            total += (nsib(c) + nsib(p)) * 32 + (len(c.indices) + len(p.indices)) * 8
+        total += nsib(self.final_proof) * 32
+        total += self.r * (8 + 64 + self.L * 16 + self.L * 128)
+        return total
+
+
+def fri_prove_queries(ctx, st, r):
+    """deep_ali/src/fri.rs:355-466: query indices from the roots (fs_seed_from_roots :176, index_seed :184-191 with its retry
+    rule) and the per-layer batched openings; every hash, RNG draw and opening runs on the device."""
+    L = len(st.schedule)
+    roots = st.roots()
+    roots_seed = tr_hash_fields_tagged(ctx, b"FRI/seed", roots)
+    one = _fr_from_u64(ctx, 1)
+    child_idx, parent_idx, cps, pps = [], [], [], []
+    for l in range(L):
+        n, m = st.layers[l].n, st.layers[l].m
+        np2 = 1 << max(n - 1, 0).bit_length()
+        fl = _fr_from_u64(ctx, l)
+        seeds = np.stack([tr_hash_fields_tagged(ctx, b"FRI/index", np.stack([roots_seed, fl, _fr_from_u64(ctx, q)])) for q in range(r)])
+        idx = index_from_seed(ctx, seeds, np2)
+        for q in range(r):
+            if idx[q] >= n:                                             # fri.rs:186-190: one re-hash, then wrap
+                rs = tr_hash_fields_tagged(ctx, b"FRI/index", np.stack([seeds[q], one]))
+                i2 = index_from_seed(ctx, rs.reshape(1, 4), np2)[0]
+                idx[q] = i2 if i2 < n else (i2 & (n - 1))
+        ci, pi = idx, [i // m for i in idx]
+        cps.append(st.layers[l].tree.open_many(ci))
+        pps.append(st.layers[l + 1].tree.open_many(pi))
+        child_idx.append(ci)
+        parent_idx.append(pi)
+    final = st.layers[L].tree.open_many([0])
+    return FriQueryProofs(roots_seed, child_idx, parent_idx, cps, pps, final, r, L)
+
+
+def deep_fri_prove(ctx, a, s, e, t, schedule, r, seed_z):
+    """deep_ali/src/fri.rs:601-641 -> (FriProverState, FriQueryProofs); .size_bytes() is the reference's published proof_bytes"""
+    f0, _z = deep_ali_build_f0(ctx, a, s, e, t)
+    st = fri_build_transcript(ctx, f0, FriProverParams(schedule, seed_z))
+    return st, fri_prove_queries(ctx, st, r)

@@ -803,6 +803,28 @@ int32_t smw_fri_roots(smw_fri* s, void* out_host) {
 int32_t smw_fri_z(smw_fri* s, void* out_host) { if (!s || !out_host) return SMW_ERR_INVALID_ARG; if (s->L == 0) return SMW_OK; cudaSetDevice(s->ctx->device); return d2h(s->ctx, out_host, s->d_z, (size_t)s->L * FR); }
 smw_tree* smw_fri_layer_tree(smw_fri* s, int32_t l) { return (s && l >= 0 && l <= s->L) ? s->tree[l] : nullptr; }
 
+// ---------------------------------------------------------------------------------------- query phase helpers ("next" tier)
+int32_t smw_index_from_seed(smw_ctx* c, const void* seeds, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem) {
+    if (!c || (n && (!seeds || !out_idx_host)) || n_pow2 == 0 || (n_pow2 & (n_pow2 - 1))) return SMW_ERR_INVALID_ARG;
+    if (n == 0) return SMW_OK;
+    cudaSetDevice(c->device);
+    In a(c, seeds, n, mem); if (a.rc) return a.rc;
+    uint64_t* d_o; SMW_CUDA(c, cudaMalloc(&d_o, n * 8));
+    int rc = launch_index_from_seed(c, a.d, n, n_pow2, d_o);
+    if (!rc) rc = d2h(c, out_idx_host, d_o, n * 8);
+    cudaStreamSynchronize(c->stream); cudaFree(d_o);
+    return rc;
+}
+int32_t smw_ali_sample_z_beta(smw_ctx* c, const void* fused_host, const void* roots_seed_host, uint64_t n0, void* z_out_host, void* beta_out_host) {
+    if (!c || !fused_host || !roots_seed_host || !z_out_host || !beta_out_host) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In a(c, fused_host, 1, SMW_HOST), b(c, roots_seed_host, 1, SMW_HOST); if (a.rc) return a.rc; if (b.rc) return b.rc;
+    Out z(c, z_out_host, 1, SMW_HOST), be(c, beta_out_host, 1, SMW_HOST); if (z.rc) return z.rc; if (be.rc) return be.rc;
+    int rc = launch_ali_sample(c, a.d, b.d, n0, z.d, be.d); if (rc) return rc;
+    rc = z.finish(); if (rc) return rc;
+    return be.finish();
+}
+
 // ---------------------------------------------------------------------------------------- range-sharded FRI commit phase
 // the fold is over contiguous blocks (fri.rs:95-100) and z_l is public (fri.rs:250), so the rank that holds
 // f_0[first, first + n_local) folds its own slice through every layer with no exchange, hashes its own leaves and builds its

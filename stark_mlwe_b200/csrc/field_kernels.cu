@@ -4,6 +4,7 @@
 // (deep_ali/src/lib.rs:60-105) and the canonical <-> Montgomery conversions.  All HBM-bound.
 #include "smw_internal.h"
 #include "fr32.cuh"
+#include "chacha.cuh"
 #include <algorithm>
 #include <vector>
 
@@ -147,6 +148,42 @@ int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, s
         case 4: k_dft_strided<4><<<grid, 128, 0, c->stream>>>(d_data, stride, count, d_wpow); break;
         default: return set_err(c, SMW_ERR_INVALID_ARG, "strided DFT length must be 2..16");
     }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+// index_from_seed (deep_ali/src/fri.rs:178-183): StdRng::from_seed(canonical LE bytes of the seed).next_u64() & (n_pow2 - 1)
+__global__ void k_index_from_seed(const uint32_t* __restrict__ seeds, size_t n, uint64_t mask, uint64_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Fr c = fr_to_canonical(fr_load(seeds + i * 8));
+    ChaChaRng g; chacha_init(g, c.v);
+    out[i] = chacha_next_u64(g) & mask;
+}
+// ali_sample_z_beta_fs after its hash (deep_ali/src/fri.rs:515-533): beta = first draw; z = first later draw c with c != 0 and
+// c^n0 != 1 (at most 1000 tries), else roots_seed + 17 if that is not an n0-th root of unity, else 19
+__global__ void k_ali_sample(const uint32_t* fused, const uint32_t* roots_seed, uint64_t n0, uint32_t* z_out, uint32_t* beta_out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Fr c = fr_to_canonical(fr_load(fused));
+    ChaChaRng g; chacha_init(g, c.v);
+    fr_store(beta_out, fr_from_u64(chacha_next_u64(g)));
+    const Fr one = fr_const(C_R32);
+    for (int tries = 0; tries < 1000; tries++) {
+        uint64_t v = chacha_next_u64(g);
+        if (v == 0) continue;
+        Fr cand = fr_from_u64(v);
+        if (!fr_eq(fr_pow_u64(cand, n0), one)) { fr_store(z_out, cand); return; }
+    }
+    Fr fb = fr_add(fr_load(roots_seed), fr_from_u64(17));
+    fr_store(z_out, fr_eq(fr_pow_u64(fb, n0), one) ? fr_from_u64(19) : fb);
+}
+int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64_t n_pow2, uint64_t* d_out) {
+    if (n == 0) return SMW_OK;
+    k_index_from_seed<<<(unsigned)((n + 63) / 64), 64, 0, c->stream>>>(d_seeds, n, n_pow2 - 1, d_out); c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta) {
+    k_ali_sample<<<1, 32, 0, c->stream>>>(d_fused, d_roots_seed, n0, d_z, d_beta); c->launches++;
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }

@@ -159,6 +159,8 @@ int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, cons
 
 int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* d_g);                     // data[i] *= g^i
 int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow);
+int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64_t n_pow2, uint64_t* d_out);
+int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta);
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 
 // ntt_kernels.cu
