@@ -422,6 +422,15 @@ def _ntt(ctx, a, inverse):
     return v
 
 
+def f52_dot(ctx, a, b, k):
+    """self-test entry of the FP64-pipe arithmetic: out[i] = sum_{j<k} a[i k + j] * b[i k + j]"""
+    pa, n, mem, _k1 = _buf(a)
+    pb, _n, _m, _k2 = _buf(b)
+    out = _out(n // k)
+    ctx.check(ctx.L.smw_diag_f52_dot(ctx.h, pa, pb, n // k, int(k), C.c_void_p(out.ctypes.data), HOST))
+    return out
+
+
 def scale_powers(ctx, buf, g):
     """buf[i] *= g^i in place (host numpy (n, 4) uint64 or a CUDA torch tensor): twiddle step of the four-step NTT, coset scaling"""
     p, n, mem, _k = _buf(buf)

@@ -183,13 +183,14 @@ int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** ou
     if (cudaSetDevice(device) != cudaSuccess) return SMW_ERR_CUDA;
     smw_ctx* c = new smw_ctx();
     c->device = device;
+    { const char* rep = getenv("SMW_REP"); c->use_f52 = !(rep && strcmp(rep, "29") == 0); }     // SMW_REP=29: integer-pipe multiplier everywhere
     if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
     else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SMW_ERR_CUDA; } c->own_stream = true; }
     *out = c;
     return SMW_OK;
 }
 int32_t smw_ctx_create(int32_t device, smw_ctx** out) { return smw_ctx_create_on_stream(device, nullptr, out); }
-static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_ext); cudaFree(p->d_prog); delete p; }
+static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_tables52); cudaFree(p->d_ext); cudaFree(p->d_prog); delete p; }
 void smw_ctx_destroy(smw_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
@@ -238,6 +239,14 @@ int32_t smw_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_
     return launch_diag_mac_rate(c, mac_per_s, warp_instr_per_clk_per_sm);
 }
 
+int32_t smw_diag_f52_dot(smw_ctx* c, const void* a, const void* b, size_t n_out, int32_t k, void* out, int32_t mem) {
+    if (!c || k < 1 || k > 200 || (n_out && (!a || !b || !out))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    In x(c, a, n_out * k, mem), y(c, b, n_out * k, mem); if (x.rc) return x.rc; if (y.rc) return y.rc;
+    Out o(c, out, n_out, mem); if (o.rc) return o.rc;
+    int rc = launch_f52_dot(c, x.d, y.d, n_out, k, o.d); if (rc) return rc;
+    return o.finish();
+}
 int32_t smw_diag_perm_macs(const smw_params* p, uint64_t* macs_out) {
     if (!p || !macs_out) return SMW_ERR_INVALID_ARG;
     *macs_out = count_macs(p->h_prog, p->perm_first, p->perm_count);

@@ -5,6 +5,7 @@
 #include "smw_internal.h"
 #include "fr32.cuh"
 #include "chacha.cuh"
+#include "fr52.cuh"
 #include <algorithm>
 #include <vector>
 
@@ -184,6 +185,28 @@ int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64
 }
 int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta) {
     k_ali_sample<<<1, 32, 0, c->stream>>>(d_fused, d_roots_seed, n0, d_z, d_beta); c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+// self-test of the FP64-pipe arithmetic (fr52.cuh): out[i] = sum_{j < k} a[i k + j] * b[i k + j], external form in and out
+__global__ void k_f52_dot(const uint32_t* __restrict__ a, const uint32_t* __restrict__ b, size_t n_out, int k, uint32_t* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_out) return;
+    const F52 kin = f52_const(C_KIN52), kout = f52_const(C_KOUT52);
+    Acc52 A; acc52_zero(A);
+    for (int j = 0; j < k; j++) {
+        Fr x = fr_load(a + (i * k + j) * 8), y = fr_load(b + (i * k + j) * 8);
+        F52 X = f52_mul(f52_repack_from32(x.v), kin), Y = f52_mul(f52_repack_from32(y.v), kin);
+        uint64_t yl[5]; f52_canonical_limbs(Y, yl);                 // table operands are canonical (< p): keep the bound of the production path
+        acc52_mac(A, X, f52_from_limbs(yl));
+    }
+    F52 r = acc52_reduce_add2(A, (uint32_t)k, f52_zero(), f52_zero());
+    uint64_t l[5]; f52_canonical_limbs(f52_mul(r, kout), l);
+    Fr o; f52_limbs_to32(l, o.v); fr_store(out + i * 8, o);
+}
+int launch_f52_dot(smw_ctx* c, const uint32_t* d_a, const uint32_t* d_b, size_t n_out, int k, uint32_t* d_out) {
+    if (n_out == 0) return SMW_OK;
+    k_f52_dot<<<(unsigned)((n_out + 63) / 64), 64, 0, c->stream>>>(d_a, d_b, n_out, k, d_out); c->launches++;
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }

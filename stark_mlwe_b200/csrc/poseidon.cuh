@@ -65,6 +65,7 @@ __host__ __device__ inline uint4 make_sqr(int lane, int dst) { return make_op((u
 struct PoseidonDev {
     int t, rp;
     const uint32_t* tbl;     // every table in internal form (x * 2^261 mod p, canonical limbs), EL words per element
+    const uint32_t* tbl52;   // the same elements as 5 doubles of x * 2^260 mod p (fr52.cuh), same EL-word slots; nullptr when not built
     const uint4* prog;       // row operations
     int perm_first, perm_count;       // the production permutation (sparse partial rounds)
     int dense_first, dense_count;     // the literal round structure (dense matrix in every partial round): test aid

@@ -29,6 +29,15 @@ template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* cp, uint32_t* d
     smw_params* p = const_cast<smw_params*>(cp);
     Segs sg; int rc = io_segs(c, p, sparse, &sg); if (rc) return rc;
     PoseidonDev P = dev_view(p);
+#if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52) {
+        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
+        rc = set_smem(c, k_permute_batch52<T>, sm); if (rc) return rc;
+        { LaunchScope ls(c, KC_PERMUTE); k_permute_batch52<T><<<grid, nt, sm, c->stream>>>(d_states, batch, sg, P); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
     rc = set_smem(c, k_permute_batch<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T><<<grid, nt, sm, c->stream>>>(d_states, batch, sg, P); }
@@ -42,6 +51,18 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
+#if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52) {
+        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt);
+        rc = set_smem(c, k_merkle_level52<T>, sm); if (rc) return rc;
+        dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
+        { LaunchScope ls(c, KC_MERKLE_LEVEL);
+          k_merkle_level52<T><<<grid, nt, sm, c->stream>>>(d_children, n_children, d_parents, n_parents, arity, level, label0, label_stride, pos_offset,
+                                                           child_col_stride, parent_col_stride, sg, out_first, P); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
     rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
     dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
@@ -57,6 +78,16 @@ template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_
     Segs sg; int rc = get_sponge_segs(c, p, 4, 2, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
+#if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52) {
+        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt);
+        rc = set_smem(c, k_pair_leaves52<T>, sm); if (rc) return rc;
+        { LaunchScope ls(c, KC_PAIR_LEAVES);
+          k_pair_leaves52<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, sg, out_first, P); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
     const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
     rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_PAIR_LEAVES);
@@ -129,7 +160,24 @@ struct InFriLeaf {
         if (idx == 1) return s ? raw_ext(s) : f29_zero();
         return raw_ext(tmpl + (size_t)(idx - 2) * 8);          // template lane idx-2: a 256-bit little-endian integer (tag / label word)
     }
+    SMW_DEV F52 f52(uint32_t idx) const {
+        if (idx == 0) return raw_ext52(f);
+        if (idx == 1) return s ? raw_ext52(s) : f52_zero();
+        return raw_ext52(tmpl + (size_t)(idx - 2) * 8);
+    }
 };
+__global__ void __launch_bounds__(Cfg52<17>::NT, Cfg52<17>::MINB)
+k_fri_leaf_hashed52(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
+                    size_t s_div, size_t n, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    StateRef52 S = state_ref52<17>(smem, blockDim.x, threadIdx.x);
+    InFriLeaf in{f + i * 8, s ? s + (i / s_div) * 8 : nullptr, tmpl_le256};
+    run_segs52<17>(blockDim.x, P, sg, in);
+    run_ops52<17>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), out + i * 8);
+}
 __global__ void __launch_bounds__(Cfg<17>::NT, Cfg<17>::MINB)
 k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
                   size_t s_div, size_t n, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
@@ -202,6 +250,14 @@ int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* ctrp, const uint32_t* d
     smw_params* trp = const_cast<smw_params*>(ctrp);
     Segs sg; int rc = get_sponge_segs(c, trp, -2, lane_f * 256 + lane_s, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, trp, &out_first); if (rc) return rc;
+    if (c->use_f52 && trp->d_tables52) {
+        const int nt = Cfg52<17>::NT; size_t sm = state_smem_bytes52<17>(nt);
+        rc = set_smem(c, k_fri_leaf_hashed52, sm); if (rc) return rc;
+        { LaunchScope ls(c, KC_FRI_LEAF);
+          k_fri_leaf_hashed52<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, d_f, d_s, s_div, n, d_out, sg, out_first, dev_view(trp)); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
     const int nt = Cfg<17>::NT; size_t sm = state_smem_bytes<17>(nt);
     rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_FRI_LEAF);

@@ -4,6 +4,7 @@
 #pragma once
 #include "smw_internal.h"
 #include "poseidon.cuh"
+#include "poseidon52.cuh"
 #include <vector>
 #include <algorithm>
 
@@ -21,6 +22,7 @@ template <> struct Cfg<129> { static constexpr int NT = 32,  MINB = 1; };
 static PoseidonDev dev_view(const smw_params* p) {
     PoseidonDev d; d.t = p->t; d.rp = p->rp; d.tbl = p->d_tables; d.prog = p->d_prog;
     d.perm_first = p->perm_first; d.perm_count = p->perm_count; d.dense_first = p->dense_first; d.dense_count = p->dense_count;
+    d.tbl52 = p->d_tables52;
     d.k_in = p->layout.k_in; d.k_out = p->layout.k_out; d.k_rr = p->layout.k_rr; d.k_one = p->layout.k_one;
     return d;
 }
@@ -53,7 +55,14 @@ SMW_DEV void zero_lanes(const StateRef& S, int n) {
 }
 
 // ------------------------------------------------------------------ batched permutation
-struct InStates { const uint32_t* st; SMW_DEV F29 operator()(uint32_t idx) const { return raw_ext(st + (size_t)idx * 8); } };
+SMW_DEV F52 raw_ext52(const uint32_t* p) { uint32_t w[8]; load_ext(p, w); return f52_repack_from32(w); }
+SMW_DEV F52 raw_one_ext52() { uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = C_R32W[i];
+    return f52_repack_from32(w); }
+SMW_DEV void emit_ext52(const F52& x, uint32_t* dst) { uint64_t l[5]; f52_canonical_limbs(x, l); uint32_t w[8]; f52_limbs_to32(l, w); store_ext(dst, w); }
+struct InStates { const uint32_t* st; SMW_DEV F29 operator()(uint32_t idx) const { return raw_ext(st + (size_t)idx * 8); }
+                  SMW_DEV F52 f52(uint32_t idx) const { return raw_ext52(st + (size_t)idx * 8); } };
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
 k_permute_batch(uint32_t* states, size_t batch, Segs sg, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -74,6 +83,10 @@ struct InChildren {
     SMW_DEV F29 operator()(uint32_t idx) const {
         if ((int)idx < cnt) return raw_ext(src + (size_t)idx * 8);
         return (int)idx == cnt ? raw_one_ext() : f29_zero();
+    }
+    SMW_DEV F52 f52(uint32_t idx) const {
+        if ((int)idx < cnt) return raw_ext52(src + (size_t)idx * 8);
+        return (int)idx == cnt ? raw_one_ext52() : f52_zero();
     }
 };
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
@@ -109,6 +122,11 @@ struct InPair {
         if (idx == 0) return raw_ext(f);
         if (idx == 1) return cp ? raw_ext(cp) : f29_zero();
         return idx == 2 ? raw_one_ext() : f29_zero();
+    }
+    SMW_DEV F52 f52(uint32_t idx) const {
+        if (idx == 0) return raw_ext52(f);
+        if (idx == 1) return cp ? raw_ext52(cp) : f52_zero();
+        return idx == 2 ? raw_one_ext52() : f52_zero();
     }
 };
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
@@ -147,6 +165,67 @@ template <int T> __global__ void k_hash_ds_single(const uint32_t* ds, int nds, c
     }
     if (cursor != 0) run_perm<T>(1, P);              // absorbing zeros only advances the cursor
     uint32_t w[8]; f29_to_ext(S.load(0), w); store_ext(out, w);
+}
+
+// ------------------------------------------------------------------ the same kernels on the FP64-pipe multiplier (poseidon52.cuh)
+template <int T> struct Cfg52;
+template <> struct Cfg52<9>  { static constexpr int NT = 256, MINB = 2; };     // 11 lanes x 40 B x 256 = 110 KB per CTA
+template <> struct Cfg52<17> { static constexpr int NT = 288, MINB = 1; };     // 19 lanes x 40 B x 288 = 214 KB: nine warps per SM
+SMW_DEV void zero_lanes52(const StateRef52& S, int n) {
+#pragma unroll 1
+    for (int i = 0; i < n; i++) S.store(i, f52_zero());
+}
+template <int T> __global__ void __launch_bounds__(Cfg52<T>::NT, Cfg52<T>::MINB)
+k_permute_batch52(uint32_t* states, size_t batch, Segs sg, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    size_t b = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= batch) return;
+    StateRef52 S = state_ref52<T>(smem, blockDim.x, threadIdx.x);
+    uint32_t* st = states + b * T * 8;
+    InStates in{st};
+    run_segs52<T>(blockDim.x, P, sg, in);
+#pragma unroll 1
+    for (int i = 0; i < T; i++) emit_ext52(S.load(i), st + i * 8);
+}
+template <int T> __global__ void __launch_bounds__(Cfg52<T>::NT, Cfg52<T>::MINB)
+k_merkle_level52(const uint32_t* __restrict__ children, size_t n_children, uint32_t* __restrict__ parents, size_t n_parents,
+                 int arity, uint32_t level, uint64_t label0, uint64_t label_stride, uint64_t pos_offset,
+                 size_t child_col_stride, size_t parent_col_stride, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_parents) return;
+    const int col = blockIdx.y;
+    StateRef52 S = state_ref52<T>(smem, blockDim.x, threadIdx.x);
+    zero_lanes52(S, T);
+    S.store(0, f52_from_u64((uint64_t)arity)); S.store(1, f52_from_u64(level)); S.store(2, f52_from_u64(q + pos_offset)); S.store(3, f52_from_u64(label0 + label_stride * col));
+    size_t base = q * (size_t)arity;
+    InChildren in;
+    in.cnt = (int)((n_children - base < (size_t)arity) ? (n_children - base) : (size_t)arity);
+    in.src = children + ((size_t)col * child_col_stride + base) * 8;
+    const int my_seg = 2 * ((4 + in.cnt + 1 + (T - 2)) / (T - 1)) - 1;
+    F52 out = f52_zero();
+#pragma unroll 1
+    for (int s = 0; s < sg.n; s++) {
+        run_ops52<T>(blockDim.x, P.tbl52, P.prog, sg.first[s], sg.count[s], in);
+        if (s == my_seg) out = S.load(0);
+    }
+    S.store(0, out);
+    run_ops52<T>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), parents + ((size_t)col * parent_col_stride + q) * 8);
+}
+template <int T> __global__ void __launch_bounds__(Cfg52<T>::NT, Cfg52<T>::MINB)
+k_pair_leaves52(const uint32_t* __restrict__ f, const uint32_t* __restrict__ cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
+                uint32_t* __restrict__ out, size_t cp_div, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    StateRef52 S = state_ref52<T>(smem, blockDim.x, threadIdx.x);
+    zero_lanes52(S, T);
+    S.store(0, f52_from_u64((uint64_t)arity)); S.store(1, f52_from_u64(0xffffffffull)); S.store(2, f52_from_u64(i + pos_offset)); S.store(3, f52_from_u64(label));
+    InPair in{f + i * 8, cp ? cp + (i / cp_div) * 8 : nullptr};
+    run_segs52<T>(blockDim.x, P, sg, in);
+    run_ops52<T>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), out + i * 8);
 }
 
 template <typename K> static int set_smem(smw_ctx* c, K kernel, size_t bytes) {

@@ -167,6 +167,21 @@ __global__ void __launch_bounds__(256) k_derive_factor(DeriveArgs a) {
     lu_inplace(a.lu_post, n, a.status, &sh_inv);
 }
 
+// internal 29-bit tables (x * 2^261, canonical) -> the FP64-pipe form (5 doubles of x * 2^260 mod p) in the same element slots
+__device__ __constant__ const uint32_t C_2P260_29[9] = {0x1fffffc1u, 0x14611707u, 0x1a9c5e9eu, 0x00b3f348u, 0x1fff790au, 0x1fffffffu, 0x1fffffffu, 0x1fffffffu, 0x003fffffu};
+SMW_DEV void gs52(uint32_t* base, size_t idx, const F52& x) { double* q = reinterpret_cast<double*>(base + idx * EL);
+#pragma unroll
+    for (int i = 0; i < 5; i++) q[i] = x.v[i];
+    q[5] = 0.0; }
+__global__ void k_tables_to_52(const uint32_t* tbl, size_t n, uint32_t* tbl52, TableLayout L) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t w[8]; f29_repack_to32(f29_canonicalize(f29_mul(gl(tbl, i), f29_const(C_2P260_29))), w);     // x 2^261 * 2^260 / 2^261
+    F52 x = f52_repack_from32(w);
+    if (i == L.k_in) x = f52_const(C_KIN52); else if (i == L.k_out) x = f52_const(C_KOUT52);
+    else if (i == L.k_rr) x = f52_const(C_KRR52); else if (i == L.k_one) x = f52_const(C_KONE52);
+    gs52(tbl52, i, x);
+}
 __global__ void k_store_consts(uint32_t* tbl, TableLayout L) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     gs(tbl, L.k_in, f29_const(C_KIN29)); gs(tbl, L.k_out, f29_const(C_KOUT29)); gs(tbl, L.k_rr, f29_const(C_RR29)); gs(tbl, L.k_one, f29_const(C_ONE29));
@@ -269,6 +284,12 @@ static int finish_params(smw_ctx* c, smw_params* p, uint32_t* mds_internal) {
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));
     cudaFree(scratch); cudaFree(d_status);
     if (st != 0) return set_err(c, st, "Poseidon matrix has a zero pivot (no LU / sparse factorisation)");
+    if (t == 9 || t == 17) {       // the throughput-bound widths also get the FP64-pipe tables (poseidon52.cuh)
+        const size_t ne = p->layout.total;
+        SMW_CUDA(c, cudaMalloc(&p->d_tables52, tables_words(t, rp) * 4));
+        k_tables_to_52<<<(unsigned)((ne + 127) / 128), 128, 0, c->stream>>>(p->d_tables, ne, p->d_tables52, p->layout); c->launches++;
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
     return SMW_OK;
 }
 int launch_derive_params(smw_ctx* c, smw_params* p, const unsigned char* seed, int seed_len) {

@@ -21,6 +21,7 @@ struct smw_params {
     smw_ctx* ctx = nullptr;
     int t = 0, rp = 0;
     uint32_t* d_tables = nullptr;     // one allocation holding every internal-form table
+    uint32_t* d_tables52 = nullptr;   // the FP64-pipe form of the same tables (widths 9 and 17 only; csrc/poseidon52.cuh)
     uint32_t* d_ext = nullptr;        // external-form copies (mds, rc_full, rc_partial) for export
     // device views (pointers into d_tables)
     const uint32_t *lu_full = nullptr, *rc_full = nullptr, *rc_part = nullptr, *sp_row = nullptr, *sp_col = nullptr, *lu_post = nullptr;
@@ -48,6 +49,7 @@ struct smw_ctx {
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
     // side streams for independent launch chains (the per-layer trees of a FRI commit phase), joined back into `stream`
     std::vector<cudaStream_t> side; std::vector<cudaEvent_t> side_ev; cudaEvent_t fan_ev = nullptr;
+    bool use_f52 = true;                         // widths 9/17 batch kernels on the FP64-pipe multiplier (SMW_REP=29 in the environment selects the integer one)
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
     bool prof_on = false;
@@ -161,6 +163,7 @@ int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* 
 int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow);
 int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64_t n_pow2, uint64_t* d_out);
 int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta);
+int launch_f52_dot(smw_ctx* c, const uint32_t* d_a, const uint32_t* d_b, size_t n_out, int k, uint32_t* d_out);
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 
 // ntt_kernels.cu
