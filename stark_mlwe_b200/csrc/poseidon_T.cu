@@ -3,6 +3,7 @@
 // transcript / FRI-leaf kernels, which are fixed at t = 17 (transcript/src/lib.rs:3).
 #include "poseidon_kernels.cuh"
 #include "chacha.cuh"
+#include <cstdlib>
 #ifndef SMW_T
 #error "compile with -DSMW_T=<width>"
 #endif
@@ -10,6 +11,14 @@
 namespace smw {
 
 constexpr int T = SMW_T;
+
+// threads per CTA actually launched: the kernels' __launch_bounds__ give the maximum (and the register budget); small CTAs
+// retire and refill independently, which measurably shortens the levels (profiles/r01r_cta_size_sweep.txt), so the
+// defaults are one or two warps per CTA.  SMW_NT52 / SMW_NT29 override them for tuning runs.
+static int launch_threads(int deflt, int max_nt, const char* env) {
+    if (const char* e = getenv(env)) { int v = atoi(e); if (v >= 32 && v <= max_nt && v % 32 == 0) return v; }
+    return deflt;
+}
 
 // segment list [load lanes][permutation][lanes -> external scale] of the batched permutation
 static int io_segs(smw_ctx* c, smw_params* p, bool sparse, Segs* sg) {
@@ -31,14 +40,14 @@ template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* cp, uint32_t* d
     PoseidonDev P = dev_view(p);
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52) {
-        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
+        const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
         rc = set_smem(c, k_permute_batch52<T>, sm); if (rc) return rc;
         { LaunchScope ls(c, KC_PERMUTE); k_permute_batch52<T><<<grid, nt, sm, c->stream>>>(d_states, batch, sg, P); }
         SMW_CUDA(c, cudaGetLastError());
         return SMW_OK;
     }
 #endif
-    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
+    const int nt = launch_threads(Cfg<T>::RUN, Cfg<T>::NT, "SMW_NT29"); size_t sm = state_smem_bytes<T>(nt); unsigned grid = (unsigned)((batch + nt - 1) / nt);
     rc = set_smem(c, k_permute_batch<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_PERMUTE); k_permute_batch<T><<<grid, nt, sm, c->stream>>>(d_states, batch, sg, P); }
     SMW_CUDA(c, cudaGetLastError());
@@ -53,7 +62,8 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     PoseidonDev P = dev_view(p);
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52) {
-        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt);
+        const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52");
+        size_t sm = state_smem_bytes52<T>(nt);
         rc = set_smem(c, k_merkle_level52<T>, sm); if (rc) return rc;
         dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
         { LaunchScope ls(c, KC_MERKLE_LEVEL);
@@ -63,7 +73,8 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
         return SMW_OK;
     }
 #endif
-    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
+    const int nt = launch_threads(Cfg<T>::RUN, Cfg<T>::NT, "SMW_NT29");
+    size_t sm = state_smem_bytes<T>(nt);
     rc = set_smem(c, k_merkle_level<T>, sm); if (rc) return rc;
     dim3 grid((unsigned)((n_parents + nt - 1) / nt), (unsigned)n_cols);
     { LaunchScope ls(c, KC_MERKLE_LEVEL);
@@ -80,7 +91,7 @@ template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_
     PoseidonDev P = dev_view(p);
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52) {
-        const int nt = Cfg52<T>::NT; size_t sm = state_smem_bytes52<T>(nt);
+        const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<T>(nt);
         rc = set_smem(c, k_pair_leaves52<T>, sm); if (rc) return rc;
         { LaunchScope ls(c, KC_PAIR_LEAVES);
           k_pair_leaves52<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, sg, out_first, P); }
@@ -88,7 +99,7 @@ template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_
         return SMW_OK;
     }
 #endif
-    const int nt = Cfg<T>::NT; size_t sm = state_smem_bytes<T>(nt);
+    const int nt = launch_threads(Cfg<T>::RUN, Cfg<T>::NT, "SMW_NT29"); size_t sm = state_smem_bytes<T>(nt);
     rc = set_smem(c, k_pair_leaves<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_PAIR_LEAVES);
       k_pair_leaves<T><<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div, sg, out_first, P); }
@@ -251,14 +262,14 @@ int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* ctrp, const uint32_t* d
     Segs sg; int rc = get_sponge_segs(c, trp, -2, lane_f * 256 + lane_s, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, trp, &out_first); if (rc) return rc;
     if (c->use_f52 && trp->d_tables52) {
-        const int nt = Cfg52<17>::NT; size_t sm = state_smem_bytes52<17>(nt);
+        const int nt = launch_threads(Cfg52<17>::RUN, Cfg52<17>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<17>(nt);
         rc = set_smem(c, k_fri_leaf_hashed52, sm); if (rc) return rc;
         { LaunchScope ls(c, KC_FRI_LEAF);
           k_fri_leaf_hashed52<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, d_f, d_s, s_div, n, d_out, sg, out_first, dev_view(trp)); }
         SMW_CUDA(c, cudaGetLastError());
         return SMW_OK;
     }
-    const int nt = Cfg<17>::NT; size_t sm = state_smem_bytes<17>(nt);
+    const int nt = launch_threads(Cfg<17>::RUN, Cfg<17>::NT, "SMW_NT29"); size_t sm = state_smem_bytes<17>(nt);
     rc = set_smem(c, k_fri_leaf_hashed, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_FRI_LEAF);
       k_fri_leaf_hashed<<<(unsigned)((n + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, d_f, d_s, s_div, n, d_out, sg, out_first, dev_view(trp)); }

@@ -13,11 +13,12 @@ namespace smw {
 // launch shape per width: threads per CTA and CTAs per SM so that the per-thread state ((T + 1) * 36 B)
 // fills shared memory: t=9 -> 2 x 256, t=17 -> 2 x 160 (207 KB), larger widths 1 CTA.
 template <int T> struct Cfg;
-template <> struct Cfg<9>   { static constexpr int NT = 256, MINB = 2; };
-template <> struct Cfg<17>  { static constexpr int NT = 160, MINB = 2; };
-template <> struct Cfg<33>  { static constexpr int NT = 160, MINB = 1; };
-template <> struct Cfg<65>  { static constexpr int NT = 96,  MINB = 1; };
-template <> struct Cfg<129> { static constexpr int NT = 32,  MINB = 1; };
+// NT / MINB: the __launch_bounds__ (register budget for that many resident threads); RUN: threads per CTA actually launched
+template <> struct Cfg<9>   { static constexpr int NT = 256, MINB = 2, RUN = 64; };
+template <> struct Cfg<17>  { static constexpr int NT = 160, MINB = 2, RUN = 64; };
+template <> struct Cfg<33>  { static constexpr int NT = 160, MINB = 1, RUN = 160; };
+template <> struct Cfg<65>  { static constexpr int NT = 96,  MINB = 1, RUN = 96; };
+template <> struct Cfg<129> { static constexpr int NT = 32,  MINB = 1, RUN = 32; };
 
 static PoseidonDev dev_view(const smw_params* p) {
     PoseidonDev d; d.t = p->t; d.rp = p->rp; d.tbl = p->d_tables; d.prog = p->d_prog;
@@ -169,8 +170,8 @@ template <int T> __global__ void k_hash_ds_single(const uint32_t* ds, int nds, c
 
 // ------------------------------------------------------------------ the same kernels on the FP64-pipe multiplier (poseidon52.cuh)
 template <int T> struct Cfg52;
-template <> struct Cfg52<9>  { static constexpr int NT = 256, MINB = 2; };     // 11 lanes x 40 B x 256 = 110 KB per CTA
-template <> struct Cfg52<17> { static constexpr int NT = 288, MINB = 1; };     // 19 lanes x 40 B x 288 = 214 KB: nine warps per SM
+template <> struct Cfg52<9>  { static constexpr int NT = 256, MINB = 2, RUN = 32; };     // 11 lanes x 40 B: 15 one-warp CTAs per SM
+template <> struct Cfg52<17> { static constexpr int NT = 288, MINB = 1, RUN = 32; };     // 19 lanes x 40 B: 9 one-warp CTAs per SM (760 B per thread)
 SMW_DEV void zero_lanes52(const StateRef52& S, int n) {
 #pragma unroll 1
     for (int i = 0; i < n; i++) S.store(i, f52_zero());
