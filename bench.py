@@ -32,10 +32,10 @@ UNIT = "Fr elems/s"
 SEED = 0x5EED0002
 SHIFT = 5                    # coset shift g = field generator
 MM_PERM_T17 = 21408          # dense Fr multiplications per t = 17 permutation, as the reference computes
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_merkle_level<17> launch from the committed ncu --set full capture
-# (profiles/r01h_ncu_merkle_level17_stalls_pipes_mix.json: level 0 of 16 columns x 2^18 leaves, whose algorithmic bytes are
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_merkle_level52<17> launch from the committed ncu --set full capture
+# (profiles/r01q_ncu_merkle_level52_stalls_pipes_mix.json: level 0 of 16 columns x 2^18 leaves, whose algorithmic bytes are
 # 16 * 2^18 * 32 * (1 + 1/16) = 142 606 336): the kernel moves what it must and nothing else; it is multiplier-bound.
-TRAFFIC_NCU = 136739584 + 6227712
+TRAFFIC_NCU = 136443392 + 7582976
 MAC_PER_MM = 136             # 32x32->64 multiply-accumulates per 8-limb CIOS Montgomery multiplication
 
 
@@ -256,16 +256,27 @@ def main():
             cn = nn
         ml_s = ml_ms * 1e-3 / args.steps        # seconds per step inside the Merkle-level kernel (all levels)
         alg_mac = perms * MM_PERM_T17 * MAC_PER_MM
-        mac_perm = smw.commitment_default_params(ctx).executed_macs()    # counted from the device program (81 per term, 45 per reduction)
-        exe_mac = perms * mac_perm
+        pdef = smw.commitment_default_params(ctx)
+        mac_perm = pdef.executed_macs()          # counted from the device program (81 per term, 45 per reduction): the integer-multiplier form
+        fp_perm = pdef.executed_fp64_ops()       # > 0 when the kernel runs on the FP64-pipe multiplier (fr52.cuh): DFMA.RZ + DADD per permutation
+        if fp_perm:
+            fp_peak, fp_winstr = ctx.fp64_rate()
+            executed = {"pipe": "fp64", "achieved": perms * fp_perm / ml_s / 1e12, "peak": fp_peak / 1e12, "unit": "T fp64 instr/s (DFMA.RZ + DADD lanes)",
+                        "frac": perms * fp_perm / ml_s / fp_peak, "fp64_ops_per_permutation": fp_perm,
+                        "integer_equivalent_mac_per_permutation": mac_perm,
+                        "peak_source": "measured live in this run: 16 DFMA.RZ chains x 512 threads/SM, ~40 ms per repetition (smw_diag_fp64_rate), %.2f warp-instr/clk/SM" % fp_winstr}
+            kernel_name = "k_merkle_level52<17> (5x52-bit limbs on the FP64 pipe; SMW_REP=29 selects the 9x29-bit IMAD.WIDE kernel)"
+        else:
+            executed = {"pipe": "imad", "achieved": perms * mac_perm / ml_s / 1e12, "frac": perms * mac_perm / ml_s / mac_peak, "mac_per_permutation": mac_perm}
+            kernel_name = "k_merkle_level<17>"
         alg_bytes = nc * (N * 32 + sum_levels_bytes(N))
         roofline = {
-            "bound": "imad", "kernel": "k_merkle_level<17>",
-            "achieved": alg_mac / ml_s / 1e12, "peak": mac_peak / 1e12, "unit": "T mac32/s (32x32+64 multiply-accumulates; algorithmic = dense reference count)",
+            "bound": "imad", "kernel": kernel_name,
+            "achieved": alg_mac / ml_s / 1e12, "peak": mac_peak / 1e12, "unit": "T mac32/s (32x32+64 multiply-accumulates; algorithmic = dense reference count of SURVEY 8d)",
             "frac": alg_mac / ml_s / mac_peak,
-            "executed": {"achieved": exe_mac / ml_s / 1e12, "frac": exe_mac / ml_s / mac_peak, "mac_per_permutation": mac_perm},
+            "executed": executed,
             "peak_source": "measured live in this run: accumulating IMAD.WIDE.U32 (32x32+64->64), 16 chains x 512 threads/SM, ~40 ms per repetition (smw_diag_mac_rate; SASS-verified loop), %.2f warp-instr/clk/SM" % winstr,
-            "frac_executed": exe_mac / ml_s / mac_peak,
+            "frac_executed": executed["frac"],
             "traffic": TRAFFIC_NCU, "traffic_launch": "ncu capture of level 0, 16 columns x 2^18 leaves: algorithmic bytes 142606336",
             "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps, "permutations_per_step": perms,
             "permutations_per_s": perms / ml_s,
@@ -275,7 +286,7 @@ def main():
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": secs * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u32 limbs (Pallas Fr, 9x29-bit lazy Montgomery in Poseidon, 8x32-bit in NTT)", "data": "synthetic",
+            "dtype": "Pallas Fr, exact integer arithmetic: 5x52-bit limbs carried in f64 (DFMA.RZ split) in the Poseidon kernels, 8x32-bit in NTT/folds", "data": "synthetic",
             "config": {"workload": "cfg2: 2^%d-row trace, %d columns per GPU, blow-up %d: coset LDE + arity-16 Poseidon-Merkle commit per column" % (args.log_n, nc, 1 << lb),
                        "field": "Pallas Fr (the field the reference uses; SURVEY.md D1)", "columns_total": world * nc, "committed_elems_per_step": world * committed_per_rank,
                        "l2": "inputs (%.1f GB) and extended columns (%.1f GB) exceed the 126 MB L2" % (nc * n * 32 / 1e9, nc * N * 32 / 1e9),

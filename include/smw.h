@@ -68,6 +68,10 @@ int32_t smw_ctx_profile_enable(smw_ctx* ctx, int32_t on);
 int32_t smw_ctx_profile_read(smw_ctx* ctx, double* ms_out, uint64_t* launches_out, int32_t n_classes);   /* syncs, sums, resets */
 int32_t smw_diag_mac_rate(smw_ctx* ctx, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 /* 32x32+64 multiply-accumulates one production permutation of this parameter set executes (counted from its program) */
+/* the FP64-pipe counterparts: measured DFMA.RZ issue rate, and the FP64 instructions (DFMA + DADD) one production permutation of
+ * this parameter set executes when it runs on the fr52 multiplier (0 otherwise) */
+int32_t smw_diag_fp64_rate(smw_ctx* ctx, double* dfma_per_s, double* warp_instr_per_clk_per_sm);
+int32_t smw_diag_perm_fp64_ops(const smw_params* params, uint64_t* ops_out);
 /* self-test of the FP64-pipe field arithmetic (csrc/fr52.cuh): out[i] = sum_{j<k} a[i k + j] * b[i k + j] */
 int32_t smw_diag_f52_dot(smw_ctx* ctx, const void* a, const void* b, size_t n_out, int32_t k, void* out, int32_t mem);
 int32_t smw_diag_perm_macs(const smw_params* params, uint64_t* macs_out);

@@ -46,7 +46,7 @@ def load():
     A = {
         "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp],
         "smw_last_error": [vp], "smw_ctx_launch_count": [vp], "smw_ctx_stream": [vp],
-        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_f52_dot": [vp, vp, vp, sz, i32, vp, i32], "smw_index_from_seed": [vp, vp, sz, u64, vp, i32], "smw_ali_sample_z_beta": [vp, vp, vp, u64, vp, vp], "smw_scale_powers": [vp, vp, sz, vp, i32], "smw_dft_strided": [vp, vp, i32, sz, sz, i32],
+        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_fp64_rate": [vp, vp, vp], "smw_diag_perm_fp64_ops": [vp, vp], "smw_diag_f52_dot": [vp, vp, vp, sz, i32, vp, i32], "smw_index_from_seed": [vp, vp, sz, u64, vp, i32], "smw_ali_sample_z_beta": [vp, vp, vp, u64, vp, vp], "smw_scale_powers": [vp, vp, sz, vp, i32], "smw_dft_strided": [vp, vp, i32, sz, sz, i32],
         "smw_fri_build_transcript_from": [vp, vp, sz, vp, i32, u64, u64, i32, vp],
         "smw_fri_shard_build": [vp, vp, sz, sz, sz, vp, i32, u64, i32, vp], "smw_fri_shard_num_local_layers": [vp],
         "smw_fri_shard_cap_info": [vp, i32, vp, vp, vp], "smw_fri_shard_cap": [vp, i32, vp, i32], "smw_fri_shard_tail_len": [vp],

@@ -97,6 +97,12 @@ class Context:
         self.check(self.L.smw_diag_mac_rate(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def fp64_rate(self):
+        """measured DFMA.RZ rate: (instructions per second over all lanes, warp instructions per clock per SM)"""
+        a, b = C.c_double(), C.c_double()
+        self.check(self.L.smw_diag_fp64_rate(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def close(self):
         if self.h:
             self.L.smw_ctx_destroy(self.h)
@@ -142,6 +148,12 @@ class PoseidonParamsDynamic:
         """32x32+64 multiply-accumulates one production permutation executes (counted from the device program)"""
         m = C.c_uint64()
         self.ctx.check(self.ctx.L.smw_diag_perm_macs(self.h, C.byref(m)))
+        return int(m.value)
+
+    def executed_fp64_ops(self):
+        """FP64-pipe instructions (DFMA + DADD) of one production permutation on the fr52 multiplier; 0 on the integer one"""
+        m = C.c_uint64()
+        self.ctx.check(self.ctx.L.smw_diag_perm_fp64_ops(self.h, C.byref(m)))
         return int(m.value)
 
     def export(self):

@@ -239,6 +239,16 @@ int32_t smw_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_
     return launch_diag_mac_rate(c, mac_per_s, warp_instr_per_clk_per_sm);
 }
 
+int32_t smw_diag_fp64_rate(smw_ctx* c, double* dfma_per_s, double* warp_instr_per_clk_per_sm) {
+    if (!c) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    return launch_diag_rate(c, 1, dfma_per_s, warp_instr_per_clk_per_sm);
+}
+int32_t smw_diag_perm_fp64_ops(const smw_params* p, uint64_t* ops_out) {       // 0 when this parameter set runs on the integer multiplier
+    if (!p || !ops_out) return SMW_ERR_INVALID_ARG;
+    *ops_out = (p->d_tables52 && p->ctx->use_f52) ? count_fp64_ops(p->h_prog, p->perm_first, p->perm_count) : 0;
+    return SMW_OK;
+}
 int32_t smw_diag_f52_dot(smw_ctx* c, const void* a, const void* b, size_t n_out, int32_t k, void* out, int32_t mem) {
     if (!c || k < 1 || k > 200 || (n_out && (!a || !b || !out))) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);

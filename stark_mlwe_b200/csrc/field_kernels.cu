@@ -283,7 +283,27 @@ __global__ void __launch_bounds__(256) k_diag_mac(uint32_t* out, const uint32_t*
     out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
-int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) {
+// the same measurement for the FP64 pipe: 16 independent DFMA.RZ chains per thread (what fr52.cuh issues)
+__global__ void __launch_bounds__(256) k_diag_dfma(uint32_t* out, const uint32_t* in, long long* cyc, int iters) {
+    double d[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) d[i] = 1.0 + 1e-9 * (double)(in[(threadIdx.x + 31 * i) & 1023] & 0xffff);
+    const double x = 1.0 - 1e-9 * (double)(in[threadIdx.x & 1023] & 0xff), y = 1e-7;
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) d[i] = __fma_rz(d[i], x, y);
+    }
+    long long t1 = clock64();
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) r ^= (uint32_t)__double_as_longlong(d[i]) ^ (uint32_t)(__double_as_longlong(d[i]) >> 32);
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = r;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) { return launch_diag_rate(c, 0, mac_per_s, winstr); }
+int launch_diag_rate(smw_ctx* c, int fp64, double* mac_per_s, double* winstr) {
     cudaDeviceProp prop; SMW_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
     // 2 CTAs x 256 threads per SM (all resident, so the in-kernel clock and the event clock agree); ~40 ms per repetition
     // so that the clocks settle under this load
@@ -297,7 +317,8 @@ int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) {
     std::vector<long long> h(grid);
     for (int rep = 0; rep < 4; rep++) {
         cudaEventRecord(e0, c->stream);
-        k_diag_mac<<<grid, block, 0, c->stream>>>(out, in, cyc, iters); c->launches++;
+        if (fp64) k_diag_dfma<<<grid, block, 0, c->stream>>>(out, in, cyc, iters); else k_diag_mac<<<grid, block, 0, c->stream>>>(out, in, cyc, iters);
+        c->launches++;
         cudaEventRecord(e1, c->stream);
         SMW_CUDA(c, cudaStreamSynchronize(c->stream));
         float ms = 0; cudaEventElapsedTime(&ms, e0, e1);

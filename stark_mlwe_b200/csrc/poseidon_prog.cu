@@ -77,6 +77,14 @@ uint64_t count_macs(const std::vector<uint4>& ops, int first, int count) {
     return m;
 }
 
+// FP64-pipe instructions (DFMA.RZ + DADD) one run of operations executes on the fr52 path: 75 per term (25 limb products x
+// (high part, subtraction, low part)) + 85 per reduction (5 steps x 14, 10 addend conversions, 5 limb conversions)
+uint64_t count_fp64_ops(const std::vector<uint4>& ops, int first, int count) {
+    uint64_t m = 0;
+    for (int k = first; k < first + count; k++) m += (uint64_t)((ops[k].y >> 8) & 255) * 75 + 85;
+    return m;
+}
+
 // Appends the permutation program; lanes 0..t-1 in, lanes 0..t-1 out, lanes t, t+1 scratch.
 void build_perm_program(std::vector<uint4>& ops, int t, int rp, bool sparse) {
     Builder B{ops, t, rp, table_layout(t, rp), t, t + 1};

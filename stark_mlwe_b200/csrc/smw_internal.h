@@ -165,6 +165,8 @@ int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64
 int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta);
 int launch_f52_dot(smw_ctx* c, const uint32_t* d_a, const uint32_t* d_b, size_t n_out, int k, uint32_t* d_out);
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
+int launch_diag_rate(smw_ctx* c, int fp64, double* per_s, double* warp_instr_per_clk_per_sm);       // fp64 = 1: DFMA.RZ issue rate
+uint64_t count_fp64_ops(const std::vector<uint4>& ops, int first, int count);                          // FP64-pipe instructions of the fr52 path
 
 // ntt_kernels.cu
 int ensure_twiddles(smw_ctx* c, int log_n);
