@@ -70,22 +70,25 @@ SMW_DEV void acc52_mac(Acc52& A, const F52& a, const F52& b) {
 }
 SMW_DEV void acc52_mul(Acc52& A, const F52& a, const F52& b) { acc52_zero(A); acc52_mac(A, a, b); }
 
-// exponent bits one term leaves in column k: nlo[k] low parts (0x433) + nhi[k] high parts (0x467); only bits 52..63 matter mod 2^64
-SMW_DEV void acc52_remove_bias(Acc52& A, uint32_t n_terms) {
-    constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
-#pragma unroll
-    for (int k = 0; k < 10; k++) {
-        const uint32_t per_term = nlo[k] * 0x433u + nhi[k] * 0x467u;
-        A.c[k] -= (uint64_t)((per_term * n_terms) & 0xfffu) << 52;
-    }
-}
 // Montgomery reduction of an accumulator of `n_terms` products, plus two addends on top of the reduced value:
 // returns s + t + (A + M p) / 2^260, limbs < 2^52 (the caller's bounds keep the value below 2^260).
+// Exponent bits: one term leaves nlo[k] low parts (0x433 << 52) and nhi[k] high parts (0x467 << 52) in column k, the five
+// reduction steps add rlo[k] / rhi[k] more, and the two addends two low parts in columns 5..9.  Only bits 52..63 are touched
+// (mod 2^64), so ALL of them are taken out up front with one 32-bit multiply-add on the high word of each column; every
+// column is exact again by the time its carry is taken (all its contributions arrive at steps <= its own index).
 SMW_DEV F52 acc52_reduce_add2(Acc52& A, uint32_t n_terms, const F52& s, const F52& t) {
-    acc52_remove_bias(A, n_terms);
+    constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
+    constexpr uint32_t rlo[10] = {1, 2, 3, 3, 3, 2, 1, 0, 0, 0}, rhi[10] = {0, 1, 2, 3, 3, 3, 2, 1, 0, 0};
 #pragma unroll
-    for (int i = 0; i < 5; i++)        // addends enter columns 5..9 as raw bit patterns of 2^52 + limb; their two exponents are removed here
-        A.c[5 + i] += (uint64_t)__double_as_longlong(s.v[i] + 0x1p52) + (uint64_t)__double_as_longlong(t.v[i] + 0x1p52) - 2 * EXP52;
+    for (int k = 0; k < 10; k++) {
+        const uint32_t per_term = (nlo[k] * 0x433u + nhi[k] * 0x467u) << 20;
+        const uint32_t fixed = (rlo[k] * 0x433u + rhi[k] * 0x467u + (k >= 5 ? 2u * 0x433u : 0u)) << 20;
+        const uint32_t h = (uint32_t)(A.c[k] >> 32) - (per_term * n_terms + fixed);
+        A.c[k] = (A.c[k] & 0xffffffffull) | ((uint64_t)h << 32);
+    }
+#pragma unroll
+    for (int i = 0; i < 5; i++)
+        A.c[5 + i] += (uint64_t)__double_as_longlong(s.v[i] + 0x1p52) + (uint64_t)__double_as_longlong(t.v[i] + 0x1p52);
     const double p0 = (double)P52_0, p1 = (double)P52_1, p2 = (double)P52_2, pinv = (double)PINV52;
 #pragma unroll
     for (int i = 0; i < 5; i++) {
@@ -97,10 +100,10 @@ SMW_DEV F52 acc52_reduce_add2(Acc52& A, uint32_t n_terms, const F52& s, const F5
         const double h0 = __fma_rz(md, p0, 0x1p104), l0 = __fma_rz(md, p0, (0x1p104 + 0x1p52) - h0);
         const double h1 = __fma_rz(md, p1, 0x1p104), l1 = __fma_rz(md, p1, (0x1p104 + 0x1p52) - h1);
         const double h2 = __fma_rz(md, p2, 0x1p104), l2 = __fma_rz(md, p2, (0x1p104 + 0x1p52) - h2);
-        A.c[i] += (uint64_t)__double_as_longlong(l0) - EXP52;                                                   // low 52 bits are now zero
-        A.c[i + 1] += (uint64_t)__double_as_longlong(h0) + (uint64_t)__double_as_longlong(l1) - (EXP104 + EXP52) + (A.c[i] >> 52);
-        A.c[i + 2] += (uint64_t)__double_as_longlong(h1) + (uint64_t)__double_as_longlong(l2) - (EXP104 + EXP52);
-        A.c[i + 3] += (uint64_t)__double_as_longlong(h2) - EXP104;
+        A.c[i] += (uint64_t)__double_as_longlong(l0);                                                             // low 52 bits are now zero
+        A.c[i + 1] += (uint64_t)__double_as_longlong(h0) + (uint64_t)__double_as_longlong(l1) + (A.c[i] >> 52);
+        A.c[i + 2] += (uint64_t)__double_as_longlong(h1) + (uint64_t)__double_as_longlong(l2);
+        A.c[i + 3] += (uint64_t)__double_as_longlong(h2);
         A.c[i + 4] += (m & 63ull) << 46;                                                                          // m * 2^46 = (m >> 6) 2^52 + (m & 63) 2^46
         A.c[i + 5] += m >> 6;
     }

@@ -79,11 +79,21 @@ __device__ __noinline__ void run_ops52(int nt, const uint32_t* __restrict__ tbl,
             acc52_mul(Q, a0, b0);
         }
         if (k < count && !((nn.y >> 24) & OPF_BSTATE)) nb = tbl52_load(tbl, nn.x);
+        // remaining terms, two per iteration with alternating table-operand registers (the next one is in flight during the products)
+        if (n > 1) {
+            F52 b2 = b1;
+            int j = 1;
 #pragma unroll 1
-        for (int j = 1; j < n; j++) {
-            F52 a1 = S.load(j0 + j), bb = b1;
-            if (j + 1 < n) b1 = tbl52_load(tbl, nd.x + j + 1);
-            acc52_mac(Q, a1, bb);
+            while (true) {
+                F52 a1 = S.load(j0 + j);
+                if (j + 1 < n) b2 = tbl52_load(tbl, nd.x + j + 1);
+                acc52_mac(Q, a1, b1);
+                if (++j >= n) break;
+                a1 = S.load(j0 + j);
+                if (j + 1 < n) b1 = tbl52_load(tbl, nd.x + j + 1);
+                acc52_mac(Q, a1, b2);
+                if (++j >= n) break;
+            }
         }
         P = Q; pd = nd; nd = nn;
     }
