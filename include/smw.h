@@ -181,6 +181,16 @@ int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, si
 int32_t smw_index_from_seed(smw_ctx* ctx, const void* seeds_fr, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem);   /* index_from_seed, deep_ali/src/fri.rs:178-183, element-wise */
 int32_t smw_ali_sample_z_beta(smw_ctx* ctx, const void* fused_fr_host, const void* roots_seed_fr_host, uint64_t n0, void* z_out_fr_host, void* beta_out_fr_host); /* the ChaCha12 part of ali_sample_z_beta_fs, fri.rs:515-533 */
 int32_t smw_tree_open_many(smw_tree* t, const uint64_t* indices, size_t n, smw_proof** out);   /* open_union_of_paths, merkle/src/lib.rs:246-315 */
+/* verify_many_ds / verify_pairs_ds (merkle/src/lib.rs:587-701, 725-773).  The MerkleProof (merkle/src/lib.rs:131-143) is passed by its fields:
+ * proof_indices[n_pidx]; for level l < n_levels, n_sib[l] siblings and n_grp[l] group sizes, levels consecutive in `siblings_host` / `group_sizes`;
+ * arity = proof.arity.  values_host: n Fr; pairs_host: n x (f, cp).  *ok_out = 1 / 0 where the reference returns true / false (malformed proofs
+ * are `false`, not errors); the hashes of every recomputed parent (and pair-leaf digest) run on the device, one launch per level. */
+int32_t smw_verify_many_ds(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t tree_label, const void* root_fr_host, const uint64_t* indices, const void* values_host, size_t n,
+                           const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                           const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out);
+int32_t smw_verify_pairs_ds(smw_ctx* ctx, smw_params* p, int32_t arity, uint64_t tree_label, const void* root_fr_host, const uint64_t* indices, const void* pairs_host, size_t n,
+                            const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                            const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out);
 int32_t smw_proof_num_levels(const smw_proof* p);
 size_t smw_proof_num_indices(const smw_proof* p);
 int32_t smw_proof_indices(const smw_proof* p, uint64_t* out);

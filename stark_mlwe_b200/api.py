@@ -277,6 +277,16 @@ class MerkleChannelCfg:
 class MerkleProof:
     """merkle/src/lib.rs:131-143"""
 
+    @classmethod
+    def from_fields(cls, indices, siblings, group_sizes, arity):
+        """a proof as it arrives at a verifier (deserialised fields, no device handle)"""
+        pr = cls.__new__(cls)
+        pr.indices = [int(i) for i in indices]
+        pr.siblings = [np.ascontiguousarray(x, dtype=np.uint64).reshape(-1, 4) for x in siblings]
+        pr.group_sizes = [np.ascontiguousarray(g, dtype=np.uint8).reshape(-1) for g in group_sizes]
+        pr.arity, pr.nlev = int(arity), len(pr.siblings)
+        return pr
+
     def __init__(self, ctx, h, arity):
         L = ctx.L
         nl = int(L.smw_proof_num_levels(h))
@@ -294,6 +304,38 @@ class MerkleProof:
         self.arity = arity
         self.nlev = nl
         L.smw_proof_free(h)
+
+
+def _verify_call(fn, root, indices, payload, per, proof, tree_label, dyn_params):
+    ctx = dyn_params.ctx
+    idx = np.ascontiguousarray(indices, dtype=np.uint64).reshape(-1)
+    pay = np.ascontiguousarray(payload, dtype=np.uint64).reshape(-1, per * 4)
+    if idx.size != pay.shape[0]:
+        return False                                    # indices.len() != values.len()
+    if len(proof.siblings) != len(proof.group_sizes):
+        return False                                    # merkle/src/lib.rs:604
+    nl = len(proof.siblings)
+    pidx = np.ascontiguousarray(proof.indices, dtype=np.uint64).reshape(-1)
+    nsib = (C.c_size_t * max(nl, 1))(*[int(x.shape[0]) for x in proof.siblings])
+    ngrp = (C.c_size_t * max(nl, 1))(*[int(g.shape[0]) for g in proof.group_sizes])
+    sib = np.ascontiguousarray(np.concatenate([x.reshape(-1, 4) for x in proof.siblings] + [np.zeros((1, 4), np.uint64)]))
+    grp = np.ascontiguousarray(np.concatenate([g for g in proof.group_sizes] + [np.zeros(1, np.uint8)]))
+    rt = _fr1(root)
+    ok = C.c_int32(0)
+    ctx.check(fn(ctx.h, dyn_params.h, int(proof.arity), int(tree_label), C.c_void_p(rt.ctypes.data),
+                 C.c_void_p(idx.ctypes.data) if idx.size else None, C.c_void_p(pay.ctypes.data) if idx.size else None, idx.size,
+                 C.c_void_p(pidx.ctypes.data) if pidx.size else None, pidx.size, nl, nsib, C.c_void_p(sib.ctypes.data), ngrp, C.c_void_p(grp.ctypes.data), C.byref(ok)))
+    return bool(ok.value)
+
+
+def verify_many_ds(root, indices, values, proof, tree_label, dyn_params):
+    """merkle/src/lib.rs:587-701 — same argument order and the same `false` cases; parents are recomputed on the device"""
+    return _verify_call(dyn_params.ctx.L.smw_verify_many_ds, root, indices, values, 1, proof, tree_label, dyn_params)
+
+
+def verify_pairs_ds(root, indices, pairs, proof, tree_label, dyn_params):
+    """merkle/src/lib.rs:725-773: `pairs` is n x (f, cp); leaf digests use LEAF_LEVEL_DS"""
+    return _verify_call(dyn_params.ctx.L.smw_verify_pairs_ds, root, indices, pairs, 2, proof, tree_label, dyn_params)
 
 
 class MerkleTree:

@@ -1099,6 +1099,137 @@ int32_t smw_proof_level(const smw_proof* p, int32_t l, void* sib_out, uint8_t* g
 }
 void smw_proof_free(smw_proof* p) { delete p; }
 
+// ---------------------------------------------------------------------------------------- verification (merkle/src/lib.rs:587-701, 725-773)
+// The index work of a multiproof check does not depend on the digests, so the host lays out EVERY level first — which pool
+// entry each child of each recomputed parent comes from (opened value, sibling, parent of the level below) — uploads that
+// once, and the device hashes level after level out of one pool: [pairs | leaves | siblings | parents level 0 | level 1 | ...].
+} // extern "C"
+namespace {
+struct VerifyPlan {
+    std::vector<uint64_t> child_idx, pos; std::vector<uint8_t> cnt;     // all levels concatenated; child_idx is [group][arity]
+    std::vector<size_t> first_group, n_groups;                          // per level
+    size_t pool_entries = 0, final_entry = 0;
+};
+// false = the reference returns false on the structure alone
+bool plan_verify(const std::vector<uint64_t>& req, size_t leaf_base, size_t sib_base, int arity, int n_levels, const size_t* n_sib, const size_t* n_grp,
+                 const uint8_t* group_sizes, VerifyPlan& pl) {
+    std::vector<uint64_t> cur_idx = req; std::vector<size_t> cur_entry(req.size());
+    for (size_t i = 0; i < req.size(); i++) cur_entry[i] = leaf_base + i;
+    size_t sib_off = sib_base, total_sib = 0, goff = 0;
+    for (int l = 0; l < n_levels; l++) total_sib += n_sib[l];
+    size_t next_entry = sib_base + total_sib;
+    for (int l = 0; l < n_levels; l++) {
+        size_t groups = 0;
+        for (size_t a = 0; a < cur_idx.size();) { const uint64_t par = cur_idx[a] / arity; while (a < cur_idx.size() && cur_idx[a] / arity == par) a++; groups++; }
+        if (groups != n_grp[l]) return false;
+        pl.first_group.push_back(pl.cnt.size()); pl.n_groups.push_back(groups);
+        std::vector<uint64_t> nidx; std::vector<size_t> nent; nidx.reserve(groups); nent.reserve(groups);
+        size_t off = 0, g = 0;
+        for (size_t i = 0; i < cur_idx.size(); g++) {
+            const uint64_t parent = cur_idx[i] / arity; size_t j = i; while (j < cur_idx.size() && cur_idx[j] / arity == parent) j++;
+            const size_t cc = group_sizes[goff + g];
+            if (cc == 0 || cc > (size_t)arity) return false;
+            size_t k = i; const size_t row = pl.child_idx.size(); pl.child_idx.resize(row + arity, 0);
+            for (size_t c = 0; c < cc; c++) {
+                if (k < j && cur_idx[k] % arity == c) pl.child_idx[row + c] = cur_entry[k++];
+                else { if (off >= n_sib[l]) return false; pl.child_idx[row + c] = sib_off + off++; }
+            }
+            pl.cnt.push_back((uint8_t)cc); pl.pos.push_back(parent);
+            nidx.push_back(parent); nent.push_back(next_entry++);
+            i = j;
+        }
+        if (off != n_sib[l]) return false;
+        sib_off += n_sib[l]; goff += n_grp[l];
+        cur_idx.swap(nidx); cur_entry.swap(nent);
+    }
+    if (cur_idx.size() != 1) return false;
+    pl.pool_entries = next_entry; pl.final_entry = cur_entry[0];
+    return true;
+}
+template <class V> int upload_vec(smw_ctx* c, const std::vector<V>& h, V** d) {
+    *d = nullptr; if (h.empty()) return SMW_OK;
+    SMW_CUDA(c, cudaMalloc(d, h.size() * sizeof(V)));
+    SMW_CUDA(c, cudaMemcpyAsync(*d, h.data(), h.size() * sizeof(V), cudaMemcpyHostToDevice, c->stream));
+    return SMW_OK;
+}
+struct DevFree { std::vector<void*> v; cudaStream_t st; ~DevFree() { cudaStreamSynchronize(st); for (void* p : v) if (p) cudaFree(p); } };
+
+// pairs != nullptr: 2 * nreq elements (f, cp interleaved, aligned with req) whose leaf digests are computed first; else leaves (nreq)
+int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void* root_host, const std::vector<uint64_t>& req,
+                const std::vector<uint8_t>& leaves, const std::vector<uint8_t>& pairs, int n_levels, const size_t* n_sib, const void* siblings_host,
+                const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+    const size_t nreq = req.size(), n_pairs = pairs.size() / FR, leaf_base = n_pairs, sib_base = leaf_base + nreq;
+    VerifyPlan pl;
+    if (!plan_verify(req, leaf_base, sib_base, arity, n_levels, n_sib, n_grp, group_sizes, pl)) { *ok_out = 0; return SMW_OK; }
+    size_t total_sib = 0; for (int l = 0; l < n_levels; l++) total_sib += n_sib[l];
+    DevFree fr{{}, c->stream};
+    uint32_t* pool = nullptr; SMW_CUDA(c, cudaMalloc(&pool, pl.pool_entries * FR)); fr.v.push_back(pool);
+    if (n_pairs) SMW_CUDA(c, cudaMemcpyAsync(pool, pairs.data(), pairs.size(), cudaMemcpyHostToDevice, c->stream));
+    else SMW_CUDA(c, cudaMemcpyAsync(pool + leaf_base * 8, leaves.data(), leaves.size(), cudaMemcpyHostToDevice, c->stream));
+    if (total_sib) SMW_CUDA(c, cudaMemcpyAsync(pool + sib_base * 8, siblings_host, total_sib * FR, cudaMemcpyHostToDevice, c->stream));
+    int rc;
+    if (n_pairs) {        // encode_leaf_digest_ds, merkle/src/lib.rs:382-390 / 752-763: H(DS(arity, u32::MAX, idx, label), [f, cp])
+        std::vector<uint64_t> ci(nreq * (size_t)arity, 0); std::vector<uint8_t> two(nreq, 2);
+        for (size_t i = 0; i < nreq; i++) { ci[i * arity] = 2 * i; ci[i * arity + 1] = 2 * i + 1; }
+        uint64_t *d_ci, *d_pos; uint8_t* d_two;
+        rc = upload_vec(c, ci, &d_ci); fr.v.push_back(d_ci); if (rc) return rc;
+        rc = upload_vec(c, req, &d_pos); fr.v.push_back(d_pos); if (rc) return rc;
+        rc = upload_vec(c, two, &d_two); fr.v.push_back(d_two); if (rc) return rc;
+        rc = launch_hash_groups(c, p, pool, d_ci, d_two, d_pos, nreq, arity, 0xffffffffu, label, pool + leaf_base * 8); if (rc) return rc;
+    }
+    uint64_t *d_child = nullptr, *d_pos = nullptr; uint8_t* d_cnt = nullptr;
+    rc = upload_vec(c, pl.child_idx, &d_child); fr.v.push_back(d_child); if (rc) return rc;
+    rc = upload_vec(c, pl.pos, &d_pos); fr.v.push_back(d_pos); if (rc) return rc;
+    rc = upload_vec(c, pl.cnt, &d_cnt); fr.v.push_back(d_cnt); if (rc) return rc;
+    size_t out_entry = sib_base + total_sib;
+    for (int l = 0; l < n_levels; l++) {
+        const size_t g0 = pl.first_group[l], ng = pl.n_groups[l];
+        rc = launch_hash_groups(c, p, pool, d_child + g0 * (size_t)arity, d_cnt + g0, d_pos + g0, ng, arity, (uint32_t)l, label, pool + out_entry * 8); if (rc) return rc;
+        out_entry += ng;
+    }
+    uint8_t got[FR]; rc = d2h(c, got, pool + pl.final_entry * 8, FR); if (rc) return rc;
+    *ok_out = memcmp(got, root_host, FR) == 0 ? 1 : 0;
+    return SMW_OK;
+}
+// sort + dedup the requested indices and align the per-index payload (`per` elements each) with them: BTreeMap insert, the last duplicate wins
+bool align_request(const uint64_t* indices, const void* payload, size_t n, size_t per, const uint64_t* proof_indices, size_t n_pidx,
+                   std::vector<uint64_t>& req, std::vector<uint8_t>& aligned) {
+    std::map<uint64_t, size_t> last; for (size_t i = 0; i < n; i++) last[indices[i]] = i;
+    req.clear(); for (auto& kv : last) req.push_back(kv.first);
+    aligned.resize(req.size() * per * FR);
+    size_t k = 0; for (auto& kv : last) { memcpy(aligned.data() + k * per * FR, (const uint8_t*)payload + kv.second * per * FR, per * FR); k++; }
+    if (n_pidx != req.size() || !proof_indices) return false;                    // proof.indices != req
+    for (size_t i = 0; i < n_pidx; i++) if (proof_indices[i] != req[i]) return false;
+    return true;
+}
+} // namespace
+extern "C" {
+
+int32_t smw_verify_many_ds(smw_ctx* c, smw_params* p, int32_t arity, uint64_t tree_label, const void* root_fr_host, const uint64_t* indices, const void* values_host, size_t n,
+                           const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                           const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+    if (!c || !p || !root_fr_host || !ok_out || n_levels < 0 || (n_levels && (!n_sib || !n_grp))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    *ok_out = 0;
+    if (n == 0 || !indices || !values_host) return SMW_OK;                       // :595
+    if (arity < 2 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :609-617 (the reference divides by the arity: < 2 cannot verify anything)
+    std::vector<uint64_t> req; std::vector<uint8_t> leaves;
+    if (!align_request(indices, values_host, n, 1, proof_indices, n_pidx, req, leaves)) return SMW_OK;   // :601
+    return verify_core(c, p, arity, tree_label, root_fr_host, req, leaves, {}, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out);
+}
+int32_t smw_verify_pairs_ds(smw_ctx* c, smw_params* p, int32_t arity, uint64_t tree_label, const void* root_fr_host, const uint64_t* indices, const void* pairs_host, size_t n,
+                            const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                            const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+    if (!c || !p || !root_fr_host || !ok_out || n_levels < 0 || (n_levels && (!n_sib || !n_grp))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    *ok_out = 0;
+    if (n == 0 || !indices || !pairs_host) return SMW_OK;                        // :733
+    if (arity < 2 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :739-747
+    std::vector<uint64_t> req; std::vector<uint8_t> pairs;
+    if (!align_request(indices, pairs_host, n, 2, proof_indices, n_pidx, req, pairs)) return SMW_OK;
+    return verify_core(c, p, arity, tree_label, root_fr_host, req, {}, pairs, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out);
+}
+
 // ---------------------------------------------------------------------------------------- DEEP-ALI merge
 int32_t smw_deep_ali_merge_evals(smw_ctx* c, const void* a, const void* s, const void* e, const void* t, size_t n, const void* omega_host, const void* z_host, void* f0_out, int32_t mem) {
     if (!c || !a || !s || !e || !t || !omega_host || !z_host || !f0_out || n < 2) return SMW_ERR_INVALID_ARG;
