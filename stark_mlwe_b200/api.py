@@ -897,3 +897,121 @@ def deep_fri_prove(ctx, a, s, e, t, schedule, r, seed_z):
     f0, _z = deep_ali_build_f0(ctx, a, s, e, t)
     st = fri_build_transcript(ctx, f0, FriProverParams(schedule, seed_z))
     return st, fri_prove_queries(ctx, st, r)
+
+
+# ------------------------------------------------------------------------------------------------ DeepFriProof + verifier
+class DeepFriParams:
+    """deep_ali/src/fri.rs:572-577"""
+
+    def __init__(self, schedule, r, seed_z):
+        self.schedule, self.r, self.seed_z = [int(m) for m in schedule], int(r), int(seed_z)
+
+
+class LayerBatchProof:
+    """deep_ali/src/fri.rs:316-326"""
+
+    def __init__(self, hashed_leaves, child_indices, child_proof, parent_indices, parent_proof):
+        self.hashed_leaves = bool(hashed_leaves)
+        self.child_indices, self.child_proof = [int(i) for i in child_indices], child_proof
+        self.parent_indices, self.parent_proof = [int(i) for i in parent_indices], parent_proof
+
+
+class FriQueryPayload:
+    """deep_ali/src/fri.rs:579-594: per layer (i, parent_index) and (f_i, s_i, f_parent_b, s_parent_b); the final pair"""
+
+    def __init__(self, refs, payloads, final_index, final_pair):
+        self.per_layer_refs, self.per_layer_payloads = refs, payloads       # [(i, b)], [(4, 4) uint64: f_i, s_i, f_parent_b, s_parent_b]
+        self.final_index, self.final_pair = int(final_index), final_pair
+
+
+class DeepFriProof:
+    """deep_ali/src/fri.rs:596-602"""
+
+    def __init__(self, roots, layers, final_proof, queries, n0, omega0):
+        self.roots, self.layers, self.final_proof, self.queries, self.n0, self.omega0 = roots, layers, final_proof, queries, int(n0), omega0
+
+
+def deep_fri_proof_from_state(ctx, st, qp, params):
+    """the assembly half of deep_fri_prove (deep_ali/src/fri.rs:618-640): batches + the per-query field payloads.  The opened
+    values are gathered from the layers the prover state keeps on the device."""
+    L = len(params.schedule)
+    fs = [(st.layers[l].f, st.layers[l].s) for l in range(L + 1)]
+    layers = []
+    for l in range(L):
+        layers.append(LayerBatchProof(st.layers[l].hashed_leaves, qp.child_proofs[l].indices, qp.child_proofs[l], qp.parent_proofs[l].indices, qp.parent_proofs[l]))
+    queries = []
+    for q in range(params.r):
+        refs, pays = [], []
+        for l in range(L):
+            i, b = int(qp.child_idx[l][q]), int(qp.parent_idx[l][q])
+            refs.append((i, b))
+            pays.append(np.stack([fs[l][0][i], fs[l][1][i], fs[l + 1][0][b], fs[l + 1][1][b]]))
+        queries.append(FriQueryPayload(refs, pays, 0, (fs[L][0][0].copy(), fs[L][1][0].copy())))
+    return DeepFriProof(st.roots(), layers, qp.final_proof, queries, st.layers[0].n, ctx.root_of_unity(st.layers[0].n.bit_length() - 1))
+
+
+def deep_fri_prove_proof(ctx, a, s, e, t, params):
+    """deep_fri_prove (deep_ali/src/fri.rs:604-641) with DeepAliRealBuilder::default() -> DeepFriProof"""
+    st, qp = deep_fri_prove(ctx, a, s, e, t, params.schedule, params.r, params.seed_z)
+    return deep_fri_proof_from_state(ctx, st, qp, params)
+
+
+def _layer_is_hashed(arity):
+    return arity in (128, 64, 32, 16, 8)
+
+
+def _verify_layer_opening(ctx, root, indices, pair_of, proof, n_layer, m, label):
+    """one batched opening of deep_fri_verify (fri.rs:672-727): hashed layers go through hash_leaf_pair + verify_single,
+    the others through verify_pairs; `pair_of` maps index -> (f, s) or is missing it (-> False)"""
+    arity = pick_arity_for_layer(n_layer, m)
+    gp = poseidon_params_for_arity(ctx, arity)             # MerkleChannelCfg::new(arity)
+    vals = []
+    for i in indices:
+        if i not in pair_of:
+            return False
+        vals.append(pair_of[i])
+    if not vals:
+        return verify_many_ds(root, [], np.zeros((0, 4), np.uint64), proof, label, gp)
+    pairs = np.stack([np.stack(v) for v in vals])          # (k, 2, 4)
+    if _layer_is_hashed(arity):
+        leaves = hash_leaf_pair(ctx, np.ascontiguousarray(pairs[:, 0]), np.ascontiguousarray(pairs[:, 1]))
+        return verify_many_ds(root, indices, leaves, proof, label, gp)
+    return verify_pairs_ds(root, indices, pairs, proof, label, gp)
+
+
+def deep_fri_verify(ctx, params, proof):
+    """deep_ali/src/fri.rs:643-762, check for check: structure, the child / parent multiproofs of every layer against the
+    roots, the local fold relation s_i == f_parent[b], the opening of the final layer at index 0.  Hashes run on the device."""
+    L = len(params.schedule)
+    if len(proof.roots) != L + 1 or len(proof.layers) != L or len(proof.queries) != params.r:
+        return False
+    sizes = [proof.n0]
+    for m in params.schedule:
+        if sizes[-1] % m:
+            raise SmwError(5, "schedule not dividing domain size")          # layer_sizes_from_schedule asserts (fri.rs:150)
+        sizes.append(sizes[-1] // m)
+    child_maps, parent_maps = [dict() for _ in range(L)], [dict() for _ in range(L)]
+    for qp in proof.queries:
+        if len(qp.per_layer_refs) != L or len(qp.per_layer_payloads) != L:
+            return False
+        for l in range(L):
+            (i, b), pay = qp.per_layer_refs[l], qp.per_layer_payloads[l]
+            child_maps[l].setdefault(int(i), (pay[0], pay[1]))               # entry().or_insert: the first payload wins
+            parent_maps[l].setdefault(int(b), (pay[2], pay[3]))
+    for l in range(L):
+        lb = proof.layers[l]
+        if not _verify_layer_opening(ctx, proof.roots[l], lb.child_indices, child_maps[l], lb.child_proof, sizes[l], params.schedule[l], l):
+            return False
+        m_next = params.schedule[l + 1] if l + 1 < L else 1
+        if not _verify_layer_opening(ctx, proof.roots[l + 1], lb.parent_indices, parent_maps[l], lb.parent_proof, sizes[l + 1], m_next, l + 1):
+            return False
+    for qp in proof.queries:                                                   # verify_local_check_fold (fri.rs:169-176)
+        for l in range(L):
+            (i, _b), pay = qp.per_layer_refs[l], qp.per_layer_payloads[l]
+            m = params.schedule[l]
+            if i // m >= sizes[l] // m or not np.array_equal(pay[1], pay[2]):
+                return False
+    if proof.queries[0].final_index != 0:
+        return False
+    fin = proof.queries[0].final_pair
+    return _verify_layer_opening(ctx, proof.roots[L], [0], {0: (fin[0], fin[1])}, proof.final_proof, sizes[L], 1, L)

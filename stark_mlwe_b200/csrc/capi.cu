@@ -1169,13 +1169,13 @@ int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void
     if (total_sib) SMW_CUDA(c, cudaMemcpyAsync(pool + sib_base * 8, siblings_host, total_sib * FR, cudaMemcpyHostToDevice, c->stream));
     int rc;
     if (n_pairs) {        // encode_leaf_digest_ds, merkle/src/lib.rs:382-390 / 752-763: H(DS(arity, u32::MAX, idx, label), [f, cp])
-        std::vector<uint64_t> ci(nreq * (size_t)arity, 0); std::vector<uint8_t> two(nreq, 2);
-        for (size_t i = 0; i < nreq; i++) { ci[i * arity] = 2 * i; ci[i * arity + 1] = 2 * i + 1; }
+        std::vector<uint64_t> ci(nreq * 2); std::vector<uint8_t> two(nreq, 2);
+        for (size_t i = 0; i < 2 * nreq; i++) ci[i] = i;
         uint64_t *d_ci, *d_pos; uint8_t* d_two;
         rc = upload_vec(c, ci, &d_ci); fr.v.push_back(d_ci); if (rc) return rc;
         rc = upload_vec(c, req, &d_pos); fr.v.push_back(d_pos); if (rc) return rc;
         rc = upload_vec(c, two, &d_two); fr.v.push_back(d_two); if (rc) return rc;
-        rc = launch_hash_groups(c, p, pool, d_ci, d_two, d_pos, nreq, arity, 0xffffffffu, label, pool + leaf_base * 8); if (rc) return rc;
+        rc = launch_hash_groups(c, p, pool, d_ci, d_two, d_pos, nreq, arity, 2, 0xffffffffu, label, pool + leaf_base * 8); if (rc) return rc;
     }
     uint64_t *d_child = nullptr, *d_pos = nullptr; uint8_t* d_cnt = nullptr;
     rc = upload_vec(c, pl.child_idx, &d_child); fr.v.push_back(d_child); if (rc) return rc;
@@ -1184,7 +1184,7 @@ int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void
     size_t out_entry = sib_base + total_sib;
     for (int l = 0; l < n_levels; l++) {
         const size_t g0 = pl.first_group[l], ng = pl.n_groups[l];
-        rc = launch_hash_groups(c, p, pool, d_child + g0 * (size_t)arity, d_cnt + g0, d_pos + g0, ng, arity, (uint32_t)l, label, pool + out_entry * 8); if (rc) return rc;
+        rc = launch_hash_groups(c, p, pool, d_child + g0 * (size_t)arity, d_cnt + g0, d_pos + g0, ng, arity, arity, (uint32_t)l, label, pool + out_entry * 8); if (rc) return rc;
         out_entry += ng;
     }
     uint8_t got[FR]; rc = d2h(c, got, pool + pl.final_entry * 8, FR); if (rc) return rc;
@@ -1212,7 +1212,7 @@ int32_t smw_verify_many_ds(smw_ctx* c, smw_params* p, int32_t arity, uint64_t tr
     cudaSetDevice(c->device);
     *ok_out = 0;
     if (n == 0 || !indices || !values_host) return SMW_OK;                       // :595
-    if (arity < 2 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :609-617 (the reference divides by the arity: < 2 cannot verify anything)
+    if (arity < 1 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :609-617 (arity 1 is the one-leaf final FRI layer; the reference divides by the arity)
     std::vector<uint64_t> req; std::vector<uint8_t> leaves;
     if (!align_request(indices, values_host, n, 1, proof_indices, n_pidx, req, leaves)) return SMW_OK;   // :601
     return verify_core(c, p, arity, tree_label, root_fr_host, req, leaves, {}, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out);
@@ -1224,7 +1224,7 @@ int32_t smw_verify_pairs_ds(smw_ctx* c, smw_params* p, int32_t arity, uint64_t t
     cudaSetDevice(c->device);
     *ok_out = 0;
     if (n == 0 || !indices || !pairs_host) return SMW_OK;                        // :733
-    if (arity < 2 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :739-747
+    if (arity < 1 || arity > 128 || width_for_arity(arity) != p->t) return SMW_OK;   // :739-747
     std::vector<uint64_t> req; std::vector<uint8_t> pairs;
     if (!align_request(indices, pairs_host, n, 2, proof_indices, n_pidx, req, pairs)) return SMW_OK;
     return verify_core(c, p, arity, tree_label, root_fr_host, req, {}, pairs, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out);

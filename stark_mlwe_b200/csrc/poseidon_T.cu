@@ -84,15 +84,15 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     return SMW_OK;
 }
 template <> int hash_groups_T<T>(smw_ctx* c, const smw_params* cp, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
-                                 size_t n_groups, int arity, uint32_t level, uint64_t label, uint32_t* d_out) {
+                                 size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out) {
     smw_params* p = const_cast<smw_params*>(cp);
-    Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
+    Segs sg; int rc = get_sponge_segs(c, p, 4, row, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
     const int nt = launch_threads(Cfg<T>::RUN, Cfg<T>::NT, "SMW_NT29"); size_t sm = state_smem_bytes<T>(nt);
     rc = set_smem(c, k_hash_groups<T>, sm); if (rc) return rc;
     { LaunchScope ls(c, KC_MERKLE_LEVEL);
-      k_hash_groups<T><<<(unsigned)((n_groups + nt - 1) / nt), nt, sm, c->stream>>>(d_pool, d_child_idx, d_cnt, d_pos, n_groups, arity, level, label, d_out, sg, out_first, P); }
+      k_hash_groups<T><<<(unsigned)((n_groups + nt - 1) / nt), nt, sm, c->stream>>>(d_pool, d_child_idx, d_cnt, d_pos, n_groups, arity, row, level, label, d_out, sg, out_first, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }

@@ -117,7 +117,7 @@ k_merkle_level(const uint32_t* __restrict__ children, size_t n_children, uint32_
     emit_ext(S.load(0), parents + ((size_t)col * parent_col_stride + q) * 8);
 }
 // ------------------------------------------------------------------ explicit groups (verification, merkle/src/lib.rs:632-690, 748-765)
-// thread g: out[g] = hash_with_ds_dynamic([arity, level, pos[g], label], pool[child_idx[g*arity + c]], c < cnt[g]).  The children
+// thread g: out[g] = hash_with_ds_dynamic([arity, level, pos[g], label], pool[child_idx[g*row + c]], c < cnt[g] <= row).  The children
 // of a recomputed parent are scattered (opened values, siblings, parents of the level below), so they are addressed through
 // an index array into one pool; cnt = 2 with level = u32::MAX is the pair-leaf digest.
 struct InGathered {
@@ -129,14 +129,14 @@ struct InGathered {
 };
 template <int T> __global__ void __launch_bounds__(Cfg<T>::NT, Cfg<T>::MINB)
 k_hash_groups(const uint32_t* __restrict__ pool, const uint64_t* __restrict__ child_idx, const uint8_t* __restrict__ cnt, const uint64_t* __restrict__ pos,
-              size_t n_groups, int arity, uint32_t level, uint64_t label, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
+              size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
     extern __shared__ __align__(16) unsigned char smem[];
     size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n_groups) return;
     StateRef S = state_ref<T>(smem, blockDim.x, threadIdx.x);
     zero_lanes(S, T);
     S.store(0, raw_u64((uint64_t)arity)); S.store(1, raw_u64(level)); S.store(2, raw_u64(pos[g])); S.store(3, raw_u64(label));
-    InGathered in{pool, child_idx + g * (size_t)arity, (int)cnt[g]};
+    InGathered in{pool, child_idx + g * (size_t)row, (int)cnt[g]};
     const int my_seg = 2 * ((4 + in.cnt + 1 + (T - 2)) / (T - 1)) - 1;
     F29 o = f29_zero();
 #pragma unroll 1

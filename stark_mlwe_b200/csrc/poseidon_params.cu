@@ -340,9 +340,9 @@ int launch_pair_leaves(smw_ctx* c, const smw_params* p, const uint32_t* d_f, con
     return SMW_OK;
 }
 int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
-                       size_t n_groups, int arity, uint32_t level, uint64_t label, uint32_t* d_out) {
+                       size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out) {
     if (n_groups == 0) return SMW_OK;
-    DISPATCH_T(p->t, return hash_groups_T<T>(c, p, d_pool, d_child_idx, d_cnt, d_pos, n_groups, arity, level, label, d_out));
+    DISPATCH_T(p->t, return hash_groups_T<T>(c, p, d_pool, d_child_idx, d_cnt, d_pos, n_groups, arity, row, level, label, d_out));
     return SMW_OK;
 }
 int launch_hash_ds_single(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out) {

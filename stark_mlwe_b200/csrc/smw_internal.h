@@ -131,9 +131,9 @@ int launch_merkle_level(smw_ctx* c, const smw_params* p, const uint32_t* d_child
 int launch_pair_leaves(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
                        uint32_t* d_out, size_t cp_div);
 int launch_hash_ds_single(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
-// out[g] = H(DS(arity, level, pos[g], label), pool[child_idx[g*arity + c]] for c < cnt[g]) — recomputed parents / pair-leaf digests of a verifier
+// out[g] = H(DS(arity, level, pos[g], label), pool[child_idx[g*row + c]] for c < cnt[g] <= row) — recomputed parents / pair-leaf digests of a verifier
 int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
-                       size_t n_groups, int arity, uint32_t level, uint64_t label, uint32_t* d_out);
+                       size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
 int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
 // transcript program: state' = run(state, pos; immediates A, ext elements B, immediates C, optional final permute)
 int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
@@ -152,7 +152,7 @@ template <int T> int merkle_level_T(smw_ctx* c, const smw_params* p, const uint3
 template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
                                    uint32_t* d_out, size_t cp_div);
 template <int T> int hash_groups_T(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
-                                   size_t n_groups, int arity, uint32_t level, uint64_t label, uint32_t* d_out);
+                                   size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
 template <int T> int hash_ds_single_T(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
 
 // field_kernels.cu
