@@ -4,7 +4,7 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libsmw.so")
+SO_PATH = os.environ.get("SMW_LIB") or os.path.join(_HERE, "libsmw.so")   # SMW_LIB: a tuning build of the same library
 HEADER = os.path.join(_HERE, "..", "include", "smw.h")
 
 OK = 0
