@@ -64,11 +64,14 @@ __device__ __noinline__ void run_ops52(int nt, const uint32_t* __restrict__ tbl,
         F52 b1 = f52_zero();
         if (n > 1) b1 = tbl52_load(tbl, nd.x + 1);
         Acc52 Q;
-        if (!(fl & OPF_DEP)) {
-            F52 a0, b0 = nb;
-            if (fl & OPF_AEXT) a0 = in.f52(nd.w); else a0 = S.load(j0);
-            if (fl & OPF_BSTATE) b0 = S.load((int)nd.x);
-            // ---- the fused block: 25 independent limb products of the new operation + the dependent chain of the old one
+        if (!(fl & (OPF_DEP | OPF_AEXT))) {
+            // operands without a branch (a state-state product reads lane nd.x, a table product re-reads lane j0 and drops it):
+            // one basic block, so the 25 independent limb products can be scheduled into the whole dependent reduction chain
+            const bool bs = (fl & OPF_BSTATE) != 0;
+            const F52 a0 = S.load(j0), bv = S.load(bs ? (int)nd.x : j0);
+            F52 b0;
+#pragma unroll
+            for (int i = 0; i < 5; i++) b0.v[i] = bs ? bv.v[i] : nb.v[i];
             acc52_mul(Q, a0, b0);
             S.store(pdst, acc52_reduce_add2(P, pn, sr, rc));
         } else {
@@ -79,21 +82,21 @@ __device__ __noinline__ void run_ops52(int nt, const uint32_t* __restrict__ tbl,
             acc52_mul(Q, a0, b0);
         }
         if (k < count && !((nn.y >> 24) & OPF_BSTATE)) nb = tbl52_load(tbl, nn.x);
-        // remaining terms, two per iteration with alternating table-operand registers (the next one is in flight during the products)
+        // remaining terms
+        // two terms per basic block (the tail of one product's additions overlaps the head of the next), one left-over term
         if (n > 1) {
-            F52 b2 = b1;
+            F52 b2;
             int j = 1;
 #pragma unroll 1
-            while (true) {
-                F52 a1 = S.load(j0 + j);
-                if (j + 1 < n) b2 = tbl52_load(tbl, nd.x + j + 1);
+            while (j + 1 < n) {
+                const F52 a1 = S.load(j0 + j), a2 = S.load(j0 + j + 1);
+                b2 = tbl52_load(tbl, nd.x + j + 1);
                 acc52_mac(Q, a1, b1);
-                if (++j >= n) break;
-                a1 = S.load(j0 + j);
-                if (j + 1 < n) b1 = tbl52_load(tbl, nd.x + j + 1);
-                acc52_mac(Q, a1, b2);
-                if (++j >= n) break;
+                if (j + 2 < n) b1 = tbl52_load(tbl, nd.x + j + 2);
+                acc52_mac(Q, a2, b2);
+                j += 2;
             }
+            if (j < n) { const F52 a1 = S.load(j0 + j); acc52_mac(Q, a1, b1); }
         }
         P = Q; pd = nd; nd = nn;
     }

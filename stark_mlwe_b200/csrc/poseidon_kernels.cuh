@@ -207,7 +207,10 @@ template <> struct Cfg52<9>  { static constexpr int NT = SMW_T9_NT, MINB = 2, RU
 #else
 template <> struct Cfg52<9>  { static constexpr int NT = 160, MINB = 2, RUN = 32; };     // 204 registers, 10 one-warp CTAs per SM: fold-2 cfg3 483-494 ms against 531-554 ms at 128 registers / 16 warps (profiles/r01z_t9_register_budget.txt)
 #endif
-template <> struct Cfg52<17> { static constexpr int NT = 288, MINB = 1, RUN = 32; };     // 19 lanes x 40 B: 9 one-warp CTAs per SM (760 B per thread)
+#ifndef SMW_T17_NT
+#define SMW_T17_NT 288
+#endif
+template <> struct Cfg52<17> { static constexpr int NT = SMW_T17_NT, MINB = 1, RUN = 32; };     // 19 lanes x 40 B: 9 one-warp CTAs per SM (760 B per thread)
 SMW_DEV void zero_lanes52(const StateRef52& S, int n) {
 #pragma unroll 1
     for (int i = 0; i < n; i++) S.store(i, f52_zero());
