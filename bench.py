@@ -35,7 +35,7 @@ MM_PERM_T17 = 21408          # dense Fr multiplications per t = 17 permutation, 
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_merkle_level52<17> launch from the committed ncu --set full capture
 # (profiles/r01q_ncu_merkle_level52_stalls_pipes_mix.json: level 0 of 16 columns x 2^18 leaves, whose algorithmic bytes are
 # 16 * 2^18 * 32 * (1 + 1/16) = 142 606 336): the kernel moves what it must and nothing else; it is multiplier-bound.
-TRAFFIC_NCU = 136443392 + 7582976
+TRAFFIC_NCU = 136450048 + 6638592   # dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01ac_ncu_full_merkle_level52_details.csv
 MAC_PER_MM = 136             # 32x32->64 multiply-accumulates per 8-limb CIOS Montgomery multiplication
 
 

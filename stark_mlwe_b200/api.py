@@ -404,7 +404,8 @@ def merkle_commit_columns(ctx, cols, arity, params, label0=0, label_stride=1):
     """One MerkleTree::new per column, batched on the device; returns the roots (n_cols, 4)."""
     if _is_torch(cols):
         n_cols, n = cols.shape[0], cols.shape[1]
-        p, mem, keep = C.c_void_p(cols.data_ptr()), DEVICE, cols
+        assert cols.is_contiguous() and cols.element_size() == 8 and cols.shape[-1] == 4
+        p, mem, keep = C.c_void_p(cols.data_ptr()), (DEVICE if cols.is_cuda else HOST), cols     # a (pinned) CPU tensor is a host buffer: staged copies
     else:
         keep = np.ascontiguousarray(cols, dtype=np.uint64)
         n_cols, n = keep.shape[0], keep.shape[1]

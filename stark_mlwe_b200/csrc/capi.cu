@@ -527,6 +527,16 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
     size_t budget = (size_t)16 << 30;
     if (const char* e = getenv("SMW_LDE_CHUNK_BYTES")) { size_t v = strtoull(e, nullptr, 10); if (v) budget = v; }
     const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_cols, budget / (N * FR)));
+    const bool host = (mem == SMW_HOST);
+    // column ranges processed one after the other.  Host input: the copy of range i + 1 runs under the compute of range i, so
+    // a short first range (1/16 of the columns) lets the kernels start after a small copy instead of after the whole input.
+    std::vector<std::pair<int, int>> ranges;      // (first column, count)
+    for (int c0 = 0; c0 < n_cols; c0 += chunk) ranges.push_back({c0, std::min(chunk, n_cols - c0)});
+    if (host && n_cols >= 16 && ranges[0].second > n_cols / 16) {
+        const int head = n_cols / 16, rest = ranges[0].second - head;
+        ranges[0] = {head, rest}; ranges.insert(ranges.begin(), {0, head});
+    }
+    const int n_chunks = (int)ranges.size();
     uint32_t* d_ext = nullptr; uint32_t* d_in[2] = {nullptr, nullptr};
     cudaStream_t copy = nullptr; cudaEvent_t copied[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
     auto cleanup = [&]() {
@@ -536,26 +546,25 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
     };
     { void* q; rc = ctx_scratch(c, smw_ctx::SLOT_EXT, N * (size_t)chunk * FR, &q); if (rc) return rc; d_ext = (uint32_t*)q; }
     cudaError_t e = cudaSuccess;
-    const bool host = (mem == SMW_HOST);
-    const int n_chunks = (n_cols + chunk - 1) / chunk;
     if (host) {
         e = cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking);
         for (int i = 0; i < 2 && e == cudaSuccess; i++) {
-            if (i < n_chunks) { void* q; if (ctx_scratch(c, smw_ctx::SLOT_IN0 + i, n * (size_t)chunk * FR, &q)) e = cudaErrorMemoryAllocation; d_in[i] = (uint32_t*)q; }
+            int widest = 0; for (int ci = i; ci < n_chunks; ci += 2) widest = std::max(widest, ranges[ci].second);      // ranges alternate between the two buffers
+            if (widest) { void* q; if (ctx_scratch(c, smw_ctx::SLOT_IN0 + i, n * (size_t)widest * FR, &q)) e = cudaErrorMemoryAllocation; d_in[i] = (uint32_t*)q; }
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&copied[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming);
         }
         if (e != cudaSuccess) { cleanup(); return cuda_err(c, e, "smw_lde_commit staging"); }
     }
-    auto enqueue_copy = [&](int ci) {      // host columns of chunk ci -> d_in[ci & 1] on the copy stream
-        const int c0 = ci * chunk, nc = std::min(chunk, n_cols - c0);
+    auto enqueue_copy = [&](int ci) {      // host columns of range ci -> d_in[ci & 1] on the copy stream
+        const int c0 = ranges[ci].first, nc = ranges[ci].second;
         if (ci >= 2) cudaStreamWaitEvent(copy, consumed[ci & 1], 0);
         cudaMemcpyAsync(d_in[ci & 1], (const uint8_t*)cols + (size_t)c0 * n * FR, (size_t)nc * n * FR, cudaMemcpyHostToDevice, copy);
         cudaEventRecord(copied[ci & 1], copy);
     };
     if (host) enqueue_copy(0);
     for (int ci = 0; ci < n_chunks && !rc; ci++) {
-        const int c0 = ci * chunk, nc = std::min(chunk, n_cols - c0);
+        const int c0 = ranges[ci].first, nc = ranges[ci].second;
         const uint32_t* src;
         if (host) {
             if (ci + 1 < n_chunks) enqueue_copy(ci + 1);
