@@ -115,3 +115,19 @@ def test_verify_openings_of_fri_layers(ctx, smw, O, rnd):
         gp = smw.poseidon_params_for_arity(ctx, pr.arity)
         assert smw.verify_many_ds(tree.root(), idx, leaves[idx], pr, l, gp)
         assert not smw.verify_many_ds(tree.root(), idx, leaves[idx], pr, l + 1, gp)
+
+
+def test_verify_deserialised_proof(ctx, smw, O, rnd):
+    """prover side: open -> bincode bytes (canonical field encoding from the device conversion); verifier side: bytes -> proof ->
+    device verifier.  The bytes equal what the same proof serialises to through the oracle's conversions."""
+    from stark_mlwe_b200 import wire
+    leaves, tree, gp, op = _tree(ctx, smw, O, rnd, 16, 3000, 991)
+    idx = [0, 1, 17, 2999]
+    pr = tree.open_many(idx)
+    blob = wire.merkle_proof_to_bincode(pr, ctx.to_canonical)
+    assert blob == wire.merkle_proof_to_bincode(pr, O.from_mont_c) and len(blob) == wire.merkle_proof_size_bincode(pr)
+    back = wire.merkle_proof_from_bincode(blob, ctx.from_canonical, smw.MerkleProof.from_fields)
+    assert smw.verify_many_ds(tree.root(), idx, leaves[idx], back, LABEL, gp)
+    flipped = bytearray(blob); flipped[8 + 8 * 4 + 8 + 8 + 8] ^= 1              # lowest byte of the first sibling
+    bad = wire.merkle_proof_from_bincode(bytes(flipped), ctx.from_canonical, smw.MerkleProof.from_fields)
+    assert not smw.verify_many_ds(tree.root(), idx, leaves[idx], bad, LABEL, gp)
