@@ -70,6 +70,18 @@ def test_lde_commit_matches_oracle_per_column(ctx, smw, O, rnd):
         assert eq(roots[c], O.commitment_commit(O.lde(cols[c], 2, shift), 40 + c).root())
 
 
+def test_cfg1_full_size_matches_oracle(ctx, smw, O):
+    """BASELINE configs[0] / SURVEY 8d cfg1 in full: 8 columns x 2^16 rows of the bench generator (seed 0x5EED0001), blow-up 4, coset
+    shift 5, one arity-16 commitment-default tree per extended column with tree_label = column index — every root equals the
+    oracle's, computed here on the host cores (about ten seconds)."""
+    from bench import gen_columns
+    cols = gen_columns(0x5EED0001, 0, 8, 1 << 16)
+    shift = O.to_mont([5])[0]
+    roots = smw.lde_commit(ctx, cols, 2, shift, label0=0)
+    for c in range(8):
+        assert eq(roots[c], O.commitment_commit(O.lde(cols[c], 2, shift), c).root()), "cfg1 column %d" % c
+
+
 def test_full_size_properties_2p20(ctx, smw, O, rnd):
     """BASELINE cfg2 column size (2^20 rows, blow-up 4), checked through size-independent properties:
     ifft(fft(x)) = x; linearity fft(a + b) = fft(a) + fft(b); LDE with shift 1 interpolates the column; and the oracle on
