@@ -1,8 +1,10 @@
 """The reference's own published data reproduced by the GPU path (no oracle in the loop for the number itself):
-crates/channel/benchmarkdata.csv:2-9, column proof_bytes, k = 11..15, on the bench's seeded inputs
+crates/channel/benchmarkdata.csv:2-9, column proof_bytes, k = 11..18 (every published row), on the bench's seeded inputs
 (channel/benches/end_to_end.rs:187-260) through deep_ali_build_f0 -> fri_build_transcript -> fri_prove_queries ->
 deep_fri_proof_size_bytes (deep_ali/src/fri.rs:535-641, 355-466, 775-805) — every sponge, Poseidon constant, DS label,
 fold, DEEP merge, ChaCha12 draw and multiproof opening runs in libsmw.so."""
+import os
+
 import numpy as np
 import pytest
 
@@ -11,8 +13,12 @@ from test_oracle_anchors import CSV, A12, kat_inputs
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("k", [11, 12, 13, 14, 15])
+@pytest.mark.parametrize("k", [11, 12, 13, 14, 15, 16, 17, 18])
 def test_proof_bytes_kat_on_gpu(ctx, smw, O, k):
+    if k > 15 and not os.environ.get("SMW_KAT_FULL"):
+        # the four ALI sponges over n0 elements are strictly serial (one thread, n0/16 permutations each): 42 / 84 / 168 s for
+        # k = 16 / 17 / 18.  All eight rows pass (profiles/r01an_pytest_gpu_proof_bytes_kat_k11_18.log); SMW_KAT_FULL=1 runs them.
+        pytest.skip("k > 15 only with SMW_KAT_FULL=1 (minutes of serial sponge)")
     a, s, e, t = kat_inputs(O, k)              # the oracle only replays rand's StdRng to produce the INPUTS
     st, proofs = smw.deep_fri_prove(ctx, a, s, e, t, [16, 16, 8], 32, 0xDEEFBAAD)
     assert proofs.size_bytes() == CSV[k]
