@@ -111,6 +111,7 @@ int get_transcript_params(smw_ctx* c, smw_params* given, smw_params** out) {
     return smw_params_transcript_default(c, out);
 }
 
+constexpr size_t COOP_ABSORB_MIN = 64;      // elements from which the warp-cooperative absorb (k_transcript_absorb_coop) pays
 // one-shot transcript hash on the device: new(label0) ; absorb_bytes(tag) ; fields ; challenge(chal)
 int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t* tag, size_t tag_len, const std::vector<Word>& imm_fields,
                  const uint32_t* d_ext, size_t n_ext, const char* chal, uint32_t* d_out) {
@@ -121,6 +122,18 @@ int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t*
     for (auto& w : imm_fields) A.push_back(w);
     push_challenge(C, (const uint8_t*)chal, strlen(chal));
     uint32_t *dA, *dC; int rc = upload_words(c, A, &dA); if (rc) return rc; rc = upload_words(c, C, &dC); if (rc) { cudaFree(dA); return rc; }
+    if (n_ext >= COOP_ABSORB_MIN) {          // long input: the serial sponge runs on one warp instead of one thread
+        uint32_t* d_st = nullptr;
+        if (cudaMalloc(&d_st, 17 * FR) != cudaSuccess) { cudaFree(dA); cudaFree(dC); return set_err(c, SMW_ERR_NOMEM, "cudaMalloc(sponge state)"); }
+        rc = launch_transcript_run(c, trp, d_st, 1, 0, dA, (int)A.size(), nullptr, 0, nullptr, 0, 0, nullptr);
+        int pos = advance_pos(0, A.size() - 1);
+        if (!rc) rc = launch_transcript_absorb_coop(c, trp, d_st, pos, d_ext, n_ext);
+        pos = advance_pos(pos, n_ext);
+        if (!rc) rc = launch_transcript_run(c, trp, d_st, 0, pos, nullptr, 0, nullptr, 0, dC, (int)C.size(), 1, d_out);
+        cudaStreamSynchronize(c->stream);
+        cudaFree(d_st); cudaFree(dA); cudaFree(dC);
+        return rc;
+    }
     rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA, (int)A.size(), d_ext, n_ext, dC, (int)C.size(), 1, d_out);
     cudaStreamSynchronize(c->stream);
     cudaFree(dA); cudaFree(dC);
@@ -609,7 +622,8 @@ int32_t smw_transcript_absorb_fields(smw_transcript* t, const void* frs, size_t 
     if (n == 0) return SMW_OK;
     smw_ctx* c = t->ctx; cudaSetDevice(c->device);
     In i(c, frs, n, mem); if (i.rc) return i.rc;
-    int rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, nullptr, 0, i.d, n, nullptr, 0, 0, nullptr);
+    int rc = n >= COOP_ABSORB_MIN ? launch_transcript_absorb_coop(c, t->params, t->d_state, t->pos, i.d, n)
+                                  : launch_transcript_run(c, t->params, t->d_state, 0, t->pos, nullptr, 0, i.d, n, nullptr, 0, 0, nullptr);
     if (!rc) t->pos = advance_pos(t->pos, n);
     return rc;
 }

@@ -174,6 +174,74 @@ __global__ void k_transcript_run(uint32_t* state, int fresh, int pos, const uint
     if (out) { f29_to_ext(S.load(0), w); store_ext(out, w); }
 }
 
+// ------------------------------------------------------------------ bulk absorb, one warp per sponge
+// The transcript sponge over n elements (tr_hash_fields_tagged over a whole evaluation vector, deep_ali/src/fri.rs:28-36, 535-560)
+// is strictly serial: n/16 permutations one after the other.  On one thread a permutation takes ~2.5 ms; here the warp runs the
+// LITERAL round structure (poseidon/src/lib.rs:219-258: ARK, S-box, dense 17x17 mat-vec) with one state lane / output row per
+// thread: 17 lazily accumulated products + one reduction per lane and round, S-boxes lane-parallel.  Field results are exact, so
+// the state after the absorb is bit-identical to the serial kernel's.
+struct CoopTables { uint32_t mds, rc_full, rc_part, k_one; int rp; };
+SMW_DEV void coop_matvec17(F29* st, const uint32_t* tbl, const CoopTables& L, int lane, bool add_rc, uint32_t rc_idx) {
+    F29 y = f29_zero();
+    if (lane < 17) {
+        Acc A; acc_zero(A);
+        F29 b = tbl_load(tbl, L.mds + (uint32_t)lane * 17);
+#pragma unroll 1
+        for (int j = 0; j < 17; j++) {
+            const F29 bb = b;
+            if (j + 1 < 17) b = tbl_load(tbl, L.mds + (uint32_t)lane * 17 + j + 1);
+            if (j == 6 || j == 12) acc_normalize(A);
+            acc_mac(A, st[j], bb);
+        }
+        F29 rc = f29_zero();
+        if (add_rc) rc = tbl_load(tbl, rc_idx);
+        y = acc_reduce_add(A, rc);
+    }
+    __syncwarp();
+    if (lane < 17) st[lane] = y;
+    __syncwarp();
+}
+SMW_DEV void coop_perm17(F29* st, const uint32_t* tbl, const CoopTables& L, int lane) {
+    if (lane < 17) {           // ARK of round 0 as a product with the Montgomery one (normalises the lazily added input lanes)
+        Acc A; acc_zero(A); acc_mac(A, st[lane], tbl_load(tbl, L.k_one));
+        st[lane] = acc_reduce_add(A, tbl_load(tbl, L.rc_full + lane));
+    }
+    __syncwarp();
+    for (int r = 0; r < 4; r++) {
+        if (lane < 17) st[lane] = f29_sbox5(st[lane]);
+        __syncwarp();
+        if (r < 3) coop_matvec17(st, tbl, L, lane, true, L.rc_full + (uint32_t)(r + 1) * 17 + lane);
+        else coop_matvec17(st, tbl, L, lane, lane == 0, L.rc_part);
+    }
+    for (int k = 0; k < L.rp; k++) {
+        if (lane == 0) st[0] = f29_sbox5(st[0]);
+        __syncwarp();
+        if (k + 1 < L.rp) coop_matvec17(st, tbl, L, lane, lane == 0, L.rc_part + (uint32_t)(k + 1));
+        else coop_matvec17(st, tbl, L, lane, true, L.rc_full + 4u * 17 + lane);
+    }
+    for (int r = 4; r < 8; r++) {
+        if (lane < 17) st[lane] = f29_sbox5(st[lane]);
+        __syncwarp();
+        coop_matvec17(st, tbl, L, lane, r < 7, L.rc_full + (uint32_t)(r + 1) * 17 + lane);
+    }
+}
+__global__ void __launch_bounds__(32) k_transcript_absorb_coop(uint32_t* state, int pos, const uint32_t* __restrict__ ext, size_t n, const uint32_t* __restrict__ tbl, CoopTables L) {
+    __shared__ F29 st[17];
+    const int lane = threadIdx.x;
+    uint32_t w[8];
+    if (lane < 17) { load_ext(state + lane * 8, w); st[lane] = f29_from_ext(w); }
+    __syncwarp();
+    size_t i = 0;
+    while (i < n) {
+        if (pos == 16) { coop_perm17(st, tbl, L, lane); pos = 0; }
+        const int cnt = (int)((n - i < (size_t)(16 - pos)) ? (n - i) : (size_t)(16 - pos));
+        if (lane >= pos && lane < pos + cnt) { load_ext(ext + (i + (size_t)(lane - pos)) * 8, w); st[lane] = f29_add(st[lane], f29_from_ext(w)); }
+        __syncwarp();
+        pos += cnt; i += (size_t)cnt;
+    }
+    if (lane < 17) { f29_to_ext(st[lane], w); store_ext(state + lane * 8, w); }
+}
+
 // FRI hashed leaves (deep_ali/src/fri.rs:38-44 hash_leaf_pair): the pre-image is a fixed 17-lane template
 // (tags and label words; transcript/src/lib.rs absorbs 9 lanes, no intermediate permutation) with f and s
 // dropped into two lanes: exactly one permutation per leaf.  s_i = s[i / s_div] (or 0 when s == nullptr).
@@ -264,6 +332,15 @@ int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, in
                           const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute, uint32_t* d_out) {
     if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
     k_transcript_run<<<1, 32, state_smem_bytes<17>(1) + 64, c->stream>>>(d_state, fresh, pos, d_immA, nA, d_extB, nB, d_immC, nC, final_permute, d_out, dev_view(p));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+int launch_transcript_absorb_coop(smw_ctx* c, const smw_params* p, uint32_t* d_state, int pos, const uint32_t* d_ext, size_t n) {
+    if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
+    if (n == 0) return SMW_OK;
+    CoopTables L{p->layout.mds, p->layout.rc_full, p->layout.rc_part, p->layout.k_one, p->rp};
+    k_transcript_absorb_coop<<<1, 32, 0, c->stream>>>(d_state, pos, d_ext, n, p->d_tables, L);
     c->launches++;
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;

@@ -139,6 +139,8 @@ int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d
 int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
                           const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute,
                           uint32_t* d_out /* optional: state[0] after the run */);
+// the B phase of launch_transcript_run for long inputs: one warp, literal dense rounds with one state lane per thread; the state must live in d_state
+int launch_transcript_absorb_coop(smw_ctx* c, const smw_params* p, uint32_t* d_state, int pos, const uint32_t* d_ext, size_t n);
 int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_template_le256 /* 17 x 8 words */, int lane_f, int lane_s,
                            const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out);
 int launch_fri_sample_z(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_templates_le256 /* L x 17 x 8 */, const uint64_t* d_level_size /* L x 2 */, int L,

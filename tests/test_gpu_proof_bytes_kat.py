@@ -15,10 +15,10 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("k", [11, 12, 13, 14, 15, 16, 17, 18])
 def test_proof_bytes_kat_on_gpu(ctx, smw, O, k):
-    if k > 15 and not os.environ.get("SMW_KAT_FULL"):
-        # the four ALI sponges over n0 elements are strictly serial (one thread, n0/16 permutations each): 42 / 84 / 168 s for
-        # k = 16 / 17 / 18.  All eight rows pass (profiles/r01an_pytest_gpu_proof_bytes_kat_k11_18.log); SMW_KAT_FULL=1 runs them.
-        pytest.skip("k > 15 only with SMW_KAT_FULL=1 (minutes of serial sponge)")
+    if k > 16 and not os.environ.get("SMW_KAT_FULL"):
+        # the four ALI sponges over n0 elements are strictly serial (n0/16 permutations each, one warp): 11 / 19 / 38 s for
+        # k = 16 / 17 / 18.  All eight rows pass (profiles/r01aq_pytest_gpu_proof_bytes_kat_k11_18.log); SMW_KAT_FULL=1 runs them all.
+        pytest.skip("k > 16 only with SMW_KAT_FULL=1 (serial sponges: about a minute)")
     a, s, e, t = kat_inputs(O, k)              # the oracle only replays rand's StdRng to produce the INPUTS
     st, proofs = smw.deep_fri_prove(ctx, a, s, e, t, [16, 16, 8], 32, 0xDEEFBAAD)
     assert proofs.size_bytes() == CSV[k]
