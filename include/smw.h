@@ -136,6 +136,9 @@ int32_t smw_transcript_challenge(smw_transcript* t, const uint8_t* label, size_t
 int32_t smw_transcript_state(smw_transcript* t, void* out_17_fr_host, int32_t* pos_out);
 void smw_transcript_free(smw_transcript* t);
 int32_t smw_tr_hash_fields_tagged(smw_ctx* ctx, const uint8_t* tag, size_t tag_len, const void* xs, size_t n, int32_t mem, void* out_fr_host);
+/* `count` independent tr_hash_fields_tagged calls whose serial sponges overlap on side streams (the four ALI sponges of DeepAliRealBuilder::build_f0, deep_ali/src/fri.rs:541-548) */
+int32_t smw_tr_hash_fields_tagged_many(smw_ctx* ctx, int32_t count, const uint8_t* const* tags, const size_t* tag_lens, const void* const* xs, const size_t* n,
+                                       int32_t mem, void* out_fr_host);
 int32_t smw_hash_leaf_pair(smw_ctx* ctx, const void* f, const void* s, size_t n, void* out, int32_t mem);   /* hash_leaf_pair, element-wise */
 
 /* ---- FRI-like commit phase (deep_ali/src/fri.rs:59-143, 220-312) --------------------------- */

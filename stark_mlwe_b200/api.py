@@ -836,10 +836,25 @@ def ali_sample_z_beta_fs(ctx, tag, n0, roots_seed):
     return z[0], beta[0]
 
 
+def tr_hash_fields_tagged_many(ctx, tags, xss):
+    """[tr_hash_fields_tagged(tag_i, xs_i)] (deep_ali/src/fri.rs:28-36) with the serial sponges overlapped on the device"""
+    k = len(tags)
+    bufs = [_buf(x) for x in xss]
+    assert all(b[2] == bufs[0][2] for b in bufs)
+    tag_bufs = [(C.c_uint8 * max(len(t), 1)).from_buffer_copy(bytes(t) if len(t) else b"\0") for t in tags]
+    tag_ptrs = (C.c_void_p * k)(*[C.cast(tb, C.c_void_p) for tb in tag_bufs])
+    tag_lens = (C.c_size_t * k)(*[len(t) for t in tags])
+    x_ptrs = (C.c_void_p * k)(*[b[0] for b in bufs])
+    ns = (C.c_size_t * k)(*[b[1] for b in bufs])
+    out = _out(k)
+    ctx.check(ctx.L.smw_tr_hash_fields_tagged_many(ctx.h, k, tag_ptrs, tag_lens, x_ptrs, ns, bufs[0][2], C.c_void_p(out.ctypes.data)))
+    return out
+
+
 def deep_ali_build_f0(ctx, a, s, e, t):
     """DeepAliRealBuilder::default().build_f0 (deep_ali/src/fri.rs:535-570): no blinding, tag "ALI/DEEP" -> (f0, z)"""
     n0 = len(a)
-    h = [tr_hash_fields_tagged(ctx, tag, x) for tag, x in ((b"ALI/A", a), (b"ALI/S", s), (b"ALI/E", e), (b"ALI/T", t))]
+    h = list(tr_hash_fields_tagged_many(ctx, [b"ALI/A", b"ALI/S", b"ALI/E", b"ALI/T"], [a, s, e, t]))      # four serial sponges, side by side
     seed_f = tr_hash_fields_tagged(ctx, b"ALI/seed", np.stack(h + [_fr_from_u64(ctx, n0)]))
     z, _beta = ali_sample_z_beta_fs(ctx, b"ALI/DEEP", n0, seed_f)
     omega = ctx.root_of_unity(n0.bit_length() - 1)                      # FriDomain::new_radix2 (fri.rs:53-56)

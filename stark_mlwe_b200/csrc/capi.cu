@@ -113,8 +113,9 @@ int get_transcript_params(smw_ctx* c, smw_params* given, smw_params** out) {
 
 constexpr size_t COOP_ABSORB_MIN = 64;      // elements from which the warp-cooperative absorb (k_transcript_absorb_coop) pays
 // one-shot transcript hash on the device: new(label0) ; absorb_bytes(tag) ; fields ; challenge(chal)
+// `defer` != nullptr: nothing is synchronised or freed here; the caller syncs the stream(s) and frees the collected pointers
 int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t* tag, size_t tag_len, const std::vector<Word>& imm_fields,
-                 const uint32_t* d_ext, size_t n_ext, const char* chal, uint32_t* d_out) {
+                 const uint32_t* d_ext, size_t n_ext, const char* chal, uint32_t* d_out, std::vector<void*>* defer = nullptr) {
     std::vector<Word> A, C;
     A.push_back(tag_word(TAG_INIT));
     push_absorb_bytes(A, (const uint8_t*)label0, strlen(label0));
@@ -130,11 +131,13 @@ int oneshot_hash(smw_ctx* c, smw_params* trp, const char* label0, const uint8_t*
         if (!rc) rc = launch_transcript_absorb_coop(c, trp, d_st, pos, d_ext, n_ext);
         pos = advance_pos(pos, n_ext);
         if (!rc) rc = launch_transcript_run(c, trp, d_st, 0, pos, nullptr, 0, nullptr, 0, dC, (int)C.size(), 1, d_out);
+        if (defer) { defer->push_back(d_st); defer->push_back(dA); defer->push_back(dC); return rc; }
         cudaStreamSynchronize(c->stream);
         cudaFree(d_st); cudaFree(dA); cudaFree(dC);
         return rc;
     }
     rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA, (int)A.size(), d_ext, n_ext, dC, (int)C.size(), 1, d_out);
+    if (defer) { defer->push_back(dA); defer->push_back(dC); return rc; }
     cudaStreamSynchronize(c->stream);
     cudaFree(dA); cudaFree(dC);
     return rc;
@@ -655,6 +658,31 @@ int32_t smw_tr_hash_fields_tagged(smw_ctx* c, const uint8_t* tag, size_t tag_len
     Out o(c, out_host, 1, SMW_HOST); if (o.rc) return o.rc;
     rc = oneshot_hash(c, p, "FRI/FS", tag, tag_len, {}, i.d, n, "out", o.d); if (rc) return rc;
     return o.finish();
+}
+// `count` independent one-shot hashes (e.g. the four ALI sponges of deep_ali_build_f0, deep_ali/src/fri.rs:541-548): each chain of
+// launches runs on its own side stream, so the strictly serial sponges overlap each other.  xs[i]: n[i] elements; out: count Fr (host).
+int32_t smw_tr_hash_fields_tagged_many(smw_ctx* c, int32_t count, const uint8_t* const* tags, const size_t* tag_lens, const void* const* xs, const size_t* n,
+                                       int32_t mem, void* out_host) {
+    if (!c || count < 0 || (count && (!tags || !tag_lens || !xs || !n || !out_host))) return SMW_ERR_INVALID_ARG;
+    if (count == 0) return SMW_OK;
+    cudaSetDevice(c->device);
+    smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
+    std::vector<std::unique_ptr<In>> ins;
+    for (int i = 0; i < count; i++) { ins.emplace_back(new In(c, xs[i], n[i], mem)); if (ins.back()->rc) return ins.back()->rc; }
+    uint32_t* d_out = nullptr; SMW_CUDA(c, cudaMalloc(&d_out, (size_t)count * FR));
+    std::vector<void*> defer;
+    {
+        StreamFan fan(c, FAN_STREAMS);
+        for (int i = 0; i < count && !rc; i++) {
+            fan.enter(i);
+            rc = oneshot_hash(c, p, "FRI/FS", tags[i], tag_lens[i], {}, ins[i]->d, n[i], "out", d_out + (size_t)i * 8, &defer);
+            fan.leave();
+        }
+    }
+    if (!rc) rc = d2h(c, out_host, d_out, (size_t)count * FR); else cudaStreamSynchronize(c->stream);
+    for (void* q : defer) cudaFree(q);
+    cudaFree(d_out);
+    return rc;
 }
 // the 17-lane pre-image template of hash_leaf_pair (deep_ali/src/fri.rs:38-44); returns the lanes of f and s
 static void leaf_template(std::vector<Word>& lanes, int* lane_f, int* lane_s) {

@@ -3,8 +3,6 @@ crates/channel/benchmarkdata.csv:2-9, column proof_bytes, k = 11..18 (every publ
 (channel/benches/end_to_end.rs:187-260) through deep_ali_build_f0 -> fri_build_transcript -> fri_prove_queries ->
 deep_fri_proof_size_bytes (deep_ali/src/fri.rs:535-641, 355-466, 775-805) — every sponge, Poseidon constant, DS label,
 fold, DEEP merge, ChaCha12 draw and multiproof opening runs in libsmw.so."""
-import os
-
 import numpy as np
 import pytest
 
@@ -15,10 +13,6 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("k", [11, 12, 13, 14, 15, 16, 17, 18])
 def test_proof_bytes_kat_on_gpu(ctx, smw, O, k):
-    if k > 16 and not os.environ.get("SMW_KAT_FULL"):
-        # the four ALI sponges over n0 elements are strictly serial (n0/16 permutations each, one warp): 11 / 19 / 38 s for
-        # k = 16 / 17 / 18.  All eight rows pass (profiles/r01aq_pytest_gpu_proof_bytes_kat_k11_18.log); SMW_KAT_FULL=1 runs them all.
-        pytest.skip("k > 16 only with SMW_KAT_FULL=1 (serial sponges: about a minute)")
     a, s, e, t = kat_inputs(O, k)              # the oracle only replays rand's StdRng to produce the INPUTS
     st, proofs = smw.deep_fri_prove(ctx, a, s, e, t, [16, 16, 8], 32, 0xDEEFBAAD)
     assert proofs.size_bytes() == CSV[k]
