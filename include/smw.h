@@ -49,7 +49,9 @@ enum {
     SMW_ERR_INVALID_ARG = 8,
     SMW_ERR_PARAMS_SINGULAR = 9,   /* matrix has a zero pivot: the exact sparse/LU factorisation does not exist */
     SMW_ERR_NOMEM = 10,
-    SMW_ERR_EMPTY_INDICES = 11     /* "open_many: empty indices"      merkle/src/lib.rs:247 */
+    SMW_ERR_EMPTY_INDICES = 11,    /* "open_many: empty indices"      merkle/src/lib.rs:247 */
+    SMW_ERR_Z_IN_DOMAIN = 12,      /* "z must be outside H"           deep_ali/src/lib.rs:77,97 */
+    SMW_ERR_COMM = 13              /* NCCL failure or no communicator; see smw_last_error */
 };
 enum { SMW_HOST = 0, SMW_DEVICE = 1 };
 

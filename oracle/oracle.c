@@ -816,6 +816,20 @@ void orc_dft_naive(const u64* coeffs, int log_n, u64* out) {
     fr x = FR_R;
     for (size_t i = 0; i < n; i++) { fr acc = FR_ZERO; for (size_t j = n; j-- > 0;) acc = fr_add(fr_mul(acc, x), ((const fr*)coeffs)[j]); ((fr*)out)[i] = acc; x = fr_mul(x, w); }
 }
+/* P(x) by Horner's rule (poly/src/lib.rs:18-105 `Poly::evaluate` wraps ark-poly's DensePolynomial::evaluate, which is Horner):
+ * pins the NTT / LDE on the DEFINITION evals[i] = P(w^i) at any size in O(n) per point                                    */
+void orc_horner(const u64* coeffs, size_t n, const u64* x_p, u64* out) {
+    orc_init(); fr x; memcpy(x.l, x_p, 32);
+    fr acc = FR_ZERO;
+    for (size_t j = n; j-- > 0;) acc = fr_add(fr_mul(acc, x), ((const fr*)coeffs)[j]);
+    memcpy(out, acc.l, 32);
+}
+void orc_fr_pow(const u64* a_p, u64 e, u64* out) {
+    orc_init(); fr a; memcpy(a.l, a_p, 32);
+    fr r = FR_R;
+    for (int b = 63; b >= 0; b--) { r = fr_mul(r, r); if ((e >> b) & 1) r = fr_mul(r, a); }
+    memcpy(out, r.l, 32);
+}
 /* coset LDE: c = ifft_n(col); c[i] *= g^i; zero-pad to beta*n; fft_{beta n} */
 void orc_lde(const u64* col, int log_n, int log_blowup, const u64* shift, u64* out) {
     orc_init(); size_t n = (size_t)1 << log_n, N = n << log_blowup;

@@ -564,6 +564,22 @@ def dft_naive(coeffs):
     return out
 
 
+def horner(coeffs, x):
+    """P(x) for P = sum coeffs[j] X^j (Horner; the definition the NTT is pinned on)"""
+    c = fr_array(coeffs).reshape(-1, 4)
+    x = fr_array(x).reshape(4)
+    out = np.zeros(4, dtype=np.uint64)
+    lib().orc_horner(_p(c), C.c_size_t(c.shape[0]), _p(x), _p(out))
+    return out
+
+
+def fr_pow(a, e):
+    a = fr_array(a).reshape(4)
+    out = np.zeros(4, dtype=np.uint64)
+    lib().orc_fr_pow(_p(a), C.c_uint64(e), _p(out))
+    return out
+
+
 def lde(col, log_blowup, shift):
     col = fr_array(col).reshape(-1, 4)
     log_n = col.shape[0].bit_length() - 1

@@ -11,7 +11,7 @@ OK = 0
 HOST, DEVICE = 0, 1
 ERR = {1: "SMW_ERR_CUDA", 2: "SMW_ERR_EMPTY", 3: "SMW_ERR_ARITY_WIDTH", 4: "SMW_ERR_LENGTH_MISMATCH", 5: "SMW_ERR_NOT_DIVISIBLE",
        6: "SMW_ERR_UNSUPPORTED_WIDTH", 7: "SMW_ERR_UNSUPPORTED_ARITY", 8: "SMW_ERR_INVALID_ARG", 9: "SMW_ERR_PARAMS_SINGULAR",
-       10: "SMW_ERR_NOMEM", 11: "SMW_ERR_EMPTY_INDICES"}
+       10: "SMW_ERR_NOMEM", 11: "SMW_ERR_EMPTY_INDICES", 12: "SMW_ERR_Z_IN_DOMAIN", 13: "SMW_ERR_COMM"}
 
 _lib = None
 

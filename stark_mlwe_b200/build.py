@@ -61,7 +61,7 @@ def build(verbose=False, force=False):
         res = list(ex.map(compile_unit, [(n, s, e, ht, verbose) for n, s, e in units()]))
     objs = [o for o, _ in res]
     if any(ch for _, ch in res) or not os.path.exists(SO) or os.path.getmtime(SO) < os.path.getmtime(os.path.join(CSRC, "smw.map")):
-        cmd = [NVCC, "-shared", "-ccbin", "/usr/bin/g++", "-o", SO] + objs + ["-Xlinker", "--version-script=" + os.path.join(CSRC, "smw.map"), "-lcudart_static", "-ldl", "-lrt", "-lpthread"]
+        cmd = [NVCC, "-shared", "-ccbin", "/usr/bin/g++", "-o", SO] + objs + ["-Xlinker", "--version-script=" + os.path.join(CSRC, "smw.map"), "--cudart", "shared", "-ldl", "-lrt", "-lpthread"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stderr[-4000:])

@@ -69,6 +69,7 @@ struct Out {
     }
     ~Out() { if (owned && d) { cudaStreamSynchronize(c->stream); cudaFree(d); } }
 };
+struct DevFree { std::vector<void*> v; cudaStream_t st; ~DevFree() { cudaStreamSynchronize(st); for (void* p : v) if (p) cudaFree(p); } };
 int d2h(smw_ctx* c, void* host, const void* dev, size_t bytes) {
     SMW_CUDA(c, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -165,22 +166,102 @@ struct StreamFan {
 };
 constexpr int FAN_STREAMS = 8;
 
-// level-by-level tree over a device level 0 (merkle/src/lib.rs:164-181)
-int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out, uint32_t first_ds_level = 0) {
-    auto t = std::make_unique<smw_tree>();
-    t->ctx = c; t->params = p; t->arity = arity; t->tree_label = label;
-    t->len.push_back(n); t->lv.push_back(d_level0); t->owned.push_back(own0);
-    uint32_t level = first_ds_level;          // DS level of the parents of d_level0 (0 = parents of the leaves)
-    while (t->len.back() > 1) {
-        size_t cn = t->len.back(), nn = (cn + arity - 1) / arity;
-        uint32_t* d_next; cudaError_t e = cudaMalloc(&d_next, nn * FR);
-        if (e != cudaSuccess) { smw_tree_free(t.release()); return cuda_err(c, e, "cudaMalloc(tree level)"); }
-        t->len.push_back(nn); t->lv.push_back(d_next); t->owned.push_back(true);
-        int rc = launch_merkle_level(c, p, t->lv[t->lv.size() - 2], cn, d_next, nn, arity, level, label, 0, 0, 1, 0, 0);
-        if (rc) { smw_tree_free(t.release()); return rc; }
-        level++;
+// ---- forests: the levels of many independent trees hashed round by round, one launch per round and (parameter set, arity)
+// level sizes of a tree over n leaves (level 0 = leaves); whole_only: stop at the last level made of complete sibling groups
+// (the "cap" of a slice of a range-sharded tree: the ragged top belongs to whoever gathers the caps)
+std::vector<size_t> level_sizes(size_t n, int arity, bool whole_only) {
+    std::vector<size_t> len{n};
+    if (arity < 2) return len;
+    while (len.back() > 1) {
+        const size_t cn = len.back();
+        if (whole_only && (cn < (size_t)arity || cn % (size_t)arity)) break;
+        len.push_back((cn + arity - 1) / arity);
     }
-    *out = t.release();
+    return len;
+}
+struct ForestTree {
+    smw_params* p; int arity; uint64_t label; uint64_t first_leaf;     // first_leaf: global index of leaf 0 (DS positions of a slice, merkle/src/lib.rs:168-173)
+    uint32_t first_ds_level; bool whole_only;
+    uint32_t* leaves; size_t n;
+    std::vector<size_t> len; std::vector<uint32_t*> lv;                // filled by build_forest: level 0 = leaves
+};
+bool has_multi(const smw_ctx* c, const smw_params* p) { return c->use_f52 && p->d_tables52 != nullptr; }
+// Hashes levels 1.. of every tree (merkle/src/lib.rs:164-181) on the context's stream.  All levels >= 1 of all trees live in ONE
+// allocation (*arena_out); the segment table goes to `defer` (freed by the caller after the stream has drained).
+int build_forest(smw_ctx* c, std::vector<ForestTree>& trees, uint32_t** arena_out, std::vector<void*>& defer) {
+    *arena_out = nullptr;
+    size_t total = 0, max_levels = 0;
+    for (auto& t : trees) {
+        t.len = level_sizes(t.n, t.arity, t.whole_only);
+        for (size_t j = 1; j < t.len.size(); j++) total += t.len[j];
+        max_levels = std::max(max_levels, t.len.size());
+    }
+    uint32_t* arena = nullptr;
+    if (total) SMW_CUDA(c, cudaMalloc(&arena, total * FR));
+    *arena_out = arena;
+    { size_t off = 0; for (auto& t : trees) { t.lv.assign(1, t.leaves); for (size_t j = 1; j < t.len.size(); j++) { t.lv.push_back(arena + off * 8); off += t.len[j]; } } }
+    struct Launch { smw_params* p; int arity; size_t seg0; int n; uint64_t total; };
+    std::vector<NodeSeg> segs; std::vector<Launch> launches;
+    for (size_t j = 0; j + 1 < max_levels; j++) {
+        std::vector<std::pair<std::pair<smw_params*, int>, std::vector<size_t>>> groups;      // insertion-ordered (params, arity) -> trees
+        for (size_t ti = 0; ti < trees.size(); ti++) {
+            const ForestTree& t = trees[ti];
+            if (j + 1 >= t.len.size()) continue;
+            auto key = std::make_pair(t.p, t.arity);
+            auto it = std::find_if(groups.begin(), groups.end(), [&](const auto& g) { return g.first == key; });
+            if (it == groups.end()) { groups.push_back({key, {}}); it = groups.end() - 1; }
+            it->second.push_back(ti);
+        }
+        for (auto& g : groups) {
+            Launch L{g.first.first, g.first.second, segs.size(), 0, 0};
+            for (size_t ti : g.second) {
+                const ForestTree& t = trees[ti];
+                uint64_t first = t.first_leaf; for (size_t q = 0; q <= j; q++) first /= (uint64_t)t.arity;      // first parent of level j + 1
+                segs.push_back(NodeSeg{t.lv[j], t.lv[j + 1], (uint64_t)t.len[j], (uint64_t)t.len[j + 1], t.label, first, t.first_ds_level + (uint32_t)j, (uint32_t)t.arity, L.total});
+                L.total += t.len[j + 1]; L.n++;
+            }
+            launches.push_back(L);
+        }
+    }
+    if (segs.empty()) return SMW_OK;
+    if (trees.size() == 1) {            // one tree: plain per-level launches, no segment table
+        for (const NodeSeg& sg : segs) {
+            int rc = launch_merkle_level(c, trees[0].p, sg.children, sg.n_children, sg.parents, sg.n_parents, trees[0].arity, sg.level, sg.label, 0, sg.pos_offset, 1, 0, 0);
+            if (rc) return rc;
+        }
+        return SMW_OK;
+    }
+    NodeSeg* d_segs = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_segs, segs.size() * sizeof(NodeSeg)));
+    defer.push_back(d_segs);
+    SMW_CUDA(c, cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(NodeSeg), cudaMemcpyHostToDevice, c->stream));   // pageable source: staged before the call returns
+    for (const Launch& L : launches) {
+        int rc = SMW_OK;
+        if (has_multi(c, L.p)) rc = launch_merkle_level_multi(c, L.p, d_segs + L.seg0, L.n, L.total, L.arity);
+        else for (int i = 0; i < L.n && !rc; i++) {
+            const NodeSeg& sg = segs[L.seg0 + i];
+            rc = launch_merkle_level(c, L.p, sg.children, sg.n_children, sg.parents, sg.n_parents, L.arity, sg.level, sg.label, 0, sg.pos_offset, 1, 0, 0);
+        }
+        if (rc) return rc;
+    }
+    return SMW_OK;
+}
+smw_tree* tree_handle(smw_ctx* c, const ForestTree& t, bool own_leaves) {
+    auto h = new smw_tree();
+    h->ctx = c; h->params = t.p; h->arity = t.arity; h->tree_label = t.label;
+    h->len = t.len; h->lv = t.lv; h->owned.assign(t.lv.size(), false); h->owned[0] = own_leaves;
+    return h;
+}
+// level-by-level tree over a device level 0 (merkle/src/lib.rs:164-181); the levels above live in one allocation owned by the tree
+int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d_level0, bool own0, size_t n, smw_tree** out, uint32_t first_ds_level = 0) {
+    std::vector<ForestTree> f(1);
+    f[0] = ForestTree{p, arity, label, 0, first_ds_level, false, d_level0, n, {}, {}};
+    uint32_t* arena = nullptr; std::vector<void*> defer;
+    int rc = build_forest(c, f, &arena, defer);
+    if (!defer.empty()) { cudaStreamSynchronize(c->stream); for (void* q : defer) cudaFree(q); }
+    if (rc) { cudaStreamSynchronize(c->stream); cudaFree(arena); if (own0) cudaFree(d_level0); return rc; }
+    smw_tree* t = tree_handle(c, f[0], own0); t->arena = arena;
+    *out = t;
     return SMW_OK;
 }
 
@@ -307,7 +388,7 @@ int32_t smw_params_from_seed(smw_ctx* c, const uint8_t* seed, size_t seed_len, i
     if (!c || !out || (!seed && seed_len)) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     if (rp_for_width(t) < 0) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "unsupported Poseidon width");
-    if (rp <= 0 || rp > 1024) return set_err(c, SMW_ERR_INVALID_ARG, "bad partial round count");
+    if (rp <= 0 || rp > 96 || (rp & 1)) return set_err(c, SMW_ERR_INVALID_ARG, "partial round count must be even and <= 96 (two-round blocks; lazy-reduction bound of the sparse form)");
     smw_params* p = new smw_params(); p->ctx = c; p->t = t; p->rp = rp;
     int rc = launch_derive_params(c, p, seed, (int)seed_len);
     if (rc) { free_params_internal(p); return rc; }
@@ -350,7 +431,7 @@ int32_t smw_params_from_tables(smw_ctx* c, int32_t t, int32_t rp, const void* md
     if (!c || !out || !mds || !rcf || !rcp) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     if (rp_for_width(t) < 0) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "unsupported Poseidon width");
-    if (rp <= 0 || rp > 1024) return set_err(c, SMW_ERR_INVALID_ARG, "bad partial round count");
+    if (rp <= 0 || rp > 96 || (rp & 1)) return set_err(c, SMW_ERR_INVALID_ARG, "partial round count must be even and <= 96 (two-round blocks; lazy-reduction bound of the sparse form)");
     In a(c, mds, (size_t)t * t, mem), b(c, rcf, (size_t)8 * t, mem), d(c, rcp, (size_t)rp, mem);
     if (a.rc) return a.rc; if (b.rc) return b.rc; if (d.rc) return d.rc;
     smw_params* p = new smw_params(); p->ctx = c; p->t = t; p->rp = rp;
@@ -407,6 +488,7 @@ static int check_tree_args(smw_ctx* c, smw_params* p, int arity, size_t n) {
     if (n == 0) return set_err(c, SMW_ERR_EMPTY, "no leaves");
     if (arity < 1 || arity > 128) return set_err(c, SMW_ERR_UNSUPPORTED_ARITY, "unsupported Merkle arity; max supported = 128");
     if (width_for_arity(arity) != p->t) return set_err(c, SMW_ERR_ARITY_WIDTH, "arity incompatible with Poseidon width t");
+    if (arity == 1 && n > 1) return set_err(c, SMW_ERR_UNSUPPORTED_ARITY, "arity 1 only admits a one-leaf tree (the reference does not terminate here)");
     return SMW_OK;
 }
 int32_t smw_merkle_new(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, const void* leaves, size_t n, int32_t mem, smw_tree** out) {
@@ -416,8 +498,11 @@ int32_t smw_merkle_new(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label,
     cudaSetDevice(c->device);
     // the tree owns a copy of the leaves, as MerkleTree::new takes the Vec by value (merkle/src/lib.rs:147)
     uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n * FR));
-    SMW_CUDA(c, cudaMemcpyAsync(d0, leaves, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
-    return build_tree(c, p, arity, label, d0, true, n, out);
+    { cudaError_t e = cudaMemcpyAsync(d0, leaves, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
+      if (e != cudaSuccess) { cudaFree(d0); return cuda_err(c, e, "copy leaves"); } }
+    rc = build_tree(c, p, arity, label, d0, true, n, out);
+    if (!rc && mem == SMW_HOST) SMW_CUDA(c, cudaStreamSynchronize(c->stream));      // the caller may reuse its host buffer as soon as the call returns
+    return rc;
 }
 int32_t smw_merkle_new_pairs(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, const void* f, const void* cp, size_t n_f, size_t n_cp, int32_t mem, smw_tree** out) {
     if (!out || !c) return SMW_ERR_INVALID_ARG;
@@ -446,6 +531,7 @@ void smw_tree_free(smw_tree* t) {
     if (!t) return;
     cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream);
     for (size_t i = 0; i < t->lv.size(); i++) if (t->owned[i]) cudaFree(t->lv[i]);
+    cudaFree(t->arena);
     delete t;
 }
 int32_t smw_merkle_commit_columns(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label0, uint64_t label_stride,
@@ -503,23 +589,20 @@ int32_t smw_dft_strided(smw_ctx* c, void* buf, int32_t log_g, size_t stride, siz
     cudaSetDevice(c->device);
     const size_t G = (size_t)1 << log_g, total = (G - 1) * stride + count;
     int rc = SMW_OK;
-    uint32_t* d_w; SMW_CUDA(c, cudaMalloc(&d_w, G * FR));
-    {   // wpow[i] = w_G^i, i < G: a vector of ones scaled by the powers of the order-G root
-        uint32_t* d_root; SMW_CUDA(c, cudaMalloc(&d_root, FR));
-        rc = launch_root_of_unity(c, log_g, d_root);
-        if (!rc) { uint32_t* d_one; cudaMalloc(&d_one, FR); rc = launch_root_of_unity(c, 0, d_one);
-                   for (size_t i = 0; !rc && i < G; i++) cudaMemcpyAsync(d_w + i * 8, d_one, FR, cudaMemcpyDeviceToDevice, c->stream);
-                   if (!rc) rc = launch_scale_powers(c, d_w, G, d_root);
-                   cudaStreamSynchronize(c->stream); cudaFree(d_one); }
-        cudaFree(d_root);
-        if (rc) { cudaFree(d_w); return rc; }
-    }
-    if (mem == SMW_DEVICE) { rc = launch_dft_strided(c, (uint32_t*)buf, log_g, stride, count, d_w); cudaStreamSynchronize(c->stream); cudaFree(d_w); return rc; }
-    In i(c, buf, total, SMW_HOST); if (i.rc) { cudaFree(d_w); return i.rc; }
-    rc = launch_dft_strided(c, i.owned, log_g, stride, count, d_w);
-    if (!rc) rc = d2h(c, buf, i.owned, total * FR);
-    cudaStreamSynchronize(c->stream); cudaFree(d_w);
-    return rc;
+    DevFree fr{{}, c->stream};
+    uint32_t *d_w = nullptr, *d_root = nullptr, *d_one = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_w, G * FR)); fr.v.push_back(d_w);
+    SMW_CUDA(c, cudaMalloc(&d_root, FR)); fr.v.push_back(d_root);
+    SMW_CUDA(c, cudaMalloc(&d_one, FR)); fr.v.push_back(d_one);
+    // wpow[i] = w_G^i, i < G: a vector of ones scaled by the powers of the order-G root
+    rc = launch_root_of_unity(c, log_g, d_root); if (rc) return rc;
+    rc = launch_root_of_unity(c, 0, d_one); if (rc) return rc;
+    for (size_t i = 0; i < G; i++) SMW_CUDA(c, cudaMemcpyAsync(d_w + i * 8, d_one, FR, cudaMemcpyDeviceToDevice, c->stream));
+    rc = launch_scale_powers(c, d_w, G, d_root); if (rc) return rc;
+    if (mem == SMW_DEVICE) return launch_dft_strided(c, (uint32_t*)buf, log_g, stride, count, d_w);      // DevFree drains the stream before freeing
+    In i(c, buf, total, SMW_HOST); if (i.rc) return i.rc;
+    rc = launch_dft_strided(c, i.owned, log_g, stride, count, d_w); if (rc) return rc;
+    return d2h(c, buf, i.owned, total * FR);
 }
 int32_t smw_lde(smw_ctx* c, const void* in, int32_t log_n, int32_t log_blowup, const void* shift_host, void* out, int32_t n_cols, int32_t mem) {
     if (!c || !in || !out || !shift_host || n_cols < 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
@@ -785,63 +868,100 @@ void smw_fri_free(smw_fri* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
     for (auto* t : s->tree) smw_tree_free(t);
-    for (auto* f : s->f) cudaFree(f);
+    cudaFree(s->arena_f); cudaFree(s->arena_leaves); cudaFree(s->arena_levels);
     cudaFree(s->d_z);
     delete s;
 }
-int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, smw_fri** out) {
-    return smw_fri_build_transcript_from(c, f0, n0, schedule, L, seed_z, 0, mem, out);
+} // extern "C"
+namespace {
+// The per-layer commitments of a FRI commit phase (deep_ali/src/fri.rs:267-301) for layers [0, K): leaf digests of every layer in
+// one launch per leaf kind, then the layer trees as a forest (one launch per level index).  The layers are independent once
+// every f_l exists (z_l is public, fri.rs:250).  n_l: elements of layer l held here (the whole layer, or this rank's slice
+// starting at global index first_l); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer (fri.rs:259-265).
+struct FriLayers {
+    std::vector<ForestTree> trees; uint32_t* arena_leaves = nullptr; uint32_t* arena_levels = nullptr;
+};
+int fri_commit_layers(smw_ctx* c, int K, int L, const std::vector<size_t>& n_glob, const std::vector<size_t>& n_loc, const std::vector<size_t>& m,
+                      const std::vector<uint64_t>& first, const std::vector<uint32_t*>& f, uint64_t level0, bool whole_only, FriLayers& out, std::vector<void*>& defer) {
+    if (K <= 0) return SMW_OK;
+    smw_params* trp; int rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
+    size_t total = 0; for (int l = 0; l < K; l++) total += n_loc[l];
+    SMW_CUDA(c, cudaMalloc(&out.arena_leaves, total * FR));
+    uint32_t* d_tmpl = nullptr; int lf = 0, ls = 0;
+    std::vector<LeafSeg> hashed_segs, pair_segs; uint64_t hashed_total = 0, pair_total = 0; smw_params* pair_p = nullptr; bool pair_uniform = true;
+    size_t off = 0;
+    for (int l = 0; l < K; l++) {
+        const int arity = smw_pick_arity_for_layer(n_glob[l], m[l]);               // chosen from the GLOBAL layer size (fri.rs:272)
+        const bool hashed = arity >= 8;                                           // fri.rs:275
+        smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) return rc;
+        uint32_t* leaves = out.arena_leaves + off * 8; off += n_loc[l];
+        const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
+        LeafSeg sg{f[l], d_s, leaves, (uint64_t)n_loc[l], level0 + (uint64_t)l, first[l], (uint64_t)m[l], (uint32_t)arity, 0, 0};
+        if (hashed) { sg.first = hashed_total; hashed_total += n_loc[l]; hashed_segs.push_back(sg); }
+        else { sg.first = pair_total; pair_total += n_loc[l]; pair_segs.push_back(sg); if (pair_p && pair_p != p) pair_uniform = false; pair_p = p; }
+        out.trees.push_back(ForestTree{p, arity, level0 + (uint64_t)l, first[l], 0, whole_only, leaves, n_loc[l], {}, {}});
+    }
+    if (!hashed_segs.empty()) {
+        rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); if (rc) return rc;
+        defer.push_back(d_tmpl);
+        if (has_multi(c, trp)) {
+            LeafSeg* d; SMW_CUDA(c, cudaMalloc(&d, hashed_segs.size() * sizeof(LeafSeg))); defer.push_back(d);
+            SMW_CUDA(c, cudaMemcpyAsync(d, hashed_segs.data(), hashed_segs.size() * sizeof(LeafSeg), cudaMemcpyHostToDevice, c->stream));
+            rc = launch_fri_leaf_hashed_multi(c, trp, d_tmpl, lf, ls, d, (int)hashed_segs.size(), hashed_total); if (rc) return rc;
+        } else for (auto& sg : hashed_segs) { rc = launch_fri_leaf_hashed(c, trp, d_tmpl, lf, ls, sg.f, sg.cp, sg.cp_div, sg.n, sg.out); if (rc) return rc; }
+    }
+    if (!pair_segs.empty()) {
+        if (pair_uniform && has_multi(c, pair_p)) {
+            LeafSeg* d; SMW_CUDA(c, cudaMalloc(&d, pair_segs.size() * sizeof(LeafSeg))); defer.push_back(d);
+            SMW_CUDA(c, cudaMemcpyAsync(d, pair_segs.data(), pair_segs.size() * sizeof(LeafSeg), cudaMemcpyHostToDevice, c->stream));
+            rc = launch_pair_leaves_multi(c, pair_p, d, (int)pair_segs.size(), pair_total); if (rc) return rc;
+        } else for (auto& sg : pair_segs) {
+            smw_params* p; rc = smw_params_for_arity(c, (int)sg.arity, &p); if (rc) return rc;
+            rc = launch_pair_leaves(c, p, sg.f, sg.cp, sg.n, (int)sg.arity, sg.label, sg.pos_offset, sg.out, sg.cp_div); if (rc) return rc;
+        }
+    }
+    return build_forest(c, out.trees, &out.arena_levels, defer);
 }
-int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, uint64_t level0, int32_t mem, smw_fri** out) {
-    if (!c || !out || !f0 || L < 0 || (L && !schedule) || n0 == 0) return SMW_ERR_INVALID_ARG;
-    cudaSetDevice(c->device);
-    // layer sizes (fri.rs:145-155) — the reference asserts divisibility level by level
-    std::vector<size_t> n(L + 1), m(L + 1); n[0] = n0;
+int fri_layer_sizes(smw_ctx* c, size_t n0, const uint64_t* schedule, int L, std::vector<size_t>& n, std::vector<size_t>& m) {
+    n.assign(L + 1, 0); m.assign(L + 1, 1); n[0] = n0;          // fri.rs:145-155 — the reference asserts divisibility level by level
     for (int l = 0; l < L; l++) {
         m[l] = (size_t)schedule[l];
         if (m[l] < 2 || m[l] > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 2..128");
         if (n[l] % m[l]) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
         n[l + 1] = n[l] / m[l];
     }
-    m[L] = 1;
+    return SMW_OK;
+}
+} // namespace
+extern "C" {
+int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, smw_fri** out) {
+    return smw_fri_build_transcript_from(c, f0, n0, schedule, L, seed_z, 0, mem, out);
+}
+int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, uint64_t level0, int32_t mem, smw_fri** out) {
+    if (!c || !out || !f0 || L < 0 || (L && !schedule) || n0 == 0) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    std::vector<size_t> n, m; int rc = fri_layer_sizes(c, n0, schedule, L, n, m); if (rc) return rc;
     auto s = std::make_unique<smw_fri>(); s->ctx = c; s->L = L; s->n = n; s->m = m;
     s->arity.resize(L + 1); s->hashed.resize(L + 1); s->f.assign(L + 1, nullptr); s->tree.assign(L + 1, nullptr);
-    int rc = SMW_OK;
-    auto fail = [&](int code) { smw_fri_free(s.release()); return code; };
-    for (int l = 0; l <= L; l++) { cudaError_t e = cudaMalloc(&s->f[l], n[l] * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri layer)")); }
+    std::vector<void*> defer;
+    auto fail = [&](int code) { cudaStreamSynchronize(c->stream); for (void* q : defer) cudaFree(q); smw_fri_free(s.release()); return code; };
+    { size_t total = 0; for (int l = 0; l <= L; l++) total += n[l];
+      cudaError_t e = cudaMalloc(&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri layers)"));
+      size_t off = 0; for (int l = 0; l <= L; l++) { s->f[l] = s->arena_f + off * 8; off += n[l]; } }
     { cudaError_t e = cudaMalloc(&s->d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc")); }
     { cudaError_t e = cudaMemcpyAsync(s->f[0], f0, n0 * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream); if (e != cudaSuccess) return fail(cuda_err(c, e, "copy f0")); }
-    // z_l depends only on public values (fri.rs:250): all levels in one launch
+    // z_l depends only on public values (fri.rs:250): all levels in one launch, then the folds (fri.rs:254)
     std::vector<uint64_t> levels(L), sizes(L);
     for (int l = 0; l < L; l++) { levels[l] = level0 + (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
     rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc);
     for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); }
-    // per-layer commitment (fri.rs:267-301); s_l[i] = f_{l+1}[i / m_l] is read in place of a materialised s layer.
-    // The layers are independent trees: each one is a chain of launches on its own side stream (StreamFan).
-    uint32_t* d_tmpl = nullptr; { int lf, ls; rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); if (rc) return fail(rc); }
-    for (int l = 0; l <= L; l++) { smw_params* p; rc = smw_params_for_arity(c, smw_pick_arity_for_layer(n[l], m[l]), &p); if (rc) { cudaFree(d_tmpl); return fail(rc); } }   // derive parameter sets before fanning out
-    {
-        StreamFan fan(c, FAN_STREAMS);
-        for (int l = 0; l <= L && !rc; l++) {
-            fan.enter(l);
-            int arity = smw_pick_arity_for_layer(n[l], m[l]);
-            bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
-            s->arity[l] = arity; s->hashed[l] = hashed;
-            smw_params* p; rc = smw_params_for_arity(c, arity, &p);
-            uint32_t* d_leaves = nullptr;
-            if (!rc) { cudaError_t e = cudaMalloc(&d_leaves, n[l] * FR); if (e != cudaSuccess) rc = cuda_err(c, e, "cudaMalloc(leaves)"); }
-            const uint32_t* d_s = (l < L) ? s->f[l + 1] : nullptr;
-            if (!rc) {
-                if (hashed) rc = hash_leaves_device(c, s->f[l], d_s, m[l], n[l], d_leaves, d_tmpl);
-                else rc = launch_pair_leaves(c, p, s->f[l], d_s, n[l], arity, level0 + (uint64_t)l, 0, d_leaves, m[l]);
-                if (rc) cudaFree(d_leaves);
-            }
-            if (!rc) rc = build_tree(c, p, arity, level0 + (uint64_t)l, d_leaves, true, n[l], &s->tree[l]);
-            fan.leave();
-        }
-    }
-    cudaStreamSynchronize(c->stream); cudaFree(d_tmpl);
+    FriLayers fl; std::vector<uint64_t> first(L + 1, 0);
+    rc = fri_commit_layers(c, L + 1, L, n, n, m, first, s->f, level0, false, fl, defer);
+    s->arena_leaves = fl.arena_leaves; s->arena_levels = fl.arena_levels;
     if (rc) return fail(rc);
+    for (int l = 0; l <= L; l++) { s->arity[l] = fl.trees[l].arity; s->hashed[l] = fl.trees[l].arity >= 8; s->tree[l] = tree_handle(c, fl.trees[l], false); }
+    cudaStreamSynchronize(c->stream);
+    for (void* q : defer) cudaFree(q);
     *out = s.release();
     return SMW_OK;
 }
@@ -905,14 +1025,14 @@ int32_t smw_ali_sample_z_beta(smw_ctx* c, const void* fused_host, const void* ro
 struct smw_fri_shard {
     smw_ctx* ctx = nullptr;
     int K = 0;                                   // layers [0, K) are committed from local slices
-    std::vector<uint32_t*> cap; std::vector<size_t> cap_n; std::vector<int> cap_level, arity;
-    uint32_t* tail = nullptr; size_t tail_n = 0;  // local slice of f_K (empty when every layer was local)
+    std::vector<uint32_t*> cap; std::vector<size_t> cap_n; std::vector<int> cap_level, arity;   // cap[l] points into arena_levels / arena_leaves
+    uint32_t* tail = nullptr; size_t tail_n = 0;  // local slice of f_K (empty when every layer was local); points into arena_f
+    uint32_t *arena_f = nullptr, *arena_leaves = nullptr, *arena_levels = nullptr;
 };
 void smw_fri_shard_free(smw_fri_shard* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
-    for (auto* q : s->cap) cudaFree(q);
-    cudaFree(s->tail);
+    cudaFree(s->arena_f); cudaFree(s->arena_leaves); cudaFree(s->arena_levels);
     delete s;
 }
 int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, size_t n0, size_t first_index, const uint64_t* schedule, int32_t L,
@@ -921,63 +1041,38 @@ int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, si
         return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     const size_t G = n0 / n_local;               // number of equal slices
-    std::vector<size_t> n(L + 1), m(L + 1); n[0] = n0;
-    for (int l = 0; l < L; l++) {
-        m[l] = (size_t)schedule[l];
-        if (m[l] < 2 || m[l] > 128) return set_err(c, SMW_ERR_INVALID_ARG, "fold factor m must be in 2..128");
-        if (n[l] % m[l]) return set_err(c, SMW_ERR_NOT_DIVISIBLE, "layer size must be divisible by m");
-        n[l + 1] = n[l] / m[l];
-    }
-    m[L] = 1;
+    std::vector<size_t> n, m; int rc = fri_layer_sizes(c, n0, schedule, L, n, m); if (rc) return rc;
     // layer l is local while the slice of f_l folds into a whole slice of f_{l+1} (the last layer needs no fold)
     int K = 0;
     while (K <= L && n[K] % G == 0 && (K == L || (n[K] / G) % m[K] == 0)) K++;
     auto s = std::make_unique<smw_fri_shard>(); s->ctx = c; s->K = K;
-    auto fail = [&](int code) { smw_fri_shard_free(s.release()); return code; };
-    std::vector<uint32_t*> f(K + 1, nullptr);     // local slices of f_0 .. f_K (f_K only when K <= L)
-    auto free_f = [&]() { cudaStreamSynchronize(c->stream); for (auto* q : f) if (q && q != s->tail) cudaFree(q); };
-    const int n_f = (K <= L) ? K + 1 : K;
-    for (int l = 0; l < n_f; l++) { cudaError_t e = cudaMalloc(&f[l], (n[l] / G) * FR); if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "cudaMalloc(fri slice)")); } }
+    std::vector<void*> defer;
+    auto fail = [&](int code) { cudaStreamSynchronize(c->stream); for (void* q : defer) cudaFree(q); smw_fri_shard_free(s.release()); return code; };
+    const int n_f = (K <= L) ? K + 1 : K;         // local slices of f_0 .. f_K (f_K only when K <= L)
+    std::vector<uint32_t*> f(L + 2, nullptr); std::vector<size_t> n_loc(L + 1, 0); std::vector<uint64_t> first(L + 1, 0);
+    { size_t total = 0; for (int l = 0; l < n_f; l++) total += n[l] / G;
+      cudaError_t e = cudaMalloc(&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri slices)"));
+      size_t off = 0; for (int l = 0; l < n_f; l++) { f[l] = s->arena_f + off * 8; off += n[l] / G; } }
+    for (int l = 0; l <= L; l++) { n_loc[l] = n[l] / G; first[l] = (uint64_t)(first_index / (n0 / n[l])); }     // slice of layer l: [first_l, first_l + n_l / G)
     { cudaError_t e = cudaMemcpyAsync(f[0], f0_slice, n_local * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
-      if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "copy f0 slice")); } }
-    uint32_t* d_z = nullptr; { cudaError_t e = cudaMalloc(&d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) { free_f(); return fail(cuda_err(c, e, "cudaMalloc")); } }
+      if (e != cudaSuccess) return fail(cuda_err(c, e, "copy f0 slice")); }
+    uint32_t* d_z = nullptr; { cudaError_t e = cudaMalloc(&d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc")); defer.push_back(d_z); }
     std::vector<uint64_t> levels(L), sizes(L);
     for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }     // GLOBAL sizes: z_l is the same on every rank
-    int rc = sample_z_device(c, seed_z, levels, sizes, d_z);
-    for (int l = 0; !rc && l + 1 < n_f; l++) rc = launch_fri_fold(c, f[l], n[l] / G, d_z + (size_t)l * 8, m[l], f[l + 1]);
-    uint32_t* d_tmpl = nullptr; if (!rc) { int lf, ls; rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); }
-    for (int l = 0; !rc && l < K; l++) { smw_params* p; rc = smw_params_for_arity(c, smw_pick_arity_for_layer(n[l], m[l]), &p); }
-    std::vector<uint32_t*> spent;                  // intermediate levels, freed after the join (cudaFree would serialise the streams)
-    if (!rc) {
-        StreamFan fan(c, FAN_STREAMS);
-        for (int l = 0; !rc && l < K; l++) {
-            fan.enter(l);
-            const size_t nl = n[l] / G, first_l = first_index / (n0 / n[l]);      // slice of layer l: [first_l, first_l + nl)
-            int arity = smw_pick_arity_for_layer(n[l], m[l]);                      // chosen from the GLOBAL layer size
-            bool hashed = (arity == 128 || arity == 64 || arity == 32 || arity == 16 || arity == 8);
-            smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) { fan.leave(); break; }
-            uint32_t* cur; { cudaError_t e = cudaMalloc(&cur, nl * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(leaves)"); fan.leave(); break; } }
-            const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
-            if (hashed) rc = hash_leaves_device(c, f[l], d_s, m[l], nl, cur, d_tmpl);
-            else rc = launch_pair_leaves(c, p, f[l], d_s, nl, arity, (uint64_t)l, first_l, cur, m[l]);
-            size_t cn = nl, first_c = first_l; int level = 0;
-            while (!rc && arity >= 2 && cn >= (size_t)arity && cn % arity == 0) {    // whole nodes only: the ragged top belongs to the finisher
-                size_t nn = cn / arity; uint32_t* nxt;
-                cudaError_t e = cudaMalloc(&nxt, nn * FR); if (e != cudaSuccess) { rc = cuda_err(c, e, "cudaMalloc(tree level)"); break; }
-                rc = launch_merkle_level(c, p, cur, cn, nxt, nn, arity, (uint32_t)level, (uint64_t)l, 0, first_c / arity, 1, 0, 0);
-                spent.push_back(cur);
-                cur = nxt; cn = nn; first_c /= arity; level++;
-            }
-            s->cap.push_back(cur); s->cap_n.push_back(cn); s->cap_level.push_back(level); s->arity.push_back(arity);
-            fan.leave();
-        }
-    }
-    cudaStreamSynchronize(c->stream);
-    for (auto* q : spent) cudaFree(q);
-    cudaFree(d_tmpl);
-    if (!rc && K <= L) { s->tail = f[K]; s->tail_n = n[K] / G; }
-    free_f(); cudaFree(d_z);
+    rc = sample_z_device(c, seed_z, levels, sizes, d_z); if (rc) return fail(rc);
+    for (int l = 0; l + 1 < n_f; l++) { rc = launch_fri_fold(c, f[l], n_loc[l], d_z + (size_t)l * 8, m[l], f[l + 1]); if (rc) return fail(rc); }
+    // whole sibling groups only: the ragged top of every layer tree belongs to the finisher (smw_merkle_root_from_level)
+    FriLayers fl;
+    rc = fri_commit_layers(c, K, L, n, n_loc, m, first, f, 0, true, fl, defer);
+    s->arena_leaves = fl.arena_leaves; s->arena_levels = fl.arena_levels;
     if (rc) return fail(rc);
+    for (int l = 0; l < K; l++) {
+        const ForestTree& t = fl.trees[l];
+        s->cap.push_back(t.lv.back()); s->cap_n.push_back(t.len.back()); s->cap_level.push_back((int)t.len.size() - 1); s->arity.push_back(t.arity);
+    }
+    if (K <= L) { s->tail = f[K]; s->tail_n = n_loc[K]; }
+    cudaStreamSynchronize(c->stream);
+    for (void* q : defer) cudaFree(q);
     *out = s.release();
     return SMW_OK;
 }
@@ -1008,7 +1103,8 @@ int32_t smw_merkle_root_from_level(smw_ctx* c, smw_params* p, int32_t arity, uin
     if (!nodes) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n * FR));
-    SMW_CUDA(c, cudaMemcpyAsync(d0, nodes, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    { cudaError_t e = cudaMemcpyAsync(d0, nodes, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
+      if (e != cudaSuccess) { cudaFree(d0); return cuda_err(c, e, "copy nodes"); } }
     smw_tree* t = nullptr;
     rc = build_tree(c, p, arity, label, d0, true, n, &t, (uint32_t)level); if (rc) return rc;
     rc = smw_tree_root(t, root_out_host);
@@ -1029,15 +1125,18 @@ int32_t smw_sumcheck_round_coeffs(smw_ctx* c, const void* layer, size_t n, void*
     cudaFree(d_c);
     return rc;
 }
-static int mf_challenge_device(smw_ctx* c, smw_params* trp, uint64_t round_idx, const uint32_t* d_root, uint32_t* d_out) {
-    // channel/src/lib.rs:592-598: new("SUMCHECK-MF/ROUND-CHAL"); absorb_bytes("SUMCHECK/MF/R"); absorb_bytes(u64le(i)); absorb_field(root); challenge("r_i")
-    std::vector<Word> A, C;
+// channel/src/lib.rs:592-598: new("SUMCHECK-MF/ROUND-CHAL"); absorb_bytes("SUMCHECK/MF/R"); absorb_bytes(u64le(i)); absorb_field(root); challenge("r_i")
+static void mf_challenge_words(uint64_t round_idx, std::vector<Word>& A, std::vector<Word>& C) {
+    A.clear(); C.clear();
     A.push_back(tag_word(TAG_INIT));
     push_absorb_bytes(A, (const uint8_t*)"SUMCHECK-MF/ROUND-CHAL", 22);
     push_absorb_bytes(A, (const uint8_t*)"SUMCHECK/MF/R", 13);
     uint8_t le[8]; for (int i = 0; i < 8; i++) le[i] = (uint8_t)(round_idx >> (8 * i));
     push_absorb_bytes(A, le, 8);
     push_challenge(C, (const uint8_t*)"r_i", 3);
+}
+static int mf_challenge_device(smw_ctx* c, smw_params* trp, uint64_t round_idx, const uint32_t* d_root, uint32_t* d_out) {
+    std::vector<Word> A, C; mf_challenge_words(round_idx, A, C);
     uint32_t *dA, *dC; int rc = upload_words(c, A, &dA); if (rc) return rc; rc = upload_words(c, C, &dC); if (rc) { cudaFree(dA); return rc; }
     rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA, (int)A.size(), d_root, 1, dC, (int)C.size(), 1, d_out);
     cudaStreamSynchronize(c->stream); cudaFree(dA); cudaFree(dC);
@@ -1060,34 +1159,45 @@ int32_t smw_mf_fold(smw_ctx* c, const void* cur, size_t n, const void* r_host, v
     int rc = launch_mf_fold(c, a.d, n, r.d, o.d); if (rc) return rc;
     return o.finish();
 }
+// The whole commit loop of SumCheckMFProver (channel/src/lib.rs:600-657) as ONE chain of launches with no host round trip and
+// no allocation inside: commit layer i (arity 16, tree_label = ds_tag; only the root is kept, two ping-pong level buffers),
+// r_i from (i, root_i) on the device, fold, repeat.  The rounds are strictly sequential (r_i needs root_i).
 int32_t smw_mf_commit_phase(smw_ctx* c, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host, void* r_out_host, void* final_out_host) {
     if (!c || !table || !roots_out_host || n == 0 || (n & (n - 1))) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     int k = 0; while (((size_t)1 << k) < n) k++;
     smw_params *cp, *trp; int rc = smw_params_commitment_default(c, &cp); if (rc) return rc; rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
     In t0(c, table, n, mem); if (t0.rc) return t0.rc;
-    uint32_t *d_roots, *d_r, *bufA = nullptr, *bufB = nullptr;
-    SMW_CUDA(c, cudaMalloc(&d_roots, (size_t)(k + 1) * FR)); SMW_CUDA(c, cudaMalloc(&d_r, (size_t)(k + 1) * FR));
-    if (k > 0) { SMW_CUDA(c, cudaMalloc(&bufA, (n / 2) * FR)); SMW_CUDA(c, cudaMalloc(&bufB, (n / 4 + 1) * FR)); }
+    DevFree fr{{}, c->stream};
+    uint32_t *d_roots = nullptr, *d_r = nullptr, *bufA = nullptr, *bufB = nullptr, *lvA = nullptr, *lvB = nullptr, *dA = nullptr, *dC = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_roots, (size_t)(k + 1) * FR)); fr.v.push_back(d_roots);
+    SMW_CUDA(c, cudaMalloc(&d_r, (size_t)(k + 1) * FR)); fr.v.push_back(d_r);
+    if (k > 0) { SMW_CUDA(c, cudaMalloc(&bufA, (n / 2) * FR)); fr.v.push_back(bufA); SMW_CUDA(c, cudaMalloc(&bufB, (n / 4 + 1) * FR)); fr.v.push_back(bufB); }
+    SMW_CUDA(c, cudaMalloc(&lvA, ((n + 15) / 16 + 1) * FR)); fr.v.push_back(lvA);
+    SMW_CUDA(c, cudaMalloc(&lvB, ((n + 255) / 256 + 1) * FR)); fr.v.push_back(lvB);
+    std::vector<Word> allA, A, C; int nA = 0;
+    for (int i = 0; i < k; i++) { mf_challenge_words((uint64_t)i, A, C); nA = (int)A.size(); allA.insert(allA.end(), A.begin(), A.end()); }
+    if (k > 0) { rc = upload_words(c, allA, &dA); fr.v.push_back(dA); if (rc) return rc; rc = upload_words(c, C, &dC); fr.v.push_back(dC); if (rc) return rc; }
     const uint32_t* cur = t0.d; size_t len = n;
     for (int i = 0; i <= k && !rc; i++) {
-        // commit the current layer (arity 16, tree_label = ds_tag); only the root is kept
-        smw_tree* tr = nullptr;
-        rc = build_tree(c, cp, 16, ds_tag, (uint32_t*)cur, false, len, &tr); if (rc) break;
-        cudaMemcpyAsync(d_roots + (size_t)i * 8, tr->lv.back(), FR, cudaMemcpyDeviceToDevice, c->stream);
-        smw_tree_free(tr);
-        if (i == k) break;
-        // r_i from (i, root_i) stays on the device and feeds the fold directly: no host round trip per round
-        rc = mf_challenge_device(c, trp, (uint64_t)i, d_roots + (size_t)i * 8, d_r + (size_t)i * 8); if (rc) break;
-        uint32_t* dst = (i % 2 == 0) ? bufA : bufB;
-        rc = launch_mf_fold(c, cur, len, d_r + (size_t)i * 8, dst); if (rc) break;
-        cur = dst; len /= 2;
+        uint32_t* d_root = d_roots + (size_t)i * 8;
+        if (len == 1) SMW_CUDA(c, cudaMemcpyAsync(d_root, cur, FR, cudaMemcpyDeviceToDevice, c->stream));      // a one-leaf tree's root is the leaf
+        const uint32_t* lv = cur; size_t cn = len; uint32_t level = 0; uint32_t* dst = lvA;
+        while (cn > 1 && !rc) {
+            const size_t nn = (cn + 15) / 16;
+            uint32_t* o = (nn == 1) ? d_root : dst;
+            rc = launch_merkle_level(c, cp, lv, cn, o, nn, 16, level, ds_tag, 0, 0, 1, 0, 0);
+            lv = o; cn = nn; level++; dst = (dst == lvA) ? lvB : lvA;
+        }
+        if (rc || i == k) break;
+        rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA + (size_t)i * nA * 8, nA, d_root, 1, dC, (int)C.size(), 1, d_r + (size_t)i * 8); if (rc) break;
+        uint32_t* nxt = (i % 2 == 0) ? bufA : bufB;
+        rc = launch_mf_fold(c, cur, len, d_r + (size_t)i * 8, nxt); if (rc) break;
+        cur = nxt; len /= 2;
     }
     if (!rc) rc = d2h(c, roots_out_host, d_roots, (size_t)(k + 1) * FR);
     if (!rc && r_out_host && k > 0) rc = d2h(c, r_out_host, d_r, (size_t)k * FR);
     if (!rc && final_out_host) rc = d2h(c, final_out_host, cur, FR);
-    cudaStreamSynchronize(c->stream);
-    cudaFree(d_roots); cudaFree(d_r); cudaFree(bufA); cudaFree(bufB);
     return rc;
 }
 
@@ -1203,7 +1313,6 @@ template <class V> int upload_vec(smw_ctx* c, const std::vector<V>& h, V** d) {
     SMW_CUDA(c, cudaMemcpyAsync(*d, h.data(), h.size() * sizeof(V), cudaMemcpyHostToDevice, c->stream));
     return SMW_OK;
 }
-struct DevFree { std::vector<void*> v; cudaStream_t st; ~DevFree() { cudaStreamSynchronize(st); for (void* p : v) if (p) cudaFree(p); } };
 
 // pairs != nullptr: 2 * nreq elements (f, cp interleaved, aligned with req) whose leaf digests are computed first; else leaves (nreq)
 int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void* root_host, const std::vector<uint64_t>& req,

@@ -246,9 +246,26 @@ int launch_mf_fold(smw_ctx* c, const uint32_t* d_cur, size_t n, const uint32_t* 
     { LaunchScope ls(c, KC_FOLD); k_mf_fold<<<(unsigned)((n_out + 255) / 256), 256, 0, c->stream>>>(d_cur, n_out, d_r, d_next); }
     SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
 }
+// deep_ali/src/lib.rs:77,97 asserts !is_in_domain(z, n): z^n == 1 would make a denominator w^j - z vanish
+__global__ void k_z_in_domain(const uint32_t* z, unsigned long long n, int* flag) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const Fr zn = fr_pow_u64(fr_ldg(z), n), one = fr_const(C_R32);
+    bool eq = true;
+    for (int i = 0; i < 8; i++) eq = eq && zn.v[i] == one.v[i];
+    *flag = eq ? 1 : 0;
+}
 int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, const uint32_t* e, const uint32_t* t, size_t n, const uint32_t* d_omega, const uint32_t* d_z, uint32_t* d_f0) {
     constexpr int CH = 8;
     size_t strips = (n + CH - 1) / CH; if (strips == 0) return SMW_OK;
+    {
+        int* d_flag; SMW_CUDA(c, cudaMalloc(&d_flag, 4));
+        k_z_in_domain<<<1, 32, 0, c->stream>>>(d_z, (unsigned long long)n, d_flag); c->launches++;
+        int flag = 0; cudaError_t er = cudaMemcpyAsync(&flag, d_flag, 4, cudaMemcpyDeviceToHost, c->stream);
+        if (er == cudaSuccess) er = cudaStreamSynchronize(c->stream);
+        cudaFree(d_flag);
+        if (er != cudaSuccess) return cuda_err(c, er, "k_z_in_domain");
+        if (flag) return set_err(c, SMW_ERR_Z_IN_DOMAIN, "z must be outside H");
+    }
     k_deep_ali_merge<CH><<<(unsigned)((strips + 127) / 128), 128, 0, c->stream>>>(a, s, e, t, n, d_omega, d_z, d_f0); c->launches++;
     SMW_CUDA(c, cudaGetLastError()); return SMW_OK;
 }

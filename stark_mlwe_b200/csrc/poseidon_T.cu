@@ -3,6 +3,9 @@
 // transcript / FRI-leaf kernels, which are fixed at t = 17 (transcript/src/lib.rs:3).
 #include "poseidon_kernels.cuh"
 #include "chacha.cuh"
+#if SMW_T == 9 || SMW_T == 17
+#include "poseidon_coop_kernels.cuh"
+#endif
 #include <cstdlib>
 #ifndef SMW_T
 #error "compile with -DSMW_T=<width>"
@@ -20,6 +23,24 @@ static int launch_threads(int deflt, int max_nt, const char* env) {
     return deflt;
 }
 
+// Launches of at most this many nodes take the cooperative kernel (one lane group per node, poseidon_coop52.cuh): below
+// one wave the thread-per-node kernel costs a lone warp's latency (3.2 ms per t = 17 node, 148 x 32 nodes or 1), the
+// cooperative one ~0.4 ms per 592 x (32 / G) nodes.  SMW_COOP_MAX overrides (0 = never).
+static uint64_t coop_max_nodes() {
+    static long v = -1;
+    if (v < 0) { const char* e = getenv("SMW_COOP_MAX"); v = e ? atol(e) : (T == 17 ? 4096 : 2048); }
+    return (uint64_t)v;
+}
+#if SMW_T == 9 || SMW_T == 17
+static int launch_nodes_coop(smw_ctx* c, const smw_params* p, const LevelBatch& B) {
+    constexpr int NG = 32 / CoopCfg<T>::G;
+    { LaunchScope ls(c, KC_MERKLE_LEVEL);
+      k_nodes_coop52<T><<<(unsigned)((B.total + NG - 1) / NG), 32, 0, c->stream>>>(B, p->d_tables52, coop_tab(p)); }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+#endif
+
 // segment list [load lanes][permutation][lanes -> external scale] of the batched permutation
 static int io_segs(smw_ctx* c, smw_params* p, bool sparse, Segs* sg) {
     Segs io; int rc = get_sponge_segs(c, p, -1, 0, &io); if (rc) return rc;      // key (-1, 0): first[0] = load ops, first[1] = output ops
@@ -36,6 +57,14 @@ static int out_first_op(smw_ctx* c, smw_params* p, int* out_first) {
 
 template <> int permute_batch_T<T>(smw_ctx* c, const smw_params* cp, uint32_t* d_states, size_t batch, bool sparse) {
     smw_params* p = const_cast<smw_params*>(cp);
+#if SMW_T == 9 || SMW_T == 17
+    if (sparse && c->use_f52 && p->d_tables52 && (uint64_t)batch <= coop_max_nodes() * (T == 17 ? 2 : 1)) {   // small batch: the latency form (a node is two permutations at t = 17)
+        constexpr int NG = 32 / CoopCfg<T>::G;
+        { LaunchScope ls(c, KC_PERMUTE); k_permute_coop52<T><<<(unsigned)((batch + NG - 1) / NG), 32, 0, c->stream>>>(d_states, batch, p->d_tables52, coop_tab(p)); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
     Segs sg; int rc = io_segs(c, p, sparse, &sg); if (rc) return rc;
     PoseidonDev P = dev_view(p);
 #if SMW_T == 9 || SMW_T == 17
@@ -61,6 +90,12 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
 #if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52 && (uint64_t)n_parents * (uint64_t)n_cols <= coop_max_nodes()) {
+        LevelBatch B{}; B.segs = nullptr; B.n_segs = 0; B.n_cols = n_cols; B.label_stride = label_stride; B.child_col_stride = child_col_stride; B.parent_col_stride = parent_col_stride;
+        B.u = NodeSeg{d_children, d_parents, (uint64_t)n_children, (uint64_t)n_parents, label0, pos_offset, level, (uint32_t)arity, 0};
+        B.total = (uint64_t)n_parents * (uint64_t)n_cols;
+        return launch_nodes_coop(c, p, B);
+    }
     if (c->use_f52 && p->d_tables52) {
         const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52");
         size_t sm = state_smem_bytes52<T>(nt);
@@ -82,6 +117,45 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
                                                      child_col_stride, parent_col_stride, sg, out_first, P); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
+}
+// several runs (explicit device segment array) of one level in one launch; widths without FP64-pipe tables take one launch per run
+template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const NodeSeg* d_segs, int n_segs, uint64_t total, int arity) {
+    smw_params* p = const_cast<smw_params*>(cp);
+    if (n_segs <= 0 || total == 0) return SMW_OK;
+#if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52) {
+        if (total <= coop_max_nodes()) {
+            LevelBatch B{}; B.segs = d_segs; B.n_segs = n_segs; B.total = total;
+            return launch_nodes_coop(c, p, B);
+        }
+        Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
+        int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
+        const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<T>(nt);
+        rc = set_smem(c, k_merkle_level52_multi<T>, sm); if (rc) return rc;
+        { LaunchScope ls(c, KC_MERKLE_LEVEL);
+          k_merkle_level52_multi<T><<<(unsigned)((total + nt - 1) / nt), nt, sm, c->stream>>>(d_segs, n_segs, total, sg, out_first, dev_view(p)); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
+    return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "multi-run level launch needs the FP64-pipe tables (t = 9, 17)");
+}
+template <> int pair_leaves_multi_T<T>(smw_ctx* c, const smw_params* cp, const LeafSeg* d_segs, int n_segs, uint64_t total) {
+    smw_params* p = const_cast<smw_params*>(cp);
+    if (n_segs <= 0 || total == 0) return SMW_OK;
+#if SMW_T == 9 || SMW_T == 17
+    if (c->use_f52 && p->d_tables52) {
+        Segs sg; int rc = get_sponge_segs(c, p, 4, 2, &sg); if (rc) return rc;
+        int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
+        const int nt = launch_threads(Cfg52<T>::RUN, Cfg52<T>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<T>(nt);
+        rc = set_smem(c, k_pair_leaves52_multi<T>, sm); if (rc) return rc;
+        { LaunchScope ls(c, KC_PAIR_LEAVES);
+          k_pair_leaves52_multi<T><<<(unsigned)((total + nt - 1) / nt), nt, sm, c->stream>>>(d_segs, n_segs, total, sg, out_first, dev_view(p)); }
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
+#endif
+    return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "multi-run leaf launch needs the FP64-pipe tables (t = 9, 17)");
 }
 template <> int hash_groups_T<T>(smw_ctx* c, const smw_params* cp, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                                  size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out) {
@@ -270,6 +344,19 @@ k_fri_leaf_hashed52(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __r
     run_ops52<17>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
     emit_ext52(S.load(0), out + i * 8);
 }
+__global__ void __launch_bounds__(Cfg52<17>::NT, Cfg52<17>::MINB)
+k_fri_leaf_hashed52_multi(const uint32_t* __restrict__ tmpl_le256, const LeafSeg* __restrict__ segs, int n_segs, uint64_t total, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    const LeafSeg ls = segs[find_seg(g, &segs[0].first, sizeof(LeafSeg) / 8, n_segs)];
+    const uint64_t i = g - ls.first;
+    StateRef52 S = state_ref52<17>(smem, blockDim.x, threadIdx.x);
+    InFriLeaf in{ls.f + i * 8, ls.cp ? ls.cp + (i / ls.cp_div) * 8 : nullptr, tmpl_le256};
+    run_segs52<17>(blockDim.x, P, sg, in);
+    run_ops52<17>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), ls.out + i * 8);
+}
 __global__ void __launch_bounds__(Cfg<17>::NT, Cfg<17>::MINB)
 k_fri_leaf_hashed(const uint32_t* __restrict__ tmpl_le256, const uint32_t* __restrict__ f, const uint32_t* __restrict__ s,
                   size_t s_div, size_t n, uint32_t* __restrict__ out, Segs sg, int out_first, PoseidonDev P) {
@@ -331,6 +418,12 @@ int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d
 int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
                           const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute, uint32_t* d_out) {
     if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
+    if (c->use_f52 && p->d_tables52) {       // one warp per sponge (poseidon_coop52.cuh): ~0.2 ms per permutation instead of 2.5 ms on one thread
+        k_transcript_coop52<<<1, 32, 0, c->stream>>>(d_state, fresh, pos, d_immA, nA, d_extB, nB, d_immC, nC, final_permute, d_out, p->d_tables52, coop_tab(p));
+        c->launches++;
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
     k_transcript_run<<<1, 32, state_smem_bytes<17>(1) + 64, c->stream>>>(d_state, fresh, pos, d_immA, nA, d_extB, nB, d_immC, nC, final_permute, d_out, dev_view(p));
     c->launches++;
     SMW_CUDA(c, cudaGetLastError());
@@ -339,6 +432,12 @@ int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, in
 int launch_transcript_absorb_coop(smw_ctx* c, const smw_params* p, uint32_t* d_state, int pos, const uint32_t* d_ext, size_t n) {
     if (p->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
     if (n == 0) return SMW_OK;
+    if (c->use_f52 && p->d_tables52) {
+        k_transcript_coop52<<<1, 32, 0, c->stream>>>(d_state, 0, pos, nullptr, 0, d_ext, n, nullptr, 0, 0, nullptr, p->d_tables52, coop_tab(p));
+        c->launches++;
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
     CoopTables L{p->layout.mds, p->layout.rc_full, p->layout.rc_part, p->layout.k_one, p->rp};
     k_transcript_absorb_coop<<<1, 32, 0, c->stream>>>(d_state, pos, d_ext, n, p->d_tables, L);
     c->launches++;
@@ -366,8 +465,27 @@ int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* ctrp, const uint32_t* d
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
+int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* ctrp, const uint32_t* d_tmpl, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, uint64_t total) {
+    if (n_segs <= 0 || total == 0) return SMW_OK;
+    smw_params* trp = const_cast<smw_params*>(ctrp);
+    if (!(c->use_f52 && trp->d_tables52)) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "multi-run leaf launch needs the FP64-pipe tables");
+    Segs sg; int rc = get_sponge_segs(c, trp, -2, lane_f * 256 + lane_s, &sg); if (rc) return rc;
+    int out_first; rc = out_first_op(c, trp, &out_first); if (rc) return rc;
+    const int nt = launch_threads(Cfg52<17>::RUN, Cfg52<17>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<17>(nt);
+    rc = set_smem(c, k_fri_leaf_hashed52_multi, sm); if (rc) return rc;
+    { LaunchScope ls(c, KC_FRI_LEAF);
+      k_fri_leaf_hashed52_multi<<<(unsigned)((total + nt - 1) / nt), nt, sm, c->stream>>>(d_tmpl, d_segs, n_segs, total, sg, out_first, dev_view(trp)); }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
 int launch_fri_sample_z(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, const uint64_t* d_sizes, int L, uint64_t seed_z, uint32_t* d_z) {
     if (L <= 0) return SMW_OK;
+    if (c->use_f52 && trp->d_tables52) {
+        k_fri_sample_z_coop52<<<L, 32, 0, c->stream>>>(d_tmpl, d_sizes, L, seed_z, d_z, trp->d_tables52, coop_tab(trp));
+        c->launches++;
+        SMW_CUDA(c, cudaGetLastError());
+        return SMW_OK;
+    }
     const int nt = 32; size_t sm = state_smem_bytes<17>(nt);
     k_fri_sample_z<<<(L + nt - 1) / nt, nt, sm, c->stream>>>(d_tmpl, d_sizes, L, seed_z, d_z, dev_view(trp));
     c->launches++;

@@ -268,6 +268,55 @@ k_pair_leaves52(const uint32_t* __restrict__ f, const uint32_t* __restrict__ cp,
     emit_ext52(S.load(0), out + i * 8);
 }
 
+// ------------------------------------------------------------------ several runs in one launch (explicit segment arrays)
+// Level j of every layer tree of a FRI commit phase, or the leaves of every layer, are hashed by ONE launch: the layers are
+// independent (z_l is public, deep_ali/src/fri.rs:250), and per-tree launches left the machine with hundreds of sub-wave launches.
+SMW_DEV int find_seg(const uint64_t g, const uint64_t* firsts, int stride_words, int n_segs) {
+    int i = 0;
+    while (i + 1 < n_segs && g >= firsts[(size_t)(i + 1) * stride_words]) i++;
+    return i;
+}
+template <int T> __global__ void __launch_bounds__(Cfg52<T>::NT, Cfg52<T>::MINB)
+k_merkle_level52_multi(const NodeSeg* __restrict__ segs, int n_segs, uint64_t total, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    const NodeSeg ns = segs[find_seg(g, &segs[0].first, sizeof(NodeSeg) / 8, n_segs)];
+    const uint64_t q = g - ns.first;
+    StateRef52 S = state_ref52<T>(smem, blockDim.x, threadIdx.x);
+    zero_lanes52(S, T);
+    S.store(0, f52_from_u64((uint64_t)ns.arity)); S.store(1, f52_from_u64(ns.level)); S.store(2, f52_from_u64(q + ns.pos_offset)); S.store(3, f52_from_u64(ns.label));
+    const uint64_t base = q * ns.arity;
+    InChildren in;
+    in.cnt = (int)((ns.n_children - base < (uint64_t)ns.arity) ? (ns.n_children - base) : (uint64_t)ns.arity);
+    in.src = ns.children + base * 8;
+    const int my_seg = 2 * ((4 + in.cnt + 1 + (T - 2)) / (T - 1)) - 1;
+    F52 out = f52_zero();
+#pragma unroll 1
+    for (int s = 0; s < sg.n; s++) {
+        run_ops52<T>(blockDim.x, P.tbl52, P.prog, sg.first[s], sg.count[s], in);
+        if (s == my_seg) out = S.load(0);
+    }
+    S.store(0, out);
+    run_ops52<T>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), ns.parents + q * 8);
+}
+template <int T> __global__ void __launch_bounds__(Cfg52<T>::NT, Cfg52<T>::MINB)
+k_pair_leaves52_multi(const LeafSeg* __restrict__ segs, int n_segs, uint64_t total, Segs sg, int out_first, PoseidonDev P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    const LeafSeg ls = segs[find_seg(g, &segs[0].first, sizeof(LeafSeg) / 8, n_segs)];
+    const uint64_t i = g - ls.first;
+    StateRef52 S = state_ref52<T>(smem, blockDim.x, threadIdx.x);
+    zero_lanes52(S, T);
+    S.store(0, f52_from_u64((uint64_t)ls.arity)); S.store(1, f52_from_u64(0xffffffffull)); S.store(2, f52_from_u64(i + ls.pos_offset)); S.store(3, f52_from_u64(ls.label));
+    InPair in{ls.f + i * 8, ls.cp ? ls.cp + (i / ls.cp_div) * 8 : nullptr};
+    run_segs52<T>(blockDim.x, P, sg, in);
+    run_ops52<T>(blockDim.x, P.tbl52, P.prog, out_first, 1, in);
+    emit_ext52(S.load(0), ls.out + i * 8);
+}
+
 template <typename K> static int set_smem(smw_ctx* c, K kernel, size_t bytes) {
     SMW_CUDA(c, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     return SMW_OK;

@@ -44,7 +44,7 @@ __global__ void k_internal_to_ext(const uint32_t* tbl, size_t n, uint32_t* ext) 
 struct DeriveArgs {
     int t, rp;
     const uint32_t* mds;   // [t][t]
-    uint32_t *lu_full, *sp_row, *sp_col, *lu_post;
+    uint32_t *lu_full, *sp_row, *sp_col, *lu_post, *post;
     uint32_t *mh, *mhi, *aug, *pw, *tmp, *vk, *wk, *vt;   // scratch
     int* status;
 };
@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(256) k_derive_factor(DeriveArgs a) {
         if ((rp >> bit) & 1) { matmul(a.aug, a.lu_post, a.pw, n); matcopy(a.lu_post, a.aug, n); }
         if ((rp >> (bit + 1)) != 0) { matmul(a.aug, a.pw, a.pw, n); matcopy(a.pw, a.aug, n); }
     }
+    matcopy(a.post, a.lu_post, n);             // the dense Mh^rp for the cooperative kernels, before the in-place LU
     lu_inplace(a.lu_post, n, a.status, &sh_inv);
 }
 
@@ -275,7 +276,7 @@ static int finish_params(smw_ctx* c, smw_params* p, uint32_t* mds_internal) {
     SMW_CUDA(c, cudaMalloc(&scratch, words * 4)); SMW_CUDA(c, cudaMalloc(&d_status, 4));
     SMW_CUDA(c, cudaMemsetAsync(d_status, 0, 4, c->stream));
     DeriveArgs a; a.t = t; a.rp = rp; a.mds = mds_internal;
-    a.lu_full = (uint32_t*)p->lu_full; a.sp_row = (uint32_t*)p->sp_row; a.sp_col = (uint32_t*)p->sp_col; a.lu_post = (uint32_t*)p->lu_post;
+    a.lu_full = (uint32_t*)p->lu_full; a.sp_row = (uint32_t*)p->sp_row; a.sp_col = (uint32_t*)p->sp_col; a.lu_post = (uint32_t*)p->lu_post; a.post = p->d_tables + (size_t)EL * p->layout.post;
     uint32_t* q = scratch; a.mh = q; q += EL * nn; a.mhi = q; q += EL * nn; a.aug = q; q += EL * 2 * nn; a.pw = q; q += EL * nn;
     a.tmp = q; q += EL * t; a.vk = q; q += EL * t; a.wk = q; q += EL * t; a.vt = q; q += EL * t; a.status = d_status;
     k_derive_factor<<<1, 256, 0, c->stream>>>(a); c->launches++;
@@ -337,6 +338,14 @@ int launch_pair_leaves(smw_ctx* c, const smw_params* p, const uint32_t* d_f, con
                        uint32_t* d_out, size_t cp_div) {
     if (n == 0) return SMW_OK;
     DISPATCH_T(p->t, return pair_leaves_T<T>(c, p, d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div));
+    return SMW_OK;
+}
+int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity) {
+    DISPATCH_T(p->t, return merkle_level_multi_T<T>(c, p, d_segs, n_segs, total_nodes, arity));
+    return SMW_OK;
+}
+int launch_pair_leaves_multi(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total) {
+    DISPATCH_T(p->t, return pair_leaves_multi_T<T>(c, p, d_segs, n_segs, total));
     return SMW_OK;
 }
 int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,

@@ -19,6 +19,7 @@ TableLayout table_layout(int t, int rp) {
     L.lu_post = q; q += (uint32_t)(t - 1) * (t - 1);
     L.mds = q; q += (uint32_t)t * t;
     L.k_in = q++; L.k_out = q++; L.k_rr = q++; L.k_one = q++;
+    L.post = q; q += (uint32_t)(t - 1) * (t - 1);      // the deferred matrix Mh^rp itself (dense; the cooperative kernels of poseidon_coop52.cuh apply it row per lane)
     L.total = q + 1;          // one padding element: the interpreter never reads past it, but keep the tail defined
     return L;
 }

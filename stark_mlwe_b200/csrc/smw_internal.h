@@ -13,8 +13,17 @@
 namespace smw {
 struct PoseidonDev;
 // element indices (EL-word elements) of the tables inside smw_params::d_tables
-struct TableLayout { uint32_t lu_full, rc_full, rc_part, sp_row, sp_col, lu_post, mds, k_in, k_out, k_rr, k_one, total; };
+struct TableLayout { uint32_t lu_full, rc_full, rc_part, sp_row, sp_col, lu_post, mds, k_in, k_out, k_rr, k_one, post, total; };
 struct Segs { int n; int first[8]; int count[8]; };   // (first, count) ranges of the op array, run in order
+// One run of sibling groups of a Merkle level: parents[q] = H(DS(arity, level, q + pos_offset, label), children[q * arity ..]),
+// q < n_parents (merkle/src/lib.rs:164-179).  `first` = index of the run's first node among all nodes of the launch.
+struct NodeSeg { const uint32_t* children; uint32_t* parents; uint64_t n_children, n_parents, label, pos_offset; uint32_t level, arity; uint64_t first; };
+// What one level launch covers: explicit runs (device array `segs`: levels of different trees hashed together, e.g. level j of
+// every layer tree of a FRI commit phase) or, with segs == nullptr, `n_cols` equal columns derived from `u`.
+struct LevelBatch { const NodeSeg* segs; int n_segs; NodeSeg u; int n_cols; uint64_t label_stride; size_t child_col_stride, parent_col_stride; uint64_t total; };
+// Leaves of one FRI layer: out[i] = pair-leaf digest H(DS(arity, u32::MAX, i + pos_offset, label), [f_i, cp_{i / cp_div}]) (merkle/src/lib.rs:382-400)
+// or hash_leaf_pair(f_i, cp_{i / cp_div}) (deep_ali/src/fri.rs:38-44); cp == nullptr stands for zeros.
+struct LeafSeg { const uint32_t* f; const uint32_t* cp; uint32_t* out; uint64_t n, label, pos_offset, cp_div; uint32_t arity, pad; uint64_t first; };
 }
 
 struct smw_params {
@@ -66,6 +75,7 @@ struct smw_tree {
     std::vector<size_t> len;          // level 0 = leaves
     std::vector<uint32_t*> lv;        // device pointers, external form
     std::vector<bool> owned;
+    uint32_t* arena = nullptr;        // the levels above level 0, when they share one allocation
 };
 
 struct smw_transcript {
@@ -83,6 +93,7 @@ struct smw_fri {
     std::vector<uint32_t*> f;         // device, external form
     uint32_t* d_z = nullptr;          // L elements
     std::vector<smw_tree*> tree;
+    uint32_t *arena_f = nullptr, *arena_leaves = nullptr, *arena_levels = nullptr;   // f layers, leaf digests and tree levels: one allocation each
 };
 
 namespace smw {
@@ -135,6 +146,10 @@ int launch_hash_ds_single(smw_ctx* c, const smw_params* p, const uint32_t* d_ds,
 int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                        size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
 int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
+// several runs of one level in one launch (explicit device segment array); all runs share the parameter set and the arity
+int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);
+int launch_pair_leaves_multi(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total);
+int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_template_le256, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, uint64_t total);
 // transcript program: state' = run(state, pos; immediates A, ext elements B, immediates C, optional final permute)
 int launch_transcript_run(smw_ctx* c, const smw_params* p, uint32_t* d_state, int fresh, int pos,
                           const uint32_t* d_immA, int nA, const uint32_t* d_extB, size_t nB, const uint32_t* d_immC, int nC, int final_permute,
@@ -155,6 +170,8 @@ template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32
                                    uint32_t* d_out, size_t cp_div);
 template <int T> int hash_groups_T(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                                    size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
+template <int T> int merkle_level_multi_T(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);
+template <int T> int pair_leaves_multi_T(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total);
 template <int T> int hash_ds_single_T(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
 
 // field_kernels.cu

@@ -101,7 +101,8 @@ def test_anchor_A11_fri_build(ctx, smw, O):
 
 
 @pytest.mark.parametrize("log_n0,schedule", [(11, [16, 16, 8]), (12, [16, 16, 8]), (10, [2] * 10), (12, [32, 32, 4]), (12, [64, 2, 8]), (9, [4, 4, 4]),
-                                             (8, []), (14, [128, 128]), (6, [64])])
+                                             (8, []), (14, [128, 128]), (6, [64]),
+                                             (13, [2] * 13), (16, [16, 16, 8]), (15, [4, 2, 8, 16])])   # the last three cross the batch / cooperative kernel boundary inside one build
 def test_fri_build_matches_oracle(ctx, smw, O, rnd, log_n0, schedule):
     """every layer's f, s, arity, leaf mode and root; includes the published-CSV schedule [16,16,8] and fold factor 2 to size 1"""
     f0 = rnd(700 + log_n0 + len(schedule), 1 << log_n0)
@@ -202,6 +203,16 @@ def test_open_many_matches_oracle_and_verifies(ctx, smw, O, rnd, arity, n):
     with pytest.raises(smw.SmwError) as e:
         tree.open_many([])
     assert e.value.code == 11
+
+
+def test_deep_ali_merge_rejects_z_in_domain(ctx, smw, O, rnd):
+    """deep_ali/src/lib.rs:77,97 asserts z outside H: z = w^3 makes a denominator vanish -> SMW_ERR_Z_IN_DOMAIN, not a poisoned strip"""
+    n = 1 << 6
+    a, s, e, t = rnd(1, n), rnd(2, n), rnd(3, n), rnd(4, n)
+    omega = O.root_of_unity(6)
+    with pytest.raises(smw.SmwError) as err:
+        smw.deep_ali_merge_evals(ctx, a, s, e, t, omega, O.fr_pow(omega, 3))
+    assert err.value.code == 12
 
 
 def test_deep_ali_merge_matches_oracle(ctx, smw, O, rnd):

@@ -36,13 +36,15 @@ def test_anchor_A1_and_A13(ctx, smw, O):
     assert O.fr_hex(out[0, 16]) == "0x325f385ebdd97e2a2ef7e298c56984b829713e53199b7aeacc04cd036e0f0e13"
 
 
-@pytest.mark.parametrize("t,batch", [(17, 1), (17, 333), (9, 1), (9, 700)])
+@pytest.mark.parametrize("t,batch", [(17, 1), (17, 333), (9, 1), (9, 700), (17, 9000), (9, 2500)])   # <= 8192 / 2048 states: the cooperative kernel; above: one thread per state
 @pytest.mark.parametrize("dense", [False, True])
 def test_permute_matches_oracle(ctx, smw, O, rnd, t, batch, dense):
     """the production path (sparse partial rounds, LU in-place mat-vec, lazy reduction) and the literal round structure
     both equal the reference's dense permutation"""
     if dense and batch > 400:
         batch = 300
+    if batch > 5000:
+        O.set_threads(O.max_threads())
     g, o = smw.poseidon_params_for_width(ctx, t), O.Params.for_width(t)
     st = rnd(1000 + t + batch, batch * t).reshape(batch, t, 4)
     st[0, :, :] = 0                                    # all-zero state
@@ -154,3 +156,33 @@ def test_commit_columns_matches_per_column_trees(ctx, smw, O, rnd):
     roots = smw.merkle_commit_columns(ctx, cols, 16, p, label0=10, label_stride=3)
     for c in range(5):
         assert eq(roots[c], O.MerkleTree.new(cols[c], 16, 10 + 3 * c, O.Params.commitment_default()).root())
+
+
+def test_unsupported_round_counts_and_arity_one_are_rejected(ctx, smw, O, rnd):
+    """the sparse two-round blocks need an even rp, the lazy-reduction bound rp <= 96: anything else is an error,
+    not a wrong digest; arity 1 over more than one leaf never terminates in the reference (merkle/src/lib.rs:164) -> error"""
+    for rp in (61, 63, 98, 200):
+        with pytest.raises(smw.SmwError) as e:
+            smw.params_from_seed(ctx, b"POSEIDON-T17-X5-SEED", 17, rp)
+        assert e.value.code == 8
+    p = smw.params_from_seed(ctx, b"SOME-OTHER-SEED", 9, 2)                 # small even rp: sparse path == dense path == oracle
+    st = rnd(31, 9 * 5).reshape(5, 9, 4)
+    want = O.permute(O.Params.from_seed(b"SOME-OTHER-SEED", 9, 2), st)
+    assert np.array_equal(smw.permute(ctx, st, p), want) and np.array_equal(smw.permute(ctx, st, p, dense=True), want)
+    cfg = smw.MerkleChannelCfg.new(ctx, 1)
+    with pytest.raises(smw.SmwError) as e:
+        smw.MerkleTree.new(rnd(1, 4), cfg)
+    assert e.value.code == 7
+    assert np.array_equal(smw.MerkleTree.new(rnd(1, 1), cfg).root(), rnd(1, 1)[0])
+
+
+@pytest.mark.parametrize("arity,n_cols,n", [(16, 3, 1 << 12), (16, 70, 256), (2, 5, 1 << 11), (8, 2, 4097), (4, 1, 3000)])
+def test_commit_columns_across_kernel_boundary(ctx, smw, O, rnd, arity, n_cols, n):
+    """column batches whose lower levels take the thread-per-node kernel and whose tops take the cooperative one (<= 4096 / 2048
+    nodes per launch): every root against the oracle"""
+    cols = rnd(arity * 100 + n_cols, n_cols * n).reshape(n_cols, n, 4)
+    p = smw.poseidon_params_for_arity(ctx, arity)
+    got = smw.merkle_commit_columns(ctx, cols, arity, p, label0=11, label_stride=3)
+    op = O.Params.for_arity(arity)
+    for c in range(n_cols):
+        assert np.array_equal(got[c], O.MerkleTree.new(cols[c], arity, 11 + 3 * c, op).root()), c

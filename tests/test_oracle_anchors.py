@@ -104,3 +104,27 @@ def test_ntt_against_naive_dft(O):
         assert np.array_equal(O.ntt(ev, inverse=True), c)
     ones = O.to_mont([1] * 8)       # the reference's only FFT test: all-ones round trip (fft/src/lib.rs:40-54)
     assert np.array_equal(O.ntt(O.ntt(ones), inverse=True), ones)
+
+
+def test_ntt_and_lde_against_horner_at_full_sizes(O):
+    """The definition pin at BASELINE sizes: evals[i] = P(w^i) by Horner's rule (poly/src/lib.rs `evaluate`) at random i, n = 2^16 and
+    2^20; the inverse transform returns the coefficients; the coset LDE at index i is P(g w_N^i) for P = ifft(column)."""
+    for log_n in (16, 20):
+        n = 1 << log_n
+        c = O.StdRng.seed_from_u64(4000 + log_n).fr_rand(n)
+        ev = O.ntt(c)
+        w = O.root_of_unity(log_n)
+        rng = np.random.default_rng(log_n)
+        for i in [0, 1, n - 1, n // 2] + [int(v) for v in rng.integers(0, n, 6)]:
+            assert np.array_equal(ev[i], O.horner(c, O.fr_pow(w, i))), (log_n, i)
+        assert np.array_equal(O.ntt(ev, inverse=True), c)
+    log_n, lb = 14, 2
+    col = O.StdRng.seed_from_u64(77).fr_rand(1 << log_n)
+    g = O.to_mont([5])[0]
+    ext = O.lde(col, lb, g)
+    coef = O.ntt(col, inverse=True)
+    wN = O.root_of_unity(log_n + lb)
+    for i in (0, 1, 4, 12345, (1 << (log_n + lb)) - 1):
+        x = O.fr_mul(g.reshape(1, 4), O.fr_pow(wN, i).reshape(1, 4))[0]
+        assert np.array_equal(ext[i], O.horner(coef, x)), i
+    assert np.array_equal(ext[::4], O.lde(col, 0, g))          # every 4th point of the blow-up-4 coset is the blow-up-1 coset

@@ -1,0 +1,40 @@
+#!/bin/bash
+# One parameterised runner for a GPU lease (replaces the per-lease scripts of round 1):
+#   gpurun --timeout 1500 -- 'bash tools/gpu_run.sh <tag> <stage> [<stage> ...]'
+# Every stage writes gpurun_out/<tag>_<stage>.* ; a failing stage does not stop the later ones.
+# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | shard<N> | dist<N>
+set -u
+TAG=${1:?tag}; shift
+OUT=gpurun_out; mkdir -p $OUT
+export PYTHONUNBUFFERED=1
+NCU_LIST="ncu --metrics gpu__time_duration.sum --clock-control none --csv"
+NCU_FULL="ncu --set full --clock-control none --import-source on"
+for stage in "$@"; do
+  echo "=== stage $stage ($(date +%T))"
+  case $stage in
+    tests)      timeout 1500 python -m pytest tests -m gpu -q --maxfail=25 --tb=short --durations=15 > $OUT/${TAG}_pytest_gpu.log 2>&1; tail -40 $OUT/${TAG}_pytest_gpu.log ;;
+    tests_fast) timeout 900 python -m pytest tests -m gpu -q --maxfail=25 --tb=short --durations=10 --deselect tests/test_gpu_full_size.py > $OUT/${TAG}_pytest_gpu_fast.log 2>&1; tail -40 $OUT/${TAG}_pytest_gpu_fast.log ;;
+    smoke)      timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${TAG}_smoke.log 2>&1; tail -3 $OUT/${TAG}_smoke.log ;;
+    bench)      timeout 900 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; tail -c 3000 $OUT/${TAG}_bench.json; tail -5 $OUT/${TAG}_bench.err ;;
+    bench_ref)  timeout 600 python bench.py --impl reference > $OUT/${TAG}_bench_reference.json 2> $OUT/${TAG}_bench_reference.err; cat $OUT/${TAG}_bench_reference.json ;;
+    fri)        timeout 600 python tools/fri_bench.py > $OUT/${TAG}_fri.json 2> $OUT/${TAG}_fri.err; cat $OUT/${TAG}_fri.json; tail -5 $OUT/${TAG}_fri.err ;;
+    kat)        timeout 900 python -m pytest tests/test_gpu_proof_bytes_kat.py -m gpu -q --durations=10 > $OUT/${TAG}_kat.log 2>&1; tail -15 $OUT/${TAG}_kat.log ;;
+    mf)         timeout 600 python tools/mf_bench.py > $OUT/${TAG}_mf.json 2> $OUT/${TAG}_mf.err; cat $OUT/${TAG}_mf.json; tail -5 $OUT/${TAG}_mf.err ;;
+    launches)   timeout 900 $NCU_LIST -c 600 --log-file $OUT/${TAG}_ncu_launches.csv python bench.py --steps 1 --warmup 1 --log-n 16 --cols 16 --no-cpu --no-e2e > $OUT/${TAG}_ncu_launches.out 2>&1; tail -3 $OUT/${TAG}_ncu_launches.out ;;
+    launches_fri) timeout 900 $NCU_LIST -c 900 --log-file $OUT/${TAG}_ncu_launches_fri.csv python tools/fri_bench.py --once > $OUT/${TAG}_ncu_launches_fri.out 2>&1; tail -3 $OUT/${TAG}_ncu_launches_fri.out ;;
+    ncu_merkle) timeout 900 $NCU_FULL -k regex:k_merkle_level52 -c 1 -o $OUT/${TAG}_ncu_merkle_level52 -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_merkle.out 2>&1
+                ncu -i $OUT/${TAG}_ncu_merkle_level52.ncu-rep --page details --csv > $OUT/${TAG}_ncu_merkle_level52_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_merkle.out ;;
+    ncu_coop)   timeout 900 $NCU_FULL -k regex:k_nodes_coop52 -c 2 -o $OUT/${TAG}_ncu_nodes_coop52 -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_coop.out 2>&1
+                ncu -i $OUT/${TAG}_ncu_nodes_coop52.ncu-rep --page details --csv > $OUT/${TAG}_ncu_nodes_coop52_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_coop.out ;;
+    ncu_ntt)    timeout 900 $NCU_FULL -k regex:k_ntt -c 3 -o $OUT/${TAG}_ncu_ntt -f python bench.py --steps 1 --warmup 0 --log-n 18 --cols 8 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_ntt.out 2>&1
+                ncu -i $OUT/${TAG}_ncu_ntt.ncu-rep --page details --csv > $OUT/${TAG}_ncu_ntt_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_ntt.out ;;
+    sanitizer)  for tool in memcheck racecheck; do
+                  timeout 1200 compute-sanitizer --tool $tool --error-exitcode 1 python -m pytest tests/test_gpu_sanitizer_subset.py -m gpu -q -x > $OUT/${TAG}_sanitizer_$tool.log 2>&1; echo "$tool exit $?" >> $OUT/${TAG}_sanitizer_$tool.log; tail -6 $OUT/${TAG}_sanitizer_$tool.log
+                done ;;
+    shard*)     N=${stage#shard}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/fri_shard_bench.py > $OUT/${TAG}_shard_n$N.json 2> $OUT/${TAG}_shard_n$N.err; cat $OUT/${TAG}_shard_n$N.json; tail -5 $OUT/${TAG}_shard_n$N.err ;;
+    dist*)      N=${stage#dist}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/ntt_fri_dist_bench.py > $OUT/${TAG}_dist_n$N.json 2> $OUT/${TAG}_dist_n$N.err; cat $OUT/${TAG}_dist_n$N.json; tail -5 $OUT/${TAG}_dist_n$N.err ;;
+    scale*)     N=${stage#scale}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N > $OUT/${TAG}_bench_n$N.json 2> $OUT/${TAG}_bench_n$N.err; tail -c 2500 $OUT/${TAG}_bench_n$N.json; tail -5 $OUT/${TAG}_bench_n$N.err ;;
+    *) echo "unknown stage $stage" ;;
+  esac
+done
+echo "=== done ($(date +%T))"
