@@ -73,6 +73,9 @@ int32_t smw_diag_mac_rate(smw_ctx* ctx, double* mac_per_s, double* warp_instr_pe
 /* the FP64-pipe counterparts: measured DFMA.RZ issue rate, and the FP64 instructions (DFMA + DADD) one production permutation of
  * this parameter set executes when it runs on the fr52 multiplier (0 otherwise) */
 int32_t smw_diag_fp64_rate(smw_ctx* ctx, double* dfma_per_s, double* warp_instr_per_clk_per_sm);
+/* the same measurements with what is needed to re-derive them: out5 = {lanes per s, warp instructions per clock per SM, SM clock (Hz) held
+ * during the measurement (in-kernel clock64 ticks / event time), SM count, nominal maximum SM clock (Hz)}; fp64 = 0: IMAD.WIDE.U32, 1: DFMA.RZ */
+int32_t smw_diag_pipe_rate(smw_ctx* ctx, int32_t fp64, double* out5);
 int32_t smw_diag_perm_fp64_ops(const smw_params* params, uint64_t* ops_out);
 /* self-test of the FP64-pipe field arithmetic (csrc/fr52.cuh): out[i] = sum_{j<k} a[i k + j] * b[i k + j] */
 int32_t smw_diag_f52_dot(smw_ctx* ctx, const void* a, const void* b, size_t n_out, int32_t k, void* out, int32_t mem);
@@ -181,6 +184,38 @@ int32_t smw_sumcheck_round_coeffs(smw_ctx* ctx, const void* layer, size_t n, voi
 int32_t smw_mf_round_challenge_from_root(smw_ctx* ctx, uint64_t round_idx, const void* prev_root_host, smw_params* tr_params_or_null, void* out_fr_host);
 int32_t smw_mf_fold(smw_ctx* ctx, const void* cur, size_t n, const void* r_fr_host, void* next, int32_t mem);
 int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host /* k+1 */, void* r_out_host /* k */, void* final_out_host);
+
+/* ---- multi-GPU data plane: one process per GPU, NCCL bound at run time -----------------------------------
+ * The reference has no distributed path; these entry points shard the SAME computations — results are
+ * bit-identical to the single-GPU calls above.  Bootstrap: rank 0 obtains a 128-byte id, the host carries it to every rank
+ * (any transport), every rank calls smw_comm_init with the context of its GPU.  All exchanges run on the context's stream
+ * on device buffers; a NULL communicator means one rank. */
+typedef struct smw_comm smw_comm;
+int32_t smw_comm_unique_id(uint8_t* out128);
+int32_t smw_comm_init(smw_ctx* ctx, const uint8_t* id128, int32_t world, int32_t rank, smw_comm** out);
+int32_t smw_comm_rank(const smw_comm* m);
+int32_t smw_comm_world(const smw_comm* m);
+void smw_comm_free(smw_comm* m);
+int32_t smw_comm_all_gather(smw_comm* m, const void* send_dev, void* recv_dev, size_t n_fr);   /* e.g. the per-column roots of a column-sharded commit */
+/* fri_build_transcript's layer roots (deep_ali/src/fri.rs:231-312) for ONE polynomial of n0 evaluations held as world * n_chunks
+ * equal contiguous slices, n_chunks per rank (chunk c of this rank = f0[first_indices[c], first_indices[c] + n_chunk)).  Every rank
+ * folds, hashes and builds the subtrees of its own slices (DS positions offset by the slice start, merkle/src/lib.rs:168-173), ONE
+ * all-gather carries every layer's cap and the first layer too small to split, every rank finishes the tops.  roots: (L + 1) Fr,
+ * identical on every rank and to smw_fri_build_transcript + smw_fri_roots. */
+int32_t smw_fri_roots_sharded(smw_ctx* ctx, smw_comm* comm_or_null, const void* chunks, size_t n_chunk, int32_t n_chunks, const uint64_t* first_indices,
+                              size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, void* roots_out_host);
+/* Forward NTT (fft/src/lib.rs:6-12 convention) of ONE vector of 2^log_n elements spread CYCLICALLY over the ranks
+ * (in[j] = x[rank + world * j], j < M = 2^log_n / world; device buffers; `in` is overwritten): local NTT, twiddle, ONE all-to-all,
+ * a length-world DFT across the received pieces.  out[k1 * (M / world) + j] = X[M * k1 + rank * (M / world) + j]: `world` contiguous chunks,
+ * the layout smw_fri_roots_sharded takes. */
+int32_t smw_ntt_cyclic_to_chunks(smw_ctx* ctx, smw_comm* comm_or_null, void* in_dev, void* out_dev, int32_t log_n);
+/* smw_mf_commit_phase for a table held as `world` equal contiguous slices (this rank: table[rank * n_local, (rank + 1) * n_local)):
+ * every round commits the local slice up to its cap, ONE all-gather of the caps per round (r_i needs the root of round i,
+ * channel/src/lib.rs:643-646; the root is then on every rank, so r_i needs no broadcast), local fold; once a slice is a single
+ * element the layer is gathered and the remaining rounds run replicated.  Outputs as smw_mf_commit_phase, identical on every rank. */
+int32_t smw_mf_commit_phase_sharded(smw_ctx* ctx, smw_comm* comm_or_null, uint64_t ds_tag, const void* table_slice, size_t n_local, int32_t mem,
+                                    void* roots_out_host, void* r_out_host, void* final_out_host);
+uint64_t smw_ctx_collective_count(const smw_ctx* ctx);   /* NCCL collectives issued through this context */
 
 /* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */
 int32_t smw_index_from_seed(smw_ctx* ctx, const void* seeds_fr, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem);   /* index_from_seed, deep_ali/src/fri.rs:178-183, element-wise */

@@ -36,17 +36,23 @@ def load():
         getattr(L, name)   # AttributeError if the library does not export a declared symbol
     L.smw_last_error.restype = C.c_char_p
     L.smw_ctx_launch_count.restype = u64
+    L.smw_ctx_collective_count.restype = u64
     L.smw_ctx_stream.restype = vp
     for n in ("smw_tree_level_len", "smw_fri_shard_tail_len", "smw_proof_num_indices", "smw_proof_level_siblings", "smw_proof_level_groups"):
         getattr(L, n).restype = sz
     L.smw_fri_layer_tree.restype = vp
-    for n in ("smw_ctx_destroy", "smw_params_free", "smw_tree_free", "smw_transcript_free", "smw_fri_free", "smw_fri_shard_free", "smw_proof_free"):
+    for n in ("smw_ctx_destroy", "smw_params_free", "smw_tree_free", "smw_transcript_free", "smw_fri_free", "smw_fri_shard_free", "smw_proof_free", "smw_comm_free"):
         getattr(L, n).restype = None
     # argument types: every pointer is passed as c_void_p, sizes as size_t, labels/seeds as uint64
     A = {
+        "smw_comm_unique_id": [vp], "smw_comm_init": [vp, vp, i32, i32, vp], "smw_comm_rank": [vp], "smw_comm_world": [vp], "smw_comm_free": [vp],
+        "smw_comm_all_gather": [vp, vp, vp, sz], "smw_ctx_collective_count": [vp],
+        "smw_fri_roots_sharded": [vp, vp, vp, sz, i32, vp, sz, vp, i32, u64, i32, vp],
+        "smw_ntt_cyclic_to_chunks": [vp, vp, vp, vp, i32],
+        "smw_mf_commit_phase_sharded": [vp, vp, u64, vp, sz, i32, vp, vp, vp],
         "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp],
         "smw_last_error": [vp], "smw_ctx_launch_count": [vp], "smw_ctx_stream": [vp],
-        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_fp64_rate": [vp, vp, vp], "smw_diag_perm_fp64_ops": [vp, vp], "smw_diag_f52_dot": [vp, vp, vp, sz, i32, vp, i32], "smw_index_from_seed": [vp, vp, sz, u64, vp, i32], "smw_ali_sample_z_beta": [vp, vp, vp, u64, vp, vp], "smw_scale_powers": [vp, vp, sz, vp, i32], "smw_dft_strided": [vp, vp, i32, sz, sz, i32],
+        "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_fp64_rate": [vp, vp, vp], "smw_diag_pipe_rate": [vp, i32, vp], "smw_diag_perm_fp64_ops": [vp, vp], "smw_diag_f52_dot": [vp, vp, vp, sz, i32, vp, i32], "smw_index_from_seed": [vp, vp, sz, u64, vp, i32], "smw_ali_sample_z_beta": [vp, vp, vp, u64, vp, vp], "smw_scale_powers": [vp, vp, sz, vp, i32], "smw_dft_strided": [vp, vp, i32, sz, sz, i32],
         "smw_fri_build_transcript_from": [vp, vp, sz, vp, i32, u64, u64, i32, vp],
         "smw_fri_shard_build": [vp, vp, sz, sz, sz, vp, i32, u64, i32, vp], "smw_fri_shard_num_local_layers": [vp],
         "smw_fri_shard_cap_info": [vp, i32, vp, vp, vp], "smw_fri_shard_cap": [vp, i32, vp, i32], "smw_fri_shard_tail_len": [vp],

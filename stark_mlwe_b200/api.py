@@ -78,6 +78,9 @@ class Context:
     def stream(self):
         return self.L.smw_ctx_stream(self.h)
 
+    def collective_count(self):
+        return int(self.L.smw_ctx_collective_count(self.h))
+
     KERNEL_CLASSES = ("merkle_level", "pair_leaves", "fri_leaf", "permute", "ntt_pass", "lde_aux", "fold", "misc")
 
     def profile(self, on=True):
@@ -102,6 +105,13 @@ class Context:
         a, b = C.c_double(), C.c_double()
         self.check(self.L.smw_diag_fp64_rate(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def pipe_rate(self, fp64):
+        """live pipe-rate measurement with its own clock record: lanes_per_s = warp_instr_per_clk_per_sm x 32 x n_sm x sm_hz_during"""
+        o = (C.c_double * 5)()
+        self.check(self.L.smw_diag_pipe_rate(self.h, 1 if fp64 else 0, o))
+        return {"pipe": "fp64 DFMA.RZ" if fp64 else "IMAD.WIDE.U32 (32x32+64)", "lanes_per_s": o[0], "warp_instr_per_clk_per_sm": o[1], "sm_hz_during": o[2],
+                "n_sm": int(o[3]), "sm_max_hz": o[4], "check_lanes_per_s": o[1] * 32 * o[3] * o[2]}
 
     def close(self):
         if self.h:
@@ -1031,3 +1041,80 @@ def deep_fri_verify(ctx, params, proof):
         return False
     fin = proof.queries[0].final_pair
     return _verify_layer_opening(ctx, proof.roots[L], [0], {0: (fin[0], fin[1])}, proof.final_proof, sizes[L], 1, L)
+
+
+# ---------------------------------------------------------------------------------------------- multi-GPU data plane
+class Comm:
+    """smw_comm: one rank of an NCCL communicator owned by the library (csrc/comm.cu).  Not in the reference (it has no distributed
+    path).  Bootstrap: `Comm.unique_id()` on rank 0, carried to every rank by the host (see shard.make_comm), `Comm(ctx, id, world, rank)`."""
+
+    def __init__(self, ctx, uid, world, rank):
+        self.ctx = ctx
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(uid))
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_comm_init(ctx.h, buf, int(world), int(rank), C.byref(h)))
+        self.h, self.world, self.rank = h, int(world), int(rank)
+
+    @staticmethod
+    def unique_id():
+        L = _lib.load()
+        buf = (C.c_uint8 * 128)()
+        rc = L.smw_comm_unique_id(buf)
+        if rc:
+            raise SmwError(rc, "ncclGetUniqueId (is libnccl.so.2 loadable?)")
+        return bytes(buf)
+
+    def all_gather(self, send):
+        """send: CUDA tensor (k, 4) int64 -> (world * k, 4) on the device, rank order; on the context's stream"""
+        import torch
+        p, n, mem, _k = _buf(send)
+        assert mem == DEVICE
+        out = torch.empty((self.world * send.shape[0], 4), dtype=send.dtype, device=send.device)
+        self.ctx.check(self.ctx.L.smw_comm_all_gather(self.h, p, C.c_void_p(out.data_ptr()), n))
+        return out
+
+    def close(self):
+        if self.h and self.ctx.h:
+            self.ctx.L.smw_comm_free(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def fri_roots_sharded(ctx, comm, chunks, first_indices, n0, params):
+    """Layer roots of fri_build_transcript (deep_ali/src/fri.rs:231-312) for one polynomial held as world * len(first_indices) equal
+    contiguous slices; chunks: (C, n_chunk, 4) host array or CUDA tensor; comm None = one rank.  One all-gather per proof."""
+    p, n, mem, _k = _buf(chunks)
+    fi = np.ascontiguousarray(first_indices, dtype=np.uint64)
+    nc = int(fi.size)
+    sch = np.ascontiguousarray(params.schedule, dtype=np.uint64)
+    out = _out(len(params.schedule) + 1)
+    ctx.check(ctx.L.smw_fri_roots_sharded(ctx.h, comm.h if comm is not None else None, p, n // nc, nc, C.c_void_p(fi.ctypes.data), int(n0),
+                                          C.c_void_p(sch.ctypes.data) if sch.size else None, len(params.schedule), params.seed_z, mem, C.c_void_p(out.ctypes.data)))
+    return out
+
+
+def ntt_cyclic_to_chunks(ctx, comm, x_local, log_n):
+    """One NTT of 2^log_n elements spread cyclically over the ranks (x_local: CUDA tensor (M, 4), overwritten) -> CUDA tensor
+    (world, M / world, 4): chunk k1 holds X[M k1 + rank M / world ..]; one all-to-all (smw_ntt_cyclic_to_chunks)"""
+    import torch
+    world = comm.world if comm is not None else 1
+    M = x_local.shape[0]
+    out = torch.empty_like(x_local)
+    ctx.check(ctx.L.smw_ntt_cyclic_to_chunks(ctx.h, comm.h if comm is not None else None, C.c_void_p(x_local.data_ptr()), C.c_void_p(out.data_ptr()), int(log_n)))
+    return out.view(world, M // world, 4)
+
+
+def mf_commit_phase_sharded(ctx, comm, table_slice, ds_tag):
+    """smw_mf_commit_phase for a table held as `world` contiguous slices: (roots, r, final), identical on every rank"""
+    p, n, mem, _k = _buf(table_slice)
+    world = comm.world if comm is not None else 1
+    k = (n * world).bit_length() - 1
+    roots, rs, fin = _out(k + 1), _out(max(k, 1)), _out(1)
+    ctx.check(ctx.L.smw_mf_commit_phase_sharded(ctx.h, comm.h if comm is not None else None, int(ds_tag), p, n, mem, C.c_void_p(roots.ctypes.data),
+                                                C.c_void_p(rs.ctypes.data), C.c_void_p(fin.ctypes.data)))
+    return roots, rs[:k], fin[0]

@@ -166,6 +166,21 @@ struct StreamFan {
 };
 constexpr int FAN_STREAMS = 8;
 
+// wpow[i] = w_G^i, i < G = 2^log_g: a vector of ones scaled by the powers of the order-G root (freed by `fr`)
+int make_wpow(smw_ctx* c, int log_g, uint32_t** d_w_out, DevFree& fr) {
+    const size_t G = (size_t)1 << log_g;
+    uint32_t *d_w = nullptr, *d_root = nullptr, *d_one = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_w, G * FR)); fr.v.push_back(d_w);
+    SMW_CUDA(c, cudaMalloc(&d_root, FR)); fr.v.push_back(d_root);
+    SMW_CUDA(c, cudaMalloc(&d_one, FR)); fr.v.push_back(d_one);
+    int rc = launch_root_of_unity(c, log_g, d_root); if (rc) return rc;
+    rc = launch_root_of_unity(c, 0, d_one); if (rc) return rc;
+    for (size_t i = 0; i < G; i++) SMW_CUDA(c, cudaMemcpyAsync(d_w + i * 8, d_one, FR, cudaMemcpyDeviceToDevice, c->stream));
+    rc = launch_scale_powers(c, d_w, G, d_root); if (rc) return rc;
+    *d_w_out = d_w;
+    return SMW_OK;
+}
+
 // ---- forests: the levels of many independent trees hashed round by round, one launch per round and (parameter set, arity)
 // level sizes of a tree over n leaves (level 0 = leaves); whole_only: stop at the last level made of complete sibling groups
 // (the "cap" of a slice of a range-sharded tree: the ragged top belongs to whoever gathers the caps)
@@ -189,6 +204,7 @@ bool has_multi(const smw_ctx* c, const smw_params* p) { return c->use_f52 && p->
 // Hashes levels 1.. of every tree (merkle/src/lib.rs:164-181) on the context's stream.  All levels >= 1 of all trees live in ONE
 // allocation (*arena_out); the segment table goes to `defer` (freed by the caller after the stream has drained).
 int build_forest(smw_ctx* c, std::vector<ForestTree>& trees, uint32_t** arena_out, std::vector<void*>& defer) {
+    Range rg("build_forest");
     *arena_out = nullptr;
     size_t total = 0, max_levels = 0;
     for (auto& t : trees) {
@@ -340,6 +356,11 @@ int32_t smw_diag_fp64_rate(smw_ctx* c, double* dfma_per_s, double* warp_instr_pe
     if (!c) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     return launch_diag_rate(c, 1, dfma_per_s, warp_instr_per_clk_per_sm);
+}
+int32_t smw_diag_pipe_rate(smw_ctx* c, int32_t fp64, double* out5) {      // out: lanes/s, warp-instr/clk/SM, SM Hz during the measurement, SM count, nominal max SM Hz
+    if (!c || !out5) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    return launch_diag_rate_ex(c, fp64 ? 1 : 0, out5, out5 + 1, out5 + 2, out5 + 3, out5 + 4);
 }
 int32_t smw_diag_perm_fp64_ops(const smw_params* p, uint64_t* ops_out) {       // 0 when this parameter set runs on the integer multiplier
     if (!p || !ops_out) return SMW_ERR_INVALID_ARG;
@@ -590,15 +611,8 @@ int32_t smw_dft_strided(smw_ctx* c, void* buf, int32_t log_g, size_t stride, siz
     const size_t G = (size_t)1 << log_g, total = (G - 1) * stride + count;
     int rc = SMW_OK;
     DevFree fr{{}, c->stream};
-    uint32_t *d_w = nullptr, *d_root = nullptr, *d_one = nullptr;
-    SMW_CUDA(c, cudaMalloc(&d_w, G * FR)); fr.v.push_back(d_w);
-    SMW_CUDA(c, cudaMalloc(&d_root, FR)); fr.v.push_back(d_root);
-    SMW_CUDA(c, cudaMalloc(&d_one, FR)); fr.v.push_back(d_one);
-    // wpow[i] = w_G^i, i < G: a vector of ones scaled by the powers of the order-G root
-    rc = launch_root_of_unity(c, log_g, d_root); if (rc) return rc;
-    rc = launch_root_of_unity(c, 0, d_one); if (rc) return rc;
-    for (size_t i = 0; i < G; i++) SMW_CUDA(c, cudaMemcpyAsync(d_w + i * 8, d_one, FR, cudaMemcpyDeviceToDevice, c->stream));
-    rc = launch_scale_powers(c, d_w, G, d_root); if (rc) return rc;
+    uint32_t* d_w = nullptr;
+    rc = make_wpow(c, log_g, &d_w, fr); if (rc) return rc;
     if (mem == SMW_DEVICE) return launch_dft_strided(c, (uint32_t*)buf, log_g, stride, count, d_w);      // DevFree drains the stream before freeing
     In i(c, buf, total, SMW_HOST); if (i.rc) return i.rc;
     rc = launch_dft_strided(c, i.owned, log_g, stride, count, d_w); if (rc) return rc;
@@ -620,6 +634,7 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
                        uint64_t label0, int32_t mem, void* roots_out_host) {
     if (!c || !cols || !roots_out_host || !shift_host || n_cols <= 0 || log_n < 0 || log_blowup < 0 || log_n + log_blowup > 32) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
+    Range rg("lde_commit");
     const size_t n = (size_t)1 << log_n, N = n << log_blowup;
     smw_params* p; int rc = smw_params_commitment_default(c, &p); if (rc) return rc;
     In g(c, shift_host, 1, SMW_HOST); if (g.rc) return g.rc;
@@ -866,6 +881,7 @@ int32_t smw_compute_s_layer(smw_ctx* c, const void* f, size_t n, const void* z_h
 }
 void smw_fri_free(smw_fri* s) {
     if (!s) return;
+    Range rg("fri_free");
     cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
     for (auto* t : s->tree) smw_tree_free(t);
     cudaFree(s->arena_f); cudaFree(s->arena_leaves); cudaFree(s->arena_levels);
@@ -881,25 +897,28 @@ namespace {
 struct FriLayers {
     std::vector<ForestTree> trees; uint32_t* arena_leaves = nullptr; uint32_t* arena_levels = nullptr;
 };
-int fri_commit_layers(smw_ctx* c, int K, int L, const std::vector<size_t>& n_glob, const std::vector<size_t>& n_loc, const std::vector<size_t>& m,
-                      const std::vector<uint64_t>& first, const std::vector<uint32_t*>& f, uint64_t level0, bool whole_only, FriLayers& out, std::vector<void*>& defer) {
-    if (K <= 0) return SMW_OK;
+// one (layer, slice) to commit: n_loc elements of layer `layer` starting at global index `first`; f_next = the matching slice of
+// the next layer (nullptr for the last layer: s = 0)
+struct LayerEntry { int layer; size_t n_glob, n_loc, m; uint64_t first; const uint32_t* f; const uint32_t* f_next; };
+int fri_commit_entries(smw_ctx* c, const std::vector<LayerEntry>& E, uint64_t level0, bool whole_only, FriLayers& out, std::vector<void*>& defer) {
+    if (E.empty()) return SMW_OK;
+    Range rg("fri.leaves+forest");
     smw_params* trp; int rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
-    size_t total = 0; for (int l = 0; l < K; l++) total += n_loc[l];
+    size_t total = 0; for (auto& e : E) total += e.n_loc;
     SMW_CUDA(c, cudaMalloc(&out.arena_leaves, total * FR));
     uint32_t* d_tmpl = nullptr; int lf = 0, ls = 0;
     std::vector<LeafSeg> hashed_segs, pair_segs; uint64_t hashed_total = 0, pair_total = 0; smw_params* pair_p = nullptr; bool pair_uniform = true;
     size_t off = 0;
-    for (int l = 0; l < K; l++) {
-        const int arity = smw_pick_arity_for_layer(n_glob[l], m[l]);               // chosen from the GLOBAL layer size (fri.rs:272)
+    for (auto& e : E) {
+        const int arity = smw_pick_arity_for_layer(e.n_glob, e.m);                 // chosen from the GLOBAL layer size (fri.rs:272)
         const bool hashed = arity >= 8;                                           // fri.rs:275
         smw_params* p; rc = smw_params_for_arity(c, arity, &p); if (rc) return rc;
-        uint32_t* leaves = out.arena_leaves + off * 8; off += n_loc[l];
-        const uint32_t* d_s = (l < L) ? f[l + 1] : nullptr;
-        LeafSeg sg{f[l], d_s, leaves, (uint64_t)n_loc[l], level0 + (uint64_t)l, first[l], (uint64_t)m[l], (uint32_t)arity, 0, 0};
-        if (hashed) { sg.first = hashed_total; hashed_total += n_loc[l]; hashed_segs.push_back(sg); }
-        else { sg.first = pair_total; pair_total += n_loc[l]; pair_segs.push_back(sg); if (pair_p && pair_p != p) pair_uniform = false; pair_p = p; }
-        out.trees.push_back(ForestTree{p, arity, level0 + (uint64_t)l, first[l], 0, whole_only, leaves, n_loc[l], {}, {}});
+        uint32_t* leaves = out.arena_leaves + off * 8; off += e.n_loc;
+        const uint64_t label = level0 + (uint64_t)e.layer;
+        LeafSeg sg{e.f, e.f_next, leaves, (uint64_t)e.n_loc, label, e.first, (uint64_t)e.m, (uint32_t)arity, 0, 0};
+        if (hashed) { sg.first = hashed_total; hashed_total += e.n_loc; hashed_segs.push_back(sg); }
+        else { sg.first = pair_total; pair_total += e.n_loc; pair_segs.push_back(sg); if (pair_p && pair_p != p) pair_uniform = false; pair_p = p; }
+        out.trees.push_back(ForestTree{p, arity, label, e.first, 0, whole_only, leaves, e.n_loc, {}, {}});
     }
     if (!hashed_segs.empty()) {
         rc = upload_leaf_template(c, &d_tmpl, &lf, &ls); if (rc) return rc;
@@ -922,6 +941,12 @@ int fri_commit_layers(smw_ctx* c, int K, int L, const std::vector<size_t>& n_glo
     }
     return build_forest(c, out.trees, &out.arena_levels, defer);
 }
+int fri_commit_layers(smw_ctx* c, int K, int L, const std::vector<size_t>& n_glob, const std::vector<size_t>& n_loc, const std::vector<size_t>& m,
+                      const std::vector<uint64_t>& first, const std::vector<uint32_t*>& f, uint64_t level0, bool whole_only, FriLayers& out, std::vector<void*>& defer) {
+    std::vector<LayerEntry> E;
+    for (int l = 0; l < K; l++) E.push_back(LayerEntry{l, n_glob[l], n_loc[l], m[l], first[l], f[l], l < L ? f[l + 1] : nullptr});
+    return fri_commit_entries(c, E, level0, whole_only, out, defer);
+}
 int fri_layer_sizes(smw_ctx* c, size_t n0, const uint64_t* schedule, int L, std::vector<size_t>& n, std::vector<size_t>& m) {
     n.assign(L + 1, 0); m.assign(L + 1, 1); n[0] = n0;          // fri.rs:145-155 — the reference asserts divisibility level by level
     for (int l = 0; l < L; l++) {
@@ -940,6 +965,7 @@ int32_t smw_fri_build_transcript(smw_ctx* c, const void* f0, size_t n0, const ui
 int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, uint64_t level0, int32_t mem, smw_fri** out) {
     if (!c || !out || !f0 || L < 0 || (L && !schedule) || n0 == 0) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
+    Range rg("fri_build_transcript");
     std::vector<size_t> n, m; int rc = fri_layer_sizes(c, n0, schedule, L, n, m); if (rc) return rc;
     auto s = std::make_unique<smw_fri>(); s->ctx = c; s->L = L; s->n = n; s->m = m;
     s->arity.resize(L + 1); s->hashed.resize(L + 1); s->f.assign(L + 1, nullptr); s->tree.assign(L + 1, nullptr);
@@ -953,13 +979,14 @@ int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, con
     // z_l depends only on public values (fri.rs:250): all levels in one launch, then the folds (fri.rs:254)
     std::vector<uint64_t> levels(L), sizes(L);
     for (int l = 0; l < L; l++) { levels[l] = level0 + (uint64_t)l; sizes[l] = (uint64_t)n[l]; }
-    rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc);
-    for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); }
+    { Range r2("fri.sample_z"); rc = sample_z_device(c, seed_z, levels, sizes, s->d_z); if (rc) return fail(rc); }
+    { Range r2("fri.folds"); for (int l = 0; l < L; l++) { rc = launch_fri_fold(c, s->f[l], n[l], s->d_z + (size_t)l * 8, m[l], s->f[l + 1]); if (rc) return fail(rc); } }
     FriLayers fl; std::vector<uint64_t> first(L + 1, 0);
-    rc = fri_commit_layers(c, L + 1, L, n, n, m, first, s->f, level0, false, fl, defer);
+    { Range r2("fri.commit_layers"); rc = fri_commit_layers(c, L + 1, L, n, n, m, first, s->f, level0, false, fl, defer); }
     s->arena_leaves = fl.arena_leaves; s->arena_levels = fl.arena_levels;
     if (rc) return fail(rc);
     for (int l = 0; l <= L; l++) { s->arity[l] = fl.trees[l].arity; s->hashed[l] = fl.trees[l].arity >= 8; s->tree[l] = tree_handle(c, fl.trees[l], false); }
+    Range r3("fri.drain");
     cudaStreamSynchronize(c->stream);
     for (void* q : defer) cudaFree(q);
     *out = s.release();
@@ -1096,6 +1123,123 @@ int32_t smw_fri_shard_tail(smw_fri_shard* s, void* out, int32_t mem) {
     SMW_CUDA(c, cudaMemcpyAsync(out, s->tail, s->tail_n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
     SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK;
 }
+// ---- the range-sharded commit phase with the exchange inside the library: ONE all-gather per proof -------------------------
+int32_t smw_fri_roots_sharded(smw_ctx* c, smw_comm* m, const void* chunks, size_t n_chunk, int32_t C, const uint64_t* first_indices,
+                              size_t n0, const uint64_t* schedule, int32_t L, uint64_t seed_z, int32_t mem, void* roots_out_host) {
+    if (!c || !chunks || !first_indices || !roots_out_host || C < 1 || L < 0 || (L && !schedule) || n0 == 0 || n_chunk == 0) return SMW_ERR_INVALID_ARG;
+    const int world = m ? m->world : 1;
+    const size_t V = (size_t)world * (size_t)C;                                   // slices in all
+    if (n_chunk * V != n0) return set_err(c, SMW_ERR_INVALID_ARG, "world * n_chunks equal slices must cover n0");
+    for (int q = 0; q < C; q++) if (first_indices[q] % n_chunk || first_indices[q] >= n0) return set_err(c, SMW_ERR_INVALID_ARG, "slice start must be a multiple of the slice length");
+    Range rg("fri_roots_sharded");
+    cudaSetDevice(c->device);
+    std::vector<size_t> n, mm; int rc = fri_layer_sizes(c, n0, schedule, L, n, mm); if (rc) return rc;
+    int K = 0;                                                                    // layers [0, K) are committed from slices (as smw_fri_shard_build)
+    while (K <= L && n[K] % V == 0 && (K == L || (n[K] / V) % mm[K] == 0)) K++;
+    const int n_f = (K <= L) ? K + 1 : K;
+    std::vector<size_t> n_loc(L + 1, 0); for (int l = 0; l <= L; l++) n_loc[l] = n[l] / V;
+    DevFree fr{{}, c->stream};
+    std::vector<void*> defer; struct DeferFree { std::vector<void*>& v; cudaStream_t st; ~DeferFree() { cudaStreamSynchronize(st); for (void* q : v) cudaFree(q); } } dfree{defer, c->stream};
+    // local slices: layer l holds the C slices back to back, so ONE fold launch per layer covers them all (a slice of a local
+    // layer is a whole number of fold blocks)
+    std::vector<uint32_t*> f(L + 2, nullptr);
+    { size_t total = 0; for (int l = 0; l < n_f; l++) total += (size_t)C * n_loc[l];
+      uint32_t* arena; SMW_CUDA(c, cudaMalloc(&arena, total * FR)); fr.v.push_back(arena);
+      size_t off = 0; for (int l = 0; l < n_f; l++) { f[l] = arena + off * 8; off += (size_t)C * n_loc[l]; } }
+    SMW_CUDA(c, cudaMemcpyAsync(f[0], chunks, (size_t)C * n_chunk * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    uint32_t* d_z = nullptr; SMW_CUDA(c, cudaMalloc(&d_z, (size_t)(L + 1) * FR)); fr.v.push_back(d_z);
+    std::vector<uint64_t> levels(L), sizes(L);
+    for (int l = 0; l < L; l++) { levels[l] = (uint64_t)l; sizes[l] = (uint64_t)n[l]; }     // GLOBAL sizes: z_l is the same on every rank
+    rc = sample_z_device(c, seed_z, levels, sizes, d_z); if (rc) return rc;
+    for (int l = 0; l + 1 < n_f; l++) { rc = launch_fri_fold(c, f[l], (size_t)C * n_loc[l], d_z + (size_t)l * 8, mm[l], f[l + 1]); if (rc) return rc; }
+    std::vector<LayerEntry> E;
+    for (int l = 0; l < K; l++) for (int q = 0; q < C; q++)
+        E.push_back(LayerEntry{l, n[l], n_loc[l], mm[l], first_indices[q] / (uint64_t)(n0 / n[l]), f[l] + (size_t)q * n_loc[l] * 8,
+                               l < L ? f[l + 1] + (size_t)q * n_loc[l + 1] * 8 : nullptr});
+    FriLayers fl;
+    rc = fri_commit_entries(c, E, 0, true, fl, defer);
+    fr.v.push_back(fl.arena_leaves); fr.v.push_back(fl.arena_levels);
+    if (rc) return rc;
+    // ---- one exchange: [slice starts | caps of every local layer | slices of f_K]
+    std::vector<size_t> cap_n(K), off_l(K); std::vector<int> cap_level(K), arity(K);
+    size_t send_n = (size_t)C;
+    for (int l = 0; l < K; l++) { const ForestTree& t = fl.trees[(size_t)l * C]; cap_n[l] = t.len.back(); cap_level[l] = (int)t.len.size() - 1; arity[l] = t.arity; off_l[l] = send_n; send_n += (size_t)C * cap_n[l]; }
+    const size_t off_tail = send_n, tail_n = (K <= L) ? n_loc[K] : 0;
+    send_n += (size_t)C * tail_n;
+    uint32_t *d_send, *d_recv;
+    SMW_CUDA(c, cudaMalloc(&d_send, send_n * FR)); fr.v.push_back(d_send);
+    SMW_CUDA(c, cudaMalloc(&d_recv, send_n * (size_t)world * FR)); fr.v.push_back(d_recv);
+    { std::vector<uint64_t> hdr((size_t)C * 4, 0); for (int q = 0; q < C; q++) hdr[(size_t)q * 4] = first_indices[q];
+      SMW_CUDA(c, cudaMemcpyAsync(d_send, hdr.data(), (size_t)C * FR, cudaMemcpyHostToDevice, c->stream)); }
+    for (int l = 0; l < K; l++) for (int q = 0; q < C; q++)
+        SMW_CUDA(c, cudaMemcpyAsync(d_send + (off_l[l] + (size_t)q * cap_n[l]) * 8, fl.trees[(size_t)l * C + q].lv.back(), cap_n[l] * FR, cudaMemcpyDeviceToDevice, c->stream));
+    if (tail_n) SMW_CUDA(c, cudaMemcpyAsync(d_send + off_tail * 8, f[K], (size_t)C * tail_n * FR, cudaMemcpyDeviceToDevice, c->stream));
+    rc = comm_all_gather_bytes(c, m, d_send, d_recv, send_n * FR); if (rc) return rc;
+    // ---- global slice order from the gathered starts
+    std::vector<uint64_t> hdr((size_t)world * C * 4);
+    SMW_CUDA(c, cudaMemcpy2DAsync(hdr.data(), (size_t)C * FR, d_recv, send_n * FR, (size_t)C * FR, (size_t)world, cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    std::vector<std::pair<uint64_t, size_t>> order(V);                            // (start, rank * C + chunk)
+    for (size_t v = 0; v < V; v++) order[v] = {hdr[v * 4], v};
+    std::sort(order.begin(), order.end());
+    for (size_t v = 0; v < V; v++) if (order[v].first != (uint64_t)v * n_chunk) return set_err(c, SMW_ERR_INVALID_ARG, "the slices of all ranks do not tile [0, n0)");
+    size_t tops_n = 0; std::vector<size_t> top_off(K);
+    for (int l = 0; l < K; l++) { top_off[l] = tops_n; tops_n += V * cap_n[l]; }
+    const size_t tail_off = tops_n; tops_n += V * tail_n;
+    std::vector<uint64_t> idx(tops_n);
+    for (int l = 0; l < K; l++) for (size_t v = 0; v < V; v++) {
+        const size_t r = order[v].second / C, q = order[v].second % C;
+        for (size_t e = 0; e < cap_n[l]; e++) idx[top_off[l] + v * cap_n[l] + e] = r * send_n + off_l[l] + q * cap_n[l] + e;
+    }
+    for (size_t v = 0; v < V; v++) { const size_t r = order[v].second / C, q = order[v].second % C; for (size_t e = 0; e < tail_n; e++) idx[tail_off + v * tail_n + e] = r * send_n + off_tail + q * tail_n + e; }
+    uint64_t* d_idx = nullptr; uint32_t* d_tops = nullptr;
+    if (tops_n) {
+        SMW_CUDA(c, cudaMalloc(&d_idx, tops_n * 8)); fr.v.push_back(d_idx);
+        SMW_CUDA(c, cudaMalloc(&d_tops, tops_n * FR)); fr.v.push_back(d_tops);
+        SMW_CUDA(c, cudaMemcpyAsync(d_idx, idx.data(), tops_n * 8, cudaMemcpyHostToDevice, c->stream));
+        rc = launch_gather(c, d_recv, d_idx, tops_n, d_tops); if (rc) return rc;
+    }
+    // ---- every rank finishes the tops of the local layers (a small forest) ...
+    std::vector<ForestTree> tops;
+    for (int l = 0; l < K; l++) {
+        smw_params* p; rc = smw_params_for_arity(c, arity[l], &p); if (rc) return rc;
+        tops.push_back(ForestTree{p, arity[l], (uint64_t)l, 0, (uint32_t)cap_level[l], false, d_tops + top_off[l] * 8, V * cap_n[l], {}, {}});
+    }
+    uint32_t* top_arena = nullptr;
+    rc = build_forest(c, tops, &top_arena, defer); fr.v.push_back(top_arena); if (rc) return rc;
+    uint32_t* d_roots; SMW_CUDA(c, cudaMalloc(&d_roots, (size_t)(L + 1) * FR)); fr.v.push_back(d_roots);
+    for (int l = 0; l < K; l++) SMW_CUDA(c, cudaMemcpyAsync(d_roots + (size_t)l * 8, tops[l].lv.back(), FR, cudaMemcpyDeviceToDevice, c->stream));
+    if (K) { rc = d2h(c, roots_out_host, d_roots, (size_t)K * FR); if (rc) return rc; }
+    // ---- ... and rebuilds the layers too small to split from the gathered f_K
+    if (K <= L) {
+        smw_fri* sub = nullptr;
+        rc = smw_fri_build_transcript_from(c, d_tops + tail_off * 8, n[K], schedule + K, L - K, seed_z, (uint64_t)K, SMW_DEVICE, &sub); if (rc) return rc;
+        rc = smw_fri_roots(sub, (uint8_t*)roots_out_host + (size_t)K * FR);
+        smw_fri_free(sub);
+    }
+    return rc;
+}
+int32_t smw_ntt_cyclic_to_chunks(smw_ctx* c, smw_comm* m, void* in_dev, void* out_dev, int32_t log_n) {
+    if (!c || !in_dev || !out_dev || log_n < 0 || log_n > 32) return SMW_ERR_INVALID_ARG;
+    const int G = m ? m->world : 1, rank = m ? m->rank : 0;
+    int log_g = 0; while ((1 << log_g) < G) log_g++;
+    if ((1 << log_g) != G || log_g > 4 || log_n < 2 * log_g) return set_err(c, SMW_ERR_INVALID_ARG, "ranks must be a power of two <= 16 and divide the local length");
+    Range rg("ntt_cyclic_to_chunks");
+    cudaSetDevice(c->device);
+    const size_t M = ((size_t)1 << log_n) >> log_g;
+    int rc = launch_ntt(c, (uint32_t*)in_dev, log_n - log_g, 0, 1, M); if (rc) return rc;       // NTT_M of the cyclic slice
+    if (G == 1) { SMW_CUDA(c, cudaMemcpyAsync(out_dev, in_dev, M * FR, cudaMemcpyDeviceToDevice, c->stream)); return SMW_OK; }
+    DevFree fr{{}, c->stream};
+    uint32_t *d_w, *d_wr; SMW_CUDA(c, cudaMalloc(&d_w, FR)); fr.v.push_back(d_w); SMW_CUDA(c, cudaMalloc(&d_wr, FR)); fr.v.push_back(d_wr);
+    rc = launch_root_of_unity(c, log_n, d_w); if (rc) return rc;
+    rc = launch_fr_pow(c, d_w, (uint64_t)rank, d_wr); if (rc) return rc;                       // w_N^rank
+    rc = launch_scale_powers(c, (uint32_t*)in_dev, M, d_wr); if (rc) return rc;                // twiddle: y[k2] *= w_N^(rank k2)
+    rc = comm_all_to_all_bytes(c, m, in_dev, out_dev, (M / G) * FR); if (rc) return rc;        // rank r receives the k2-range [r M / G, (r + 1) M / G) of every rank
+    uint32_t* d_wpow = nullptr; rc = make_wpow(c, log_g, &d_wpow, fr); if (rc) return rc;
+    return launch_dft_strided(c, (uint32_t*)out_dev, log_g, M / G, M / G, d_wpow);             // length-G DFT across the received pieces
+}
+uint64_t smw_ctx_collective_count(const smw_ctx* c) { return c ? c->collectives : 0; }
+
 // root of the tree whose DS-level-`level` children are `nodes` (level 0: the leaves / leaf digests themselves)
 int32_t smw_merkle_root_from_level(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, int32_t level, const void* nodes, size_t n, int32_t mem, void* root_out_host) {
     if (!root_out_host || level < 0) return SMW_ERR_INVALID_ARG;
@@ -1159,46 +1303,125 @@ int32_t smw_mf_fold(smw_ctx* c, const void* cur, size_t n, const void* r_host, v
     int rc = launch_mf_fold(c, a.d, n, r.d, o.d); if (rc) return rc;
     return o.finish();
 }
+} // extern "C"
+namespace {
+// Device-resident pieces of the Merkle-folded sum-check commit loop (channel/src/lib.rs:600-657): roots, challenges, ping-pong
+// layer and level buffers, the challenge pre-images of every round.  Nothing is allocated inside the loop.
+struct MfBufs {
+    uint32_t *d_roots = nullptr, *d_r = nullptr, *bufA = nullptr, *bufB = nullptr, *lvA = nullptr, *lvB = nullptr, *dA = nullptr, *dC = nullptr;
+    int nA = 0, nC = 0;
+};
+int mf_alloc(smw_ctx* c, int k, size_t n_layer0, MfBufs& B, DevFree& fr) {
+    SMW_CUDA(c, cudaMalloc(&B.d_roots, (size_t)(k + 1) * FR)); fr.v.push_back(B.d_roots);
+    SMW_CUDA(c, cudaMalloc(&B.d_r, (size_t)(k + 1) * FR)); fr.v.push_back(B.d_r);
+    SMW_CUDA(c, cudaMalloc(&B.bufA, (n_layer0 / 2 + 1) * FR)); fr.v.push_back(B.bufA);
+    SMW_CUDA(c, cudaMalloc(&B.bufB, (n_layer0 / 4 + 1) * FR)); fr.v.push_back(B.bufB);
+    SMW_CUDA(c, cudaMalloc(&B.lvA, ((n_layer0 + 15) / 16 + 1) * FR)); fr.v.push_back(B.lvA);
+    SMW_CUDA(c, cudaMalloc(&B.lvB, ((n_layer0 + 255) / 256 + 1) * FR)); fr.v.push_back(B.lvB);
+    std::vector<Word> allA, A, C;
+    for (int i = 0; i < k; i++) { mf_challenge_words((uint64_t)i, A, C); B.nA = (int)A.size(); B.nC = (int)C.size(); allA.insert(allA.end(), A.begin(), A.end()); }
+    if (k > 0) { int rc = upload_words(c, allA, &B.dA); fr.v.push_back(B.dA); if (rc) return rc; rc = upload_words(c, C, &B.dC); fr.v.push_back(B.dC); if (rc) return rc; }
+    return SMW_OK;
+}
+// root of the arity-16 tree (tree_label = ds_tag) whose DS-level-`level` children are `nodes` -> d_root; uses the two level buffers
+int mf_tree_top(smw_ctx* c, smw_params* cp, uint64_t ds_tag, const uint32_t* nodes, size_t cn, uint32_t level, uint64_t first, uint32_t* lvA, uint32_t* lvB, uint32_t* d_root) {
+    if (cn == 1) { SMW_CUDA(c, cudaMemcpyAsync(d_root, nodes, FR, cudaMemcpyDeviceToDevice, c->stream)); return SMW_OK; }      // a one-leaf tree's root is the leaf
+    const uint32_t* lv = nodes; uint32_t* dst = (nodes == lvA) ? lvB : lvA;
+    while (cn > 1) {
+        const size_t nn = (cn + 15) / 16; first /= 16;
+        uint32_t* o = (nn == 1) ? d_root : dst;
+        int rc = launch_merkle_level(c, cp, lv, cn, o, nn, 16, level, ds_tag, 0, first, 1, 0, 0); if (rc) return rc;
+        lv = o; cn = nn; level++; dst = (dst == lvA) ? lvB : lvA;
+    }
+    return SMW_OK;
+}
+// rounds i0 .. k on one rank holding the whole layer `cur` (len elements); returns the final layer pointer (one element)
+int mf_rounds(smw_ctx* c, smw_params* cp, smw_params* trp, uint64_t ds_tag, const uint32_t* cur, size_t len, int i0, int k, MfBufs& B, const uint32_t** final_out) {
+    int rc = SMW_OK;
+    for (int i = i0; i <= k && !rc; i++) {
+        uint32_t* d_root = B.d_roots + (size_t)i * 8;
+        rc = mf_tree_top(c, cp, ds_tag, cur, len, 0, 0, B.lvA, B.lvB, d_root);
+        if (rc || i == k) break;
+        // r_i from (i, root_i) stays on the device and feeds the fold directly: no host round trip per round
+        rc = launch_transcript_run(c, trp, nullptr, 1, 0, B.dA + (size_t)i * B.nA * 8, B.nA, d_root, 1, B.dC, B.nC, 1, B.d_r + (size_t)i * 8); if (rc) break;
+        uint32_t* nxt = (cur == B.bufA) ? B.bufB : B.bufA;
+        rc = launch_mf_fold(c, cur, len, B.d_r + (size_t)i * 8, nxt); if (rc) break;
+        cur = nxt; len /= 2;
+    }
+    *final_out = cur;
+    return rc;
+}
+int mf_outputs(smw_ctx* c, int k, const MfBufs& B, const uint32_t* fin, void* roots_out_host, void* r_out_host, void* final_out_host) {
+    int rc = d2h(c, roots_out_host, B.d_roots, (size_t)(k + 1) * FR);
+    if (!rc && r_out_host && k > 0) rc = d2h(c, r_out_host, B.d_r, (size_t)k * FR);
+    if (!rc && final_out_host) rc = d2h(c, final_out_host, fin, FR);
+    return rc;
+}
+} // namespace
+extern "C" {
 // The whole commit loop of SumCheckMFProver (channel/src/lib.rs:600-657) as ONE chain of launches with no host round trip and
-// no allocation inside: commit layer i (arity 16, tree_label = ds_tag; only the root is kept, two ping-pong level buffers),
-// r_i from (i, root_i) on the device, fold, repeat.  The rounds are strictly sequential (r_i needs root_i).
+// no allocation inside: commit layer i (arity 16, tree_label = ds_tag; only the root is kept), r_i from (i, root_i) on the
+// device, fold, repeat.  The rounds are strictly sequential (r_i needs root_i).
 int32_t smw_mf_commit_phase(smw_ctx* c, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host, void* r_out_host, void* final_out_host) {
     if (!c || !table || !roots_out_host || n == 0 || (n & (n - 1))) return SMW_ERR_INVALID_ARG;
+    Range rg("mf_commit_phase");
     cudaSetDevice(c->device);
     int k = 0; while (((size_t)1 << k) < n) k++;
     smw_params *cp, *trp; int rc = smw_params_commitment_default(c, &cp); if (rc) return rc; rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
     In t0(c, table, n, mem); if (t0.rc) return t0.rc;
-    DevFree fr{{}, c->stream};
-    uint32_t *d_roots = nullptr, *d_r = nullptr, *bufA = nullptr, *bufB = nullptr, *lvA = nullptr, *lvB = nullptr, *dA = nullptr, *dC = nullptr;
-    SMW_CUDA(c, cudaMalloc(&d_roots, (size_t)(k + 1) * FR)); fr.v.push_back(d_roots);
-    SMW_CUDA(c, cudaMalloc(&d_r, (size_t)(k + 1) * FR)); fr.v.push_back(d_r);
-    if (k > 0) { SMW_CUDA(c, cudaMalloc(&bufA, (n / 2) * FR)); fr.v.push_back(bufA); SMW_CUDA(c, cudaMalloc(&bufB, (n / 4 + 1) * FR)); fr.v.push_back(bufB); }
-    SMW_CUDA(c, cudaMalloc(&lvA, ((n + 15) / 16 + 1) * FR)); fr.v.push_back(lvA);
-    SMW_CUDA(c, cudaMalloc(&lvB, ((n + 255) / 256 + 1) * FR)); fr.v.push_back(lvB);
-    std::vector<Word> allA, A, C; int nA = 0;
-    for (int i = 0; i < k; i++) { mf_challenge_words((uint64_t)i, A, C); nA = (int)A.size(); allA.insert(allA.end(), A.begin(), A.end()); }
-    if (k > 0) { rc = upload_words(c, allA, &dA); fr.v.push_back(dA); if (rc) return rc; rc = upload_words(c, C, &dC); fr.v.push_back(dC); if (rc) return rc; }
-    const uint32_t* cur = t0.d; size_t len = n;
-    for (int i = 0; i <= k && !rc; i++) {
-        uint32_t* d_root = d_roots + (size_t)i * 8;
-        if (len == 1) SMW_CUDA(c, cudaMemcpyAsync(d_root, cur, FR, cudaMemcpyDeviceToDevice, c->stream));      // a one-leaf tree's root is the leaf
-        const uint32_t* lv = cur; size_t cn = len; uint32_t level = 0; uint32_t* dst = lvA;
-        while (cn > 1 && !rc) {
-            const size_t nn = (cn + 15) / 16;
-            uint32_t* o = (nn == 1) ? d_root : dst;
-            rc = launch_merkle_level(c, cp, lv, cn, o, nn, 16, level, ds_tag, 0, 0, 1, 0, 0);
-            lv = o; cn = nn; level++; dst = (dst == lvA) ? lvB : lvA;
+    DevFree fr{{}, c->stream}; MfBufs B;
+    rc = mf_alloc(c, k, n, B, fr); if (rc) return rc;
+    const uint32_t* fin = nullptr;
+    rc = mf_rounds(c, cp, trp, ds_tag, t0.d, n, 0, k, B, &fin); if (rc) return rc;
+    return mf_outputs(c, k, B, fin, roots_out_host, r_out_host, final_out_host);
+}
+// The same loop for a table split into `world` contiguous slices: while a slice holds at least one fold pair, the
+// rank commits its slice up to the cap (whole sibling groups, DS positions offset by the slice start), ONE all-gather carries
+// the caps, every rank finishes the top (so the root, and r_i, exist on every rank without a broadcast) and folds its own slice.
+int32_t smw_mf_commit_phase_sharded(smw_ctx* c, smw_comm* m, uint64_t ds_tag, const void* table_slice, size_t n_local, int32_t mem,
+                                    void* roots_out_host, void* r_out_host, void* final_out_host) {
+    if (!c || !table_slice || !roots_out_host || n_local == 0 || (n_local & (n_local - 1))) return SMW_ERR_INVALID_ARG;
+    const int world = m ? m->world : 1, rank = m ? m->rank : 0;
+    if (world & (world - 1)) return set_err(c, SMW_ERR_INVALID_ARG, "the number of ranks must be a power of two");
+    Range rg("mf_commit_phase_sharded");
+    cudaSetDevice(c->device);
+    const size_t n = n_local * (size_t)world;
+    int k = 0; while (((size_t)1 << k) < n) k++;
+    smw_params *cp, *trp; int rc = smw_params_commitment_default(c, &cp); if (rc) return rc; rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
+    In t0(c, table_slice, n_local, mem); if (t0.rc) return t0.rc;
+    DevFree fr{{}, c->stream}; MfBufs B;
+    rc = mf_alloc(c, k, std::max<size_t>(n_local, (size_t)world * 16), B, fr); if (rc) return rc;
+    uint32_t *d_send = nullptr, *d_recv = nullptr;
+    SMW_CUDA(c, cudaMalloc(&d_send, 16 * FR)); fr.v.push_back(d_send);
+    SMW_CUDA(c, cudaMalloc(&d_recv, (size_t)world * 16 * FR)); fr.v.push_back(d_recv);
+    const uint32_t* cur = t0.d; size_t len_loc = n_local; int i = 0;
+    while (world > 1 && len_loc >= 2) {
+        // local subtree: whole sibling groups only
+        const uint32_t* lv = cur; size_t cn = len_loc; uint32_t level = 0; uint64_t first = (uint64_t)rank * len_loc; uint32_t* dst = B.lvA;
+        while (cn >= 16 && cn % 16 == 0) {
+            const size_t nn = cn / 16; first /= 16;
+            rc = launch_merkle_level(c, cp, lv, cn, dst, nn, 16, level, ds_tag, 0, first, 1, 0, 0); if (rc) return rc;
+            lv = dst; cn = nn; level++; dst = (dst == B.lvA) ? B.lvB : B.lvA;
         }
-        if (rc || i == k) break;
-        rc = launch_transcript_run(c, trp, nullptr, 1, 0, dA + (size_t)i * nA * 8, nA, d_root, 1, dC, (int)C.size(), 1, d_r + (size_t)i * 8); if (rc) break;
-        uint32_t* nxt = (i % 2 == 0) ? bufA : bufB;
-        rc = launch_mf_fold(c, cur, len, d_r + (size_t)i * 8, nxt); if (rc) break;
-        cur = nxt; len /= 2;
+        // cap: cn <= 15 nodes (or the < 16 leaves themselves) per rank, in rank order = global order
+        rc = comm_all_gather_bytes(c, m, lv, d_recv, cn * FR); if (rc) return rc;
+        uint32_t* d_root = B.d_roots + (size_t)i * 8;
+        rc = mf_tree_top(c, cp, ds_tag, d_recv, cn * (size_t)world, level, 0, B.lvA, B.lvB, d_root); if (rc) return rc;
+        rc = launch_transcript_run(c, trp, nullptr, 1, 0, B.dA + (size_t)i * B.nA * 8, B.nA, d_root, 1, B.dC, B.nC, 1, B.d_r + (size_t)i * 8); if (rc) return rc;
+        uint32_t* nxt = (cur == B.bufA) ? B.bufB : B.bufA;
+        rc = launch_mf_fold(c, cur, len_loc, B.d_r + (size_t)i * 8, nxt); if (rc) return rc;
+        cur = nxt; len_loc /= 2; i++;
     }
-    if (!rc) rc = d2h(c, roots_out_host, d_roots, (size_t)(k + 1) * FR);
-    if (!rc && r_out_host && k > 0) rc = d2h(c, r_out_host, d_r, (size_t)k * FR);
-    if (!rc && final_out_host) rc = d2h(c, final_out_host, cur, FR);
-    return rc;
+    size_t len = len_loc;
+    if (world > 1) {        // one element per rank left: gather the layer, the remaining rounds run replicated
+        SMW_CUDA(c, cudaMemcpyAsync(d_send, cur, FR, cudaMemcpyDeviceToDevice, c->stream));
+        uint32_t* full = (cur == B.bufA) ? B.bufB : B.bufA;
+        rc = comm_all_gather_bytes(c, m, d_send, full, FR); if (rc) return rc;
+        cur = full; len = (size_t)world;
+    }
+    const uint32_t* fin = nullptr;
+    rc = mf_rounds(c, cp, trp, ds_tag, cur, len, i, k, B, &fin); if (rc) return rc;
+    return mf_outputs(c, k, B, fin, roots_out_host, r_out_host, final_out_host);
 }
 
 // ---------------------------------------------------------------------------------------- openings (merkle/src/lib.rs:246-315)

@@ -138,6 +138,15 @@ int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* 
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
+__global__ void k_fr_pow(const uint32_t* base, unsigned long long e, uint32_t* out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    fr_store(out, fr_pow_u64(fr_ldg(base), e));
+}
+int launch_fr_pow(smw_ctx* c, const uint32_t* d_base, uint64_t e, uint32_t* d_out) {
+    k_fr_pow<<<1, 32, 0, c->stream>>>(d_base, (unsigned long long)e, d_out); c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
 int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow) {
     if (count == 0 || log_g == 0) return SMW_OK;
     unsigned grid = (unsigned)((count + 127) / 128);
@@ -320,7 +329,10 @@ __global__ void __launch_bounds__(256) k_diag_dfma(uint32_t* out, const uint32_t
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* winstr) { return launch_diag_rate(c, 0, mac_per_s, winstr); }
-int launch_diag_rate(smw_ctx* c, int fp64, double* mac_per_s, double* winstr) {
+int launch_diag_rate(smw_ctx* c, int fp64, double* mac_per_s, double* winstr) { return launch_diag_rate_ex(c, fp64, mac_per_s, winstr, nullptr, nullptr, nullptr); }
+// also reports the SM clock the GPU held DURING the measurement (in-kernel clock64 ticks / event time), the SM count and the
+// nominal maximum clock, so that lanes_per_s = warp_instr_per_clk_per_sm x 32 x n_sm x sm_hz_during can be re-derived by the reader
+int launch_diag_rate_ex(smw_ctx* c, int fp64, double* mac_per_s, double* winstr, double* sm_hz_during, double* n_sm_out, double* sm_max_hz) {
     cudaDeviceProp prop; SMW_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
     // 2 CTAs x 256 threads per SM (all resident, so the in-kernel clock and the event clock agree); ~40 ms per repetition
     // so that the clocks settle under this load
@@ -330,7 +342,7 @@ int launch_diag_rate(smw_ctx* c, int fp64, double* mac_per_s, double* winstr) {
     std::vector<uint32_t> hin(4096); for (int i = 0; i < 4096; i++) hin[i] = 0x9E3779B9u * (uint32_t)(i + 1) ^ ((uint32_t)i << 7);
     SMW_CUDA(c, cudaMemcpyAsync(in, hin.data(), 4096 * 4, cudaMemcpyHostToDevice, c->stream));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
-    double best = 0, best_w = 0;
+    double best = 0, best_w = 0, best_hz = 0;
     std::vector<long long> h(grid);
     for (int rep = 0; rep < 4; rep++) {
         cudaEventRecord(e0, c->stream);
@@ -342,11 +354,14 @@ int launch_diag_rate(smw_ctx* c, int fp64, double* mac_per_s, double* winstr) {
         cudaMemcpy(h.data(), cyc, (size_t)grid * 8, cudaMemcpyDeviceToHost);
         double avg = 0; for (int i = 0; i < grid; i++) avg += (double)h[i]; avg /= grid;
         double rate = (double)grid * block * (double)iters * 16 / (ms * 1e-3);
-        if (rep > 0 && rate > best) { best = rate; best_w = per_sm * (block / 32.0) * (double)iters * 16 / avg; }
+        if (rep > 0 && rate > best) { best = rate; best_w = per_sm * (block / 32.0) * (double)iters * 16 / avg; best_hz = avg / (ms * 1e-3); }
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out); cudaFree(cyc); cudaFree(in);
     if (mac_per_s) *mac_per_s = best;
     if (winstr) *winstr = best_w;
+    if (sm_hz_during) *sm_hz_during = best_hz;
+    if (n_sm_out) *n_sm_out = (double)nsm;
+    if (sm_max_hz) *sm_max_hz = (double)prop.clockRate * 1e3;
     return SMW_OK;
 }
 

@@ -8,6 +8,11 @@
 #include <vector>
 #include <map>
 #include <mutex>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <nvtx3/nvToolsExt.h>
+#include <nccl.h>                   // types and prototypes only: the functions are bound at run time (comm.cu)
 #include "../../include/smw.h"
 
 namespace smw {
@@ -60,6 +65,7 @@ struct smw_ctx {
     std::vector<cudaStream_t> side; std::vector<cudaEvent_t> side_ev; cudaEvent_t fan_ev = nullptr;
     bool use_f52 = true;                         // widths 9/17 batch kernels on the FP64-pipe multiplier (SMW_REP=29 in the environment selects the integer one)
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
+    uint64_t collectives = 0;                    // NCCL collectives / grouped exchanges issued through this context
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
     bool prof_on = false;
     struct ProfRec { int cls; cudaEvent_t a, b; };
@@ -76,6 +82,12 @@ struct smw_tree {
     std::vector<uint32_t*> lv;        // device pointers, external form
     std::vector<bool> owned;
     uint32_t* arena = nullptr;        // the levels above level 0, when they share one allocation
+};
+
+struct smw_comm {
+    smw_ctx* ctx = nullptr;
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
 };
 
 struct smw_transcript {
@@ -98,6 +110,19 @@ struct smw_fri {
 
 namespace smw {
 
+// A named host-side range: an NVTX range (visible in nsys / ncu --nvtx; a no-op without a tool attached) and, with SMW_TRACE=1 in
+// the environment, a line on stderr with the host time spent inside — what located the per-call overheads of the small builds.
+inline bool trace_on() { static int v = -1; if (v < 0) { const char* e = getenv("SMW_TRACE"); v = (e && *e && *e != '0') ? 1 : 0; } return v == 1; }
+struct Range {
+    const char* name; std::chrono::steady_clock::time_point t0;
+    explicit Range(const char* n) : name(n) { nvtxRangePushA(n); if (trace_on()) t0 = std::chrono::steady_clock::now(); }
+    ~Range() {
+        nvtxRangePop();
+        if (trace_on()) fprintf(stderr, "[smw] %-28s %9.3f ms (host)\n", name, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
+};
+static const char* const KC_NAMES[] = {"merkle_level", "pair_leaves", "fri_leaf", "permute", "ntt_pass", "lde_aux", "fold", "misc"};
+
 // kernel classes for the optional device-side timing (smw_ctx_profile_*)
 enum { KC_MERKLE_LEVEL = 0, KC_PAIR_LEAVES, KC_FRI_LEAF, KC_PERMUTE, KC_NTT_PASS, KC_LDE_AUX, KC_FOLD, KC_MISC, KC_COUNT };
 // counts one launch; when profiling is on, brackets it with two events on the context's stream
@@ -105,6 +130,7 @@ struct LaunchScope {
     smw_ctx* c; cudaEvent_t b = nullptr;
     LaunchScope(smw_ctx* ctx, int cls) : c(ctx) {
         c->launches++;
+        nvtxRangePushA(KC_NAMES[cls < 8 ? cls : 7]);
         if (!c->prof_on) return;
         cudaEvent_t a;
         if (c->prof_pool.size() >= 2) { a = c->prof_pool.back(); c->prof_pool.pop_back(); b = c->prof_pool.back(); c->prof_pool.pop_back(); }
@@ -112,11 +138,21 @@ struct LaunchScope {
         cudaEventRecord(a, c->stream);
         c->prof.push_back({cls, a, b});
     }
-    ~LaunchScope() { if (b) cudaEventRecord(b, c->stream); }
+    ~LaunchScope() { if (b) cudaEventRecord(b, c->stream); nvtxRangePop(); }
 };
 
 // returns a device buffer of at least `bytes` for `slot` (valid until the next request for the same slot on this context)
 int ctx_scratch(smw_ctx* c, int slot, size_t bytes, void** out);
+
+// NCCL entry points, bound by dlopen (comm.cu)
+struct NcclApi {
+    decltype(&ncclGetUniqueId) GetUniqueId; decltype(&ncclCommInitRank) CommInitRank; decltype(&ncclCommDestroy) CommDestroy;
+    decltype(&ncclAllGather) AllGather; decltype(&ncclSend) Send; decltype(&ncclRecv) Recv;
+    decltype(&ncclGroupStart) GroupStart; decltype(&ncclGroupEnd) GroupEnd; decltype(&ncclGetErrorString) GetErrorString;
+};
+const NcclApi* nccl_api(std::string* err);
+int comm_all_gather_bytes(smw_ctx* c, smw_comm* m, const void* send, void* recv, size_t bytes);        // m == nullptr or world 1: a device copy
+int comm_all_to_all_bytes(smw_ctx* c, smw_comm* m, const void* send, void* recv, size_t piece_bytes);  // grouped ncclSend / ncclRecv
 
 // status helpers
 int set_err(smw_ctx* c, int code, const char* what);
@@ -185,11 +221,13 @@ int launch_deep_ali_merge(smw_ctx* c, const uint32_t* a, const uint32_t* s, cons
 
 int launch_scale_powers(smw_ctx* c, uint32_t* d_data, size_t n, const uint32_t* d_g);                     // data[i] *= g^i
 int launch_dft_strided(smw_ctx* c, uint32_t* d_data, int log_g, size_t stride, size_t count, const uint32_t* d_wpow);
+int launch_fr_pow(smw_ctx* c, const uint32_t* d_base, uint64_t e, uint32_t* d_out);                       // out = base^e (one thread)
 int launch_index_from_seed(smw_ctx* c, const uint32_t* d_seeds, size_t n, uint64_t n_pow2, uint64_t* d_out);
 int launch_ali_sample(smw_ctx* c, const uint32_t* d_fused, const uint32_t* d_roots_seed, uint64_t n0, uint32_t* d_z, uint32_t* d_beta);
 int launch_f52_dot(smw_ctx* c, const uint32_t* d_a, const uint32_t* d_b, size_t n_out, int k, uint32_t* d_out);
 int launch_diag_mac_rate(smw_ctx* c, double* mac_per_s, double* warp_instr_per_clk_per_sm);
 int launch_diag_rate(smw_ctx* c, int fp64, double* per_s, double* warp_instr_per_clk_per_sm);       // fp64 = 1: DFMA.RZ issue rate
+int launch_diag_rate_ex(smw_ctx* c, int fp64, double* per_s, double* warp_instr_per_clk_per_sm, double* sm_hz_during, double* n_sm, double* sm_max_hz);
 uint64_t count_fp64_ops(const std::vector<uint4>& ops, int first, int count);                          // FP64-pipe instructions of the fr52 path
 
 // ntt_kernels.cu

@@ -51,6 +51,20 @@ def gather_roots(local_roots, n_cols, device=None):
     return np.concatenate(parts, axis=0)
 
 
+def make_comm(ctx):
+    """The library's own NCCL communicator for this rank (api.Comm): rank 0 makes the unique id, torch.distributed (already
+    initialised by the launcher, any backend) only carries its 128 bytes; every exchange afterwards happens inside libsmw.so on
+    device buffers.  Returns None when there is one rank."""
+    import torch.distributed as dist
+    from . import api
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return None
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [api.Comm.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return api.Comm(ctx, box[0], world, rank)
+
+
 # ----------------------------------------------------------------------------- one large polynomial, sharded by ranges
 def fri_shard_plan(n0, schedule, world):
     """Which layers of the FRI-like commit phase (deep_ali/src/fri.rs:231-312) a rank can commit from its own slice when

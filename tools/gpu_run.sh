@@ -2,7 +2,7 @@
 # One parameterised runner for a GPU lease (replaces the per-lease scripts of round 1):
 #   gpurun --timeout 1500 -- 'bash tools/gpu_run.sh <tag> <stage> [<stage> ...]'
 # Every stage writes gpurun_out/<tag>_<stage>.* ; a failing stage does not stop the later ones.
-# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | shard<N> | dist<N>
+# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | mgpu<N> | scale<N>
 set -u
 TAG=${1:?tag}; shift
 OUT=gpurun_out; mkdir -p $OUT
@@ -31,8 +31,7 @@ for stage in "$@"; do
     sanitizer)  for tool in memcheck racecheck; do
                   timeout 1200 compute-sanitizer --tool $tool --error-exitcode 1 python -m pytest tests/test_gpu_sanitizer_subset.py -m gpu -q -x > $OUT/${TAG}_sanitizer_$tool.log 2>&1; echo "$tool exit $?" >> $OUT/${TAG}_sanitizer_$tool.log; tail -6 $OUT/${TAG}_sanitizer_$tool.log
                 done ;;
-    shard*)     N=${stage#shard}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/fri_shard_bench.py > $OUT/${TAG}_shard_n$N.json 2> $OUT/${TAG}_shard_n$N.err; cat $OUT/${TAG}_shard_n$N.json; tail -5 $OUT/${TAG}_shard_n$N.err ;;
-    dist*)      N=${stage#dist}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/ntt_fri_dist_bench.py > $OUT/${TAG}_dist_n$N.json 2> $OUT/${TAG}_dist_n$N.err; cat $OUT/${TAG}_dist_n$N.json; tail -5 $OUT/${TAG}_dist_n$N.err ;;
+    mgpu*)      N=${stage#mgpu}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py > $OUT/${TAG}_multi_gpu_check_n$N.json 2> $OUT/${TAG}_multi_gpu_check_n$N.err; cat $OUT/${TAG}_multi_gpu_check_n$N.json; tail -8 $OUT/${TAG}_multi_gpu_check_n$N.err ;;
     scale*)     N=${stage#scale}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N > $OUT/${TAG}_bench_n$N.json 2> $OUT/${TAG}_bench_n$N.err; tail -c 2500 $OUT/${TAG}_bench_n$N.json; tail -5 $OUT/${TAG}_bench_n$N.err ;;
     *) echo "unknown stage $stage" ;;
   esac
