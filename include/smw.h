@@ -185,6 +185,18 @@ int32_t smw_mf_round_challenge_from_root(smw_ctx* ctx, uint64_t round_idx, const
 int32_t smw_mf_fold(smw_ctx* ctx, const void* cur, size_t n, const void* r_fr_host, void* next, int32_t mem);
 int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host /* k+1 */, void* r_out_host /* k */, void* final_out_host);
 
+/* ---- legacy trees (merkle/src/lib.rs:196-223 new_legacy, :448-470 new_pairs_legacy, :487-584 verify_many, :704-721 verify_pairs_legacy):
+ * fixed t = 17, chunks of poseidon::RATE = 16, every node / pair leaf = hash_with_ds(children, ds_tag) (poseidon/src/lib.rs:85-100).
+ * params NULL = merkle::default_params (:364-370).  The handle is an ordinary tree of arity 16: smw_tree_root / _level / _open_many apply. */
+int32_t smw_merkle_new_legacy(smw_ctx* ctx, smw_params* p_or_null, const void* ds_tag_fr_host, const void* leaves, size_t n, int32_t mem, smw_tree** out);
+int32_t smw_merkle_new_pairs_legacy(smw_ctx* ctx, smw_params* p_or_null, const void* ds_tag_fr_host, const void* f, const void* cp, size_t n_f, size_t n_cp, int32_t mem, smw_tree** out);
+int32_t smw_verify_many_legacy(smw_ctx* ctx, smw_params* p_or_null, int32_t proof_arity, const void* ds_tag_fr_host, const void* root_fr_host, const uint64_t* indices, const void* values_host, size_t n,
+                               const uint64_t* proof_indices, size_t n_proof_indices, int32_t n_levels, const size_t* n_siblings_per_level, const void* siblings_host,
+                               const size_t* n_groups_per_level, const uint8_t* group_sizes, int32_t* ok_out);
+int32_t smw_verify_pairs_legacy(smw_ctx* ctx, smw_params* p_or_null, int32_t proof_arity, const void* ds_tag_fr_host, const void* root_fr_host, const uint64_t* indices, const void* pairs_host, size_t n,
+                                const uint64_t* proof_indices, size_t n_proof_indices, int32_t n_levels, const size_t* n_siblings_per_level, const void* siblings_host,
+                                const size_t* n_groups_per_level, const uint8_t* group_sizes, int32_t* ok_out);
+
 /* ---- multi-GPU data plane: one process per GPU, NCCL bound at run time -----------------------------------
  * The reference has no distributed path; these entry points shard the SAME computations — results are
  * bit-identical to the single-GPU calls above.  Bootstrap: rank 0 obtains a 128-byte id, the host carries it to every rank

@@ -434,13 +434,23 @@ void orc_hash_leaf_pair(const u64* f, const u64* s, u64* out, size_t n) {
 
 /* ----------------------------------------------------------------- Merkle --
  * merkle/src/lib.rs:58-74 DsLabel, :147-193 MerkleTree::new, :380-445 new_pairs */
-typedef struct { int arity; u64 tree_label; const pparams* p; int nlevels; size_t* len; fr** lv; } mtree;
+typedef struct { int arity; u64 tree_label; const pparams* p; int nlevels; size_t* len; fr** lv; int legacy; fr ds_tag; } mtree;
 
 static void ds_fields(int arity, u64 level, u64 position, u64 label, fr out[4]) {
     out[0] = fr_from_u64((u64)arity); out[1] = fr_from_u64(level); out[2] = fr_from_u64(position); out[3] = fr_from_u64(label);
 }
-static mtree* tree_build(fr* level0 /* takes ownership */, size_t n, const pparams* p, int arity, u64 label) {
+/* poseidon/src/lib.rs:85-100 hash_with_ds (legacy sponge: state[16] = ds_tag, 16-chunks, no padding; static t = 17) */
+static fr hash_with_ds_legacy(const pparams* p, const fr* in, size_t n, fr ds_tag) {
+    fr s[17];
+    for (int i = 0; i < 17; i++) s[i] = FR_ZERO;
+    s[16] = ds_tag;
+    for (size_t off = 0; off < n; off += 16) { size_t c = n - off < 16 ? n - off : 16; for (size_t i = 0; i < c; i++) s[i] = fr_add(s[i], in[off + i]); permute(p, s); }
+    return s[0];
+}
+/* legacy != 0: merkle/src/lib.rs:196-223 new_legacy — chunks of poseidon::RATE = 16, every node hash_with_ds(chunk, ds_tag) */
+static mtree* tree_build_ex(fr* level0 /* takes ownership */, size_t n, const pparams* p, int arity, u64 label, int legacy, fr ds_tag) {
     mtree* T = malloc(sizeof *T);
+    T->legacy = legacy; T->ds_tag = ds_tag;
     T->arity = arity; T->tree_label = label; T->p = p;
     T->len = malloc(sizeof(size_t) * 70); T->lv = malloc(sizeof(fr*) * 70);
     T->nlevels = 1; T->len[0] = n; T->lv[0] = level0;
@@ -452,11 +462,27 @@ static mtree* tree_build(fr* level0 /* takes ownership */, size_t n, const ppara
         for (size_t q = 0; q < nn; q++) {
             fr ds[4]; ds_fields(arity, cur_level, q, label, ds);
             size_t base = q * arity, c = cn - base < (size_t)arity ? cn - base : (size_t)arity;
-            next[q] = hash_with_ds_dynamic(p, ds, 4, cur + base, c);
+            next[q] = legacy ? hash_with_ds_legacy(p, cur + base, c, ds_tag) : hash_with_ds_dynamic(p, ds, 4, cur + base, c);
         }
         T->len[T->nlevels] = nn; T->lv[T->nlevels] = next; T->nlevels++; cur_level++;
     }
     return T;
+}
+static mtree* tree_build(fr* level0, size_t n, const pparams* p, int arity, u64 label) { return tree_build_ex(level0, n, p, arity, label, 0, FR_ZERO); }
+/* merkle/src/lib.rs:196-223 MerkleTree::new_legacy, :448-470 new_pairs_legacy (leaf = hash_with_ds([f, cp], ds_tag), :373-375) */
+void* orc_merkle_new_legacy(void* params, const u64* ds_tag, const u64* leaves, size_t n) {
+    const pparams* p = params; if (n == 0 || p->t != 17) return NULL;
+    fr tag; memcpy(tag.l, ds_tag, 32);
+    fr* l0 = malloc(sizeof(fr) * n); memcpy(l0, leaves, sizeof(fr) * n);
+    return tree_build_ex(l0, n, p, 16, 0, 1, tag);
+}
+void* orc_merkle_new_pairs_legacy(void* params, const u64* ds_tag, const u64* f, const u64* cp, size_t n) {
+    const pparams* p = params; if (n == 0 || p->t != 17) return NULL;
+    fr tag; memcpy(tag.l, ds_tag, 32);
+    fr* l0 = malloc(sizeof(fr) * n);
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; i++) { fr pr[2] = {((const fr*)f)[i], ((const fr*)cp)[i]}; l0[i] = hash_with_ds_legacy(p, pr, 2, tag); }
+    return tree_build_ex(l0, n, p, 16, 0, 1, tag);
 }
 static int width_ok(int arity, int t) { return orc_width_for_arity(arity) == t; }
 void* orc_merkle_new(void* params, int arity, u64 label, const u64* leaves, size_t n) {
@@ -526,12 +552,28 @@ void orc_proof_level(void* p, int l, u64* sib, u8* grp) { mproof* pr = p; if (si
 void orc_proof_free(void* p) { mproof* pr = p; if (!pr) return; for (int l = 0; l < pr->nlev; l++) { free(pr->sib[l]); free(pr->grp[l]); } free(pr->sib); free(pr->grp); free(pr->nsib); free(pr->ngrp); free(pr->idx); free(pr); }
 
 /* merkle/src/lib.rs:587-701 verify_many_ds.  Proof passed flattened (as orc_proof_level lays it out). */
+static int verify_many_core(const u64* root, const u64* indices, const u64* values, size_t n,
+                       const u64* proof_indices, size_t n_pidx, int nlev, const size_t* nsib, const u64* sib_flat,
+                       const size_t* ngrp, const u8* grp_flat, int arity, u64 tree_label, void* params, const u64* legacy_tag);
 int orc_verify_many_ds(const u64* root, const u64* indices, const u64* values, size_t n,
                        const u64* proof_indices, size_t n_pidx, int nlev, const size_t* nsib, const u64* sib_flat,
                        const size_t* ngrp, const u8* grp_flat, int arity, u64 tree_label, void* params) {
+    return verify_many_core(root, indices, values, n, proof_indices, n_pidx, nlev, nsib, sib_flat, ngrp, grp_flat, arity, tree_label, params, NULL);
+}
+/* merkle/src/lib.rs:487-584 verify_many (legacy: parents are hash_with_ds(children, ds_tag); arity = proof.arity) */
+int orc_verify_many_legacy(const u64* root, const u64* indices, const u64* values, size_t n,
+                           const u64* proof_indices, size_t n_pidx, int nlev, const size_t* nsib, const u64* sib_flat,
+                           const size_t* ngrp, const u8* grp_flat, int arity, const u64* ds_tag, void* params) {
+    return verify_many_core(root, indices, values, n, proof_indices, n_pidx, nlev, nsib, sib_flat, ngrp, grp_flat, arity, 0, params, ds_tag);
+}
+static int verify_many_core(const u64* root, const u64* indices, const u64* values, size_t n,
+                       const u64* proof_indices, size_t n_pidx, int nlev, const size_t* nsib, const u64* sib_flat,
+                       const size_t* ngrp, const u8* grp_flat, int arity, u64 tree_label, void* params, const u64* legacy_tag) {
     const pparams* p = params;
+    fr ltag = FR_ZERO; if (legacy_tag) memcpy(ltag.l, legacy_tag, 32);
     if (n == 0) return 0;
-    if (!width_ok(arity, p->t)) return 0;
+    if (!legacy_tag && !width_ok(arity, p->t)) return 0;
+    if (legacy_tag && (arity < 1 || arity > 16)) return 0;
     size_t* req = malloc(sizeof(size_t) * n); for (size_t i = 0; i < n; i++) req[i] = (size_t)indices[i];
     size_t nreq = sort_dedup(req, n);
     int ok = (nreq == n_pidx);
@@ -560,7 +602,7 @@ int orc_verify_many_ds(const u64* root, const u64* indices, const u64* values, s
             }
             if (!ok) break;
             fr ds[4]; ds_fields(arity, (u64)lev, parent, tree_label, ds);
-            nidx[nn] = parent; nval[nn] = hash_with_ds_dynamic(p, ds, 4, children, cc); nn++;
+            nidx[nn] = parent; nval[nn] = legacy_tag ? hash_with_ds_legacy(p, children, cc, ltag) : hash_with_ds_dynamic(p, ds, 4, children, cc); nn++;
             i = j;
         }
         if (ok && off != nsib[lev]) ok = 0;

@@ -43,7 +43,7 @@ def lib():
         for name in ("orc_rng_seed_from_u64", "orc_rng_from_seed", "orc_params_new", "orc_params_for_width",
                      "orc_params_for_arity", "orc_transcript_default_params", "orc_commitment_default_params",
                      "orc_tr_new", "orc_merkle_new", "orc_merkle_new_pairs", "orc_tree_open", "orc_fri_build",
-                     "orc_fri_layer_tree", "orc_commitment_commit"):
+                     "orc_fri_layer_tree", "orc_commitment_commit", "orc_merkle_new_legacy", "orc_merkle_new_pairs_legacy"):
             getattr(L, name).restype = C.c_void_p
         for name in ("orc_rng_next_u64",):
             getattr(L, name).restype = C.c_uint64
@@ -379,6 +379,21 @@ class MerkleTree:
         assert f.shape == cp.shape, "f and cp length mismatch"
         return cls(lib().orc_merkle_new_pairs(_vp(params.h), int(arity), C.c_uint64(tree_label), _p(f), _p(cp), C.c_size_t(f.shape[0])), params, arity, tree_label)
 
+    @classmethod
+    def new_legacy(cls, leaves, ds_tag, params=None):
+        """merkle/src/lib.rs:196-223 (fixed t = 17, chunks of 16, one ds_tag)"""
+        params = params or Params.commitment_default()
+        lv, tag = fr_array(leaves).reshape(-1, 4), fr_array(ds_tag).reshape(4)
+        return cls(lib().orc_merkle_new_legacy(_vp(params.h), _p(tag), _p(lv), C.c_size_t(lv.shape[0])), params, 16, 0)
+
+    @classmethod
+    def new_pairs_legacy(cls, f, cp, ds_tag, params=None):
+        """merkle/src/lib.rs:448-470"""
+        params = params or Params.commitment_default()
+        f, cp, tag = fr_array(f).reshape(-1, 4), fr_array(cp).reshape(-1, 4), fr_array(ds_tag).reshape(4)
+        assert f.shape == cp.shape, "f and cp length mismatch"
+        return cls(lib().orc_merkle_new_pairs_legacy(_vp(params.h), _p(tag), _p(f), _p(cp), C.c_size_t(f.shape[0])), params, 16, 0)
+
     def root(self):
         out = np.zeros(4, dtype=np.uint64)
         lib().orc_tree_root(_vp(self.h), _p(out))
@@ -419,6 +434,35 @@ def verify_many_ds(root, indices, values, proof, tree_label, params, arity):
     rt = fr_array(root).reshape(4)
     return bool(lib().orc_verify_many_ds(_p(rt), _p(idx), _p(vals), C.c_size_t(idx.size), _p(pidx), C.c_size_t(len(proof.indices)),
                                          proof.nlev, nsib, _p(sib), ngrp, grp.ctypes.data_as(u8p), int(arity), C.c_uint64(tree_label), _vp(params.h)))
+
+
+def verify_many_legacy(root, indices, values, proof, ds_tag, params=None):
+    """merkle/src/lib.rs:487-584 verify_many (legacy sponge in the parents; arity = proof.arity)"""
+    params = params or Params.commitment_default()
+    idx = np.ascontiguousarray(indices, dtype=np.uint64)
+    vals = fr_array(values).reshape(-1, 4)
+    if idx.size != vals.shape[0]:
+        return False
+    if len(proof.siblings) != len(proof.group_sizes):
+        return False
+    pidx = np.ascontiguousarray(proof.indices if len(proof.indices) else [0], dtype=np.uint64)
+    nsib = (C.c_size_t * max(proof.nlev, 1))(*[s.shape[0] for s in proof.siblings])
+    ngrp = (C.c_size_t * max(proof.nlev, 1))(*[g.shape[0] for g in proof.group_sizes])
+    sib = np.ascontiguousarray(np.concatenate([s.reshape(-1, 4) for s in proof.siblings] + [np.zeros((1, 4), dtype=np.uint64)]))
+    grp = np.ascontiguousarray(np.concatenate([g for g in proof.group_sizes] + [np.zeros(1, dtype=np.uint8)]))
+    rt, tag = fr_array(root).reshape(4), fr_array(ds_tag).reshape(4)
+    return bool(lib().orc_verify_many_legacy(_p(rt), _p(idx), _p(vals), C.c_size_t(idx.size), _p(pidx), C.c_size_t(len(proof.indices)),
+                                             proof.nlev, nsib, _p(sib), ngrp, grp.ctypes.data_as(u8p), int(getattr(proof, "arity", 16) or 16), _p(tag), _vp(params.h)))
+
+
+def verify_pairs_legacy(root, indices, pairs, proof, ds_tag, params=None):
+    """merkle/src/lib.rs:704-721: leaf digests hash_with_ds([f, cp], ds_tag), then verify_many"""
+    params = params or Params.commitment_default()
+    pr = fr_array(pairs).reshape(-1, 2, 4)
+    if len(indices) != pr.shape[0] or len(indices) == 0:
+        return False
+    leaves = np.stack([hash_with_ds_legacy(params, pr[i], ds_tag) for i in range(pr.shape[0])])
+    return verify_many_legacy(root, indices, leaves, proof, ds_tag, params)
 
 
 def commitment_commit(leaves, ds_tag, params=None):

@@ -45,6 +45,9 @@ def load():
         getattr(L, n).restype = None
     # argument types: every pointer is passed as c_void_p, sizes as size_t, labels/seeds as uint64
     A = {
+        "smw_merkle_new_legacy": [vp, vp, vp, vp, sz, i32, vp], "smw_merkle_new_pairs_legacy": [vp, vp, vp, vp, vp, sz, sz, i32, vp],
+        "smw_verify_many_legacy": [vp, vp, i32, vp, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
+        "smw_verify_pairs_legacy": [vp, vp, i32, vp, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
         "smw_comm_unique_id": [vp], "smw_comm_init": [vp, vp, i32, i32, vp], "smw_comm_rank": [vp], "smw_comm_world": [vp], "smw_comm_free": [vp],
         "smw_comm_all_gather": [vp, vp, vp, sz], "smw_ctx_collective_count": [vp],
         "smw_fri_roots_sharded": [vp, vp, vp, sz, i32, vp, sz, vp, i32, u64, i32, vp],

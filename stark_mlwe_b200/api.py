@@ -348,6 +348,35 @@ def verify_pairs_ds(root, indices, pairs, proof, tree_label, dyn_params):
     return _verify_call(dyn_params.ctx.L.smw_verify_pairs_ds, root, indices, pairs, 2, proof, tree_label, dyn_params)
 
 
+def _verify_legacy_call(ctx, fn, root, indices, payload, per, proof, ds_tag, params):
+    idx = np.ascontiguousarray(indices, dtype=np.uint64).reshape(-1)
+    pay = np.ascontiguousarray(payload, dtype=np.uint64).reshape(-1, per * 4)
+    if idx.size != pay.shape[0] or len(proof.siblings) != len(proof.group_sizes):
+        return False                                    # merkle/src/lib.rs:495, 505
+    nl = len(proof.siblings)
+    pidx = np.ascontiguousarray(proof.indices, dtype=np.uint64).reshape(-1)
+    nsib = (C.c_size_t * max(nl, 1))(*[int(x.shape[0]) for x in proof.siblings])
+    ngrp = (C.c_size_t * max(nl, 1))(*[int(g.shape[0]) for g in proof.group_sizes])
+    sib = np.ascontiguousarray(np.concatenate([x.reshape(-1, 4) for x in proof.siblings] + [np.zeros((1, 4), np.uint64)]))
+    grp = np.ascontiguousarray(np.concatenate([g for g in proof.group_sizes] + [np.zeros(1, np.uint8)]))
+    rt, tag = _fr1(root), _fr1(ds_tag)
+    ok = C.c_int32(0)
+    ctx.check(fn(ctx.h, params.h if params else None, int(proof.arity), C.c_void_p(tag.ctypes.data), C.c_void_p(rt.ctypes.data),
+                 C.c_void_p(idx.ctypes.data) if idx.size else None, C.c_void_p(pay.ctypes.data) if idx.size else None, idx.size,
+                 C.c_void_p(pidx.ctypes.data) if pidx.size else None, pidx.size, nl, nsib, C.c_void_p(sib.ctypes.data), ngrp, C.c_void_p(grp.ctypes.data), C.byref(ok)))
+    return bool(ok.value)
+
+
+def verify_many(ctx, root, indices, values, proof, ds_tag, params=None):
+    """merkle/src/lib.rs:487-584 (legacy: parents are hash_with_ds(children, ds_tag))"""
+    return _verify_legacy_call(ctx, ctx.L.smw_verify_many_legacy, root, indices, values, 1, proof, ds_tag, params)
+
+
+def verify_pairs_legacy(ctx, root, indices, pairs, proof, ds_tag, params=None):
+    """merkle/src/lib.rs:704-721"""
+    return _verify_legacy_call(ctx, ctx.L.smw_verify_pairs_legacy, root, indices, pairs, 2, proof, ds_tag, params)
+
+
 class MerkleTree:
     """merkle/src/lib.rs:114-128, 147-193, 392-445. `levels[0]` are the leaves."""
 
@@ -371,6 +400,26 @@ class MerkleTree:
         h = C.c_void_p()
         ctx.check(ctx.L.smw_merkle_new_pairs(ctx.h, cfg.params.h, int(cfg.arity), int(cfg.tree_label), pf, pc, nf, nc, memf, C.byref(h)))
         return cls(ctx, h, cfg)
+
+    @classmethod
+    def new_legacy(cls, ctx, leaves, ds_tag, params=None):
+        """merkle/src/lib.rs:196-223: chunks of poseidon::RATE = 16, every node hash_with_ds(chunk, ds_tag); params None = merkle::default_params"""
+        p, n, mem, _k = _buf(leaves)
+        tag = _fr1(ds_tag)
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_merkle_new_legacy(ctx.h, params.h if params else None, C.c_void_p(tag.ctypes.data), p, n, mem, C.byref(h)))
+        return cls(ctx, h, None)
+
+    @classmethod
+    def new_pairs_legacy(cls, ctx, f_vals, cp_vals, ds_tag, params=None):
+        """merkle/src/lib.rs:448-470: leaf i = hash_with_ds([f_i, cp_i], ds_tag), then new_legacy"""
+        pf, nf, memf, _k1 = _buf(f_vals)
+        pc, nc, memc, _k2 = _buf(cp_vals)
+        assert memf == memc
+        tag = _fr1(ds_tag)
+        h = C.c_void_p()
+        ctx.check(ctx.L.smw_merkle_new_pairs_legacy(ctx.h, params.h if params else None, C.c_void_p(tag.ctypes.data), pf, pc, nf, nc, memf, C.byref(h)))
+        return cls(ctx, h, None)
 
     def root(self):
         out = _out(1)

@@ -306,3 +306,58 @@ class SumCheckMFVerifier:
 
     def current_root(self):
         return self.cur_root
+
+
+# ------------------------------------------------------------------------------------------------ prove_mf / verify_mf
+def build_vk_mf(kit, k, ds_tag_fr, queries_per_round):
+    """channel/src/lib.rs:1034-1041: tree_label = low 64 bits of the canonical tag (fr_tag_to_u64, :120-124)"""
+    from . import wire
+    return wire.VK(int(kit.to_canonical(ds_tag_fr)[0]), k, queries_per_round)
+
+
+def prove_mf(kit, vk, witness):
+    """channel/src/lib.rs:1130-1174: transcript "E2E/MF", SumCheckMFProver over the witness table, one RoundMF per variable"""
+    from . import wire
+    assert vk.queries_per_round is not None, "wrong VK variant"
+    chan = ProverChannel(kit.transcript(b"E2E/MF"))
+    cfg = MerkleChannelCfg(kit, tree_label=vk.tree_label)
+    sp = SumCheckMFProver(SumCheckMFConfig(vk.queries_per_round), cfg, chan, witness)
+    initial_root = np.array(sp.current_root(), dtype=np.uint64)
+    sp.send_claim()
+    rounds = []
+    for i in range(vk.k):
+        c0, c1, _r, next_root, op = sp.round(i)
+        rounds.append(wire.RoundMF(c0, c1, np.array(next_root, dtype=np.uint64), op.cur_indices, op.cur_values, op.cur_proof,
+                                   op.next_indices, op.next_values, op.next_proof))
+    return wire.ProofMF(initial_root, rounds, sp.finalize_eval())
+
+
+def verify_mf(kit, vk, proof):
+    """channel/src/lib.rs:1176-1240.  Like the reference, the claim is not carried by ProofMF: round 0 starts from 2 c0 + c1 and
+    the final check is finalize_and_check(final_eval, running) (which asserts inside the verifier; a failed check returns False here)."""
+    if vk.queries_per_round is None:
+        return False
+    chan = VerifierChannel(kit.transcript(b"E2E/MF"))
+    cfg = MerkleChannelCfg(kit, tree_label=vk.tree_label)
+    sv = SumCheckMFVerifier(SumCheckMFConfig(vk.queries_per_round), cfg, chan, proof.initial_root, vk.k)
+    sv.receive_initial_root(proof.initial_root)
+    running, prev_root = None, proof.initial_root
+    for i, r in enumerate(proof.rounds):
+        if running is None:
+            v = (2 * _limbs_to_int(kit.to_canonical(r.c0)) + _limbs_to_int(kit.to_canonical(r.c1))) % P_MOD
+            running = kit.from_canonical(_int_to_limbs(v))
+        try:
+            sv.start_round(i, running, r.c0, r.c1)
+        except AssertionError:
+            return False
+        r_i = sv.derive_round_challenge(i)
+        sv.recv_next_root(r.next_root)
+        if not sv.verify_fold_openings(r.cur_indices, r.cur_values, r.cur_proof, r.next_indices, r.next_values, r.next_proof, r_i, prev_root, r.next_root):
+            return False
+        running = sv.compute_s_next(r.c0, r.c1, r_i)
+        prev_root = r.next_root
+    try:
+        sv.finalize_and_check(proof.final_eval, running if running is not None else proof.final_eval)
+    except AssertionError:
+        return False
+    return True

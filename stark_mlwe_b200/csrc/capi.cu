@@ -1538,14 +1538,17 @@ template <class V> int upload_vec(smw_ctx* c, const std::vector<V>& h, V** d) {
 }
 
 // pairs != nullptr: 2 * nreq elements (f, cp interleaved, aligned with req) whose leaf digests are computed first; else leaves (nreq)
+// legacy_tag_host != nullptr: the legacy sponge (hash_with_ds(children, ds_tag), merkle/src/lib.rs:487-584, 704-721) instead of the DS one
 int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void* root_host, const std::vector<uint64_t>& req,
                 const std::vector<uint8_t>& leaves, const std::vector<uint8_t>& pairs, int n_levels, const size_t* n_sib, const void* siblings_host,
-                const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+                const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out, const void* legacy_tag_host = nullptr) {
     const size_t nreq = req.size(), n_pairs = pairs.size() / FR, leaf_base = n_pairs, sib_base = leaf_base + nreq;
     VerifyPlan pl;
     if (!plan_verify(req, leaf_base, sib_base, arity, n_levels, n_sib, n_grp, group_sizes, pl)) { *ok_out = 0; return SMW_OK; }
     size_t total_sib = 0; for (int l = 0; l < n_levels; l++) total_sib += n_sib[l];
     DevFree fr{{}, c->stream};
+    uint32_t* d_tag = nullptr;
+    if (legacy_tag_host) { SMW_CUDA(c, cudaMalloc(&d_tag, FR)); fr.v.push_back(d_tag); SMW_CUDA(c, cudaMemcpyAsync(d_tag, legacy_tag_host, FR, cudaMemcpyHostToDevice, c->stream)); }
     uint32_t* pool = nullptr; SMW_CUDA(c, cudaMalloc(&pool, pl.pool_entries * FR)); fr.v.push_back(pool);
     if (n_pairs) SMW_CUDA(c, cudaMemcpyAsync(pool, pairs.data(), pairs.size(), cudaMemcpyHostToDevice, c->stream));
     else SMW_CUDA(c, cudaMemcpyAsync(pool + leaf_base * 8, leaves.data(), leaves.size(), cudaMemcpyHostToDevice, c->stream));
@@ -1558,7 +1561,9 @@ int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void
         rc = upload_vec(c, ci, &d_ci); fr.v.push_back(d_ci); if (rc) return rc;
         rc = upload_vec(c, req, &d_pos); fr.v.push_back(d_pos); if (rc) return rc;
         rc = upload_vec(c, two, &d_two); fr.v.push_back(d_two); if (rc) return rc;
-        rc = launch_hash_groups(c, p, pool, d_ci, d_two, d_pos, nreq, arity, 2, 0xffffffffu, label, pool + leaf_base * 8); if (rc) return rc;
+        if (d_tag) rc = launch_legacy_nodes(c, p, 2, pool, nullptr, 2, d_ci, d_two, nreq, d_tag, pool + leaf_base * 8);       // encode_leaf_digest_legacy, :373-375
+        else rc = launch_hash_groups(c, p, pool, d_ci, d_two, d_pos, nreq, arity, 2, 0xffffffffu, label, pool + leaf_base * 8);
+        if (rc) return rc;
     }
     uint64_t *d_child = nullptr, *d_pos = nullptr; uint8_t* d_cnt = nullptr;
     rc = upload_vec(c, pl.child_idx, &d_child); fr.v.push_back(d_child); if (rc) return rc;
@@ -1567,7 +1572,9 @@ int verify_core(smw_ctx* c, smw_params* p, int arity, uint64_t label, const void
     size_t out_entry = sib_base + total_sib;
     for (int l = 0; l < n_levels; l++) {
         const size_t g0 = pl.first_group[l], ng = pl.n_groups[l];
-        rc = launch_hash_groups(c, p, pool, d_child + g0 * (size_t)arity, d_cnt + g0, d_pos + g0, ng, arity, arity, (uint32_t)l, label, pool + out_entry * 8); if (rc) return rc;
+        if (d_tag) rc = launch_legacy_nodes(c, p, 2, pool, nullptr, (size_t)arity, d_child + g0 * (size_t)arity, d_cnt + g0, ng, d_tag, pool + out_entry * 8);
+        else rc = launch_hash_groups(c, p, pool, d_child + g0 * (size_t)arity, d_cnt + g0, d_pos + g0, ng, arity, arity, (uint32_t)l, label, pool + out_entry * 8);
+        if (rc) return rc;
         out_entry += ng;
     }
     uint8_t got[FR]; rc = d2h(c, got, pool + pl.final_entry * 8, FR); if (rc) return rc;
@@ -1611,6 +1618,83 @@ int32_t smw_verify_pairs_ds(smw_ctx* c, smw_params* p, int32_t arity, uint64_t t
     std::vector<uint64_t> req; std::vector<uint8_t> pairs;
     if (!align_request(indices, pairs_host, n, 2, proof_indices, n_pidx, req, pairs)) return SMW_OK;
     return verify_core(c, p, arity, tree_label, root_fr_host, req, {}, pairs, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out);
+}
+
+// ---------------------------------------------------------------------------------------- legacy trees
+// merkle/src/lib.rs:196-223 new_legacy, :448-470 new_pairs_legacy: fixed t = 17, chunks of poseidon::RATE = 16, every node
+// hash_with_ds(chunk, ds_tag) — one permutation, no DS label, no padding.  The tree handle is an ordinary smw_tree (arity 16),
+// so smw_tree_open_many serves it (open_union_of_paths is shared, :246-325).
+static int legacy_tree(smw_ctx* c, smw_params* p, const void* ds_tag_host, uint32_t* d_level0, size_t n, smw_tree** out) {
+    DevFree fr{{}, c->stream};
+    uint32_t* d_tag; SMW_CUDA(c, cudaMalloc(&d_tag, FR)); fr.v.push_back(d_tag);
+    SMW_CUDA(c, cudaMemcpyAsync(d_tag, ds_tag_host, FR, cudaMemcpyHostToDevice, c->stream));
+    auto t = std::make_unique<smw_tree>(); t->ctx = c; t->params = p; t->arity = 16; t->tree_label = 0;
+    t->len = level_sizes(n, 16, false);
+    size_t total = 0; for (size_t j = 1; j < t->len.size(); j++) total += t->len[j];
+    if (total) { cudaError_t e = cudaMalloc(&t->arena, total * FR); if (e != cudaSuccess) { cudaFree(d_level0); return cuda_err(c, e, "cudaMalloc(tree levels)"); } }
+    t->lv.push_back(d_level0); t->owned.push_back(true);
+    size_t off = 0; for (size_t j = 1; j < t->len.size(); j++) { t->lv.push_back(t->arena + off * 8); t->owned.push_back(false); off += t->len[j]; }
+    for (size_t j = 0; j + 1 < t->len.size(); j++) {
+        int rc = launch_legacy_nodes(c, p, 0, t->lv[j], nullptr, t->len[j], nullptr, nullptr, t->len[j + 1], d_tag, t->lv[j + 1]);
+        if (rc) { smw_tree_free(t.release()); return rc; }
+    }
+    *out = t.release();
+    return SMW_OK;
+}
+static int legacy_params(smw_ctx* c, smw_params** p) {
+    if (!*p) { int rc = smw_params_commitment_default(c, p); if (rc) return rc; }          // merkle/src/lib.rs:364-370 default_params: "POSEIDON-T17-X5-SEED"
+    if ((*p)->t != 17) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "legacy trees are fixed at t = 17");
+    return SMW_OK;
+}
+int32_t smw_merkle_new_legacy(smw_ctx* c, smw_params* p, const void* ds_tag_host, const void* leaves, size_t n, int32_t mem, smw_tree** out) {
+    if (!c || !out || !ds_tag_host) return SMW_ERR_INVALID_ARG;
+    if (n == 0) return set_err(c, SMW_ERR_EMPTY, "no leaves");
+    if (!leaves) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    int rc = legacy_params(c, &p); if (rc) return rc;
+    uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n * FR));
+    { cudaError_t e = cudaMemcpyAsync(d0, leaves, n * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
+      if (e != cudaSuccess) { cudaFree(d0); return cuda_err(c, e, "copy leaves"); } }
+    return legacy_tree(c, p, ds_tag_host, d0, n, out);
+}
+int32_t smw_merkle_new_pairs_legacy(smw_ctx* c, smw_params* p, const void* ds_tag_host, const void* f, const void* cp, size_t n_f, size_t n_cp, int32_t mem, smw_tree** out) {
+    if (!c || !out || !ds_tag_host) return SMW_ERR_INVALID_ARG;
+    if (n_f != n_cp) return set_err(c, SMW_ERR_LENGTH_MISMATCH, "f and cp length mismatch");
+    if (n_f == 0) return set_err(c, SMW_ERR_EMPTY, "no leaves");
+    if (!f || !cp) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    int rc = legacy_params(c, &p); if (rc) return rc;
+    In a(c, f, n_f, mem), b(c, cp, n_f, mem), tg(c, ds_tag_host, 1, SMW_HOST); if (a.rc) return a.rc; if (b.rc) return b.rc; if (tg.rc) return tg.rc;
+    uint32_t* d0; SMW_CUDA(c, cudaMalloc(&d0, n_f * FR));
+    rc = launch_legacy_nodes(c, p, 1, a.d, b.d, n_f, nullptr, nullptr, n_f, tg.d, d0);            // encode_leaf_digest_legacy (:373-375)
+    if (rc) { cudaFree(d0); return rc; }
+    return legacy_tree(c, p, ds_tag_host, d0, n_f, out);
+}
+int32_t smw_verify_many_legacy(smw_ctx* c, smw_params* p, int32_t arity, const void* ds_tag_host, const void* root_fr_host, const uint64_t* indices, const void* values_host, size_t n,
+                               const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                               const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+    if (!c || !ds_tag_host || !root_fr_host || !ok_out || n_levels < 0 || (n_levels && (!n_sib || !n_grp))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    *ok_out = 0;
+    int rc = legacy_params(c, &p); if (rc) return rc;
+    if (n == 0 || !indices || !values_host) return SMW_OK;                       // :495
+    if (arity < 1 || arity > 16) return SMW_OK;                                  // more children than the rate cannot be one hash_with_ds block of a tree node
+    std::vector<uint64_t> req; std::vector<uint8_t> leaves;
+    if (!align_request(indices, values_host, n, 1, proof_indices, n_pidx, req, leaves)) return SMW_OK;   // :502
+    return verify_core(c, p, arity, 0, root_fr_host, req, leaves, {}, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out, ds_tag_host);
+}
+int32_t smw_verify_pairs_legacy(smw_ctx* c, smw_params* p, int32_t arity, const void* ds_tag_host, const void* root_fr_host, const uint64_t* indices, const void* pairs_host, size_t n,
+                                const uint64_t* proof_indices, size_t n_pidx, int32_t n_levels, const size_t* n_sib, const void* siblings_host,
+                                const size_t* n_grp, const uint8_t* group_sizes, int32_t* ok_out) {
+    if (!c || !ds_tag_host || !root_fr_host || !ok_out || n_levels < 0 || (n_levels && (!n_sib || !n_grp))) return SMW_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    *ok_out = 0;
+    int rc = legacy_params(c, &p); if (rc) return rc;
+    if (n == 0 || !indices || !pairs_host) return SMW_OK;                        // :712
+    if (arity < 1 || arity > 16) return SMW_OK;
+    std::vector<uint64_t> req; std::vector<uint8_t> pairs;
+    if (!align_request(indices, pairs_host, n, 2, proof_indices, n_pidx, req, pairs)) return SMW_OK;
+    return verify_core(c, p, arity, 0, root_fr_host, req, {}, pairs, n_levels, n_sib, siblings_host, n_grp, group_sizes, ok_out, ds_tag_host);
 }
 
 // ---------------------------------------------------------------------------------------- DEEP-ALI merge

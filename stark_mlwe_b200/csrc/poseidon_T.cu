@@ -478,6 +478,15 @@ int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* ctrp, const uint3
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
+int launch_legacy_nodes(smw_ctx* c, const smw_params* p, int mode, const uint32_t* d_src, const uint32_t* d_cp, size_t n_src, const uint64_t* d_idx, const uint8_t* d_cnt,
+                        size_t n_out, const uint32_t* d_tag, uint32_t* d_out) {
+    if (n_out == 0) return SMW_OK;
+    if (p->t != 17 || !p->d_tables52) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "legacy trees are fixed at t = 17 (poseidon::RATE = 16)");
+    { LaunchScope ls(c, KC_MERKLE_LEVEL);
+      k_legacy_nodes_coop52<<<(unsigned)n_out, 32, 0, c->stream>>>(mode, d_src, d_cp, n_src, d_idx, d_cnt, n_out, d_tag, d_out, p->d_tables52, coop_tab(p)); }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
 int launch_fri_sample_z(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, const uint64_t* d_sizes, int L, uint64_t seed_z, uint32_t* d_z) {
     if (L <= 0) return SMW_OK;
     if (c->use_f52 && trp->d_tables52) {

@@ -123,6 +123,28 @@ k_transcript_coop52(uint32_t* state, int fresh, int pos, const uint32_t* __restr
     if (lane == 0 && out) emit_ext52(e, out);
 }
 
+// ------------------------------------------------------------------ legacy trees (merkle/src/lib.rs:196-223, 373-375, 448-470, 487-584)
+// out[g] = hash_with_ds(children of g, ds_tag) (poseidon/src/lib.rs:85-100: state[16] = ds_tag, children added into lanes 0.., ONE
+// permutation, no padding) — one warp per node.  Children: mode 0 = src[16 g .. 16 g + 16) clipped to n_src; mode 1 = the pair
+// (src[g], cp[g]); mode 2 = pool entries src[idx[row g + c]], c < cnt[g] (the recomputed parents of a verifier; n_src carries `row`).
+__global__ void __launch_bounds__(32)
+k_legacy_nodes_coop52(int mode, const uint32_t* __restrict__ src, const uint32_t* __restrict__ cp, size_t n_src, const uint64_t* __restrict__ idx,
+                      const uint8_t* __restrict__ cnt, size_t n_out, const uint32_t* __restrict__ tag, uint32_t* __restrict__ out, const uint32_t* __restrict__ tbl, CoopTab L) {
+    __shared__ __align__(16) double sh[17 * 6];
+    const int lane = threadIdx.x; const size_t g = blockIdx.x;
+    if (g >= n_out) return;
+    CoopCx<17, 32> c{tbl, L, sh, lane, 0};
+    F52 raw = f52_zero();
+    if (lane == 16) raw = raw_ext52(tag);
+    else if (mode == 0) { const size_t i = g * 16 + lane; if (lane < 16 && i < n_src) raw = raw_ext52(src + i * 8); }
+    else if (mode == 1) { if (lane == 0) raw = raw_ext52(src + g * 8); else if (lane == 1) raw = raw_ext52(cp + g * 8); }
+    else { if (lane < (int)cnt[g] && lane < 16) raw = raw_ext52(src + (size_t)idx[g * n_src + lane] * 8); }
+    F52 s = coop_mr(raw, c.tab(L.k_in), f52_zero());
+    s = coop_perm<17, 32>(c, s);
+    const F52 e = coop_mr(s, c.tab(L.k_out), f52_zero());
+    if (lane == 0) emit_ext52(e, out + g * 8);
+}
+
 // fri_sample_z_ell (deep_ali/src/fri.rs:59-82) for all L levels at once, one warp per level: the warp hashes the level's template
 // (one permutation), lane 0 seeds ChaCha12 with the canonical bytes of the digest and takes the first u64 c with c != 0, c^n != 1.
 __global__ void __launch_bounds__(32)

@@ -181,6 +181,9 @@ int launch_hash_ds_single(smw_ctx* c, const smw_params* p, const uint32_t* d_ds,
 // out[g] = H(DS(arity, level, pos[g], label), pool[child_idx[g*row + c]] for c < cnt[g] <= row) — recomputed parents / pair-leaf digests of a verifier
 int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                        size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
+// legacy-sponge nodes, one warp each: mode 0 chunks of 16 of d_src, 1 pairs (d_src[g], d_cp[g]), 2 gathered pool entries (d_idx rows of 16, d_cnt)
+int launch_legacy_nodes(smw_ctx* c, const smw_params* p, int mode, const uint32_t* d_src, const uint32_t* d_cp, size_t n_src, const uint64_t* d_idx, const uint8_t* d_cnt,
+                        size_t n_out, const uint32_t* d_tag, uint32_t* d_out);
 int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
 // several runs of one level in one launch (explicit device segment array); all runs share the parameter set and the arity
 int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);

@@ -46,3 +46,32 @@ def test_mf_round_trip_over_oracle(O, rnd, k, q):
         s_prev = ver.compute_s_next(c0, c1, r_i)
     ver.finalize_and_check(g["final"], s_prev)
     assert np.array_equal(vchan.challenge_scalar(b"tail"), g["tail"])
+
+
+@pytest.mark.parametrize("k,q", [(4, 2), (5, 3)])
+def test_prove_mf_verify_mf_and_wire_round_trip_over_oracle(O, rnd, k, q):
+    """prove_mf -> ProofMF -> bincode -> ProofMF -> verify_mf (channel/src/lib.rs:945-979, 1130-1240) over the oracle kit; tampered
+    and malformed proofs are rejected"""
+    from stark_mlwe_b200 import channel as ch, wire
+    from stark_mlwe_b200.api import MerkleProof
+    kit = OracleKit(O)
+    table = rnd(4321 + k, 1 << k)
+    vk = ch.build_vk_mf(kit, k, O.to_mont([0xABCD])[0], q)
+    assert vk.tree_label == 0xABCD and vk.to_bincode()[:15] == (7).to_bytes(8, "little") + b"default"
+    proof = ch.prove_mf(kit, vk, table)
+    assert len(proof.rounds) == k and ch.verify_mf(kit, vk, proof)
+    blob = wire.proof_mf_to_bincode(proof, O.from_mont_c)
+    back = wire.proof_mf_from_bincode(blob, O.to_mont_c, MerkleProof.from_fields)
+    assert wire.proof_mf_to_bincode(back, O.from_mont_c) == blob and ch.verify_mf(kit, vk, back)
+    # layout: initial_root = u64 32 + canonical little-endian bytes, then the round count
+    assert blob[:8] == (32).to_bytes(8, "little") and int.from_bytes(blob[8:40], "little") == O.from_mont(proof.initial_root.reshape(1, 4))[0]
+    assert int.from_bytes(blob[40:48], "little") == k
+    back.rounds[1].next_values[0, 0] ^= np.uint64(1)
+    assert not ch.verify_mf(kit, vk, back)
+    back = wire.proof_mf_from_bincode(blob, O.to_mont_c, MerkleProof.from_fields)
+    back.rounds[0].c1 = back.rounds[0].c0
+    assert not ch.verify_mf(kit, vk, back)
+    assert not ch.verify_mf(kit, wire.VK(0xABCD, k, None), proof)                 # wrong VK variant
+    for bad in (blob[:-1], blob + b"\0", blob[:40] + (1 << 40).to_bytes(8, "little") + blob[48:]):
+        with pytest.raises(wire.WireError):
+            wire.proof_mf_from_bincode(bad, O.to_mont_c, MerkleProof.from_fields)

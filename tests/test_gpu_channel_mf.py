@@ -80,3 +80,22 @@ def test_merkle_prover_commit_vector_and_open(ctx, O, rnd):
     (r0, v0, p0, c0, l0), (r1, v1, p1, c1, l1) = outs
     assert l0 == l1 and eq(r0, r1) and eq(v0, v1) and eq(c0, c1) and p0.indices == p1.indices
     assert all(eq(x, y) for x, y in zip(p0.siblings, p1.siblings))
+
+
+@pytest.mark.parametrize("k,q", [(6, 3), (3, 8)])
+def test_prove_mf_on_device_serialises_to_the_same_bytes_as_the_oracle(ctx, O, rnd, k, q):
+    """prove_mf / verify_mf (channel/src/lib.rs:1130-1240) on the device; the ProofMF bincode bytes equal those of the same
+    protocol run over the CPU oracle, and a deserialised proof verifies on the device"""
+    from stark_mlwe_b200 import channel as ch, wire
+    from stark_mlwe_b200.api import MerkleProof
+    table = rnd(4400 + k, 1 << k)
+    gk, ok = ch.GpuKit(ctx), OracleKit(O)
+    tag = O.to_mont([2025])[0]
+    vk = ch.build_vk_mf(gk, k, tag, q)
+    pg, po = ch.prove_mf(gk, vk, table), ch.prove_mf(ok, ch.build_vk_mf(ok, k, tag, q), table)
+    bg, bo = wire.proof_mf_to_bincode(pg, ctx.to_canonical), wire.proof_mf_to_bincode(po, O.from_mont_c)
+    assert bg == bo
+    back = wire.proof_mf_from_bincode(bg, ctx.from_canonical, MerkleProof.from_fields)
+    assert ch.verify_mf(gk, vk, back) and ch.verify_mf(ok, vk, back)
+    back.rounds[-1].cur_values[0, 1] ^= np.uint64(1)
+    assert not ch.verify_mf(gk, vk, back)

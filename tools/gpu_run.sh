@@ -17,7 +17,7 @@ for stage in "$@"; do
     smoke)      timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${TAG}_smoke.log 2>&1; tail -3 $OUT/${TAG}_smoke.log ;;
     bench)      timeout 900 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; tail -c 3000 $OUT/${TAG}_bench.json; tail -5 $OUT/${TAG}_bench.err ;;
     bench_ref)  timeout 600 python bench.py --impl reference > $OUT/${TAG}_bench_reference.json 2> $OUT/${TAG}_bench_reference.err; cat $OUT/${TAG}_bench_reference.json ;;
-    fri)        timeout 600 python tools/fri_bench.py > $OUT/${TAG}_fri.json 2> $OUT/${TAG}_fri.err; cat $OUT/${TAG}_fri.json; tail -5 $OUT/${TAG}_fri.err ;;
+    fri)        SMW_TRACE=1 timeout 600 python tools/fri_bench.py > $OUT/${TAG}_fri.json 2> $OUT/${TAG}_fri.err; cat $OUT/${TAG}_fri.json; tail -5 $OUT/${TAG}_fri.err ;;
     kat)        timeout 900 python -m pytest tests/test_gpu_proof_bytes_kat.py -m gpu -q --durations=10 > $OUT/${TAG}_kat.log 2>&1; tail -15 $OUT/${TAG}_kat.log ;;
     mf)         timeout 600 python tools/mf_bench.py > $OUT/${TAG}_mf.json 2> $OUT/${TAG}_mf.err; cat $OUT/${TAG}_mf.json; tail -5 $OUT/${TAG}_mf.err ;;
     launches)   timeout 900 $NCU_LIST -c 600 --log-file $OUT/${TAG}_ncu_launches.csv python bench.py --steps 1 --warmup 1 --log-n 16 --cols 16 --no-cpu --no-e2e > $OUT/${TAG}_ncu_launches.out 2>&1; tail -3 $OUT/${TAG}_ncu_launches.out ;;
