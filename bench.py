@@ -345,11 +345,29 @@ def cfg5_leg(ctx, smw, comm, T, rank, world, torch, log_n):
     def fri():
         return smw.fri_roots_sharded(ctx, comm, state["chunks"], firsts, N, prm)
     ntt(); fri()
+    c0 = ctx.collective_count()
     t_ntt, _ = T.run(ntt, 1)
     t_fri, roots = T.run(fri, 1)
-    return {"workload": "cfg5: one column of 2^%d, NTT + FRI commit phase [16,16,8]" % log_n, "ntt_ms": t_ntt * 1e3, "fri_ms": t_fri * 1e3,
-            "ntt_elems_per_s": N / t_ntt, "fri_n0_per_s": N / t_fri, "all_to_all_bytes_per_rank": M * 32 * (world - 1) // world,
-            "root0": [int(v) for v in roots[0]]}
+    rec = {"workload": "cfg5: one column of 2^%d, NTT + FRI commit phase [16,16,8]" % log_n, "ntt_ms": t_ntt * 1e3, "fri_ms": t_fri * 1e3,
+           "ntt_elems_per_s": N / t_ntt, "fri_n0_per_s": N / t_fri, "all_to_all_bytes_per_rank": M * 32 * (world - 1) // world,
+           "collectives": ctx.collective_count() - c0, "root0": [int(v) for v in roots[0]]}
+    if world > 1:
+        # the single-GPU path on the full vector (2 GiB at 2^26: it fits one B200) as the checker of the distributed one: equal layer
+        # roots mean an equal transform, every root depends on every transformed element
+        del x_loc
+        state.clear()
+        torch.cuda.empty_cache()
+        ok = None
+        if rank == 0:
+            X = gen_columns_torch(0x5EED0005, 0, 1, N, "cuda")[0].contiguous()
+            smw._ntt(ctx, X, 0)
+            want = smw.fri_roots_sharded(ctx, None, X.view(1, N, 4), [0], N, prm)
+            ok = bool(np.array_equal(want, roots))
+            del X
+            torch.cuda.empty_cache()
+            assert ok, "distributed NTT + FRI differs from the single-GPU path"
+        rec["equal_single_gpu"] = ok
+    return rec
 
 
 def main():

@@ -69,6 +69,22 @@ SMW_DEV void acc52_mac(Acc52& A, const F52& a, const F52& b) {
         }
 }
 SMW_DEV void acc52_mul(Acc52& A, const F52& a, const F52& b) { acc52_zero(A); acc52_mac(A, a, b); }
+// A = a * a with 15 limb products instead of 25: an off-diagonal product a_i a_j (i < j) is split once and its two bit patterns are
+// added TWICE (a doubled operand would leave the 2^104 window of the split).  Every column receives exactly as many low / high
+// patterns as in acc52_mul, so the exponent bookkeeping of acc52_reduce_add2 (n_terms = 1) is unchanged.
+SMW_DEV void acc52_sqr(Acc52& A, const F52& a) {
+    acc52_zero(A);
+#pragma unroll
+    for (int i = 0; i < 5; i++)
+#pragma unroll
+        for (int j = i; j < 5; j++) {
+            const double hi = __fma_rz(a.v[i], a.v[j], 0x1p104);
+            const double lo = __fma_rz(a.v[i], a.v[j], (0x1p104 + 0x1p52) - hi);
+            const uint64_t h = (uint64_t)__double_as_longlong(hi), l = (uint64_t)__double_as_longlong(lo);
+            if (i == j) { A.c[i + j + 1] += h; A.c[i + j] += l; }
+            else { A.c[i + j + 1] += h + h; A.c[i + j] += l + l; }
+        }
+}
 
 // Montgomery reduction of an accumulator of `n_terms` products, plus two addends on top of the reduced value:
 // returns s + t + (A + M p) / 2^260, limbs < 2^52 (the caller's bounds keep the value below 2^260).

@@ -35,6 +35,11 @@ static __device__ __noinline__ F52 coop_mr(F52 a, F52 b, F52 s) {
     Acc52 A; acc52_mul(A, a, b);
     return acc52_reduce_add2(A, 1, s, f52_zero());
 }
+// r = (a^2 + M p) / 2^260 (15 limb products): the two squarings of every S-box
+static __device__ __noinline__ F52 coop_sq(F52 a) {
+    Acc52 A; acc52_sqr(A, a);
+    return acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
+}
 // r = (a1 b1 + a2 b2 + M p) / 2^260 + s
 static __device__ __noinline__ F52 coop_mr2(F52 a1, F52 b1, F52 a2, F52 b2, F52 s) {
     Acc52 A; acc52_mul(A, a1, b1); acc52_mac(A, a2, b2);
@@ -122,7 +127,7 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
     // full rounds 0..3
 #pragma unroll 1
     for (int r = 0; r < 4; r++) {
-        const F52 x2 = coop_mr(s, s, zero), x4 = coop_mr(x2, x2, zero); s = coop_mr(x4, s, zero);
+        const F52 x2 = coop_sq(s), x4 = coop_sq(x2); s = coop_mr(x4, s, zero);
         F52 rc = zero;                                    // the next round's constant: full round r + 1, or partial round 0 (lane 0 only)
         if (r < 3) { if (in) rc = c.tab(L.rc_full + (uint32_t)(r + 1) * T + lc); } else if (l0) rc = c.tab(L.rc_part);
         s = coop_matvec<T, G>(c, s, L.mds, T, 0, rc);
@@ -137,7 +142,7 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
         if (lu && k > 0) { const uint32_t q = L.sp_col + (uint32_t)((k >> 1) - 1) * 2 * n + 2 * (uint32_t)(lane - 1); ca = c.tab(q); cb = c.tab(q + 1); }
         F52 r = coop_mr2(l0 ? s : ca, l0 ? s : pxa, l0 ? zero : cb, l0 ? zero : pxb, l0 ? zero : s);
         F52 x2 = r; if (!l0) s = r;
-        F52 x4 = coop_mr(x2, x2, zero);
+        F52 x4 = coop_sq(x2);
         F52 xa = c.bcast0(coop_mr(x4, s, zero));          // x_a = S-box output of round k (lane 0's s is the S-box input)
         // slot D1: lane 0: M00 x_a + rc_{k+1}; lanes 1..n: row_k[j] u_j; summed over the group -> the new lane 0
         F52 a = l0 ? xa : (lu ? s : zero), b = c.tab(rowA + (l0 ? (uint32_t)n : (uint32_t)(lu ? lane - 1 : 0)));
@@ -145,7 +150,7 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
         F52 t0 = c.group_sum(sel52(in, r, zero));
         if (l0) s = t0;
         // second round of the block
-        x2 = coop_mr(s, s, zero); x4 = coop_mr(x2, x2, zero);
+        x2 = coop_sq(s); x4 = coop_sq(x2);
         F52 xb = c.bcast0(coop_mr(x4, s, zero));
         const bool lg = lane == T;                        // the lane that carries G x_a
         a = l0 ? xb : (lu ? s : (lg ? xa : zero));
@@ -167,7 +172,7 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
     // full rounds 4..7
 #pragma unroll 1
     for (int r = 4; r < 8; r++) {
-        const F52 x2 = coop_mr(s, s, zero), x4 = coop_mr(x2, x2, zero); s = coop_mr(x4, s, zero);
+        const F52 x2 = coop_sq(s), x4 = coop_sq(x2); s = coop_mr(x4, s, zero);
         s = coop_matvec<T, G>(c, s, L.mds, T, 0, (r < 7 && in) ? c.tab(L.rc_full + (uint32_t)(r + 1) * T + lc) : zero);
     }
     return sel52(in, s, zero);
