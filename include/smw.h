@@ -142,6 +142,9 @@ int32_t smw_transcript_state(smw_transcript* t, void* out_17_fr_host, int32_t* p
 void smw_transcript_free(smw_transcript* t);
 int32_t smw_tr_hash_fields_tagged(smw_ctx* ctx, const uint8_t* tag, size_t tag_len, const void* xs, size_t n, int32_t mem, void* out_fr_host);
 /* `count` independent tr_hash_fields_tagged calls whose serial sponges overlap on side streams (the four ALI sponges of DeepAliRealBuilder::build_f0, deep_ali/src/fri.rs:541-548) */
+/* `count` one-shot hashes sharing `tag`, k field elements each (xs: count x k), one launch, one permutation per hash — the
+ * index seeds of fri_prove_queries (deep_ali/src/fri.rs:184-191, 388-400).  The pre-image must fit one rate block (k <= ~8). */
+int32_t smw_tr_hash_fields_tagged_batch(smw_ctx* ctx, const uint8_t* tag, size_t tag_len, const void* xs, int32_t k, size_t count, int32_t mem, void* out);
 int32_t smw_tr_hash_fields_tagged_many(smw_ctx* ctx, int32_t count, const uint8_t* const* tags, const size_t* tag_lens, const void* const* xs, const size_t* n,
                                        int32_t mem, void* out_fr_host);
 int32_t smw_hash_leaf_pair(smw_ctx* ctx, const void* f, const void* s, size_t n, void* out, int32_t mem);   /* hash_leaf_pair, element-wise */

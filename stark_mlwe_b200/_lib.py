@@ -89,6 +89,7 @@ def load():
         "smw_proof_level_siblings": [vp, i32], "smw_proof_level_groups": [vp, i32], "smw_proof_level": [vp, i32, vp, vp], "smw_proof_free": [vp],
         "smw_deep_ali_merge_evals": [vp, vp, vp, vp, vp, sz, vp, vp, vp, i32],
         "smw_tr_hash_fields_tagged_many": [vp, i32, vp, vp, vp, vp, i32, vp],
+        "smw_tr_hash_fields_tagged_batch": [vp, vp, sz, vp, i32, sz, i32, vp],
         "smw_verify_many_ds": [vp, vp, i32, u64, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
         "smw_verify_pairs_ds": [vp, vp, i32, u64, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
     }

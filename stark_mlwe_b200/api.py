@@ -59,7 +59,11 @@ class Context:
     def __init__(self, device=0, stream=None):
         self.L = _lib.load()
         h = C.c_void_p()
-        rc = self.L.smw_ctx_create_on_stream(int(device), C.c_void_p(stream) if stream else None, C.byref(h))
+        # stream: None = the library creates its own (non-blocking) stream; a cudaStream_t handle = run there.  The handle 0 is the legacy
+        # default stream (what torch.cuda.current_stream().cuda_stream returns until a stream is set): it is passed as cudaStreamLegacy
+        # (0x1), NOT as "none" — a private non-blocking stream does not order with work the caller enqueues on the default stream.
+        sp = None if stream is None else C.c_void_p(int(stream) if int(stream) != 0 else 1)
+        rc = self.L.smw_ctx_create_on_stream(int(device), sp, C.byref(h))
         if rc:
             raise SmwError(rc, "cannot create a context on CUDA device %d (no CPU fallback exists)" % device)
         self.h = h
@@ -939,6 +943,16 @@ class FriQueryProofs:
         return total
 
 
+def tr_hash_fields_tagged_batch(ctx, tag, xs):
+    """xs: (count, k, 4) -> (count, 4): count one-shot hashes tr_hash_fields_tagged(tag, xs[i]) in one launch (k small)"""
+    a = np.ascontiguousarray(xs, dtype=np.uint64)
+    count, k = a.shape[0], a.shape[1]
+    buf, n = _bytes(tag)
+    out = _out(count)
+    ctx.check(ctx.L.smw_tr_hash_fields_tagged_batch(ctx.h, buf, n, C.c_void_p(a.ctypes.data), k, count, HOST, C.c_void_p(out.ctypes.data)))
+    return out
+
+
 def fri_prove_queries(ctx, st, r):
     """deep_ali/src/fri.rs:355-466: query indices from the roots (fs_seed_from_roots :176, index_seed :184-191 with its retry
     rule) and the per-layer batched openings; every hash, RNG draw and opening runs on the device."""
@@ -947,11 +961,17 @@ def fri_prove_queries(ctx, st, r):
     roots_seed = tr_hash_fields_tagged(ctx, b"FRI/seed", roots)
     one = _fr_from_u64(ctx, 1)
     child_idx, parent_idx, cps, pps = [], [], [], []
+    # every index seed H("FRI/index", [roots_seed, l, q]) of the proof in ONE launch (r * L hashes, one warp each)
+    small = ctx.from_canonical(np.array([[v, 0, 0, 0] for v in range(max(L, r, 1))], dtype=np.uint64))      # the integers 0 .. as field elements
+    pre = np.empty((L, r, 3, 4), dtype=np.uint64)
+    pre[:, :, 0] = roots_seed
+    pre[:, :, 1] = small[:L, None, :] if L else 0
+    pre[:, :, 2] = small[None, :r, :]
+    all_seeds = tr_hash_fields_tagged_batch(ctx, b"FRI/index", pre.reshape(L * r, 3, 4)).reshape(L, r, 4) if L * r else np.zeros((L, r, 4), dtype=np.uint64)
     for l in range(L):
         n, m = st.layers[l].n, st.layers[l].m
         np2 = 1 << max(n - 1, 0).bit_length()
-        fl = _fr_from_u64(ctx, l)
-        seeds = np.stack([tr_hash_fields_tagged(ctx, b"FRI/index", np.stack([roots_seed, fl, _fr_from_u64(ctx, q)])) for q in range(r)])
+        seeds = all_seeds[l]
         idx = index_from_seed(ctx, seeds, np2)
         for q in range(r):
             if idx[q] >= n:                                             # fri.rs:186-190: one re-hash, then wrap

@@ -757,6 +757,30 @@ int32_t smw_tr_hash_fields_tagged(smw_ctx* c, const uint8_t* tag, size_t tag_len
     rc = oneshot_hash(c, p, "FRI/FS", tag, tag_len, {}, i.d, n, "out", o.d); if (rc) return rc;
     return o.finish();
 }
+// `count` one-shot hashes with the same tag and k field elements each (k small: the whole pre-image fits one rate block), in ONE
+// launch — e.g. the r * L index seeds of fri_prove_queries (deep_ali/src/fri.rs:184-191, 388-400): xs is count x k, out count Fr.
+int32_t smw_tr_hash_fields_tagged_batch(smw_ctx* c, const uint8_t* tag, size_t tag_len, const void* xs, int32_t k, size_t count, int32_t mem, void* out) {
+    if (!c || (!tag && tag_len) || k < 0 || (count && ((k && !xs) || !out))) return SMW_ERR_INVALID_ARG;
+    if (count == 0) return SMW_OK;
+    cudaSetDevice(c->device);
+    smw_params* p; int rc = smw_params_transcript_default(c, &p); if (rc) return rc;
+    std::vector<Word> seq;                                  // transcript/src/lib.rs:55-101 as a lane template
+    push_absorb_bytes(seq, (const uint8_t*)"FRI/FS", 6);
+    push_absorb_bytes(seq, tag, tag_len);
+    const int lane0 = (int)seq.size();
+    for (int i = 0; i < k; i++) seq.push_back(Word{});
+    push_challenge(seq, (const uint8_t*)"out", 3);
+    if (seq.size() > 16) return set_err(c, SMW_ERR_INVALID_ARG, "batched one-shot hash: the pre-image must fit one rate block (use smw_tr_hash_fields_tagged)");
+    std::vector<Word> lanes(17, Word{});
+    for (size_t i = 0; i < seq.size(); i++) lanes[i] = seq[i];
+    lanes[16] = tag_word(TAG_INIT);
+    DevFree fr{{}, c->stream};
+    uint32_t* d_t; rc = upload_words(c, lanes, &d_t); fr.v.push_back(d_t); if (rc) return rc;
+    In i(c, xs, count * (size_t)k, mem); if (i.rc) return i.rc;
+    Out o(c, out, count, mem); if (o.rc) return o.rc;
+    rc = launch_tr_hash_batch(c, p, d_t, lane0, k, i.d, count, o.d); if (rc) return rc;
+    return o.finish();
+}
 // `count` independent one-shot hashes (e.g. the four ALI sponges of deep_ali_build_f0, deep_ali/src/fri.rs:541-548): each chain of
 // launches runs on its own side stream, so the strictly serial sponges overlap each other.  xs[i]: n[i] elements; out: count Fr (host).
 int32_t smw_tr_hash_fields_tagged_many(smw_ctx* c, int32_t count, const uint8_t* const* tags, const size_t* tag_lens, const void* const* xs, const size_t* n,

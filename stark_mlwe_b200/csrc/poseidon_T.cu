@@ -478,6 +478,14 @@ int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* ctrp, const uint3
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
+int launch_tr_hash_batch(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, int lane0, int k, const uint32_t* d_xs, size_t count, uint32_t* d_out) {
+    if (count == 0) return SMW_OK;
+    if (trp->t != 17 || !trp->d_tables52) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "transcript is fixed at t = 17");
+    k_tr_hash_batch_coop52<<<(unsigned)count, 32, 0, c->stream>>>(d_tmpl, lane0, k, d_xs, count, d_out, trp->d_tables52, coop_tab(trp));
+    c->launches++;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
 int launch_legacy_nodes(smw_ctx* c, const smw_params* p, int mode, const uint32_t* d_src, const uint32_t* d_cp, size_t n_src, const uint64_t* d_idx, const uint8_t* d_cnt,
                         size_t n_out, const uint32_t* d_tag, uint32_t* d_out) {
     if (n_out == 0) return SMW_OK;

@@ -145,6 +145,26 @@ k_legacy_nodes_coop52(int mode, const uint32_t* __restrict__ src, const uint32_t
     if (lane == 0) emit_ext52(e, out + g * 8);
 }
 
+// `count` one-shot transcript hashes that share label, tag and challenge and differ in their k field elements
+// (tr_hash_fields_tagged, deep_ali/src/fri.rs:28-36, e.g. every index seed of the query phase, :184-191), one warp each: the
+// pre-image template (tags and label words, 256-bit little-endian integers; all of it fits the 16-lane rate, so ONE permutation)
+// with the item's k elements dropped into lanes lane0 .. lane0 + k - 1.
+__global__ void __launch_bounds__(32)
+k_tr_hash_batch_coop52(const uint32_t* __restrict__ tmpl_le256, int lane0, int k, const uint32_t* __restrict__ xs, size_t count, uint32_t* __restrict__ out,
+                       const uint32_t* __restrict__ tbl, CoopTab L) {
+    __shared__ __align__(16) double sh[17 * 6];
+    const int lane = threadIdx.x; const size_t g = blockIdx.x;
+    if (g >= count) return;
+    CoopCx<17, 32> c{tbl, L, sh, lane, 0};
+    F52 raw = f52_zero(), cst = c.tab(L.k_rr);
+    if (lane >= lane0 && lane < lane0 + k) { raw = raw_ext52(xs + (g * (size_t)k + (size_t)(lane - lane0)) * 8); cst = c.tab(L.k_in); }
+    else if (lane < 17) raw = raw_ext52(tmpl_le256 + (size_t)lane * 8);
+    F52 s = coop_mr(raw, cst, f52_zero());
+    s = coop_perm<17, 32>(c, s);
+    const F52 e = coop_mr(s, c.tab(L.k_out), f52_zero());
+    if (lane == 0) emit_ext52(e, out + g * 8);
+}
+
 // fri_sample_z_ell (deep_ali/src/fri.rs:59-82) for all L levels at once, one warp per level: the warp hashes the level's template
 // (one permutation), lane 0 seeds ChaCha12 with the canonical bytes of the digest and takes the first u64 c with c != 0, c^n != 1.
 __global__ void __launch_bounds__(32)

@@ -184,6 +184,8 @@ int launch_hash_groups(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, 
 // legacy-sponge nodes, one warp each: mode 0 chunks of 16 of d_src, 1 pairs (d_src[g], d_cp[g]), 2 gathered pool entries (d_idx rows of 16, d_cnt)
 int launch_legacy_nodes(smw_ctx* c, const smw_params* p, int mode, const uint32_t* d_src, const uint32_t* d_cp, size_t n_src, const uint64_t* d_idx, const uint8_t* d_cnt,
                         size_t n_out, const uint32_t* d_tag, uint32_t* d_out);
+// count one-shot hashes sharing a 17-lane template (LE256 words), item i's k elements in lanes lane0.. : one warp and one permutation each
+int launch_tr_hash_batch(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, int lane0, int k, const uint32_t* d_xs, size_t count, uint32_t* d_out);
 int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
 // several runs of one level in one launch (explicit device segment array); all runs share the parameter set and the arity
 int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);

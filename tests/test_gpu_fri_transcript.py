@@ -221,3 +221,15 @@ def test_deep_ali_merge_matches_oracle(ctx, smw, O, rnd):
     omega, z = O.root_of_unity(10), rnd(5, 1)[0]
     f0, _ = O.deep_ali_merge_evals(a, s, e, t, omega, z)
     assert eq(smw.deep_ali_merge_evals(ctx, a, s, e, t, omega, z), f0)
+
+
+@pytest.mark.parametrize("k,count", [(3, 96), (1, 5), (2, 1), (6, 40)])
+def test_tr_hash_fields_tagged_batch_matches_oracle(ctx, smw, O, rnd, k, count):
+    """count one-shot hashes in one launch (the index seeds of fri_prove_queries, deep_ali/src/fri.rs:184-191) against the
+    oracle's tr_hash_fields_tagged one by one; a pre-image beyond one rate block is refused"""
+    xs = rnd(31 * k + count, count * k).reshape(count, k, 4)
+    got = smw.tr_hash_fields_tagged_batch(ctx, b"FRI/index", xs)
+    for i in range(count):
+        assert eq(got[i], O.tr_hash_fields_tagged(b"FRI/index", xs[i])), i
+    with pytest.raises(smw.SmwError):
+        smw.tr_hash_fields_tagged_batch(ctx, b"FRI/index", rnd(1, 12).reshape(1, 12, 4))

@@ -61,6 +61,7 @@ def test_single_rank_forms_equal_the_plain_calls(ctx, smw, O, rnd):
     assert all(np.array_equal(x, y) for x, y in zip(a, b))
     x = rnd(6, 1 << 10)
     t = torch.from_numpy(x.view(np.int64).copy()).cuda()
+    torch.cuda.synchronize()                 # the context runs on its own stream: the copy must have landed
     out = smw.ntt_cyclic_to_chunks(ctx, None, t, 10)
     ctx.sync()
     assert np.array_equal(out.cpu().numpy().view(np.uint64)[0], O.ntt(x))

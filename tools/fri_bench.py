@@ -10,7 +10,8 @@ import torch
 from stark_mlwe_b200 import api as smw
 from bench import gen_columns
 
-ctx = smw.Context(0, stream=torch.cuda.current_stream().cuda_stream)
+_st = torch.cuda.Stream(); torch.cuda.set_stream(_st)
+ctx = smw.Context(0, stream=_st.cuda_stream)       # torch's work and the library's share one explicit stream
 out = {}
 for name, k, sched in (("cfg3_fold2_2p22", 22, [2] * 22), ("paper_16_16_8_2p22", 22, [16, 16, 8]), ("paper_16_16_8_2p18", 18, [16, 16, 8])):
     f0 = torch.from_numpy(gen_columns(0x5EED0003, 0, 1, 1 << k)[0].view(np.int64)).cuda()

@@ -9,7 +9,8 @@ import torch
 from stark_mlwe_b200 import api as smw
 from bench import gen_columns_torch
 
-ctx = smw.Context(0, stream=torch.cuda.current_stream().cuda_stream)
+_st = torch.cuda.Stream(); torch.cuda.set_stream(_st)
+ctx = smw.Context(0, stream=_st.cuda_stream)       # torch's work and the library's share one explicit stream
 out = {}
 for k in (12, 16, 20, 22):
     table = gen_columns_torch(0x5EED0006, 0, 1, 1 << k, "cuda")[0]

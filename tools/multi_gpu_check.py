@@ -23,7 +23,8 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 if world > 1:
     dist.init_process_group("nccl", device_id=dev)
-ctx = smw.Context(local, stream=torch.cuda.current_stream().cuda_stream)
+_st = torch.cuda.Stream(); torch.cuda.set_stream(_st)
+ctx = smw.Context(local, stream=_st.cuda_stream)       # torch's work and the library's share one explicit stream
 comm = shard.make_comm(ctx)
 res = {"world": world, "checks": []}
 
