@@ -11,11 +11,12 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-BUILD = os.path.join(HERE, "build")
-SO = os.path.join(HERE, "libsmw.so")
+BUILD = os.path.join(HERE, os.environ.get("SMW_BUILD_DIR", "build"))
+SO = os.path.join(HERE, os.environ.get("SMW_BUILD_SO", "libsmw.so"))      # SMW_BUILD_SO / SMW_BUILD_DIR / SMW_EXTRA_FLAGS: tuning builds beside the product library
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-ccbin", "/usr/bin/g++", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
+FLAGS += os.environ.get("SMW_EXTRA_FLAGS", "").split()
 WIDTHS = [9, 17, 33, 65, 129]
 
 

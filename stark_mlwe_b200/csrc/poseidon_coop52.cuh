@@ -29,19 +29,25 @@ static inline CoopTab coop_tab(const smw_params* p) {
     return CoopTab{L.mds, L.rc_full, L.rc_part, L.sp_row, L.sp_col, L.post, L.k_in, L.k_out, L.k_rr, L.k_one, p->rp};
 }
 
+// SMW_COOP_INLINE (tuning builds): the same bodies inlined at every call site
+#ifdef SMW_COOP_INLINE
+#define SMW_COOP_FN static __device__ __forceinline__
+#else
+#define SMW_COOP_FN static __device__ __noinline__
+#endif
 // r = (a b + M p) / 2^260 + s : one multiplication slot.  noinline: ~15 call sites share one ~350-instruction body, which
 // keeps the whole permutation inside the instruction cache (a lone warp has no other warp to hide a miss behind).
-static __device__ __noinline__ F52 coop_mr(F52 a, F52 b, F52 s) {
+SMW_COOP_FN F52 coop_mr(F52 a, F52 b, F52 s) {
     Acc52 A; acc52_mul(A, a, b);
     return acc52_reduce_add2(A, 1, s, f52_zero());
 }
 // r = (a^2 + M p) / 2^260 (15 limb products): the two squarings of every S-box
-static __device__ __noinline__ F52 coop_sq(F52 a) {
+SMW_COOP_FN F52 coop_sq(F52 a) {
     Acc52 A; acc52_sqr(A, a);
     return acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
 }
 // r = (a1 b1 + a2 b2 + M p) / 2^260 + s
-static __device__ __noinline__ F52 coop_mr2(F52 a1, F52 b1, F52 a2, F52 b2, F52 s) {
+SMW_COOP_FN F52 coop_mr2(F52 a1, F52 b1, F52 a2, F52 b2, F52 s) {
     Acc52 A; acc52_mul(A, a1, b1); acc52_mac(A, a2, b2);
     return acc52_reduce_add2(A, 2, s, f52_zero());
 }
