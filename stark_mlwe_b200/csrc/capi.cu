@@ -694,17 +694,26 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
 }
 
 // ---------------------------------------------------------------------------------------- transcript
+// immediates of one transcript call -> the transcript's own device scratch (64 words) or, for a very long label, a temporary
+static int tr_words(smw_transcript* t, const std::vector<Word>& w, uint32_t** d, bool* temp) {
+    smw_ctx* c = t->ctx; *temp = false; *d = t->d_imm;
+    if (w.empty()) return SMW_OK;
+    if (w.size() > 64) { *temp = true; return upload_words(c, w, d); }
+    SMW_CUDA(c, cudaMemcpyAsync(t->d_imm, w.data(), w.size() * FR, cudaMemcpyHostToDevice, c->stream));      // pageable source: staged before the call returns
+    return SMW_OK;
+}
 int32_t smw_transcript_new(smw_ctx* c, const uint8_t* label, size_t len, smw_params* params, smw_transcript** out) {
     if (!c || !out || (!label && len)) return SMW_ERR_INVALID_ARG;
     cudaSetDevice(c->device);
     smw_params* p; int rc = get_transcript_params(c, params, &p); if (rc) return rc;
     auto t = std::make_unique<smw_transcript>(); t->ctx = c; t->params = p;
-    SMW_CUDA(c, cudaMalloc(&t->d_state, 17 * FR));
+    SMW_CUDA(c, cudaMalloc(&t->d_state, (17 + 64 + 1) * FR));
+    t->d_imm = t->d_state + 17 * 8; t->d_out = t->d_imm + 64 * 8;
     std::vector<Word> A; A.push_back(tag_word(TAG_INIT)); push_absorb_bytes(A, label, len);
-    uint32_t* dA; rc = upload_words(c, A, &dA); if (rc) { cudaFree(t->d_state); return rc; }
+    uint32_t* dA; bool temp; rc = tr_words(t.get(), A, &dA, &temp); if (rc) { cudaFree(t->d_state); return rc; }
     rc = launch_transcript_run(c, p, t->d_state, 1, 0, dA, (int)A.size(), nullptr, 0, nullptr, 0, 0, nullptr);
-    cudaStreamSynchronize(c->stream); cudaFree(dA);
-    if (rc) { cudaFree(t->d_state); return rc; }
+    if (temp) { cudaStreamSynchronize(c->stream); cudaFree(dA); }
+    if (rc) { cudaStreamSynchronize(c->stream); cudaFree(t->d_state); return rc; }
     t->pos = advance_pos(0, A.size() - 1);
     *out = t.release(); return SMW_OK;
 }
@@ -712,9 +721,9 @@ int32_t smw_transcript_absorb_bytes(smw_transcript* t, const uint8_t* bytes, siz
     if (!t || (!bytes && len)) return SMW_ERR_INVALID_ARG;
     smw_ctx* c = t->ctx; cudaSetDevice(c->device);
     std::vector<Word> A; push_absorb_bytes(A, bytes, len);
-    uint32_t* dA; int rc = upload_words(c, A, &dA); if (rc) return rc;
+    uint32_t* dA; bool temp; int rc = tr_words(t, A, &dA, &temp); if (rc) return rc;
     rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, dA, (int)A.size(), nullptr, 0, nullptr, 0, 0, nullptr);
-    cudaStreamSynchronize(c->stream); cudaFree(dA);
+    if (temp) { cudaStreamSynchronize(c->stream); cudaFree(dA); }
     if (!rc) t->pos = advance_pos(t->pos, A.size());
     return rc;
 }
@@ -733,11 +742,10 @@ int32_t smw_transcript_challenge(smw_transcript* t, const uint8_t* label, size_t
     if (!t || !out_host || (!label && len)) return SMW_ERR_INVALID_ARG;
     smw_ctx* c = t->ctx; cudaSetDevice(c->device);
     std::vector<Word> A; push_challenge(A, label, len);
-    uint32_t *dA, *d_out; int rc = upload_words(c, A, &dA); if (rc) return rc;
-    SMW_CUDA(c, cudaMalloc(&d_out, FR));
-    rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, dA, (int)A.size(), nullptr, 0, nullptr, 0, 1, d_out);
-    if (!rc) rc = d2h(c, out_host, d_out, FR);
-    cudaStreamSynchronize(c->stream); cudaFree(dA); cudaFree(d_out);
+    uint32_t* dA; bool temp; int rc = tr_words(t, A, &dA, &temp); if (rc) return rc;
+    rc = launch_transcript_run(c, t->params, t->d_state, 0, t->pos, dA, (int)A.size(), nullptr, 0, nullptr, 0, 1, t->d_out);
+    if (!rc) rc = d2h(c, out_host, t->d_out, FR);          // the one synchronisation: the challenge goes to the host
+    if (temp) { cudaStreamSynchronize(c->stream); cudaFree(dA); }
     if (!rc) t->pos = 0;
     return rc;
 }

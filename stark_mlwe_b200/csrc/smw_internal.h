@@ -93,7 +93,9 @@ struct smw_comm {
 struct smw_transcript {
     smw_ctx* ctx = nullptr;
     smw_params* params = nullptr;
-    uint32_t* d_state = nullptr;      // 17 elements, external form
+    uint32_t* d_state = nullptr;      // 17 elements, external form; followed in the same allocation by 64 immediate words and one output slot
+    uint32_t* d_imm = nullptr;        // scratch for the 256-bit immediates of one call (tags, label words): no allocation per absorb / challenge
+    uint32_t* d_out = nullptr;
     int pos = 0;                      // rate cursor: a function of the call sequence only, so tracked on the host
 };
 
