@@ -670,25 +670,29 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
         }
         if (e != cudaSuccess) { cleanup(); return cuda_err(c, e, "smw_lde_commit staging"); }
     }
-    auto enqueue_copy = [&](int ci) {      // host columns of range ci -> d_in[ci & 1] on the copy stream
+    auto enqueue_copy = [&](int ci) -> cudaError_t {      // host columns of range ci -> d_in[ci & 1] on the copy stream
         const int c0 = ranges[ci].first, nc = ranges[ci].second;
-        if (ci >= 2) cudaStreamWaitEvent(copy, consumed[ci & 1], 0);
-        cudaMemcpyAsync(d_in[ci & 1], (const uint8_t*)cols + (size_t)c0 * n * FR, (size_t)nc * n * FR, cudaMemcpyHostToDevice, copy);
-        cudaEventRecord(copied[ci & 1], copy);
+        cudaError_t er = cudaSuccess;
+        if (ci >= 2) er = cudaStreamWaitEvent(copy, consumed[ci & 1], 0);
+        if (er == cudaSuccess) er = cudaMemcpyAsync(d_in[ci & 1], (const uint8_t*)cols + (size_t)c0 * n * FR, (size_t)nc * n * FR, cudaMemcpyHostToDevice, copy);
+        if (er == cudaSuccess) er = cudaEventRecord(copied[ci & 1], copy);
+        return er;
     };
-    if (host) enqueue_copy(0);
-    for (int ci = 0; ci < n_chunks && !rc; ci++) {
+    if (host) e = enqueue_copy(0);
+    for (int ci = 0; ci < n_chunks && !rc && e == cudaSuccess; ci++) {
         const int c0 = ranges[ci].first, nc = ranges[ci].second;
         const uint32_t* src;
         if (host) {
-            if (ci + 1 < n_chunks) enqueue_copy(ci + 1);
-            cudaStreamWaitEvent(c->stream, copied[ci & 1], 0);
+            if (ci + 1 < n_chunks) e = enqueue_copy(ci + 1);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, copied[ci & 1], 0);
+            if (e != cudaSuccess) break;
             src = d_in[ci & 1];
         } else src = (const uint32_t*)cols + (size_t)c0 * n * 8;
         rc = launch_lde(c, src, log_n, log_blowup, g.d, d_ext, nc);
-        if (host) cudaEventRecord(consumed[ci & 1], c->stream);
-        if (!rc) rc = smw_merkle_commit_columns(c, p, 16, label0 + (uint64_t)c0, 1, d_ext, N, nc, SMW_DEVICE, (uint8_t*)roots_out_host + (size_t)c0 * FR);
+        if (host && !rc) e = cudaEventRecord(consumed[ci & 1], c->stream);
+        if (!rc && e == cudaSuccess) rc = smw_merkle_commit_columns(c, p, 16, label0 + (uint64_t)c0, 1, d_ext, N, nc, SMW_DEVICE, (uint8_t*)roots_out_host + (size_t)c0 * FR);
     }
+    if (!rc && e != cudaSuccess) rc = cuda_err(c, e, "smw_lde_commit: staged host copy (cudaMemcpyAsync / cudaStreamWaitEvent / cudaEventRecord)");
     cleanup();
     return rc;
 }

@@ -210,9 +210,10 @@ int launch_ntt(smw_ctx* c, uint32_t* d_buf, int log_n, int inverse, int n_cols, 
     if (log_n == 0 || n_cols == 0) return SMW_OK;
     int rc = run_passes(c, d_buf, log_n, true, inverse, 0, n_cols, col_stride); if (rc) return rc;
     const size_t n = (size_t)1 << log_n;
-    uint32_t *d_scale = nullptr, *pow2 = nullptr;
-    if (inverse) {   // 1/n: the g-power table kernel with g = pow2[0] = 1 gives lo[0] = 1/n
-        SMW_CUDA(c, cudaMalloc(&pow2, 33 * 32)); SMW_CUDA(c, cudaMalloc(&d_scale, 1025 * 32));
+    uint32_t *d_scale = nullptr;
+    if (inverse) {   // 1/n: the g-power table kernel with g = pow2[0] = 1 gives lo[0] = 1/n; tables in a context scratch slot (no allocation, no sync per call)
+        void* q; rc = ctx_scratch(c, smw_ctx::SLOT_NTT_SCALE, (size_t)(33 + 1025) * 32, &q); if (rc) return rc;
+        uint32_t* pow2 = (uint32_t*)q; d_scale = pow2 + 33 * 8;
         k_pow2_roots<<<1, 32, 0, c->stream>>>(pow2);
         k_gpow_tables<<<4, 256, 0, c->stream>>>(pow2, log_n, d_scale, d_scale + 8 * 1024, 1);
         c->launches += 2;
@@ -220,7 +221,6 @@ int launch_ntt(smw_ctx* c, uint32_t* d_buf, int log_n, int inverse, int n_cols, 
     k_bitrev_scale<<<dim3((unsigned)((n + 255) / 256), n_cols), 256, 0, c->stream>>>(d_buf, log_n, d_scale, col_stride);
     c->launches++;
     SMW_CUDA(c, cudaGetLastError());
-    if (inverse) { SMW_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(pow2); cudaFree(d_scale); }
     return SMW_OK;
 }
 

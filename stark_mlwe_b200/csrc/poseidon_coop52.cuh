@@ -29,14 +29,15 @@ static inline CoopTab coop_tab(const smw_params* p) {
     return CoopTab{L.mds, L.rc_full, L.rc_part, L.sp_row, L.sp_col, L.post, L.k_in, L.k_out, L.k_rr, L.k_one, p->rp};
 }
 
-// SMW_COOP_INLINE (tuning builds): the same bodies inlined at every call site
-#ifdef SMW_COOP_INLINE
-#define SMW_COOP_FN static __device__ __forceinline__
-#else
+// The multiplication slots are inlined at their ~15 call sites (the whole permutation is ~90 KB of code): measured 11 % faster than
+// one shared noinline body (proof_bytes KAT k = 18: 3.52 -> 3.14 s, profiles/r02h_kat*.log) — the call overhead (30 operand
+// registers in, 10 out) outweighs the instruction-cache footprint for a lone warp.  SMW_COOP_NOINLINE selects the shared body.
+#ifdef SMW_COOP_NOINLINE
 #define SMW_COOP_FN static __device__ __noinline__
+#else
+#define SMW_COOP_FN static __device__ __forceinline__
 #endif
-// r = (a b + M p) / 2^260 + s : one multiplication slot.  noinline: ~15 call sites share one ~350-instruction body, which
-// keeps the whole permutation inside the instruction cache (a lone warp has no other warp to hide a miss behind).
+// r = (a b + M p) / 2^260 + s : one multiplication slot (~350 instructions)
 SMW_COOP_FN F52 coop_mr(F52 a, F52 b, F52 s) {
     Acc52 A; acc52_mul(A, a, b);
     return acc52_reduce_add2(A, 1, s, f52_zero());

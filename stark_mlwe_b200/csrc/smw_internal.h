@@ -58,7 +58,7 @@ struct smw_ctx {
     uint32_t* d_twiddles = nullptr;              // w_N^i, i < N/2, external Montgomery form
     int twiddle_log_n = 0;
     // grow-only device scratch slots reused across calls (cudaMalloc/cudaFree of GB-sized buffers cost ~100 ms per chunk)
-    enum { SLOT_LDE_COEF = 0, SLOT_LDE_G, SLOT_TREE_A, SLOT_TREE_B, SLOT_EXT, SLOT_IN0, SLOT_IN1, N_SLOTS };
+    enum { SLOT_LDE_COEF = 0, SLOT_LDE_G, SLOT_TREE_A, SLOT_TREE_B, SLOT_EXT, SLOT_IN0, SLOT_IN1, SLOT_NTT_SCALE, N_SLOTS };
     void* slot_ptr[N_SLOTS] = {}; size_t slot_bytes[N_SLOTS] = {};
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
     // side streams for independent launch chains (the per-layer trees of a FRI commit phase), joined back into `stream`

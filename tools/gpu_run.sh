@@ -33,7 +33,7 @@ for stage in "$@"; do
                 done ;;
     mgpu*)      N=${stage#mgpu}; timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py > $OUT/${TAG}_multi_gpu_check_n$N.json 2> $OUT/${TAG}_multi_gpu_check_n$N.err; cat $OUT/${TAG}_multi_gpu_check_n$N.json; tail -8 $OUT/${TAG}_multi_gpu_check_n$N.err ;;
     scale*)     N=${stage#scale}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N > $OUT/${TAG}_bench_n$N.json 2> $OUT/${TAG}_bench_n$N.err; tail -c 2500 $OUT/${TAG}_bench_n$N.json; tail -5 $OUT/${TAG}_bench_n$N.err ;;
-    kat_inline) SMW_LIB=$PWD/stark_mlwe_b200/libsmw_coop_inline.so timeout 900 python -m pytest tests/test_gpu_proof_bytes_kat.py -m gpu -q --durations=4 > $OUT/${TAG}_kat_inline.log 2>&1; tail -8 $OUT/${TAG}_kat_inline.log ;;
+
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
     e2e*)       K=${stage#e2e}; timeout 1700 python tools/deep_fri_e2e.py $K > $OUT/${TAG}_deep_fri_e2e_2p$K.json 2> $OUT/${TAG}_deep_fri_e2e_2p$K.err; cat $OUT/${TAG}_deep_fri_e2e_2p$K.json; tail -5 $OUT/${TAG}_deep_fri_e2e_2p$K.err ;;
     *) echo "unknown stage $stage" ;;
