@@ -132,6 +132,48 @@ SMW_DEV F52 acc52_reduce_add2(Acc52& A, uint32_t n_terms, const F52& s, const F5
     }
     return r;
 }
+// The same reduction with a SHORTER DEPENDENCY CHAIN, for the cooperative (latency-bound, one lone warp) kernels: the quotient
+// digit m = -c_i / p mod 2^52 and the low halves of m * p_j come from 64-bit integer multiplies (IMAD.WIDE + 2 IMAD, ~5 cycles each,
+// running beside the FP64 pipe), only the high halves floor(m p_j / 2^52) stay on DFMA.RZ.  Per step the chain to the next column is
+// ~9 integer operations instead of ~14 operations of which 8 are dependent FP64 instructions; the instruction count is higher
+// (~225 against ~160), which is why the throughput-bound batch interpreter keeps acc52_reduce_add2.  Same value, bit for bit.
+SMW_DEV F52 acc52_reduce_add2_lat(Acc52& A, uint32_t n_terms, const F52& s, const F52& t) {
+    constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
+    constexpr uint32_t rhi[10] = {0, 1, 2, 3, 3, 3, 2, 1, 0, 0};          // high-half patterns (0x467 << 52) the five steps add to column k; low halves are plain integers here
+#pragma unroll
+    for (int k = 0; k < 10; k++) {
+        const uint32_t per_term = (nlo[k] * 0x433u + nhi[k] * 0x467u) << 20;
+        const uint32_t fixed = (rhi[k] * 0x467u + (k >= 5 ? 2u * 0x433u : 0u)) << 20;
+        const uint32_t h = (uint32_t)(A.c[k] >> 32) - (per_term * n_terms + fixed);
+        A.c[k] = (A.c[k] & 0xffffffffull) | ((uint64_t)h << 32);
+    }
+#pragma unroll
+    for (int i = 0; i < 5; i++)
+        A.c[5 + i] += (uint64_t)__double_as_longlong(s.v[i] + 0x1p52) + (uint64_t)__double_as_longlong(t.v[i] + 0x1p52);
+    const double p0 = (double)P52_0, p1 = (double)P52_1, p2 = (double)P52_2;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        const uint64_t m = (A.c[i] * PINV52) & M52;                       // only the low 52 bits of the column matter
+        const double md = u52_to_double(m);
+        const uint64_t h0 = (uint64_t)__double_as_longlong(__fma_rz(md, p0, 0x1p104)), h1 = (uint64_t)__double_as_longlong(__fma_rz(md, p1, 0x1p104)),
+                       h2 = (uint64_t)__double_as_longlong(__fma_rz(md, p2, 0x1p104));
+        const uint64_t l0 = (m * P52_0) & M52, l1 = (m * P52_1) & M52, l2 = (m * P52_2) & M52;
+        A.c[i] += l0;                                                                      // low 52 bits are now zero
+        A.c[i + 1] += h0 + l1 + (A.c[i] >> 52);
+        A.c[i + 2] += h1 + l2;
+        A.c[i + 3] += h2;
+        A.c[i + 4] += (m & 63ull) << 46;                                                   // m * 2^46 = (m >> 6) 2^52 + (m & 63) 2^46
+        A.c[i + 5] += m >> 6;
+    }
+    F52 r; uint64_t carry = 0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const uint64_t v = A.c[5 + k] + carry;
+        r.v[k] = u52_to_double(k < 4 ? (v & M52) : v);
+        carry = v >> 52;
+    }
+    return r;
+}
 SMW_DEV F52 f52_mul(const F52& a, const F52& b) { Acc52 A; acc52_mul(A, a, b); return acc52_reduce_add2(A, 1, f52_zero(), f52_zero()); }
 
 // ---- boundary conversions -------------------------------------------------------------------

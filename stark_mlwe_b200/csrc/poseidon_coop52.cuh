@@ -32,6 +32,12 @@ static inline CoopTab coop_tab(const smw_params* p) {
 // The multiplication slots are inlined at their ~15 call sites (the whole permutation is ~90 KB of code): measured 11 % faster than
 // one shared noinline body (proof_bytes KAT k = 18: 3.52 -> 3.14 s, profiles/r02h_kat*.log) — the call overhead (30 operand
 // registers in, 10 out) outweighs the instruction-cache footprint for a lone warp.  SMW_COOP_NOINLINE selects the shared body.
+// SMW_COOP_REDUCE_FP64 (tuning builds): the batch kernels' all-FP64 reduction instead of the short-chain one (fr52.cuh)
+#ifdef SMW_COOP_REDUCE_FP64
+#define COOP_REDUCE acc52_reduce_add2
+#else
+#define COOP_REDUCE acc52_reduce_add2_lat
+#endif
 #ifdef SMW_COOP_NOINLINE
 #define SMW_COOP_FN static __device__ __noinline__
 #else
@@ -40,17 +46,22 @@ static inline CoopTab coop_tab(const smw_params* p) {
 // r = (a b + M p) / 2^260 + s : one multiplication slot (~350 instructions)
 SMW_COOP_FN F52 coop_mr(F52 a, F52 b, F52 s) {
     Acc52 A; acc52_mul(A, a, b);
-    return acc52_reduce_add2(A, 1, s, f52_zero());
+    return COOP_REDUCE(A, 1, s, f52_zero());
+}
+// r = (a b + M p) / 2^260 + s + t
+SMW_COOP_FN F52 coop_mr_t(F52 a, F52 b, F52 s, F52 t) {
+    Acc52 A; acc52_mul(A, a, b);
+    return COOP_REDUCE(A, 1, s, t);
 }
 // r = (a^2 + M p) / 2^260 (15 limb products): the two squarings of every S-box
 SMW_COOP_FN F52 coop_sq(F52 a) {
     Acc52 A; acc52_sqr(A, a);
-    return acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
+    return COOP_REDUCE(A, 1, f52_zero(), f52_zero());
 }
 // r = (a1 b1 + a2 b2 + M p) / 2^260 + s
 SMW_COOP_FN F52 coop_mr2(F52 a1, F52 b1, F52 a2, F52 b2, F52 s) {
     Acc52 A; acc52_mul(A, a1, b1); acc52_mac(A, a2, b2);
-    return acc52_reduce_add2(A, 2, s, f52_zero());
+    return COOP_REDUCE(A, 2, s, f52_zero());
 }
 SMW_DEV F52 sel52(bool c, const F52& a, const F52& b) { F52 r;
 #pragma unroll
@@ -66,6 +77,10 @@ template <int T, int G> struct CoopCx {
     SMW_DEV F52 bcast0(const F52& x) const { F52 r;                       // value of the group's lane 0, to every lane of the group
 #pragma unroll
         for (int i = 0; i < 5; i++) r.v[i] = __shfl_sync(FULL, x.v[i], 0, G);
+        return r; }
+    SMW_DEV F52 bcast(const F52& x, int src) const { F52 r;             // value of the group's lane `src`, to every lane of the group
+#pragma unroll
+        for (int i = 0; i < 5; i++) r.v[i] = __shfl_sync(FULL, x.v[i], src, G);
         return r; }
     SMW_DEV void publish(int slot, const F52& x) const {
         double2* q = reinterpret_cast<double2*>(sh + slot * 6);
@@ -116,7 +131,7 @@ __device__ __noinline__ F52 coop_matvec(const CoopCx<T, G> c, F52 s, uint32_t ma
         if (j + 1 < n) b = c.tab(base + j + 1);
         acc52_mac(A, c.fetch(first_lane + j), bb);
     }
-    const F52 y = acc52_reduce_add2(A, (uint32_t)n, rc, f52_zero());
+    const F52 y = COOP_REDUCE(A, (uint32_t)n, rc, f52_zero());
     __syncwarp();
     return sel52(mine, y, s);
 }
@@ -139,6 +154,48 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
         if (r < 3) { if (in) rc = c.tab(L.rc_full + (uint32_t)(r + 1) * T + lc); } else if (l0) rc = c.tab(L.rc_part);
         s = coop_matvec<T, G>(c, s, L.mds, T, 0, rc);
     }
+#ifndef SMW_COOP_4SLOT
+    // Partial rounds, two per block, THREE dependent multiplication slots per round instead of four.  The serial chain of a round is
+    // l0 -> x^2 -> x^4 -> x^5 -> M00 x^5 + row . u + c; since x^5 = x^4 l0, the last two links collapse into x^4 (M00 l0) + (row . u) + c
+    // with y = M00 l0 computed by a spare lane BESIDE the first squaring, and the row products (which do not depend on this round's
+    // S-box) computed by the u lanes beside the second.  x^5 itself (needed for the rank-1 updates and the G term) is computed by
+    // another spare lane beside the last slot.  Roles: lane 0 the S-box lane, lanes 1..n hold u, lane T computes y, lane T + 1
+    // computes x^5, lane T + 2 the G term of the block's second round (T + 2 < G for both widths).
+    const bool ly = lane == T, lx = lane == T + 1, lg = lane == T + 2;
+    F52 pxa = zero, pxb = zero;                           // the previous block's S-box outputs (pending rank-1 update)
+#pragma unroll 1
+    for (int k = 0; k < L.rp; k += 2) {
+        const uint32_t rowA = L.sp_row + (uint32_t)k * (T + 1), rowB = rowA + (T + 1);
+        F52 l0b = c.bcast(s, 0);                          // the S-box input, known to the spare lanes
+        // slot A1: lane 0 squares; lane T: y = M00 l0; lanes 1..n apply the pending update u += colA x_a + colB x_b of the previous block
+        F52 ca = zero, cb = zero;
+        if (lu && k > 0) { const uint32_t q = L.sp_col + (uint32_t)((k >> 1) - 1) * 2 * n + 2 * (uint32_t)(lane - 1); ca = c.tab(q); cb = c.tab(q + 1); }
+        F52 r = coop_mr2(l0 ? s : (lu ? ca : (ly ? c.tab(rowA + (uint32_t)n) : zero)), l0 ? s : (lu ? pxa : (ly ? l0b : zero)),
+                         lu ? cb : zero, lu ? pxb : zero, lu ? s : zero);
+        F52 x2 = r, y = r; if (lu) s = r;
+        // slot B1: lane 0 squares again; lanes 1..n: row_k[j] u_j (u is not updated inside the block: the second round carries the G term)
+        r = coop_mr(l0 ? x2 : (lu ? s : zero), l0 ? x2 : (lu ? c.tab(rowA + (uint32_t)(lane - 1)) : zero), zero);
+        F52 sum = c.group_sum(sel52(lu, r, zero));
+        F52 x4b = c.bcast(r, 0), yb = c.bcast(y, T);
+        // slot C1: lane 0: l0' = x^4 y + sum + c_{k+1}; lane T + 1: x_a = x^4 l0
+        r = coop_mr_t((l0 || lx) ? x4b : zero, l0 ? yb : (lx ? l0b : zero), l0 ? sum : zero, l0 ? c.tab(L.rc_part + (uint32_t)k + 1) : zero);
+        if (l0) s = r;
+        const F52 xa = c.bcast(r, T + 1);
+        l0b = c.bcast(r, 0);
+        // second round.  slot A2: lane 0 squares; lane T: y = M00 l0'; lane T + 2: G x_a + the next constant
+        const uint32_t next_rc = (k + 2 < L.rp) ? L.rc_part + (uint32_t)k + 2 : L.rc_full + 4u * T;
+        r = coop_mr(l0 ? s : (ly ? c.tab(rowB + (uint32_t)n + 1) : (lg ? c.tab(rowB + (uint32_t)n) : zero)), l0 ? s : (ly ? l0b : (lg ? xa : zero)),
+                    lg ? c.tab(next_rc) : zero);
+        x2 = r; y = r; const F52 g = r;
+        r = coop_mr(l0 ? x2 : (lu ? s : zero), l0 ? x2 : (lu ? c.tab(rowB + (uint32_t)(lane - 1)) : zero), zero);
+        sum = c.group_sum(sel52(lu, r, zero));
+        x4b = c.bcast(r, 0); yb = c.bcast(y, T);
+        const F52 gb = c.bcast(g, T + 2);
+        r = coop_mr_t((l0 || lx) ? x4b : zero, l0 ? yb : (lx ? l0b : zero), l0 ? sum : zero, l0 ? gb : zero);
+        if (l0) s = r;
+        pxa = xa; pxb = c.bcast(r, T + 1);
+    }
+#else
     // partial rounds, two per block.  Lane 0: the S-box lane; lanes 1..n: u; lane T: the G term of the second round.
     F52 pxa = zero, pxb = zero;                           // the previous block's S-box outputs (pending rank-1 update)
 #pragma unroll 1
@@ -168,6 +225,7 @@ __device__ __noinline__ F52 coop_perm(const CoopCx<T, G> c, F52 s) {
         if (l0) s = t0;
         pxa = xa; pxb = xb;
     }
+#endif
     {   // the last block's pending update
         F52 ca = zero, cb = zero;
         if (lu) { const uint32_t q = L.sp_col + (uint32_t)((L.rp >> 1) - 1) * 2 * n + 2 * (uint32_t)(lane - 1); ca = c.tab(q); cb = c.tab(q + 1); }
