@@ -32,11 +32,14 @@ static inline CoopTab coop_tab(const smw_params* p) {
 // The multiplication slots are inlined at their ~15 call sites (the whole permutation is ~90 KB of code): measured 11 % faster than
 // one shared noinline body (proof_bytes KAT k = 18: 3.52 -> 3.14 s, profiles/r02h_kat*.log) — the call overhead (30 operand
 // registers in, 10 out) outweighs the instruction-cache footprint for a lone warp.  SMW_COOP_NOINLINE selects the shared body.
-// SMW_COOP_REDUCE_FP64 (tuning builds): the batch kernels' all-FP64 reduction instead of the short-chain one (fr52.cuh)
-#ifdef SMW_COOP_REDUCE_FP64
-#define COOP_REDUCE acc52_reduce_add2
-#else
+// SMW_COOP_REDUCE_LAT (tuning builds): the short-dependency-chain reduction of fr52.cuh (integer quotient digit and low halves).
+// Measured equal to the all-FP64 one (deep_fri_prove 2^18: 3.05 s both, profiles/r02j_ab_coop.txt): a lone warp here is bound by
+// its issue rate (~2.65 cycles per instruction), not by the five-step chain, so the shorter chain buys what its extra
+// instructions cost.  The default is the one reduction the batch kernels use as well.
+#ifdef SMW_COOP_REDUCE_LAT
 #define COOP_REDUCE acc52_reduce_add2_lat
+#else
+#define COOP_REDUCE acc52_reduce_add2
 #endif
 #ifdef SMW_COOP_NOINLINE
 #define SMW_COOP_FN static __device__ __noinline__
