@@ -13,6 +13,8 @@
 // bit-reversal permutation.  Twiddles w_N^i (i < N/2) are precomputed once per context.
 #include "smw_internal.h"
 #include "fr32.cuh"
+#include "fr29.cuh"
+#include <cstdlib>
 #include <algorithm>
 #include <vector>
 
@@ -102,6 +104,108 @@ template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass(uint32_t* 
         g[0] = s_lo[l]; g[1] = s_hi[l];
     }
 }
+// ------------------------------------------------------------------ the same pass on the carry-free multiplier (round 2)
+// k_ntt_pass above spends ~850 instructions per butterfly: the 8 x 32-bit CIOS product compiles to IMAD.WIDE + IADD3 / IADD3.X carry
+// pairs + shifts (322 IMAD, 248 IADD3, 91 SHF in its SASS).  Here a tile element is nine 29-bit limbs, LAZILY reduced, in the
+// caller's scale (x 2^256): the product with a twiddle kept in the internal form (w 2^261) is 81 independent IMAD.WIDE into 17 column
+// accumulators + a 45-IMAD.WIDE Montgomery reduction (-p^-1 = -1 mod 2^29: the quotient digit is a negation), fr29.cuh — and comes
+// back in the caller's scale; additions are limb-wise, subtractions add a multiple of p whose limbs dominate the subtrahend's.
+//   DIT  x = u + t, y = u + 4p - t, t = v w < 1.5 p : a value grows by <= 4p per stage, < 33p < 2^260 after <= 8 stages
+//   DIF  x = u + v (then minus a multiple of p read off the top limb: < 2.1 p again), y = (u + 4p - v) w < 1.1 p
+// A pass loads canonical elements and stores canonical elements (top-limb reduction + one conditional subtraction), so the
+// kernels between the passes (expansion, bit reversal) and the caller see the same bytes as before: results are bit-identical.
+constexpr int TW29 = 12;      // twiddle stride in words (9 used; 48 B keeps the 16-byte loads aligned)
+struct Tile29 {
+    uint4* q0; uint4* q1; uint32_t* w;
+    SMW_DEV F29 load(int i) const { const uint4 a = q0[i], b = q1[i]; F29 r; r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w; r.v[8] = w[i]; return r; }
+    SMW_DEV void store(int i, const F29& x) const { q0[i] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]); q1[i] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]); w[i] = x.v[8]; }
+};
+SMW_DEV F29 tw29_load(const uint32_t* tw, size_t idx) {
+    const uint4* q = reinterpret_cast<const uint4*>(tw + idx * TW29);
+    const uint4 a = __ldg(q), b = __ldg(q + 1); F29 r;
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w; r.v[8] = __ldg(reinterpret_cast<const uint32_t*>(q + 2));
+    return r;
+}
+// u + 4p - t with the limbs carried back below 2^29 (t: limbs < 2^29, top limb < 2^24 - 1, i.e. t < 3.9 p)
+SMW_DEV F29 f29_sub_lazy(const F29& u, const F29& t) {
+    // 4p with a borrow lent to every limb: d_0 = 4 p_0 + 2^29, d_i = 4 p_i + 2^29 - 1 (0 < i < 8), d_8 = 4 p_8 - 1 — every d_i dominates t_i
+    constexpr uint32_t D[9] = {4u + (1u << 29), 4u * P29_1 + M29, 4u * P29_2 + M29, 4u * P29_3 + M29, 4u * P29_4 + M29, M29, M29, M29, 4u * P29_8 - 1u};
+    F29 r; uint32_t c = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { const uint32_t s = u.v[i] + (D[i] - t.v[i]) + c; r.v[i] = s & M29; c = s >> 29; }
+    r.v[8] = u.v[8] + (D[8] - t.v[8]) + c;
+    return r;
+}
+// x - (q - 1) p with q = floor(x / 2^254) read off the top limb (0 when q = 0): the result is < 2 * 2^254 < 2p and >= 0
+SMW_DEV F29 f29_top_reduce(const F29& x) {
+    uint32_t q = x.v[8] >> 22; q = q ? q - 1u : 0u;
+    const uint32_t pl[9] = {1u, P29_1, P29_2, P29_3, P29_4, 0u, 0u, 0u, P29_8};
+    F29 r; long long c = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { const long long s = (long long)x.v[i] - (long long)((uint64_t)q * pl[i]) + c; r.v[i] = (uint32_t)s & M29; c = s >> 29; }
+    r.v[8] = (uint32_t)((long long)x.v[8] - (long long)((uint64_t)q * pl[8]) + c);
+    return r;
+}
+template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass29(uint32_t* data, const uint32_t* __restrict__ tw, PassArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tile_elems = 1 << a.tile_log, nthr = blockDim.x;
+    Tile29 S{reinterpret_cast<uint4*>(smem_raw), reinterpret_cast<uint4*>(smem_raw) + tile_elems, reinterpret_cast<uint32_t*>(reinterpret_cast<uint4*>(smem_raw) + 2 * tile_elems)};
+    uint32_t* col = data + (size_t)blockIdx.y * a.col_stride * 8;
+    const size_t tile = blockIdx.x, half = (size_t)1 << (a.L - 1);
+    for (int l = threadIdx.x; l < tile_elems; l += nthr) {
+        uint32_t w[8]; const uint4* g = reinterpret_cast<const uint4*>(col + tile_global(a, tile, l) * 8);
+        const uint4 x = g[0], y = g[1];
+        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w; w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
+        S.store(l, f29_repack_from32(w));
+    }
+    __syncthreads();
+    const int nstages = a.s_end - a.s_begin;
+    for (int st = 0; st < nstages; st++) {
+        const int s = DIF ? (a.s_end - 1 - st) : (a.s_begin + st);
+        const int lb = s - a.lo + a.c;                 // local bit position of global bit s
+        for (int b = threadIdx.x; b < tile_elems / 2; b += nthr) {
+            const int i0 = ((b >> lb) << (lb + 1)) | (b & ((1 << lb) - 1)), i1 = i0 | (1 << lb);
+            const size_t gi = tile_global(a, tile, i0);
+            const size_t e = (gi & (((size_t)1 << s) - 1)) << (a.L - 1 - s);
+            // forward: w^e.  inverse: w^-e = -w^(N/2 - e) for e > 0 — the sign goes into the order of the subtraction
+            const bool neg = a.inverse && e != 0;
+            const F29 w = tw29_load(tw, (neg ? half - e : e) << a.tw_shift);
+            const F29 u = S.load(i0), v = S.load(i1);
+            if (DIF) {
+                const F29 x = f29_top_reduce(f29_add(u, v));
+                const F29 d = neg ? f29_sub_lazy(v, u) : f29_sub_lazy(u, v);
+                Acc A; acc_mul(A, d, w);
+                S.store(i0, x); S.store(i1, acc_reduce(A));
+            } else {
+                Acc A; acc_mul(A, v, w);
+                const F29 t = acc_reduce(A);
+                const F29 p = f29_add(u, t), m = f29_sub_lazy(u, t);
+                S.store(i0, neg ? m : p); S.store(i1, neg ? p : m);
+            }
+        }
+        __syncthreads();
+    }
+    for (int l = threadIdx.x; l < tile_elems; l += nthr) {
+        uint32_t w[8]; f29_repack_to32(f29_canonicalize(f29_top_reduce(S.load(l))), w);
+        uint4* g = reinterpret_cast<uint4*>(col + tile_global(a, tile, l) * 8);
+        g[0] = make_uint4(w[0], w[1], w[2], w[3]); g[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
+}
+// ext twiddles (w 2^256, canonical) -> internal form (w 2^261, canonical limbs), 48-byte stride
+__global__ void k_twiddles_to29(const uint32_t* ext, size_t n, uint32_t* out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t w[8]; const uint4* g = reinterpret_cast<const uint4*>(ext + i * 8);
+    const uint4 x = g[0], y = g[1];
+    w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w; w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
+    const F29 r = f29_canonicalize(f29_from_ext(w));
+    uint32_t* q = out + i * TW29;
+#pragma unroll
+    for (int k = 0; k < 9; k++) q[k] = r.v[k];
+    q[9] = 0; q[10] = 0; q[11] = 0;
+}
+static bool ntt_use29() { static int v = -1; if (v < 0) { const char* e = getenv("SMW_NTT"); v = (e && atoi(e) == 32) ? 0 : 1; } return v == 1; }   // SMW_NTT=32: the CIOS kernel (A/B)
+
 SMW_DEV size_t bitrev(size_t x, int bits) { return bits == 0 ? 0 : (size_t)(__brevll((unsigned long long)x) >> (64 - bits)); }
 // in-place bit-reversal permutation, optionally scaled (scale == nullptr: none)
 __global__ void k_bitrev_scale(uint32_t* data, int L, const uint32_t* scale, size_t col_stride) {
@@ -152,13 +256,22 @@ int ensure_twiddles(smw_ctx* c, int log_n) {
     if (log_n > 32) return set_err(c, SMW_ERR_INVALID_ARG, "NTT size exceeds the field's two-adicity (2^32)");
     if (c->d_twiddles) { cudaStreamSynchronize(c->stream); cudaFree(c->d_twiddles); c->d_twiddles = nullptr; }
     size_t half = (size_t)1 << (log_n - 1);
-    uint32_t* pow2;
+    uint32_t *pow2, *ext;
     SMW_CUDA(c, cudaMalloc(&pow2, 33 * 32));
-    SMW_CUDA(c, cudaMalloc(&c->d_twiddles, half * 32));
+    SMW_CUDA(c, cudaMalloc(&ext, half * 32));
     k_pow2_roots<<<1, 32, 0, c->stream>>>(pow2);
-    k_twiddles<<<(unsigned)((half + 255) / 256), 256, 0, c->stream>>>(c->d_twiddles, log_n, pow2);
+    k_twiddles<<<(unsigned)((half + 255) / 256), 256, 0, c->stream>>>(ext, log_n, pow2);
     c->launches += 2;
-    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (ntt_use29()) {        // the table the pass kernel reads: internal 29-bit form, 48-byte stride
+        cudaError_t e = cudaMalloc(&c->d_twiddles, half * TW29 * 4);
+        if (e != cudaSuccess) { cudaStreamSynchronize(c->stream); cudaFree(pow2); cudaFree(ext); return cuda_err(c, e, "cudaMalloc(twiddles)"); }
+        k_twiddles_to29<<<(unsigned)((half + 255) / 256), 256, 0, c->stream>>>(ext, half, c->d_twiddles); c->launches++;
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(ext);
+    } else {
+        SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->d_twiddles = ext;
+    }
     cudaFree(pow2);
     c->twiddle_log_n = log_n;
     return SMW_OK;
@@ -196,10 +309,16 @@ static int run_passes(smw_ctx* c, uint32_t* d, int L, bool dif, int inverse, int
         size_t tiles = ((size_t)1 << L) >> a.tile_log;
         int threads = (1 << a.tile_log) / 2; if (threads < 32) threads = 32; if (threads > 512) threads = 512;
         dim3 grid((unsigned)tiles, (unsigned)n_cols);
-        size_t sm = (size_t)32 << a.tile_log;
         LaunchScope ls(c, KC_NTT_PASS);
-        if (dif) k_ntt_pass<true><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
-        else k_ntt_pass<false><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+        if (ntt_use29()) {
+            const size_t sm = (size_t)36 << a.tile_log;
+            if (dif) k_ntt_pass29<true><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+            else k_ntt_pass29<false><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+        } else {
+            const size_t sm = (size_t)32 << a.tile_log;
+            if (dif) k_ntt_pass<true><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+            else k_ntt_pass<false><<<grid, threads, sm, c->stream>>>(d, c->d_twiddles, a);
+        }
     }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
