@@ -111,7 +111,8 @@ template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass(uint32_t* 
 // accumulators + a 45-IMAD.WIDE Montgomery reduction (-p^-1 = -1 mod 2^29: the quotient digit is a negation), fr29.cuh — and comes
 // back in the caller's scale; additions are limb-wise, subtractions add a multiple of p whose limbs dominate the subtrahend's.
 //   DIT  x = u + t, y = u + 4p - t, t = v w < 1.5 p : a value grows by <= 4p per stage, < 33p < 2^260 after <= 8 stages
-//   DIF  x = u + v (then minus a multiple of p read off the top limb: < 2.1 p again), y = (u + 4p - v) w < 1.1 p
+//   DIF  x = u + v doubles per stage: every fourth stage a multiple of p read off the top limb is taken out (< 2p again, so a
+//        value stays <= 32p); y = (u + 32p - v) w < 1.2 p
 // A pass loads canonical elements and stores canonical elements (top-limb reduction + one conditional subtraction), so the
 // kernels between the passes (expansion, bit reversal) and the caller see the same bytes as before: results are bit-identical.
 constexpr int TW29 = 12;      // twiddle stride in words (9 used; 48 B keeps the 16-byte loads aligned)
@@ -126,14 +127,17 @@ SMW_DEV F29 tw29_load(const uint32_t* tw, size_t idx) {
     r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w; r.v[8] = __ldg(reinterpret_cast<const uint32_t*>(q + 2));
     return r;
 }
-// u + 4p - t with the limbs carried back below 2^29 (t: limbs < 2^29, top limb < 2^24 - 1, i.e. t < 3.9 p)
-SMW_DEV F29 f29_sub_lazy(const F29& u, const F29& t) {
-    // 4p with a borrow lent to every limb: d_0 = 4 p_0 + 2^29, d_i = 4 p_i + 2^29 - 1 (0 < i < 8), d_8 = 4 p_8 - 1 — every d_i dominates t_i
-    constexpr uint32_t D[9] = {4u + (1u << 29), 4u * P29_1 + M29, 4u * P29_2 + M29, 4u * P29_3 + M29, 4u * P29_4 + M29, M29, M29, M29, 4u * P29_8 - 1u};
+// u + K p - t with the limbs carried back below 2^29.  K p is written with a borrow lent to every limb (d_0 = e_0 + 2^29,
+// d_i = e_i + 2^29 - 1 for 0 < i < 8, d_8 = e_8 - 1, e = the normalised limbs of K p), so that every d_i dominates t_i:
+// t needs limbs < 2^29 and a top limb <= d_8, i.e. t < 3.9 p for K = 4 and t < 31.9 p for K = 32.
+template <int K> SMW_DEV F29 f29_sub_lazy(const F29& u, const F29& t) {
+    static_assert(K == 4 || K == 32, "tables exist for 4p and 32p");
+    constexpr uint32_t D4[9]  = {0x20000004u, 0x28dd641fu, 0x34a8dd8bu, 0x34c7e04bu, 0x20000890u, 0x1fffffffu, 0x1fffffffu, 0x1fffffffu, 0x00ffffffu};
+    constexpr uint32_t D32[9] = {0x20000020u, 0x26eb20ffu, 0x2546ec61u, 0x263f0264u, 0x2000448cu, 0x1fffffffu, 0x1fffffffu, 0x1fffffffu, 0x07ffffffu};
     F29 r; uint32_t c = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) { const uint32_t s = u.v[i] + (D[i] - t.v[i]) + c; r.v[i] = s & M29; c = s >> 29; }
-    r.v[8] = u.v[8] + (D[8] - t.v[8]) + c;
+    for (int i = 0; i < 8; i++) { const uint32_t s = u.v[i] + ((K == 4 ? D4[i] : D32[i]) - t.v[i]) + c; r.v[i] = s & M29; c = s >> 29; }
+    r.v[8] = u.v[8] + ((K == 4 ? D4[8] : D32[8]) - t.v[8]) + c;
     return r;
 }
 // x - (q - 1) p with q = floor(x / 2^254) read off the top limb (0 when q = 0): the result is < 2 * 2^254 < 2p and >= 0
@@ -166,20 +170,21 @@ template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass29(uint32_t
         for (int b = threadIdx.x; b < tile_elems / 2; b += nthr) {
             const int i0 = ((b >> lb) << (lb + 1)) | (b & ((1 << lb) - 1)), i1 = i0 | (1 << lb);
             const size_t gi = tile_global(a, tile, i0);
-            const size_t e = (gi & (((size_t)1 << s) - 1)) << (a.L - 1 - s);
+            const size_t e = (size_t)(((uint32_t)gi & ((1u << s) - 1u)) << (a.L - 1 - s));     // s <= L - 1 <= 31: the masked index and the exponent (< N / 2) fit 32 bits
             // forward: w^e.  inverse: w^-e = -w^(N/2 - e) for e > 0 — the sign goes into the order of the subtraction
             const bool neg = a.inverse && e != 0;
             const F29 w = tw29_load(tw, (neg ? half - e : e) << a.tw_shift);
             const F29 u = S.load(i0), v = S.load(i1);
             if (DIF) {
-                const F29 x = f29_top_reduce(f29_add(u, v));
-                const F29 d = neg ? f29_sub_lazy(v, u) : f29_sub_lazy(u, v);
+                F29 x = f29_add(u, v);
+                if ((st & 3) == 3) x = f29_top_reduce(x);                 // inputs <= 16p here; uniform over the CTA
+                const F29 d = neg ? f29_sub_lazy<32>(v, u) : f29_sub_lazy<32>(u, v);
                 Acc A; acc_mul(A, d, w);
                 S.store(i0, x); S.store(i1, acc_reduce(A));
             } else {
                 Acc A; acc_mul(A, v, w);
                 const F29 t = acc_reduce(A);
-                const F29 p = f29_add(u, t), m = f29_sub_lazy(u, t);
+                const F29 p = f29_add(u, t), m = f29_sub_lazy<4>(u, t);
                 S.store(i0, neg ? m : p); S.store(i1, neg ? p : m);
             }
         }
