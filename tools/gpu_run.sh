@@ -36,6 +36,7 @@ for stage in "$@"; do
 
     ntt_ab)     timeout 600 python -m pytest tests/test_gpu_ntt_lde.py tests/test_gpu_full_size.py tests/test_gpu_ntt_distributed.py -m gpu -q --tb=short > $OUT/${TAG}_ntt_tests.log 2>&1; tail -5 $OUT/${TAG}_ntt_tests.log
                 for v in 29 32; do SMW_NTT=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_NTT=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_ntt_ab.txt; done ;;
+    ntt_thr)    for v in 128 64 32; do SMW_NTT_THREADS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_NTT_THREADS=$v', 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_ntt_threads.txt; done ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
     e2e*)       K=${stage#e2e}; timeout 1700 python tools/deep_fri_e2e.py $K > $OUT/${TAG}_deep_fri_e2e_2p$K.json 2> $OUT/${TAG}_deep_fri_e2e_2p$K.err; cat $OUT/${TAG}_deep_fri_e2e_2p$K.json; tail -5 $OUT/${TAG}_deep_fri_e2e_2p$K.err ;;
     *) echo "unknown stage $stage" ;;
