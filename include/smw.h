@@ -231,6 +231,9 @@ int32_t smw_ntt_cyclic_to_chunks(smw_ctx* ctx, smw_comm* comm_or_null, void* in_
 int32_t smw_mf_commit_phase_sharded(smw_ctx* ctx, smw_comm* comm_or_null, uint64_t ds_tag, const void* table_slice, size_t n_local, int32_t mem,
                                     void* roots_out_host, void* r_out_host, void* final_out_host);
 uint64_t smw_ctx_collective_count(const smw_ctx* ctx);   /* NCCL collectives issued through this context */
+/* Tuning: Merkle levels of at least `n` full arity-16 nodes (t = 17) run their linear layers on the INT8 tensor cores
+ * (csrc/poseidon_tc.cuh; same digests).  0 = never.  The default comes from SMW_TC_MIN in the environment. */
+int32_t smw_ctx_set_tc_min_nodes(smw_ctx* ctx, uint64_t n);
 
 /* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */
 int32_t smw_index_from_seed(smw_ctx* ctx, const void* seeds_fr, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem);   /* index_from_seed, deep_ali/src/fri.rs:178-183, element-wise */

@@ -85,6 +85,10 @@ class Context:
     def collective_count(self):
         return int(self.L.smw_ctx_collective_count(self.h))
 
+    def set_tc_min_nodes(self, n):
+        """Merkle levels of >= n full arity-16 nodes run their linear layers on the INT8 tensor cores (0 = never)"""
+        self.check(self.L.smw_ctx_set_tc_min_nodes(self.h, int(n)))
+
     KERNEL_CLASSES = ("merkle_level", "pair_leaves", "fri_leaf", "permute", "ntt_pass", "lde_aux", "fold", "misc")
 
     def profile(self, on=True):

@@ -23,7 +23,7 @@ WIDTHS = [9, 17, 33, 65, 129]
 def units():
     u = [("capi", "capi.cu", []), ("poseidon_params", "poseidon_params.cu", []),
          ("ntt_kernels", "ntt_kernels.cu", []), ("field_kernels", "field_kernels.cu", []),
-         ("poseidon_prog", "poseidon_prog.cu", []), ("comm", "comm.cu", [])]
+         ("poseidon_prog", "poseidon_prog.cu", []), ("comm", "comm.cu", []), ("poseidon_tc", "poseidon_tc.cu", [])]
     for t in WIDTHS:
         u.append(("poseidon_T%d" % t, "poseidon_T.cu", ["-DSMW_T=%d" % t]))
     return u

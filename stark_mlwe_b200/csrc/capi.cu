@@ -296,6 +296,7 @@ int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** ou
     if (cudaSetDevice(device) != cudaSuccess) return SMW_ERR_CUDA;
     smw_ctx* c = new smw_ctx();
     c->device = device;
+    { const char* e = getenv("SMW_TC_MIN"); if (e && atoll(e) > 0) c->tc_min_nodes = (uint64_t)atoll(e); }
     { const char* rep = getenv("SMW_REP"); c->use_f52 = !(rep && strcmp(rep, "29") == 0); }     // SMW_REP=29: integer-pipe multiplier everywhere
     if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
     else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SMW_ERR_CUDA; } c->own_stream = true; }
@@ -303,7 +304,7 @@ int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** ou
     return SMW_OK;
 }
 int32_t smw_ctx_create(int32_t device, smw_ctx** out) { return smw_ctx_create_on_stream(device, nullptr, out); }
-static void free_params_internal(smw_params* p) { if (!p) return; cudaFree(p->d_tables); cudaFree(p->d_tables52); cudaFree(p->d_ext); cudaFree(p->d_prog); delete p; }
+static void free_params_internal(smw_params* p) { if (!p) return; if (p->tc && p->tc_free) p->tc_free(p->tc); cudaFree(p->d_tables); cudaFree(p->d_tables52); cudaFree(p->d_ext); cudaFree(p->d_prog); delete p; }
 void smw_ctx_destroy(smw_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
@@ -1275,6 +1276,7 @@ int32_t smw_ntt_cyclic_to_chunks(smw_ctx* c, smw_comm* m, void* in_dev, void* ou
     return launch_dft_strided(c, (uint32_t*)out_dev, log_g, M / G, M / G, d_wpow);             // length-G DFT across the received pieces
 }
 uint64_t smw_ctx_collective_count(const smw_ctx* c) { return c ? c->collectives : 0; }
+int32_t smw_ctx_set_tc_min_nodes(smw_ctx* c, uint64_t n) { if (!c) return SMW_ERR_INVALID_ARG; c->tc_min_nodes = n ? n : ~0ull; return SMW_OK; }
 
 // root of the tree whose DS-level-`level` children are `nodes` (level 0: the leaves / leaf digests themselves)
 int32_t smw_merkle_root_from_level(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label, int32_t level, const void* nodes, size_t n, int32_t mem, void* root_out_host) {

@@ -164,29 +164,18 @@ template <bool DIF> __global__ void __launch_bounds__(512) k_ntt_pass29(uint32_t
     }
     __syncthreads();
     const int nstages = a.s_end - a.s_begin;
-    // twiddle of butterfly b of stage st; the sign of an inverse twiddle (w^-e = -w^(N/2 - e), e > 0) goes into the order of the
-    // subtraction.  It is requested ONE BUTTERFLY AHEAD — across the stage barrier too — so that its L2 latency is covered by the
-    // current butterfly's arithmetic instead of stalling the multiplication that needs it.
-    auto twiddle_of = [&](int st, int b, bool& neg) -> F29 {
-        const int s = DIF ? (a.s_end - 1 - st) : (a.s_begin + st);
-        const int lb = s - a.lo + a.c;
-        const int i0 = ((b >> lb) << (lb + 1)) | (b & ((1 << lb) - 1));
-        const size_t gi = tile_global(a, tile, i0);
-        const size_t e = (size_t)(((uint32_t)gi & ((1u << s) - 1u)) << (a.L - 1 - s));     // s <= L - 1 <= 31: the masked index and the exponent (< N / 2) fit 32 bits
-        neg = a.inverse && e != 0;
-        return tw29_load(tw, (neg ? half - e : e) << a.tw_shift);
-    };
-    bool neg_next = false;
-    F29 w_next = f29_zero();
-    if ((int)threadIdx.x < tile_elems / 2 && nstages > 0) w_next = twiddle_of(0, threadIdx.x, neg_next);
     for (int st = 0; st < nstages; st++) {
         const int s = DIF ? (a.s_end - 1 - st) : (a.s_begin + st);
         const int lb = s - a.lo + a.c;                 // local bit position of global bit s
         for (int b = threadIdx.x; b < tile_elems / 2; b += nthr) {
             const int i0 = ((b >> lb) << (lb + 1)) | (b & ((1 << lb) - 1)), i1 = i0 | (1 << lb);
-            const F29 w = w_next; const bool neg = neg_next;
-            if (b + nthr < tile_elems / 2) w_next = twiddle_of(st, b + nthr, neg_next);
-            else if (st + 1 < nstages) w_next = twiddle_of(st + 1, threadIdx.x, neg_next);
+            const size_t gi = tile_global(a, tile, i0);
+            const size_t e = (size_t)(((uint32_t)gi & ((1u << s) - 1u)) << (a.L - 1 - s));     // s <= L - 1 <= 31: the masked index and the exponent (< N / 2) fit 32 bits
+            // forward: w^e.  inverse: w^-e = -w^(N/2 - e) for e > 0 — the sign goes into the order of the subtraction.
+            // (Requesting the twiddle one butterfly ahead was tried: 84.5 ms against 81.0 ms per cfg2 step, profiles/r02q_ntt_ab.txt —
+            // four resident CTAs per SM already cover the L2 latency, the extra registers only cost occupancy.)
+            const bool neg = a.inverse && e != 0;
+            const F29 w = tw29_load(tw, (neg ? half - e : e) << a.tw_shift);
             const F29 u = S.load(i0), v = S.load(i1);
             if (DIF) {
                 F29 x = f29_add(u, v);

@@ -89,6 +89,15 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
+#if SMW_T == 17
+    // full arity-16 levels above the threshold: linear layers on the INT8 tensor cores (poseidon_tc.cuh)
+    if (c->use_f52 && p->d_tables52 && arity == 16 && n_children == n_parents * 16 && (uint64_t)n_parents * (uint64_t)n_cols >= c->tc_min_nodes) {
+        LevelBatch B{}; B.segs = nullptr; B.n_segs = 0; B.n_cols = n_cols; B.label_stride = label_stride; B.child_col_stride = child_col_stride; B.parent_col_stride = parent_col_stride;
+        B.u = NodeSeg{d_children, d_parents, (uint64_t)n_children, (uint64_t)n_parents, label0, pos_offset, level, (uint32_t)arity, 0};
+        B.total = (uint64_t)n_parents * (uint64_t)n_cols;
+        return tc::merkle_level_tc(c, p, B);
+    }
+#endif
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52 && (uint64_t)n_parents * (uint64_t)n_cols <= coop_max_nodes()) {
         LevelBatch B{}; B.segs = nullptr; B.n_segs = 0; B.n_cols = n_cols; B.label_stride = label_stride; B.child_col_stride = child_col_stride; B.parent_col_stride = parent_col_stride;

@@ -1,0 +1,214 @@
+// poseidon_tc.cu — host side of the tensor-core node hash (poseidon_tc.cuh): the word-level matrices of every stage, derived on
+// the host from the parameter set's external-form tables (small modular arithmetic, once per parameter set), their Toeplitz
+// byte expansion in the UMMA block layout, and the launch sequence of one Merkle level.
+#include "poseidon_tc.cuh"
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+namespace smw {
+namespace tc {
+
+// ------------------------------------------------------------------ host arithmetic mod p (Pallas Fr), Montgomery radix 2^256 = the external form
+namespace {
+struct U256 { uint64_t v[4]; };
+const U256 PMOD = {{0x8c46eb2100000001ull, 0x224698fc0994a8ddull, 0x0ull, 0x4000000000000000ull}};
+const uint64_t PINV64 = 0x8c46eb20ffffffffull;          // -p^-1 mod 2^64
+bool geq(const U256& a, const U256& b) { for (int i = 3; i >= 0; i--) if (a.v[i] != b.v[i]) return a.v[i] > b.v[i]; return true; }
+U256 sub_raw(const U256& a, const U256& b) { U256 r; unsigned __int128 br = 0; for (int i = 0; i < 4; i++) { unsigned __int128 d = (unsigned __int128)a.v[i] - b.v[i] - (uint64_t)br; r.v[i] = (uint64_t)d; br = (d >> 64) & 1; } return r; }
+U256 addm(const U256& a, const U256& b) {
+    U256 r; unsigned __int128 c = 0;
+    for (int i = 0; i < 4; i++) { c += (unsigned __int128)a.v[i] + b.v[i]; r.v[i] = (uint64_t)c; c >>= 64; }
+    if (c || geq(r, PMOD)) r = sub_raw(r, PMOD);
+    return r;
+}
+// a * b / 2^256 mod p, canonical (CIOS over 64-bit digits)
+U256 mont_mul(const U256& a, const U256& b) {
+    uint64_t t[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < 4; i++) {
+        unsigned __int128 c = 0;
+        for (int j = 0; j < 4; j++) { c += (unsigned __int128)a.v[j] * b.v[i] + t[j]; t[j] = (uint64_t)c; c >>= 64; }
+        c += t[4]; t[4] = (uint64_t)c; t[5] = (uint64_t)(c >> 64);
+        const uint64_t m = t[0] * PINV64;
+        c = (unsigned __int128)m * PMOD.v[0] + t[0]; c >>= 64;
+        for (int j = 1; j < 4; j++) { c += (unsigned __int128)m * PMOD.v[j] + t[j]; t[j - 1] = (uint64_t)c; c >>= 64; }
+        c += t[4]; t[3] = (uint64_t)c; t[4] = t[5] + (uint64_t)(c >> 64);
+    }
+    U256 r = {{t[0], t[1], t[2], t[3]}};
+    if (t[4] || geq(r, PMOD)) r = sub_raw(r, PMOD);
+    return r;
+}
+U256 pow2_mod(int e) { U256 x = {{1, 0, 0, 0}}; for (int i = 0; i < e; i++) x = addm(x, x); return x; }
+const U256 ZERO = {{0, 0, 0, 0}};
+typedef std::vector<std::vector<U256>> Mat;           // entries in the external (2^256 Montgomery) form
+Mat mat(int r, int c) { return Mat(r, std::vector<U256>(c, ZERO)); }
+Mat matmul(const Mat& A, const Mat& B) {
+    Mat C = mat((int)A.size(), (int)B[0].size());
+    for (size_t i = 0; i < A.size(); i++) for (size_t j = 0; j < B[0].size(); j++) { U256 s = ZERO; for (size_t k = 0; k < B.size(); k++) s = addm(s, mont_mul(A[i][k], B[k][j])); C[i][j] = s; }
+    return C;
+}
+
+size_t core_pos(int rows, int row, int k) { return (size_t)(k / 16) * rows * 16 + (size_t)(row / 8) * 128 + (size_t)(row % 8) * 16 + (size_t)(k % 16); }
+// Toeplitz byte blocks [chunk][k-step] of W (nw x kw words; entries converted to the canonical 2^260-form integers the state uses)
+std::vector<uint8_t> toeplitz_blocks(const Mat& W, const U256& c260) {
+    const int nw = (int)W.size(), kw = (int)W[0].size(), n_chunks = (nw + CHUNK_WORDS - 1) / CHUNK_WORDS;
+    std::vector<uint8_t> out((size_t)n_chunks * kw * B_BLOCK_MAX, 0);
+    for (int c = 0; c < n_chunks; c++) {
+        const int words = std::min(CHUNK_WORDS, nw - c * CHUNK_WORDS), n_rows = words * WCOLS;
+        for (int j = 0; j < kw; j++) {
+            uint8_t* blk = out.data() + (size_t)c * kw * B_BLOCK_MAX + (size_t)j * n_rows * 32;
+            for (int w = 0; w < words; w++) {
+                const U256 e = mont_mul(W[c * CHUNK_WORDS + w][j], c260);
+                uint8_t byte[32]; memcpy(byte, e.v, 32);
+                for (int col = 0; col < WCOLS; col++)
+                    for (int a = 0; a < 32; a++) { const int d = col - a; if (d >= 0 && d < 32) blk[core_pos(n_rows, w * WCOLS + col, a)] = byte[d]; }
+            }
+        }
+    }
+    return out;
+}
+} // namespace
+
+struct Tables {
+    int G = 0;
+    uint8_t *b_full = nullptr, *b_r3 = nullptr, *b_grp = nullptr, *b_last = nullptr, *b_final = nullptr;
+    double* gamma = nullptr; int* d_err = nullptr;
+    uint8_t *buf_p = nullptr, *buf_q = nullptr; double* dots = nullptr; uint64_t cap_nodes = 0;
+    int n_sm = 0;
+};
+void free_tables(void* q) {
+    Tables* t = (Tables*)q; if (!t) return;
+    cudaFree(t->b_full); cudaFree(t->b_r3); cudaFree(t->b_grp); cudaFree(t->b_last); cudaFree(t->b_final); cudaFree(t->gamma); cudaFree(t->d_err);
+    cudaFree(t->buf_p); cudaFree(t->buf_q); cudaFree(t->dots);
+    delete t;
+}
+static int upload(smw_ctx* c, const std::vector<uint8_t>& h, uint8_t** d) {
+    SMW_CUDA(c, cudaMalloc(d, h.size()));
+    SMW_CUDA(c, cudaMemcpyAsync(*d, h.data(), h.size(), cudaMemcpyHostToDevice, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SMW_OK;
+}
+static int build_tables(smw_ctx* c, smw_params* p, int G, Tables** out) {
+    const int t = p->t, rp = p->rp;
+    if (t != 17 || G < 1 || G > MAX_G || rp % G) return set_err(c, SMW_ERR_INVALID_ARG, "tensor-core node hash: t = 17 and a group size dividing rp only");
+    std::vector<uint64_t> ext((size_t)t * t * 4);
+    SMW_CUDA(c, cudaMemcpyAsync(ext.data(), p->d_ext, ext.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    Mat M = mat(t, t), Mh = mat(t, t);
+    for (int i = 0; i < t; i++) for (int j = 0; j < t; j++) { memcpy(M[i][j].v, &ext[((size_t)i * t + j) * 4], 32); Mh[i][j] = j == 0 ? ZERO : M[i][j]; }
+    const U256 one = pow2_mod(256), c260 = pow2_mod(260);
+    // rows[d] = e0^T Mh^d, cols[d] = Mh^d m0, d < G;  MhG = Mh^G
+    std::vector<std::vector<U256>> rows(G, std::vector<U256>(t, ZERO)), cols(G, std::vector<U256>(t, ZERO));
+    rows[0][0] = one;
+    for (int i = 0; i < t; i++) cols[0][i] = M[i][0];
+    for (int d = 1; d < G; d++)
+        for (int j = 0; j < t; j++) {
+            U256 s = ZERO, u = ZERO;
+            for (int i = 0; i < t; i++) { s = addm(s, mont_mul(rows[d - 1][i], Mh[i][j])); u = addm(u, mont_mul(Mh[j][i], cols[d - 1][i])); }
+            rows[d][j] = s; cols[d][j] = u;
+        }
+    Mat MhG = Mh; for (int d = 1; d < G; d++) MhG = matmul(Mh, MhG);
+    Mat Wv = mat(t, t + G);
+    for (int i = 0; i < t; i++) { for (int j = 0; j < t; j++) Wv[i][j] = MhG[i][j]; for (int m = 0; m < G; m++) Wv[i][t + m] = cols[G - 1 - m][i]; }
+    Mat R = mat(G, t); for (int k = 0; k < G; k++) R[k] = rows[k];
+    Mat Wd = matmul(R, Wv), D0 = matmul(R, M);
+    Mat Br3 = M; for (int k = 0; k < G; k++) Br3.push_back(D0[k]);
+    Mat Bgrp = Wv; for (int k = 0; k < G; k++) Bgrp.push_back(Wd[k]);
+    Mat Bfin(1, M[0]);
+    Tables* T = new Tables; T->G = G;
+    int rc = upload(c, toeplitz_blocks(M, c260), &T->b_full);
+    if (!rc) rc = upload(c, toeplitz_blocks(Br3, c260), &T->b_r3);
+    if (!rc) rc = upload(c, toeplitz_blocks(Bgrp, c260), &T->b_grp);
+    if (!rc) rc = upload(c, toeplitz_blocks(Wv, c260), &T->b_last);
+    if (!rc) rc = upload(c, toeplitz_blocks(Bfin, c260), &T->b_final);
+    if (!rc) {
+        std::vector<double> gm((size_t)G * 5);
+        for (int d = 0; d < G; d++) {
+            const U256 e = mont_mul(cols[d][0], c260);
+            const uint64_t l[5] = {e.v[0] & M52, ((e.v[0] >> 52) | (e.v[1] << 12)) & M52, ((e.v[1] >> 40) | (e.v[2] << 24)) & M52, ((e.v[2] >> 28) | (e.v[3] << 36)) & M52, e.v[3] >> 16};
+            for (int i = 0; i < 5; i++) gm[(size_t)d * 5 + i] = (double)l[i];
+        }
+        std::vector<uint8_t> raw((uint8_t*)gm.data(), (uint8_t*)gm.data() + gm.size() * 8);
+        uint8_t* q = nullptr; rc = upload(c, raw, &q); T->gamma = (double*)q;
+    }
+    if (!rc && cudaMalloc(&T->d_err, 4) != cudaSuccess) rc = set_err(c, SMW_ERR_CUDA, "cudaMalloc");
+    if (!rc) { cudaMemsetAsync(T->d_err, 0, 4, c->stream); cudaDeviceGetAttribute(&T->n_sm, cudaDevAttrMultiProcessorCount, c->device); }
+    if (rc) { free_tables(T); return rc; }
+    *out = T;
+    return SMW_OK;
+}
+
+// ------------------------------------------------------------------ one Merkle level
+static int group_size() { static int g = -1; if (g < 0) { const char* e = getenv("SMW_TC_GROUP"); g = e ? atoi(e) : 8; if (g < 1 || g > MAX_G) g = 8; } return g; }
+static uint64_t batch_nodes() { static long v = -1; if (v < 0) { const char* e = getenv("SMW_TC_BATCH"); v = e ? atol(e) : (1L << 20); if (v < TILE_M) v = 1L << 20; } return (uint64_t)v; }
+
+template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageArgs a) {
+    const size_t sm = sizeof(StageSmem) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) { SMW_CUDA(c, cudaFuncSetAttribute(k_tc_stage<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); attr_set = true; }
+    a.err = T->d_err;
+    const unsigned grid = (unsigned)std::min<uint64_t>(a.n_tiles, (uint64_t)T->n_sm);
+    { LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_stage<MODE><<<grid, STAGE_THREADS, sm, c->stream>>>(a); }
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
+
+// Hashes the nodes of `B` (every node with exactly 16 children) with the tensor-core pipeline.  The caller has checked the shape.
+int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
+    if (!p->tc) { Tables* T = nullptr; int rc = build_tables(c, p, group_size(), &T); if (rc) return rc; p->tc = T; p->tc_free = free_tables; }
+    Tables* T = (Tables*)p->tc;
+    const int t = p->t, G = T->G, NG = p->rp / G;
+    const TableLayout& L = p->layout;
+    const uint64_t batch = std::min<uint64_t>(batch_nodes(), (B.total + TILE_M - 1) / TILE_M * TILE_M);
+    if (T->cap_nodes < batch) {
+        cudaFree(T->buf_p); cudaFree(T->buf_q); cudaFree(T->dots); T->buf_p = T->buf_q = nullptr; T->dots = nullptr; T->cap_nodes = 0;
+        const size_t tiles = (size_t)(batch / TILE_M);
+        SMW_CUDA(c, cudaMalloc(&T->buf_p, tiles * MAX_KW * KSTEP_BYTES)); SMW_CUDA(c, cudaMalloc(&T->buf_q, tiles * MAX_KW * KSTEP_BYTES));
+        SMW_CUDA(c, cudaMalloc(&T->dots, (size_t)MAX_G * 5 * batch * sizeof(double)));
+        T->cap_nodes = batch;
+    }
+    const size_t tile_stride = (size_t)MAX_KW * KSTEP_BYTES;
+    for (uint64_t node0 = 0; node0 < B.total; node0 += batch) {
+        const uint64_t n = std::min<uint64_t>(batch, B.total - node0), n_tiles = (n + TILE_M - 1) / TILE_M;
+        uint8_t *P = T->buf_p, *Q = T->buf_q;
+        StageArgs base{}; base.in_tile_stride = tile_stride; base.out_tile_stride = tile_stride; base.tbl = p->d_tables52; base.rc_idx = -1; base.n_tiles = n_tiles;
+        base.B = B; base.node0 = node0; base.dots = T->dots; base.dots_stride = T->cap_nodes; base.nbytes = t;
+        auto full_round = [&](int round_next) -> int {          // P: x of a full round -> Q: x of the next one
+            StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_full; a.nw = t; a.out = Q; a.rc_idx = (int)(L.rc_full + (uint32_t)round_next * t);
+            int rc = launch_stage<EPI_SBOX>(c, T, a); std::swap(P, Q); return rc;
+        };
+        { HeadArgs h{B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
+          LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h); }
+        SMW_CUDA(c, cudaGetLastError());
+        for (int perm = 0; perm < 2; perm++) {
+            int rc = 0;
+            for (int r = 1; r <= 3 && !rc; r++) rc = full_round(r);
+            if (rc) return rc;
+            { StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_r3; a.nw = t + G; a.out = Q; rc = launch_stage<EPI_WORDS>(c, T, a); std::swap(P, Q); if (rc) return rc; }
+            for (int g = 0; g < NG; g++) {
+                { ChainArgs ch{T->dots, (size_t)T->cap_nodes, n, P, tile_stride, t, G, T->gamma, p->d_tables52, (int)(L.rc_part + (uint32_t)g * G)};
+                  LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_chain<<<(unsigned)((n + CHAIN_THREADS - 1) / CHAIN_THREADS), CHAIN_THREADS, 0, c->stream>>>(ch); }
+                SMW_CUDA(c, cudaGetLastError());
+                StageArgs a = base; a.in = P; a.kw = t + G; a.out = Q;
+                if (g + 1 < NG) { a.bmat = T->b_grp; a.nw = t + G; rc = launch_stage<EPI_WORDS>(c, T, a); }
+                else { a.bmat = T->b_last; a.nw = t; a.rc_idx = (int)(L.rc_full + 4u * t); rc = launch_stage<EPI_SBOX>(c, T, a); }
+                std::swap(P, Q);
+                if (rc) return rc;
+            }
+            for (int r = 5; r <= 7 && !rc; r++) rc = full_round(r);
+            if (rc) return rc;
+            StageArgs a = base; a.in = P; a.kw = t; a.out = Q;
+            if (perm == 0) { a.bmat = T->b_full; a.nw = t; a.rc_idx = (int)L.rc_full; a.absorb_first = t - 1; rc = launch_stage<EPI_ABSORB_SBOX>(c, T, a); std::swap(P, Q); }
+            else { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT>(c, T, a); }
+            if (rc) return rc;
+        }
+    }
+    int err = 0;
+    SMW_CUDA(c, cudaMemcpyAsync(&err, T->d_err, 4, cudaMemcpyDeviceToHost, c->stream));
+    SMW_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (err) { cudaMemsetAsync(T->d_err, 0, 4, c->stream); return set_err(c, SMW_ERR_CUDA, "tensor-core stage: mbarrier protocol timeout"); }
+    return SMW_OK;
+}
+
+} // namespace tc
+} // namespace smw

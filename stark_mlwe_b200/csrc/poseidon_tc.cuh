@@ -1,0 +1,353 @@
+// poseidon_tc.cuh — the Poseidon permutation of the arity-16 Merkle node hash (t = 17) with every linear layer on the INT8 tensor
+// cores (tcgen05.mma kind::i8, accumulators in TMEM) and only the S-boxes and Montgomery reductions on the FP64 pipe.
+//
+// Why it is exact.  A state word is an integer < 2^256 (the 2^260-Montgomery form of fr52.cuh), written as 32 unsigned bytes; a
+// constant matrix W (n_out x n_in words, canonical entries) is Toeplitz-expanded over its bytes, B[(i, c)][(j, a)] =
+// byte_{c - a}(W[i][j]), so that the int32 accumulator column (i, c) is column c (weight 2^(8c)) of the exact integer row product
+// sum_j W[i][j] x[j]: a sum of <= 25 * 32 byte products < 2^16, < 2^26.  The epilogue packs the 63 columns of a word into ten 52-bit
+// limb columns and runs the SAME Montgomery reduction as the batch interpreter (fr52.cuh acc52_reduce_add2), so the values agree
+// mod p with poseidon/src/lib.rs:219-272 and the emitted digests are bit-identical (tests/test_gpu_poseidon_tc.py).
+//
+// Round structure (scratch/tc_model.py is the big-integer model; checked against the oracle's permutation):
+//   full rounds     x = sbox(v + rc);  v' = M x                 -> one stage per round: GEMM 17 -> 17 words, epilogue reduce + rc' + x^5
+//   partial rounds  v' = Mh v + m0 sbox(v_0 + c_k),  Mh = M with column 0 zeroed, m0 = column 0 of M.  G rounds form a group:
+//                   the S-box inputs of a group are  s_k = e0^T Mh^k v + sum_{m<k} gamma_{k-1-m} x_m + c_k   (gamma_d = e0^T Mh^d m0)
+//                   so a group is: [chain kernel] G dependent S-boxes per permutation, each with a <= G-1 term correction, from the
+//                   G "dots" e0^T Mh^k v;  [stage] GEMM (17 + G) -> (17 + G) words giving the next group's v and dots.
+// Every GEMM input is an S-box output (< 2^254.3) or a stage output (< 2^255.3), so 32 bytes per word always suffice; the lazily
+// reduced S-box inputs (< 2^260) never enter a GEMM.
+//
+// Data: "byte tiles" of 128 permutations, one 4 KB k-step per word in the UMMA no-swizzle K-major core-matrix layout
+// ([16-byte half][8-row group][row][16 bytes]) — what the stage kernel's bulk copies bring into shared memory unchanged.
+#pragma once
+#include "poseidon_kernels.cuh"
+#include "poseidon_coop_kernels.cuh"      // resolve_node
+
+namespace smw {
+namespace tc {
+
+constexpr int TILE_M = 128;               // permutations per tile = TMEM lanes
+constexpr int KSTEP_BYTES = TILE_M * 32;  // one word of every permutation of a tile
+constexpr int WCOLS = 64;                 // accumulator columns per output word (63 used)
+constexpr int CHUNK_WORDS = 4;            // output words per MMA (N = 256 columns)
+constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // 8192 bytes: one k-step of one chunk
+constexpr int NSTAGE = 8;                 // B blocks in flight
+constexpr int MAX_KW = 25;                // k-steps (input words) per tile: 17 state words + a group of up to 8 S-box outputs
+constexpr int EPI_WARPS = 16;             // 4 TMEM lane quarters x 4 words of a chunk
+constexpr int STAGE_THREADS = 64 + 32 * EPI_WARPS;
+
+struct StageSmem {
+    alignas(1024) uint8_t a[MAX_KW * KSTEP_BYTES];        // 100 KB: the tile's input words
+    alignas(1024) uint8_t b[NSTAGE][B_BLOCK_MAX];         // 64 KB
+    alignas(8) uint64_t b_full[NSTAGE], b_empty[NSTAGE], a_full, a_empty, acc_full[2], acc_empty[2];
+    uint32_t tmem_base;
+};
+
+SMW_DEV uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+SMW_DEV void mbar_init(uint64_t* b, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(b)), "r"(count)); }
+SMW_DEV void mbar_expect_tx(uint64_t* b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(b)), "r"(bytes) : "memory"); }
+SMW_DEV void mbar_arrive(uint64_t* b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(b)) : "memory"); }
+// bounded wait (~2^26 non-blocking polls, about a second): a protocol error ends the kernel with a flag instead of hanging the GPU
+SMW_DEV bool mbar_wait(uint64_t* b, uint32_t parity) {
+    const uint32_t addr = smem_u32(b);
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 26); spin++) {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) return true;
+    }
+    return false;
+}
+SMW_DEV void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// UMMA shared-memory descriptor, K-major, no swizzle, version 1 (sm_100): start >> 4, LBO (distance of the two 16-byte K halves) >> 4
+// at bit 16, SBO (distance of consecutive 8-row groups) >> 4 at bit 32
+SMW_DEV uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
+}
+// kind::i8 instruction descriptor: D = s32 (bits 4-5 = 2), A and B unsigned 8-bit, K-major; N >> 3 at bit 17, M >> 4 at bit 24
+SMW_DEV uint32_t umma_idesc(int m, int n) { return (2u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24); }
+SMW_DEV void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+SMW_DEV void umma_commit(uint64_t* bar) { asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+SMW_DEV void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+SMW_DEV void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+SMW_DEV void tmem_ld16(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+}
+SMW_DEV void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// 16 int32 columns k0 .. k0+15 (weights 2^(8k), each < 2^26) added into the ten lazily carried 52-bit limb columns.
+// Column 63 is structurally zero.  All shifts and masks are compile-time constants.
+template <int K0> SMW_DEV void columns_to_limbs16(const uint32_t* c, uint64_t* acc) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int k = K0 + i;
+        if (k >= 63) continue;
+        const int bit = 8 * k, l = bit / 52, sh = bit % 52;
+        const uint64_t v = c[i];
+        if (sh <= 30) acc[l] += v << sh;
+        else { acc[l] += (v & ((1ull << (52 - sh)) - 1ull)) << sh; acc[l + 1] += v >> (52 - sh); }
+    }
+}
+
+// byte-tile address of word `kstep` of row `row` (first 16-byte half; the second half is 2048 bytes further)
+SMW_DEV size_t tile_word_offset(int kstep, int row) { return (size_t)kstep * KSTEP_BYTES + (size_t)(row >> 3) * 128 + (size_t)(row & 7) * 16; }
+// value < 2^256 with limbs < 2^52 -> 32 little-endian bytes at the two halves of a tile word
+SMW_DEV void store_word_bytes(uint8_t* tile, int kstep, int row, const F52& x) {
+    uint64_t l[5];
+#pragma unroll
+    for (int i = 0; i < 5; i++) l[i] = double_to_u52(x.v[i]);
+    const uint64_t x0 = l[0] | (l[1] << 52), x1 = (l[1] >> 12) | (l[2] << 40), x2 = (l[2] >> 24) | (l[3] << 28), x3 = (l[3] >> 36) | (l[4] << 16);
+    uint8_t* q = tile + tile_word_offset(kstep, row);
+    *reinterpret_cast<uint4*>(q) = make_uint4((uint32_t)x0, (uint32_t)(x0 >> 32), (uint32_t)x1, (uint32_t)(x1 >> 32));
+    *reinterpret_cast<uint4*>(q + TILE_M * 16) = make_uint4((uint32_t)x2, (uint32_t)(x2 >> 32), (uint32_t)x3, (uint32_t)(x3 >> 32));
+}
+// x^5 (poseidon/src/lib.rs:24-29): two squarings with 15 limb products each and one general product
+SMW_DEV F52 sbox52(const F52& s) {
+    Acc52 A;
+    acc52_sqr(A, s); const F52 x2 = acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
+    acc52_sqr(A, x2); const F52 x4 = acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
+    acc52_mul(A, x4, s); return acc52_reduce_add2(A, 1, f52_zero(), f52_zero());
+}
+// a canonical external-form element (x * 2^256 mod p, < p) -> limbs of 16 * that (= x * 2^260 mod p up to a multiple of p, < 2^259)
+SMW_DEV F52 ext_times16(const uint32_t* src) {
+    uint32_t w[8]; load_ext(src, w);
+    const uint64_t x0 = (uint64_t)w[0] | ((uint64_t)w[1] << 32), x1 = (uint64_t)w[2] | ((uint64_t)w[3] << 32),
+                   x2 = (uint64_t)w[4] | ((uint64_t)w[5] << 32), x3 = (uint64_t)w[6] | ((uint64_t)w[7] << 32);
+    const uint64_t y0 = x0 << 4, y1 = (x1 << 4) | (x0 >> 60), y2 = (x2 << 4) | (x1 >> 60), y3 = (x3 << 4) | (x2 >> 60), y4 = x3 >> 60;
+    uint64_t l[5];
+    l[0] = y0 & M52; l[1] = ((y0 >> 52) | (y1 << 12)) & M52; l[2] = ((y1 >> 40) | (y2 << 24)) & M52; l[3] = ((y2 >> 28) | (y3 << 36)) & M52; l[4] = (y3 >> 16) | (y4 << 48);
+    return f52_from_limbs(l);
+}
+
+// ------------------------------------------------------------------ the GEMM stage
+enum { EPI_WORDS = 0, EPI_SBOX = 1, EPI_ABSORB_SBOX = 2, EPI_EMIT = 3 };
+struct StageArgs {
+    const uint8_t* in; size_t in_tile_stride; int kw;            // input byte tiles: kw k-steps are read from each
+    const uint8_t* bmat; int nw;                                 // Toeplitz blocks [chunk][k-step] of the stage's matrix, nw output words
+    uint8_t* out; size_t out_tile_stride; int out_koff;          // output byte tiles: word w -> k-step out_koff + w
+    int nbytes;                                                  // EPI_WORDS: words < nbytes leave as bytes, the others as dots
+    double* dots; size_t dots_stride;                            // dots[(w - nbytes) * 5 + limb][perm], row stride dots_stride
+    const uint32_t* tbl; int rc_idx;                             // tbl52 table and element index of the constant added to word 0 (rc_idx + w for word w); < 0: none
+    uint64_t n_tiles;
+    LevelBatch B; uint64_t node0;                                // EPI_ABSORB_SBOX / EPI_EMIT: the nodes of this batch are node0 .. of the level launch
+    int absorb_first;                                            // EPI_ABSORB_SBOX: sponge element index of lane 0 in this rate block (16 for the second block)
+    int* err;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    StageSmem& S = *reinterpret_cast<StageSmem*>(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_chunks = (g.nw + CHUNK_WORDS - 1) / CHUNK_WORDS;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NSTAGE; i++) { mbar_init(&S.b_full[i], 1); mbar_init(&S.b_empty[i], 1); }
+        mbar_init(&S.a_full, 1); mbar_init(&S.a_empty, 1);
+        for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&S.tmem_base)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    const uint64_t my_tiles = g.n_tiles > blockIdx.x ? (g.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp == 0 && lane == 0) {
+        // ---------------- producer: the tile's input words, then the matrix blocks of every (chunk, k-step) through the ring
+        uint32_t bit = 0;
+        for (uint64_t it = 0; it < my_tiles; it++) {
+            const uint64_t tile = blockIdx.x + it * gridDim.x;
+            if (!mbar_wait(&S.a_empty, (uint32_t)(it & 1) ^ 1)) { atomicExch(g.err, 1); break; }
+            mbar_expect_tx(&S.a_full, (uint32_t)g.kw * KSTEP_BYTES);
+            bulk_g2s(S.a, g.in + tile * g.in_tile_stride, (uint32_t)g.kw * KSTEP_BYTES, &S.a_full);
+            bool bad = false;
+            for (int c = 0; c < n_chunks && !bad; c++) {
+                const int words = min(CHUNK_WORDS, g.nw - c * CHUNK_WORDS);
+                const uint32_t bytes = (uint32_t)words * WCOLS * 32u;
+                const uint8_t* src = g.bmat + (size_t)c * g.kw * B_BLOCK_MAX;
+                for (int s = 0; s < g.kw; s++, bit++) {
+                    const int st = bit % NSTAGE;
+                    if (!mbar_wait(&S.b_empty[st], ((bit / NSTAGE) & 1) ^ 1)) { atomicExch(g.err, 2); bad = true; break; }
+                    mbar_expect_tx(&S.b_full[st], bytes);
+                    bulk_g2s(S.b[st], src + (size_t)s * bytes, bytes, &S.b_full[st]);
+                }
+            }
+            if (bad) break;
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------- MMA issuer: one accumulator stage (256 TMEM columns) per chunk, double-buffered against the epilogue
+        uint32_t bit = 0, accit = 0;
+        for (uint64_t it = 0; it < my_tiles; it++) {
+            if (!mbar_wait(&S.a_full, (uint32_t)(it & 1))) { atomicExch(g.err, 3); break; }
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(S.a);
+            bool bad = false;
+            for (int c = 0; c < n_chunks && !bad; c++, accit++) {
+                const int as = accit & 1, n = min(CHUNK_WORDS, g.nw - c * CHUNK_WORDS) * WCOLS;
+                if (!mbar_wait(&S.acc_empty[as], ((accit >> 1) & 1) ^ 1)) { atomicExch(g.err, 4); bad = true; break; }
+                tc_fence_after();
+                const uint32_t idesc = umma_idesc(TILE_M, n);
+                for (int s = 0; s < g.kw; s++, bit++) {
+                    const int st = bit % NSTAGE;
+                    if (!mbar_wait(&S.b_full[st], (bit / NSTAGE) & 1)) { atomicExch(g.err, 5); bad = true; break; }
+                    tc_fence_after();
+                    const uint64_t ad = umma_desc(a_addr + (uint32_t)s * KSTEP_BYTES, TILE_M * 16, 128);
+                    const uint64_t bd = umma_desc(smem_u32(S.b[st]), (uint32_t)n * 16u, 128);
+                    umma_i8(tmem + (uint32_t)as * 256u, ad, bd, idesc, s > 0 ? 1u : 0u);
+                    umma_commit(&S.b_empty[st]);
+                }
+                if (!bad) umma_commit(&S.acc_full[as]);
+            }
+            if (bad) break;
+            umma_commit(&S.a_empty);
+        }
+    } else if (warp >= 2) {
+        // ---------------- epilogue: warp (quarter q, word slot wg) owns word 4 c + wg of every chunk for the 32 permutations of its TMEM lane quarter
+        const int q = warp & 3, wg = (warp - 2) >> 2, row = 32 * q + lane;
+        uint32_t accit = 0; bool bad = false;
+        for (uint64_t it = 0; it < my_tiles && !bad; it++) {
+            const uint64_t tile = blockIdx.x + it * gridDim.x;
+            const uint64_t perm = tile * TILE_M + row;
+            for (int c = 0; c < n_chunks; c++, accit++) {
+                const int as = accit & 1, word = c * CHUNK_WORDS + wg;
+                bool ok = mbar_wait(&S.acc_full[as], (accit >> 1) & 1);
+                ok = __all_sync(0xffffffffu, ok);
+                if (!ok) { if (lane == 0) atomicExch(g.err, 6); bad = true; break; }
+                tc_fence_after();
+                if (word < g.nw) {
+                    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * 256u + (uint32_t)wg * WCOLS;
+                    Acc52 A;
+#pragma unroll
+                    for (int i = 0; i < 10; i++) A.c[i] = 0;
+                    { uint32_t col[32];
+                      tmem_ld16(taddr, col); tmem_ld16(taddr + 16, col + 16); tmem_ld_wait();
+                      columns_to_limbs16<0>(col, A.c); columns_to_limbs16<16>(col + 16, A.c);
+                      tmem_ld16(taddr + 32, col); tmem_ld16(taddr + 48, col + 16); tmem_ld_wait();
+                      columns_to_limbs16<32>(col, A.c); columns_to_limbs16<48>(col + 16, A.c); }
+                    // the accumulator stage may be reused as soon as every warp has read its columns
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&S.acc_empty[as]);
+                    F52 rc = f52_zero();
+                    if (g.rc_idx >= 0) rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + word));
+                    F52 add = f52_zero();
+                    NodeSeg ns; uint64_t nq = 0; bool valid = true;
+                    if (MODE == EPI_ABSORB_SBOX || MODE == EPI_EMIT) valid = resolve_node(g.B, g.node0 + perm, ns, nq);
+                    if (MODE == EPI_ABSORB_SBOX && valid) {
+                        const int e = g.absorb_first + word - 4;                       // input index of this lane (4 DS fields precede the children)
+                        if (word < 16) {
+                            if (e < (int)ns.arity) add = ext_times16(ns.children + (nq * ns.arity + (uint64_t)e) * 8);
+                            else if (e == (int)ns.arity) add = f52_const(C_KONE52);    // the padding one: 2^260 mod p
+                        }
+                    }
+                    F52 r = acc52_reduce_add2(A, 0, rc, add);
+                    uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+                    if (MODE == EPI_WORDS) {
+                        if (word < g.nbytes) store_word_bytes(out_tile, g.out_koff + word, row, r);
+                        else {
+                            double* d = g.dots + (size_t)(word - g.nbytes) * 5 * g.dots_stride + perm;
+#pragma unroll
+                            for (int i = 0; i < 5; i++) d[(size_t)i * g.dots_stride] = r.v[i];
+                        }
+                    } else if (MODE == EPI_SBOX || MODE == EPI_ABSORB_SBOX) {
+                        store_word_bytes(out_tile, g.out_koff + word, row, sbox52(r));
+                    } else if (MODE == EPI_EMIT) {
+                        if (valid && word == 0) {
+                            Acc52 Q; acc52_mul(Q, r, f52_const(C_KOUT52));
+                            emit_ext52(acc52_reduce_add2(Q, 1, f52_zero(), f52_zero()), ns.parents + nq * 8);
+                        }
+                    }
+                } else {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&S.acc_empty[as]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(512u) : "memory");
+}
+
+// ------------------------------------------------------------------ head: the first rate block of the node sponge, ARK and S-boxes of round 0
+// lane l of node q = element l of [arity, level, q + pos_offset, label, child_0 ..] (merkle/src/lib.rs:164-179, poseidon/src/lib.rs:288-312);
+// x_l = (lane + rc_full[0][l])^5 goes to k-step l of the node's byte tile.  blockDim = (128 rows, 4): threadIdx.y strides the lanes.
+struct HeadArgs { LevelBatch B; uint64_t node0, n_nodes; uint8_t* out; size_t out_tile_stride; const uint32_t* tbl; int rc_idx; };
+template <int T> __global__ void __launch_bounds__(512) k_tc_head(const HeadArgs g) {
+    const int row = threadIdx.x;
+    const uint64_t tile = blockIdx.x, perm = tile * TILE_M + row;
+    NodeSeg ns; uint64_t q = 0;
+    const bool valid = perm < g.n_nodes && resolve_node(g.B, g.node0 + perm, ns, q);
+    uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+    const F52 k_rr = f52_const(C_KRR52);
+#pragma unroll 1
+    for (int l = threadIdx.y; l < T; l += blockDim.y) {
+        const F52 rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + l));
+        F52 s = rc;
+        if (valid && l < T - 1) {
+            Acc52 A;
+            if (l < 4) {                       // a DS integer d -> d * 2^520 / 2^260
+                acc52_mul(A, f52_from_u64(l == 0 ? (uint64_t)ns.arity : l == 1 ? (uint64_t)ns.level : l == 2 ? q + ns.pos_offset : ns.label), k_rr);
+                s = acc52_reduce_add2(A, 1, rc, f52_zero());
+            } else {
+                const int e = l - 4;
+                F52 add = f52_zero();
+                if (e < (int)ns.arity) add = ext_times16(ns.children + (q * ns.arity + (uint64_t)e) * 8);
+                else if (e == (int)ns.arity) add = f52_const(C_KONE52);
+                acc52_zero(A);
+                s = acc52_reduce_add2(A, 0, rc, add);          // rc + add with the carries normalised (limbs < 2^52)
+            }
+        }
+        store_word_bytes(out_tile, l, row, sbox52(s));
+    }
+}
+
+// ------------------------------------------------------------------ chain: the G dependent S-boxes of one group of partial rounds
+// s_k = dot_k + sum_{m<k} gamma[k-1-m] x_m + rc_part[round0 + k],  x_k = s_k^5;  x_k -> k-step koff + k of the permutation's tile.
+// One thread per permutation; the group's x values stay in shared memory ([k][limb][thread], conflict-free).
+constexpr int CHAIN_THREADS = 128, MAX_G = 8;
+struct ChainArgs { const double* dots; size_t dots_stride; uint64_t n_perm; uint8_t* out; size_t out_tile_stride; int koff; int G;
+                   const double* gamma; const uint32_t* tbl; int rc_idx; };
+__global__ void __launch_bounds__(CHAIN_THREADS) k_tc_chain(const ChainArgs g) {
+    __shared__ double xs[MAX_G * 5 * CHAIN_THREADS];
+    const uint64_t perm = (uint64_t)blockIdx.x * CHAIN_THREADS + threadIdx.x;
+    if (perm >= g.n_perm) return;
+    const uint64_t tile = perm / TILE_M; const int row = (int)(perm % TILE_M);
+    uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+#pragma unroll 1
+    for (int k = 0; k < g.G; k++) {
+        F52 d;
+#pragma unroll
+        for (int i = 0; i < 5; i++) d.v[i] = g.dots[((size_t)k * 5 + i) * g.dots_stride + perm];
+        const F52 rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + k));
+        Acc52 A; acc52_zero(A);
+#pragma unroll 1
+        for (int m = 0; m < k; m++) {
+            F52 x, gm;
+#pragma unroll
+            for (int i = 0; i < 5; i++) { x.v[i] = xs[(m * 5 + i) * CHAIN_THREADS + threadIdx.x]; gm.v[i] = __ldg(g.gamma + (size_t)(k - 1 - m) * 5 + i); }
+            acc52_mac(A, x, gm);
+        }
+        const F52 x = sbox52(acc52_reduce_add2(A, (uint32_t)k, d, rc));
+#pragma unroll
+        for (int i = 0; i < 5; i++) xs[(k * 5 + i) * CHAIN_THREADS + threadIdx.x] = x.v[i];
+        store_word_bytes(out_tile, g.koff + k, row, x);
+    }
+}
+
+} // namespace tc
+} // namespace smw

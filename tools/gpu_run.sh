@@ -2,7 +2,7 @@
 # One parameterised runner for a GPU lease (replaces the per-lease scripts of round 1):
 #   gpurun --timeout 1500 -- 'bash tools/gpu_run.sh <tag> <stage> [<stage> ...]'
 # Every stage writes gpurun_out/<tag>_<stage>.* ; a failing stage does not stop the later ones.
-# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | mgpu<N> | scale<N>
+# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | umma | mgpu<N> | scale<N>
 set -u
 TAG=${1:?tag}; shift
 OUT=gpurun_out; mkdir -p $OUT
@@ -37,6 +37,10 @@ for stage in "$@"; do
     ntt_ab)     timeout 600 python -m pytest tests/test_gpu_ntt_lde.py tests/test_gpu_full_size.py tests/test_gpu_ntt_distributed.py -m gpu -q --tb=short > $OUT/${TAG}_ntt_tests.log 2>&1; tail -5 $OUT/${TAG}_ntt_tests.log
                 for v in 29 32; do SMW_NTT=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_NTT=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_ntt_ab.txt; done ;;
     ntt_thr)    for v in 128 64 32; do SMW_NTT_THREADS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_NTT_THREADS=$v', 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_ntt_threads.txt; done ;;
+    tc)         timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_tests.log 2>&1; tail -25 $OUT/${TAG}_tc_tests.log ;;
+    tc_ab)      for v in 0 16384; do SMW_TC_MIN=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_MIN=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_ab.txt; done ;;
+    umma)       timeout 120 tools/_bin/umma_i8 ${UMMA_TILES:-16} $OUT/${TAG}_umma_dump.bin > $OUT/${TAG}_umma_i8.json 2> $OUT/${TAG}_umma_i8.err; echo "exit $?"; cat $OUT/${TAG}_umma_i8.json; tail -3 $OUT/${TAG}_umma_i8.err
+                timeout 120 python tools/umma_i8_check.py $OUT/${TAG}_umma_dump.bin | tee $OUT/${TAG}_umma_check.json; rm -f $OUT/${TAG}_umma_dump.bin ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
     e2e*)       K=${stage#e2e}; timeout 1700 python tools/deep_fri_e2e.py $K > $OUT/${TAG}_deep_fri_e2e_2p$K.json 2> $OUT/${TAG}_deep_fri_e2e_2p$K.err; cat $OUT/${TAG}_deep_fri_e2e_2p$K.json; tail -5 $OUT/${TAG}_deep_fri_e2e_2p$K.err ;;
     *) echo "unknown stage $stage" ;;
