@@ -147,7 +147,7 @@ template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageAr
     static bool attr_set = false;
     if (!attr_set) { SMW_CUDA(c, cudaFuncSetAttribute(k_tc_stage<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); attr_set = true; }
     a.err = T->d_err;
-    const unsigned grid = (unsigned)std::min<uint64_t>(a.n_tiles, (uint64_t)T->n_sm);
+    const unsigned grid = (unsigned)std::min<uint64_t>((a.n_tiles + PAIR - 1) / PAIR, (uint64_t)T->n_sm);
     { LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_stage<MODE><<<grid, STAGE_THREADS, sm, c->stream>>>(a); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;

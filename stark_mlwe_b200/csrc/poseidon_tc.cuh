@@ -29,16 +29,29 @@ namespace tc {
 constexpr int TILE_M = 128;               // permutations per tile = TMEM lanes
 constexpr int KSTEP_BYTES = TILE_M * 32;  // one word of every permutation of a tile
 constexpr int WCOLS = 64;                 // accumulator columns per output word (63 used)
-constexpr int CHUNK_WORDS = 4;            // output words per MMA (N = 256 columns)
-constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // 8192 bytes: one k-step of one chunk
-constexpr int NSTAGE = 8;                 // B blocks in flight
+#ifndef SMW_TC_PAIR
+#define SMW_TC_PAIR 1
+#endif
+constexpr int PAIR = SMW_TC_PAIR;         // tiles that share every B block (PAIR MMAs per block)
+constexpr int CHUNK_WORDS = 4 / PAIR;     // output words per MMA (N = 256 / PAIR columns)
+constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // bytes of one k-step of one chunk
 constexpr int MAX_KW = 25;                // k-steps (input words) per tile: 17 state words + a group of up to 8 S-box outputs
-constexpr int EPI_WARPS = 16;             // 4 TMEM lane quarters x 4 words of a chunk
+#ifndef SMW_TC_KSUB
+#define SMW_TC_KSUB 4
+#endif
+constexpr int KSUB = SMW_TC_KSUB;         // k-steps per ring stage: one bulk copy and one commit for KSUB MMAs (the issue loop, not the L2 stream, paced the kernel at KSUB = 1)
+#ifdef SMW_TC_NSTAGE
+constexpr int NSTAGE = SMW_TC_NSTAGE;
+#else
+constexpr int NSTAGE = (PAIR == 1 ? 112 : 24) * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words
+#endif
+constexpr int EPI_WARPS = 16;             // 4 TMEM lane quarters x (words of a chunk x tiles = 4)
 constexpr int STAGE_THREADS = 64 + 32 * EPI_WARPS;
+constexpr int ACC_COLS = PAIR * CHUNK_WORDS * WCOLS;      // 256 TMEM columns per accumulator stage: [tile][word][64]
 
 struct StageSmem {
-    alignas(1024) uint8_t a[MAX_KW * KSTEP_BYTES];        // 100 KB: the tile's input words
-    alignas(1024) uint8_t b[NSTAGE][B_BLOCK_MAX];         // 64 KB
+    alignas(1024) uint8_t a[PAIR][MAX_KW * KSTEP_BYTES];  // 100 KB per tile: its input words
+    alignas(1024) uint8_t b[NSTAGE][KSUB * B_BLOCK_MAX];
     alignas(8) uint64_t b_full[NSTAGE], b_empty[NSTAGE], a_full, a_empty, acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
@@ -47,16 +60,21 @@ SMW_DEV uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_sh
 SMW_DEV void mbar_init(uint64_t* b, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(b)), "r"(count)); }
 SMW_DEV void mbar_expect_tx(uint64_t* b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(b)), "r"(bytes) : "memory"); }
 SMW_DEV void mbar_arrive(uint64_t* b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(b)) : "memory"); }
-// bounded wait (~2^26 non-blocking polls, about a second): a protocol error ends the kernel with a flag instead of hanging the GPU
+// bounded wait: mbarrier.try_wait suspends the thread in hardware (no polling traffic); ~2 s of wall time without the phase
+// completing is a protocol error that ends the kernel with a flag instead of hanging the GPU
 SMW_DEV bool mbar_wait(uint64_t* b, uint32_t parity) {
     const uint32_t addr = smem_u32(b);
+    uint64_t t0 = 0;
 #pragma unroll 1
-    for (uint32_t spin = 0; spin < (1u << 26); spin++) {
+    for (uint32_t spin = 0; ; spin++) {
         uint32_t ok;
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
         if (ok) return true;
+        if ((spin & 63) == 63) {
+            uint64_t now; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now; else if (now - t0 > 2000000000ull) return false;
+        }
     }
-    return false;
 }
 SMW_DEV void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -74,6 +92,11 @@ SMW_DEV void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t i
                  :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 SMW_DEV void umma_commit(uint64_t* bar) { asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+SMW_DEV bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, 0xffffffff;\n\tselp.b32 %0, 1, 0, px;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 SMW_DEV void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 SMW_DEV void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 SMW_DEV void tmem_ld16(uint32_t taddr, uint32_t* r) {
@@ -163,72 +186,97 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = S.tmem_base;
-    const uint64_t my_tiles = g.n_tiles > blockIdx.x ? (g.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const uint64_t n_pairs = (g.n_tiles + PAIR - 1) / PAIR;
+    const uint64_t my_pairs = n_pairs > blockIdx.x ? (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
     if (warp == 0 && lane == 0) {
-        // ---------------- producer: the tile's input words, then the matrix blocks of every (chunk, k-step) through the ring
+        // ---------------- producer: the input words of the pair's tiles, then the matrix blocks of every (chunk, k-step) through the ring
         uint32_t bit = 0;
-        for (uint64_t it = 0; it < my_tiles; it++) {
-            const uint64_t tile = blockIdx.x + it * gridDim.x;
+        for (uint64_t it = 0; it < my_pairs; it++) {
+            const uint64_t tile0 = (blockIdx.x + it * gridDim.x) * PAIR;
+            const int nt = (int)min((uint64_t)PAIR, g.n_tiles - tile0);
             if (!mbar_wait(&S.a_empty, (uint32_t)(it & 1) ^ 1)) { atomicExch(g.err, 1); break; }
-            mbar_expect_tx(&S.a_full, (uint32_t)g.kw * KSTEP_BYTES);
-            bulk_g2s(S.a, g.in + tile * g.in_tile_stride, (uint32_t)g.kw * KSTEP_BYTES, &S.a_full);
+            mbar_expect_tx(&S.a_full, (uint32_t)(nt * g.kw) * KSTEP_BYTES);
+            for (int tl = 0; tl < nt; tl++) bulk_g2s(S.a[tl], g.in + (tile0 + tl) * g.in_tile_stride, (uint32_t)g.kw * KSTEP_BYTES, &S.a_full);
             bool bad = false;
             for (int c = 0; c < n_chunks && !bad; c++) {
                 const int words = min(CHUNK_WORDS, g.nw - c * CHUNK_WORDS);
                 const uint32_t bytes = (uint32_t)words * WCOLS * 32u;
                 const uint8_t* src = g.bmat + (size_t)c * g.kw * B_BLOCK_MAX;
-                for (int s = 0; s < g.kw; s++, bit++) {
-                    const int st = bit % NSTAGE;
+                for (int s = 0; s < g.kw; s += KSUB, bit++) {
+                    const int st = bit % NSTAGE, ks = min(KSUB, g.kw - s);
                     if (!mbar_wait(&S.b_empty[st], ((bit / NSTAGE) & 1) ^ 1)) { atomicExch(g.err, 2); bad = true; break; }
-                    mbar_expect_tx(&S.b_full[st], bytes);
-                    bulk_g2s(S.b[st], src + (size_t)s * bytes, bytes, &S.b_full[st]);
+                    mbar_expect_tx(&S.b_full[st], bytes * ks);
+                    bulk_g2s(S.b[st], src + (size_t)s * bytes, bytes * ks, &S.b_full[st]);
                 }
             }
             if (bad) break;
         }
-    } else if (warp == 1 && lane == 0) {
-        // ---------------- MMA issuer: one accumulator stage (256 TMEM columns) per chunk, double-buffered against the epilogue
+    } else if (warp == 1) {
+        // ---------------- MMA issuer: the whole warp runs the loop converged (descriptors stay in uniform registers: no per-MMA
+        // election loop, measured 2.4x on the issue rate), one elected lane issues.  One accumulator stage (256 TMEM columns:
+        // [tile][word][64]) per chunk, double-buffered against the epilogue.
         uint32_t bit = 0, accit = 0;
-        for (uint64_t it = 0; it < my_tiles; it++) {
-            if (!mbar_wait(&S.a_full, (uint32_t)(it & 1))) { atomicExch(g.err, 3); break; }
+        const bool leader = elect_one();
+        const uint32_t hi = (128u >> 4) | (1u << 14), a_lbo = (uint32_t)((TILE_M * 16) >> 4) << 16;
+        for (uint64_t it = 0; it < my_pairs; it++) {
+            const uint64_t tile0 = (blockIdx.x + it * gridDim.x) * PAIR;
+            const int nt = (int)min((uint64_t)PAIR, g.n_tiles - tile0);
+            if (!mbar_wait(&S.a_full, (uint32_t)(it & 1))) { if (leader) atomicExch(g.err, 3); break; }
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(S.a);
             bool bad = false;
             for (int c = 0; c < n_chunks && !bad; c++, accit++) {
                 const int as = accit & 1, n = min(CHUNK_WORDS, g.nw - c * CHUNK_WORDS) * WCOLS;
-                if (!mbar_wait(&S.acc_empty[as], ((accit >> 1) & 1) ^ 1)) { atomicExch(g.err, 4); bad = true; break; }
+                if (!mbar_wait(&S.acc_empty[as], ((accit >> 1) & 1) ^ 1)) { if (leader) atomicExch(g.err, 4); bad = true; break; }
                 tc_fence_after();
-                const uint32_t idesc = umma_idesc(TILE_M, n);
-                for (int s = 0; s < g.kw; s++, bit++) {
-                    const int st = bit % NSTAGE;
-                    if (!mbar_wait(&S.b_full[st], (bit / NSTAGE) & 1)) { atomicExch(g.err, 5); bad = true; break; }
+                const uint32_t idesc = umma_idesc(TILE_M, n), b_lbo = (uint32_t)((n * 16) >> 4) << 16;
+                for (int s = 0; s < g.kw; s += KSUB, bit++) {
+                    const int st = bit % NSTAGE, ks = min(KSUB, g.kw - s);
+                    if (!mbar_wait(&S.b_full[st], (bit / NSTAGE) & 1)) { if (leader) atomicExch(g.err, 5); bad = true; break; }
                     tc_fence_after();
-                    const uint64_t ad = umma_desc(a_addr + (uint32_t)s * KSTEP_BYTES, TILE_M * 16, 128);
-                    const uint64_t bd = umma_desc(smem_u32(S.b[st]), (uint32_t)n * 16u, 128);
-                    umma_i8(tmem + (uint32_t)as * 256u, ad, bd, idesc, s > 0 ? 1u : 0u);
-                    umma_commit(&S.b_empty[st]);
+                    const uint32_t b_lo = (smem_u32(S.b[st]) & 0x3ffffu) >> 4;
+                    if (leader) {
+#pragma unroll
+                        for (int k = 0; k < KSUB; k++) {
+                            if (k < ks) {
+                                const uint64_t bd = (uint64_t)((b_lo + (uint32_t)k * (uint32_t)(n * 2)) | b_lbo) | ((uint64_t)hi << 32);
+#pragma unroll
+                                for (int tl = 0; tl < PAIR; tl++) {
+                                    if (tl < nt) {
+                                        const uint32_t a_lo = ((smem_u32(S.a[tl]) & 0x3ffffu) >> 4) + (uint32_t)(s + k) * (KSTEP_BYTES >> 4);
+                                        umma_i8(tmem + (uint32_t)as * ACC_COLS + (uint32_t)tl * (CHUNK_WORDS * WCOLS), (uint64_t)(a_lo | a_lbo) | ((uint64_t)hi << 32), bd, idesc, (s + k) > 0 ? 1u : 0u);
+                                    }
+                                }
+                            }
+                        }
+                        umma_commit(&S.b_empty[st]);
+                    }
+                    __syncwarp();
                 }
-                if (!bad) umma_commit(&S.acc_full[as]);
+                if (!bad && leader) umma_commit(&S.acc_full[as]);
+                __syncwarp();
             }
             if (bad) break;
-            umma_commit(&S.a_empty);
+            if (leader) umma_commit(&S.a_empty);
+            __syncwarp();
         }
     } else if (warp >= 2) {
-        // ---------------- epilogue: warp (quarter q, word slot wg) owns word 4 c + wg of every chunk for the 32 permutations of its TMEM lane quarter
-        const int q = warp & 3, wg = (warp - 2) >> 2, row = 32 * q + lane;
+        // ---------------- epilogue: warp (quarter q, word slot wg, tile tl) owns word CHUNK_WORDS * c + wg of every chunk for the 32 permutations of its TMEM lane quarter
+        const int q = warp & 3, wg = ((warp - 2) >> 2) % CHUNK_WORDS, tl = ((warp - 2) >> 2) / CHUNK_WORDS, row = 32 * q + lane;
         uint32_t accit = 0; bool bad = false;
-        for (uint64_t it = 0; it < my_tiles && !bad; it++) {
-            const uint64_t tile = blockIdx.x + it * gridDim.x;
+        for (uint64_t it = 0; it < my_pairs && !bad; it++) {
+            const uint64_t tile = (blockIdx.x + it * gridDim.x) * PAIR + tl;
+            const bool have_tile = tile < g.n_tiles;
             const uint64_t perm = tile * TILE_M + row;
             for (int c = 0; c < n_chunks; c++, accit++) {
-                const int as = accit & 1, word = c * CHUNK_WORDS + wg;
-                bool ok = mbar_wait(&S.acc_full[as], (accit >> 1) & 1);
-                ok = __all_sync(0xffffffffu, ok);
+                const int as = accit & 1, word = have_tile ? c * CHUNK_WORDS + wg : g.nw;
+                bool ok = true;
+                if (lane == 0) ok = mbar_wait(&S.acc_full[as], (accit >> 1) & 1);      // one lane waits, the warp follows
+                ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
                 if (!ok) { if (lane == 0) atomicExch(g.err, 6); bad = true; break; }
                 tc_fence_after();
                 if (word < g.nw) {
-                    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * 256u + (uint32_t)wg * WCOLS;
+                    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * ACC_COLS + (uint32_t)(tl * CHUNK_WORDS + wg) * WCOLS;
                     Acc52 A;
 #pragma unroll
                     for (int i = 0; i < 10; i++) A.c[i] = 0;

@@ -39,6 +39,24 @@ for stage in "$@"; do
     ntt_thr)    for v in 128 64 32; do SMW_NTT_THREADS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_NTT_THREADS=$v', 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_ntt_threads.txt; done ;;
     tc)         timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_tests.log 2>&1; tail -25 $OUT/${TAG}_tc_tests.log ;;
     tc_ab)      for v in 0 16384; do SMW_TC_MIN=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_MIN=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_ab.txt; done ;;
+    launches_tc) SMW_TC_MIN=4096 timeout 900 $NCU_LIST -c 400 --log-file $OUT/${TAG}_ncu_launches_tc.csv python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_launches_tc.out 2>&1; tail -3 $OUT/${TAG}_ncu_launches_tc.out
+                python - <<PYEOF | tee $OUT/${TAG}_ncu_launches_tc_summary.txt
+import csv, collections, re
+rows = [r for r in csv.reader(open("$OUT/${TAG}_ncu_launches_tc.csv")) if len(r) > 10]
+h = rows[0]; ki = h.index("Kernel Name"); vi = h.index("Metric Value"); ui = h.index("Metric Unit")
+d = collections.defaultdict(lambda: [0, 0.0])
+for r in rows[1:]:
+    try: v = float(r[vi].replace(",", ""))
+    except ValueError: continue
+    v *= {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(r[ui], 1e-6)
+    k = re.sub(r"\(.*", "", r[ki]); d[k][0] += 1; d[k][1] += v
+tot = sum(v[1] for v in d.values())
+for k, v in sorted(d.items(), key=lambda kv: -kv[1][1]): print("%-60s n=%4d  %9.3f ms  %5.1f%%" % (k[:60], v[0], v[1], 100 * v[1] / tot))
+PYEOF
+                ;;
+    tc_var)     for lib in libsmw.so libsmw_k4.so libsmw_pair2.so; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_MIN=16384 timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_variants.txt; done ;;
+    ncu_tc)     SMW_TC_MIN=4096 timeout 900 $NCU_FULL -k regex:k_tc_stage -s 5 -c 3 -o $OUT/${TAG}_ncu_tc_stage -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_tc.out 2>&1
+                ncu -i $OUT/${TAG}_ncu_tc_stage.ncu-rep --page details --csv > $OUT/${TAG}_ncu_tc_stage_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_tc.out ;;
     umma)       timeout 120 tools/_bin/umma_i8 ${UMMA_TILES:-16} $OUT/${TAG}_umma_dump.bin > $OUT/${TAG}_umma_i8.json 2> $OUT/${TAG}_umma_i8.err; echo "exit $?"; cat $OUT/${TAG}_umma_i8.json; tail -3 $OUT/${TAG}_umma_i8.err
                 timeout 120 python tools/umma_i8_check.py $OUT/${TAG}_umma_dump.bin | tee $OUT/${TAG}_umma_check.json; rm -f $OUT/${TAG}_umma_dump.bin ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;

@@ -39,7 +39,10 @@ constexpr int NCHUNK = 5;                                    // N chunks per til
 constexpr int A_KSTEP_BYTES = TILE_M * 32;                   // 4096: [k16 (2)][m8 (16)][8 rows x 16 B]
 constexpr int A_TILE_BYTES = KSTEPS * A_KSTEP_BYTES;         // 69 632
 constexpr int B_BLOCK_MAX = 256 * 32;                        // 8192: [k16 (2)][n8 (32)][8 rows x 16 B]
-constexpr int NSTAGE = 8;                                    // B blocks in flight
+#ifndef KSUB
+#define KSUB 1
+#endif
+constexpr int NSTAGE = 8 / KSUB;                             // B stages in flight, KSUB k-steps (one bulk copy, one commit) each
 constexpr int NTHREADS = 192;
 __host__ __device__ constexpr int chunk_n(int c) { return c < 4 ? 256 : 64; }
 __host__ __device__ constexpr int chunk_words(int c) { return c < 4 ? 4 : 1; }
@@ -48,7 +51,7 @@ constexpr size_t B_TOTAL_BYTES = 4 * (size_t)KSTEPS * B_BLOCK_MAX + (size_t)KSTE
 
 struct Smem {
     alignas(1024) uint8_t a[2][A_TILE_BYTES];
-    alignas(1024) uint8_t b[NSTAGE][B_BLOCK_MAX];
+    alignas(1024) uint8_t b[NSTAGE][KSUB * B_BLOCK_MAX];
     alignas(8) uint64_t b_full[NSTAGE], b_empty[NSTAGE], a_full[2], a_empty[2], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
@@ -82,7 +85,17 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
                  :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// timing-only variant: the same operands read as e4m3 with an f32 accumulator (kind::f8f6f4) — tells whether the int8 kind is paced differently
+__device__ __forceinline__ void umma_f8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) { asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory"); }
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, 0xffffffff;\n\tselp.b32 %0, 1, 0, px;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // 16 consecutive 32-bit TMEM columns of this thread's lane
@@ -111,7 +124,7 @@ __device__ __forceinline__ void columns_to_limbs(const uint32_t* c, uint64_t* ac
 struct Args {
     const uint8_t* a_tiles; int n_a_tiles;      // A tiles, UMMA core-matrix layout, A_TILE_BYTES each
     const uint8_t* b_blocks;                    // Toeplitz blocks [chunk][k-step], UMMA core-matrix layout
-    int tiles_per_cta, mode;                    // mode 0: columns -> limbs; 1: + Montgomery reduction (fr52); 2: MMA only (epilogue reads one column)
+    int tiles_per_cta, mode, flags;   // mode 0: columns -> limbs; 1: + Montgomery reduction (fr52); 2: MMA only (epilogue reads one column)
     uint64_t* checksum;                         // [grid * 128]
     uint64_t* raw_out; uint64_t* red_out;       // tile 0: [128][17][10] limbs, [128][17][5] double bit patterns
     int* err;
@@ -147,42 +160,56 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_matvec_umma(Args g) {
             bool bad = false;
             for (int c = 0; c < NCHUNK && !bad; c++) {
                 const uint32_t bytes = (uint32_t)chunk_n(c) * 32u;
-                for (int s = 0; s < KSTEPS; s++, bit++) {
-                    const int st = bit % NSTAGE;
+                for (int s = 0; s < KSTEPS; s += KSUB, bit++) {
+                    const int st = bit % NSTAGE, ks = min(KSUB, KSTEPS - s);
                     if (!mbar_wait(&S.b_empty[st], ((bit / NSTAGE) & 1) ^ 1)) { atomicExch(g.err, 2); bad = true; break; }
-                    mbar_expect_tx(&S.b_full[st], bytes);
-                    bulk_g2s(S.b[st], g.b_blocks + chunk_offset(c) + (size_t)s * bytes, bytes, &S.b_full[st]);
+                    if (g.flags & 2) { mbar_arrive(&S.b_full[st]); continue; }
+                    mbar_expect_tx(&S.b_full[st], bytes * ks);
+                    bulk_g2s(S.b[st], g.b_blocks + ((g.flags & 1) ? (size_t)blockIdx.x * B_TOTAL_BYTES : 0) + chunk_offset(c) + (size_t)s * bytes, bytes * ks, &S.b_full[st]);
                 }
             }
             if (bad) break;
         }
-    } else if (warp == 1 && lane == 0) {
-        // ---------------- MMA issuer
+    } else if (warp == 1) {
+        // ---------------- MMA issuer: the WHOLE warp runs the loop converged (descriptors stay in uniform registers), one elected lane issues
         uint32_t bit = 0, accit = 0;
+        const bool leader = elect_one();
         for (int it = 0; it < g.tiles_per_cta; it++) {
             const int ab = it & 1;
-            if (!mbar_wait(&S.a_full[ab], (it >> 1) & 1)) { atomicExch(g.err, 3); break; }
+            if (!mbar_wait(&S.a_full[ab], (it >> 1) & 1)) { if (leader) atomicExch(g.err, 3); break; }
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(S.a[ab]);
+            const uint32_t a_lo = (smem_u32(S.a[ab]) & 0x3ffffu) >> 4;
             bool bad = false;
             for (int c = 0; c < NCHUNK && !bad; c++, accit++) {
                 const int as = accit & 1, n = chunk_n(c);
-                if (!mbar_wait(&S.acc_empty[as], ((accit >> 1) & 1) ^ 1)) { atomicExch(g.err, 4); bad = true; break; }
+                if (!mbar_wait(&S.acc_empty[as], ((accit >> 1) & 1) ^ 1)) { if (leader) atomicExch(g.err, 4); bad = true; break; }
                 tc_fence_after();
                 const uint32_t idesc = umma_idesc(TILE_M, n);
-                for (int s = 0; s < KSTEPS; s++, bit++) {
-                    const int st = bit % NSTAGE;
-                    if (!mbar_wait(&S.b_full[st], (bit / NSTAGE) & 1)) { atomicExch(g.err, 5); bad = true; break; }
+                const uint32_t a_hi = (uint32_t)((TILE_M * 16) >> 4) << 16, hi = (128u >> 4) | (1u << 14), b_hi_lbo = (uint32_t)((n * 16) >> 4) << 16;
+                for (int s = 0; s < KSTEPS; s += KSUB, bit++) {
+                    const int st = bit % NSTAGE, ks = min(KSUB, KSTEPS - s);
+                    if (!mbar_wait(&S.b_full[st], (bit / NSTAGE) & 1)) { if (leader) atomicExch(g.err, 5); bad = true; break; }
                     tc_fence_after();
-                    const uint64_t ad = umma_desc(a_addr + (uint32_t)s * A_KSTEP_BYTES, TILE_M * 16, 128);
-                    const uint64_t bd = umma_desc(smem_u32(S.b[st]), (uint32_t)n * 16u, 128);
-                    umma_i8(tmem + (uint32_t)as * 256u, ad, bd, idesc, s > 0 ? 1u : 0u);
-                    umma_commit(&S.b_empty[st]);
+                    const uint32_t b_lo = (smem_u32(S.b[st]) & 0x3ffffu) >> 4;
+                    if (leader) {
+#pragma unroll
+                        for (int k = 0; k < KSUB; k++) {
+                            if (k < ks) {
+                                const uint64_t ad = (uint64_t)((a_lo + (uint32_t)(s + k) * (A_KSTEP_BYTES >> 4)) | a_hi) | ((uint64_t)hi << 32);
+                                const uint64_t bd = (uint64_t)((b_lo + (uint32_t)k * (uint32_t)(n * 2)) | b_hi_lbo) | ((uint64_t)hi << 32);
+                                umma_i8(tmem + (uint32_t)as * 256u, ad, bd, idesc, (s + k) > 0 ? 1u : 0u);
+                            }
+                        }
+                        umma_commit(&S.b_empty[st]);
+                    }
+                    __syncwarp();
                 }
-                if (!bad) umma_commit(&S.acc_full[as]);
+                if (!bad && leader) umma_commit(&S.acc_full[as]);
+                __syncwarp();
             }
             if (bad) break;
-            umma_commit(&S.a_empty[ab]);
+            if (leader) umma_commit(&S.a_empty[ab]);
+            __syncwarp();
         }
     } else if (warp >= 2) {
         // ---------------- epilogue: TMEM lane quarter warp % 4, one permutation per thread
@@ -279,10 +306,10 @@ int main(int argc, char** argv) {
             }
         }
     uint8_t *d_a, *d_b; uint64_t *d_chk, *d_raw, *d_red; int* d_err;
-    CHK(cudaMalloc(&d_a, a_tiles.size())); CHK(cudaMalloc(&d_b, b_blocks.size()));
+    CHK(cudaMalloc(&d_a, a_tiles.size())); CHK(cudaMalloc(&d_b, b_blocks.size() * (size_t)grid));
     CHK(cudaMalloc(&d_chk, (size_t)grid * TILE_M * 8)); CHK(cudaMalloc(&d_raw, (size_t)TILE_M * T * 10 * 8)); CHK(cudaMalloc(&d_red, (size_t)TILE_M * T * 5 * 8));
     CHK(cudaMalloc(&d_err, 4));
-    CHK(cudaMemcpy(d_a, a_tiles.data(), a_tiles.size(), cudaMemcpyHostToDevice)); CHK(cudaMemcpy(d_b, b_blocks.data(), b_blocks.size(), cudaMemcpyHostToDevice));
+    CHK(cudaMemcpy(d_a, a_tiles.data(), a_tiles.size(), cudaMemcpyHostToDevice)); for (int i = 0; i < grid; i++) CHK(cudaMemcpy(d_b + (size_t)i * b_blocks.size(), b_blocks.data(), b_blocks.size(), cudaMemcpyHostToDevice));
     CHK(cudaMemset(d_err, 0, 4)); CHK(cudaMemset(d_raw, 0, (size_t)TILE_M * T * 10 * 8)); CHK(cudaMemset(d_red, 0, (size_t)TILE_M * T * 5 * 8));
     const size_t smem = sizeof(Smem) + 1024;
     CHK(cudaFuncSetAttribute(k_matvec_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -290,7 +317,7 @@ int main(int argc, char** argv) {
     printf("{\"tool\": \"umma_i8_matvec\", \"device\": \"%s\", \"sms\": %d, \"tiles_per_cta\": %d, \"smem_bytes\": %zu, \"b_stream_bytes_per_tile\": %zu", prop.name, grid, tiles_per_cta, smem, B_TOTAL_BYTES);
     // correctness pass: mode 1 with the dump of tile 0 (raw limbs and reduced values)
     {
-        Args g{d_a, n_a_tiles, d_b, 1, 1, d_chk, d_raw, d_red, d_err};
+        Args g{d_a, n_a_tiles, d_b, 1, 1, 0, d_chk, d_raw, d_red, d_err};
         k_matvec_umma<<<grid, NTHREADS, smem>>>(g);
         CHK(cudaDeviceSynchronize());
         int err = 0; CHK(cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost));
@@ -306,9 +333,10 @@ int main(int argc, char** argv) {
         }
     }
     // timing: three epilogue modes, best of 3 after one warm-up launch each
-    const char* names[3] = {"limbs", "limbs_and_montgomery_reduction", "mma_only"};
-    for (int mode = 0; mode < 3; mode++) {
-        Args g{d_a, n_a_tiles, d_b, tiles_per_cta, mode, d_chk, nullptr, nullptr, d_err};
+    const char* names[6] = {"limbs", "limbs_and_montgomery_reduction", "mma_only", "mma_only_private_b_copies", "mma_only_no_b_loads", "mma_only_no_b_loads_kind_f8f6f4"};
+    for (int v = 0; v < 6; v++) {
+        const int mode = v < 3 ? v : 2, flags = v == 3 ? 1 : v == 4 ? 2 : v == 5 ? 6 : 0;
+        Args g{d_a, n_a_tiles, d_b, tiles_per_cta, mode, flags, d_chk, nullptr, nullptr, d_err};
         k_matvec_umma<<<grid, NTHREADS, smem>>>(g);
         CHK(cudaDeviceSynchronize());
         float best = 1e30f;
@@ -319,7 +347,7 @@ int main(int argc, char** argv) {
         int err = 0; CHK(cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost));
         const double matvecs = (double)grid * tiles_per_cta * TILE_M;
         printf(", \"%s\": {\"ms\": %.4f, \"matvec_per_s\": %.4e, \"word_products_per_s\": %.4e, \"int8_mac_per_s\": %.4e, \"protocol_error\": %d}",
-               names[mode], best, matvecs / (best * 1e-3), matvecs * T * T / (best * 1e-3), matvecs * (double)KTOT * T * WCOLS / (best * 1e-3), err);
+               names[v], best, matvecs / (best * 1e-3), matvecs * T * T / (best * 1e-3), matvecs * (double)KTOT * T * WCOLS / (best * 1e-3), err);
     }
     printf("}\n");
     return 0;
