@@ -232,7 +232,7 @@ int32_t smw_mf_commit_phase_sharded(smw_ctx* ctx, smw_comm* comm_or_null, uint64
                                     void* roots_out_host, void* r_out_host, void* final_out_host);
 uint64_t smw_ctx_collective_count(const smw_ctx* ctx);   /* NCCL collectives issued through this context */
 /* Tuning: Merkle levels of at least `n` full arity-16 nodes (t = 17) run their linear layers on the INT8 tensor cores
- * (csrc/poseidon_tc.cuh; same digests).  0 = never.  The default comes from SMW_TC_MIN in the environment. */
+ * (csrc/poseidon_tc.cuh; same digests).  0 = never.  Default 16384, or SMW_TC_MIN from the environment. */
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* ctx, uint64_t n);
 
 /* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */

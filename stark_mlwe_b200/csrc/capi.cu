@@ -253,7 +253,9 @@ int build_forest(smw_ctx* c, std::vector<ForestTree>& trees, uint32_t** arena_ou
     SMW_CUDA(c, cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(NodeSeg), cudaMemcpyHostToDevice, c->stream));   // pageable source: staged before the call returns
     for (const Launch& L : launches) {
         int rc = SMW_OK;
-        if (has_multi(c, L.p)) rc = launch_merkle_level_multi(c, L.p, d_segs + L.seg0, L.n, L.total, L.arity);
+        bool all_full = true;
+        for (int i = 0; i < L.n; i++) { const NodeSeg& sg = segs[L.seg0 + i]; all_full = all_full && sg.n_children == sg.n_parents * (uint64_t)L.arity; }
+        if (has_multi(c, L.p)) rc = launch_merkle_level_multi(c, L.p, d_segs + L.seg0, L.n, L.total, L.arity, all_full);
         else for (int i = 0; i < L.n && !rc; i++) {
             const NodeSeg& sg = segs[L.seg0 + i];
             rc = launch_merkle_level(c, L.p, sg.children, sg.n_children, sg.parents, sg.n_parents, L.arity, sg.level, sg.label, 0, sg.pos_offset, 1, 0, 0);
@@ -296,7 +298,7 @@ int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** ou
     if (cudaSetDevice(device) != cudaSuccess) return SMW_ERR_CUDA;
     smw_ctx* c = new smw_ctx();
     c->device = device;
-    { const char* e = getenv("SMW_TC_MIN"); if (e && atoll(e) > 0) c->tc_min_nodes = (uint64_t)atoll(e); }
+    { const char* e = getenv("SMW_TC_MIN"); if (e) c->tc_min_nodes = atoll(e) > 0 ? (uint64_t)atoll(e) : ~0ull; }     // SMW_TC_MIN=0: the tensor-core node hash is never taken
     { const char* rep = getenv("SMW_REP"); c->use_f52 = !(rep && strcmp(rep, "29") == 0); }     // SMW_REP=29: integer-pipe multiplier everywhere
     if (cuda_stream) { c->stream = (cudaStream_t)cuda_stream; c->own_stream = false; }
     else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return SMW_ERR_CUDA; } c->own_stream = true; }

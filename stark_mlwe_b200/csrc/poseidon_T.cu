@@ -128,9 +128,15 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     return SMW_OK;
 }
 // several runs (explicit device segment array) of one level in one launch; widths without FP64-pipe tables take one launch per run
-template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const NodeSeg* d_segs, int n_segs, uint64_t total, int arity) {
+template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const NodeSeg* d_segs, int n_segs, uint64_t total, int arity, bool all_full) {
     smw_params* p = const_cast<smw_params*>(cp);
     if (n_segs <= 0 || total == 0) return SMW_OK;
+#if SMW_T == 17
+    if (c->use_f52 && p->d_tables52 && arity == 16 && all_full && total >= c->tc_min_nodes) {
+        LevelBatch B{}; B.segs = d_segs; B.n_segs = n_segs; B.total = total;
+        return tc::merkle_level_tc(c, p, B);
+    }
+#endif
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52) {
         if (total <= coop_max_nodes()) {

@@ -340,8 +340,8 @@ int launch_pair_leaves(smw_ctx* c, const smw_params* p, const uint32_t* d_f, con
     DISPATCH_T(p->t, return pair_leaves_T<T>(c, p, d_f, d_cp, n, arity, label, pos_offset, d_out, cp_div));
     return SMW_OK;
 }
-int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity) {
-    DISPATCH_T(p->t, return merkle_level_multi_T<T>(c, p, d_segs, n_segs, total_nodes, arity));
+int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity, bool all_full) {
+    DISPATCH_T(p->t, return merkle_level_multi_T<T>(c, p, d_segs, n_segs, total_nodes, arity, all_full));
     return SMW_OK;
 }
 int launch_pair_leaves_multi(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total) {

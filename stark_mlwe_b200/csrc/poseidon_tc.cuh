@@ -107,17 +107,22 @@ SMW_DEV void tmem_ld16(uint32_t taddr, uint32_t* r) {
 }
 SMW_DEV void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// 16 int32 columns k0 .. k0+15 (weights 2^(8k), each < 2^26) added into the ten lazily carried 52-bit limb columns.
-// Column 63 is structurally zero.  All shifts and masks are compile-time constants.
+// 16 int32 columns k0 .. k0+15 (weights 2^(8k), each < 2^26) added into the ten lazily carried 52-bit limb columns (each stays < 2^60).
+// Column 63 is structurally zero.  A column lands at bit sh = 8k mod 52 of limb 8k / 52: for sh < 32 that is ONE multiply-add on the
+// FMA pipe (IMAD.WIDE.U32 c, 2^sh, acc: shift and 64-bit accumulation in one instruction — the ALU pipe is the busiest pipe of the
+// epilogue); for sh >= 32 the part below bit 52 goes into the high word of the limb and the rest into the next limb.
 template <int K0> SMW_DEV void columns_to_limbs16(const uint32_t* c, uint64_t* acc) {
 #pragma unroll
     for (int i = 0; i < 16; i++) {
         const int k = K0 + i;
         if (k >= 63) continue;
         const int bit = 8 * k, l = bit / 52, sh = bit % 52;
-        const uint64_t v = c[i];
-        if (sh <= 30) acc[l] += v << sh;
-        else { acc[l] += (v & ((1ull << (52 - sh)) - 1ull)) << sh; acc[l + 1] += v >> (52 - sh); }
+        if (sh < 32) acc[l] += (uint64_t)c[i] * (uint64_t)(1u << sh);
+        else {
+            const uint32_t lo = c[i] & ((1u << (52 - sh)) - 1u);                    // 52 - sh <= 20 bits, shifted to bit sh - 32 of the high word
+            acc[l] += (uint64_t)(lo << (sh - 32)) << 32;
+            acc[l + 1] += (uint64_t)(c[i] >> (52 - sh));
+        }
     }
 }
 

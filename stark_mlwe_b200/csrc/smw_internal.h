@@ -65,7 +65,7 @@ struct smw_ctx {
     // side streams for independent launch chains (the per-layer trees of a FRI commit phase), joined back into `stream`
     std::vector<cudaStream_t> side; std::vector<cudaEvent_t> side_ev; cudaEvent_t fan_ev = nullptr;
     bool use_f52 = true;                         // widths 9/17 batch kernels on the FP64-pipe multiplier (SMW_REP=29 in the environment selects the integer one)
-    uint64_t tc_min_nodes = ~0ull;               // full arity-16 levels of at least this many nodes take the tensor-core pipeline (poseidon_tc.cu); SMW_TC_MIN / smw_ctx_set_tc_min_nodes
+    uint64_t tc_min_nodes = 16384;               // full arity-16 levels of at least this many nodes take the tensor-core pipeline (poseidon_tc.cu); SMW_TC_MIN / smw_ctx_set_tc_min_nodes
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
     uint64_t collectives = 0;                    // NCCL collectives / grouped exchanges issued through this context
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
@@ -192,7 +192,7 @@ int launch_legacy_nodes(smw_ctx* c, const smw_params* p, int mode, const uint32_
 int launch_tr_hash_batch(smw_ctx* c, const smw_params* trp, const uint32_t* d_tmpl, int lane0, int k, const uint32_t* d_xs, size_t count, uint32_t* d_out);
 int launch_hash_legacy_single(smw_ctx* c, const smw_params* p, const uint32_t* d_in, size_t n, const uint32_t* d_tag, uint32_t* d_out);
 // several runs of one level in one launch (explicit device segment array); all runs share the parameter set and the arity
-int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);
+int launch_merkle_level_multi(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity, bool all_full = false);   // all_full: every node of every run has exactly `arity` children
 int launch_pair_leaves_multi(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total);
 int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* tr_params, const uint32_t* d_template_le256, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, uint64_t total);
 // transcript program: state' = run(state, pos; immediates A, ext elements B, immediates C, optional final permute)
@@ -216,7 +216,7 @@ template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32
 template <int T> int hash_groups_T(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                                    size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
 namespace tc { int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B); }     // poseidon_tc.cu
-template <int T> int merkle_level_multi_T(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity);
+template <int T> int merkle_level_multi_T(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity, bool all_full);
 template <int T> int pair_leaves_multi_T(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total);
 template <int T> int hash_ds_single_T(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);
 

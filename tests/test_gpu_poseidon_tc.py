@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 def tc_ctx(ctx):
     ctx.set_tc_min_nodes(1)          # every full arity-16 level takes the tensor-core pipeline
     yield ctx
-    ctx.set_tc_min_nodes(0)
+    ctx.set_tc_min_nodes(16384)      # the library's default
 
 
 @pytest.mark.parametrize("n,label", [(16, 0), (16 * 5, 3), (16 * 128, 7), (16 * 300, 0), (1 << 16, 11)])
@@ -43,10 +43,11 @@ def test_commit_columns_matches_oracle(tc_ctx, smw, O, rnd):
 def test_same_digests_as_the_interpreter(ctx, smw, rnd):
     leaves = rnd(5, 1 << 14)
     cfg = smw.MerkleChannelCfg.new(ctx, 16)
-    a = smw.MerkleTree.new(leaves, cfg).root()
-    ctx.set_tc_min_nodes(1)
     try:
+        ctx.set_tc_min_nodes(0)                  # never: thread-per-node interpreter / cooperative kernels
+        a = smw.MerkleTree.new(leaves, cfg).root()
+        ctx.set_tc_min_nodes(1)
         b = smw.MerkleTree.new(leaves, cfg).root()
     finally:
-        ctx.set_tc_min_nodes(0)
+        ctx.set_tc_min_nodes(16384)
     assert np.array_equal(a, b)
