@@ -382,6 +382,7 @@ def main():
     ap.add_argument("--cpu-cols", type=int, default=2)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-interp", action="store_true", help="skip the one comparison step on the thread-per-node interpreter")
     ap.add_argument("--no-fri", action="store_true", help="skip the cfg3 / cfg4 / cfg5 sub-records")
     ap.add_argument("--cfg4-log-n", type=int, default=-1, help="rows (log2) of the strong-scaling leg; default 20, and the full 24 at 8 GPUs")
     ap.add_argument("--cfg5-log-n", type=int, default=26)
@@ -438,6 +439,16 @@ def main():
     clocks = sampler.stop() if sampler else None
     value = world * committed_per_rank * args.steps / secs
 
+    # ---- the same step on the thread-per-node interpreter (tensor-core path off), once, for the roofline record
+    interp = None
+    if rank == 0 and world == 1 and not args.no_interp and ctx.tc_node_counts(smw.commitment_default_params(ctx))["fp64_instr"]:
+        keep = ctx.tc_node_counts(smw.commitment_default_params(ctx))["min_nodes"]
+        ctx.set_tc_min_nodes(0)
+        i_secs, roots_i = T.run(lambda: step(dev), 1)
+        ctx.set_tc_min_nodes(keep if keep < (1 << 63) else 0)
+        assert np.array_equal(roots_i, roots), "tensor-core and interpreter node hashes disagree"
+        interp = {"value": world * committed_per_rank / i_secs, "unit": UNIT, "ms_per_step": i_secs * 1e3}
+
     # ---- e2e: the same call with HOST buffers (pinned input copied H2D, roots D2H) inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -463,13 +474,13 @@ def main():
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": secs * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "Pallas Fr, exact integer arithmetic: 5x52-bit limbs carried in f64 (DFMA.RZ split) in the Poseidon kernels, 8x32-bit in NTT/folds", "data": "synthetic",
+            "dtype": "Pallas Fr, exact integer arithmetic: u8 limbs x u8 Toeplitz constants -> s32 on the tensor cores for the Poseidon linear layers, 5x52-bit limbs carried in f64 (DFMA.RZ split) for S-boxes and Montgomery reductions, 9x29-bit in the NTT", "data": "synthetic",
             "config": {"workload": "cfg2: 2^%d-row trace, %d columns per GPU, blow-up %d: coset LDE + arity-16 Poseidon-Merkle commit per column" % (args.log_n, nc, 1 << lb),
                        "field": "Pallas Fr (the field the reference uses; SURVEY.md D1)", "columns_total": world * nc, "committed_elems_per_step": world * committed_per_rank,
                        "l2": "inputs (%.1f GB) and extended columns (%.1f GB) exceed the 126 MB L2" % (nc * n * 32 / 1e9, nc * N * 32 / 1e9),
                        "sharding": "columns, %d per GPU; roots all-gathered by the library's NCCL communicator" % nc,
                        "vs_baseline_note": "BASELINE.json publishes no number for this metric (published: {})"},
-            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline_record(ctx, smw, prof, args, nc, N),
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline_record(ctx, smw, prof, args, nc, N, interp),
         }
         out.update(legs)
         if not args.no_cpu and world == 1:
@@ -483,30 +494,69 @@ def main():
         dist.destroy_process_group()
 
 
-def roofline_record(ctx, smw, prof, args, nc, N):
-    """Dominant kernel k_merkle_level52<17>.  frac = instructions the kernel ISSUES on the pipe it is bound by (DFMA.RZ + DADD of the
-    device program, counted from the program) / kernel time / that pipe's rate measured live in this run.  The dense count of the
-    reference is reported beside it as `algorithmic_speedup`, never as a fraction."""
+def peak_int8_tmacs():
+    """dense INT8 multiply-accumulates per second of the tensor cores: twice the bf16 rate measured on this pool (MEASURED_PEAKS.json,
+    sustained figure: the stages run inside a long step), else twice the fallback of B200_PROFILING.md; 1 MAC = 2 ops"""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"]) * 2 / 2, "2 x MEASURED_PEAKS.json bf16_tflops_sustained / 2 ops per MAC"
+    except Exception:
+        return 1650.0, "2 x the bf16 fallback of B200_PROFILING.md / 2 ops per MAC"
+
+
+def tc_split(ctx, smw, nc, N):
+    """nodes of one step that the tensor-core node hash takes (full arity-16 levels of >= min_nodes nodes per launch) and the rest"""
+    cnt = ctx.tc_node_counts(smw.commitment_default_params(ctx))
+    tc_nodes, other_perms, cn = 0, 0, N
+    while cn > 1:
+        nn = (cn + 15) // 16
+        if cnt["fp64_instr"] and cn == nn * 16 and nn * nc >= cnt["min_nodes"]:
+            tc_nodes += nn * nc
+        else:
+            full, rem = cn // 16, cn % 16
+            other_perms += nc * (full * 2 + (((4 + rem + 1 + 15) // 16) if rem else 0))
+        cn = nn
+    return cnt, tc_nodes, other_perms
+
+
+def roofline_record(ctx, smw, prof, args, nc, N, interp=None):
+    """Dominant kernels: the staged tensor-core node hash (k_tc_stage<*>, k_tc_chain, k_tc_head; csrc/poseidon_tc.cuh) when the levels are
+    large enough, else k_merkle_level52<17>.  Two pipes carry the work, so two fractions are reported, both from counts of what the
+    kernels EXECUTE (never the reference's dense count): `frac` = FP64-pipe instructions (S-boxes, Montgomery reductions) / kernel time /
+    the DFMA rate measured live in this run; `tensor.frac` = int8 MACs of the linear layers / kernel time / the dense INT8 rate.  The
+    epilogues are bound by instruction issue across the ALU and FP64 pipes (profiles/r03*_ncu_tc_stage*), so neither reaches 1."""
     ml_ms, ml_launches = prof["merkle_level"]
     perms = nc * tree_perms(N, 16, 16)
     ml_s = ml_ms * 1e-3 / args.steps
     pdef = smw.commitment_default_params(ctx)
     fp_perm, mac_perm = pdef.executed_fp64_ops(), pdef.executed_macs()
     fp, mac = ctx.pipe_rate(1), ctx.pipe_rate(0)
+    cnt, tc_nodes, other_perms = tc_split(ctx, smw, nc, N)
     alg_bytes = nc * (N * 32 + sum_levels_bytes(N))
-    rec = {"kernel": "k_merkle_level52<17> (+ k_nodes_coop52<17> for the tree tops)", "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps,
+    name = "k_merkle_level52<17> (+ k_nodes_coop52<17> for the tree tops)"
+    if tc_nodes:
+        name = "tensor-core node hash: k_tc_stage<0..3> + k_tc_chain + k_tc_head (%.1f %% of the nodes; the rest k_merkle_level52<17> / k_nodes_coop52<17>)" % (100.0 * 2 * tc_nodes / perms)
+    rec = {"kernel": name, "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps,
            "permutations_per_step": perms, "permutations_per_s": perms / ml_s,
            "hbm": {"achieved": alg_bytes / ml_s / 1e9, "peak": peak_hbm(), "unit": "GB/s", "frac": alg_bytes / ml_s / 1e9 / peak_hbm()},
            "traffic": TRAFFIC_NCU["bytes"], "traffic_source": TRAFFIC_NCU,
            "step_share_ms": {k: v[0] / args.steps for k, v in prof.items() if v[1]}}
     if fp_perm:
-        ach = perms * fp_perm / ml_s
+        fp_exec = tc_nodes * cnt["fp64_instr"] + other_perms * fp_perm
+        ach = fp_exec / ml_s
         rec.update({"bound": "fp64", "unit": "T fp64 lane-instr/s (DFMA.RZ + DADD)", "achieved": ach / 1e12, "peak": fp["lanes_per_s"] / 1e12, "frac": ach / fp["lanes_per_s"],
-                    "fp64_ops_per_permutation": fp_perm,
+                    "fp64_ops_per_permutation": fp_exec / perms, "fp64_ops_per_permutation_interpreter": fp_perm,
                     "peak_measurement": dict(fp, how="16 independent DFMA.RZ chains x 512 threads/SM, ~40 ms per repetition, best of 3 (smw_diag_pipe_rate); "
                                                      "lanes_per_s = warp_instr_per_clk_per_sm x 32 x n_sm x sm_hz_during, sm_hz_during = in-kernel clock64 ticks / event time"),
                     "peak_at_max_clock": fp["warp_instr_per_clk_per_sm"] * 32 * fp["n_sm"] * fp["sm_max_hz"] / 1e12,
                     "frac_at_max_clock": ach / (fp["warp_instr_per_clk_per_sm"] * 32 * fp["n_sm"] * fp["sm_max_hz"])})
+        if tc_nodes:
+            pk, how = peak_int8_tmacs()
+            tm = tc_nodes * cnt["int8_mac"] / ml_s / 1e12
+            rec["tensor"] = {"bound": "tensor", "unit": "T int8 MAC/s (tcgen05.mma kind::i8, Toeplitz zeros included)", "achieved": tm, "peak": pk, "frac": tm / pk, "peak_source": how,
+                             "int8_mac_per_node": cnt["int8_mac"], "word_products_per_node": cnt["word_products"], "group": cnt["group"], "launches_per_batch": cnt["launches_per_batch"]}
+        if interp:
+            rec["interpreter_same_run"] = dict(interp, note="the same step with the tensor-core path switched off (smw_ctx_set_tc_min_nodes(0)): thread-per-node FP64 interpreter, "
+                                                            "%d FP64 instructions per permutation" % fp_perm)
     else:
         ach = perms * mac_perm / ml_s
         rec.update({"bound": "imad", "unit": "T mac32/s", "achieved": ach / 1e12, "peak": mac["lanes_per_s"] / 1e12, "frac": ach / mac["lanes_per_s"], "mac_per_permutation": mac_perm})

@@ -234,6 +234,9 @@ uint64_t smw_ctx_collective_count(const smw_ctx* ctx);   /* NCCL collectives iss
 /* Tuning: Merkle levels of at least `n` full arity-16 nodes (t = 17) run their linear layers on the INT8 tensor cores
  * (csrc/poseidon_tc.cuh; same digests).  0 = never.  Default 16384, or SMW_TC_MIN from the environment. */
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* ctx, uint64_t n);
+/* What one arity-16 node costs on that path: out6 = {FP64-pipe instructions, int8 MACs on the tensor cores, word products,
+ * kernel launches per batch, partial-round group size, the context's current threshold}; zeros 0..4 when the path is unavailable. */
+int32_t smw_diag_tc_node_counts(const smw_ctx* ctx, const smw_params* params, uint64_t* out6);
 
 /* ---- "next" tier: openings, verification, DEEP-ALI merge ---------------------------------- */
 int32_t smw_index_from_seed(smw_ctx* ctx, const void* seeds_fr, size_t n, uint64_t n_pow2, uint64_t* out_idx_host, int32_t mem);   /* index_from_seed, deep_ali/src/fri.rs:178-183, element-wise */

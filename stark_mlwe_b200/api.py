@@ -85,6 +85,12 @@ class Context:
     def collective_count(self):
         return int(self.L.smw_ctx_collective_count(self.h))
 
+    def tc_node_counts(self, params):
+        """{fp64_instr, int8_mac, word_products, launches_per_batch, group, min_nodes} of one arity-16 node on the tensor-core path"""
+        out = (C.c_uint64 * 6)()
+        self.check(self.L.smw_diag_tc_node_counts(self.h, params.h, out))
+        return dict(zip(("fp64_instr", "int8_mac", "word_products", "launches_per_batch", "group", "min_nodes"), [int(v) for v in out]))
+
     def set_tc_min_nodes(self, n):
         """Merkle levels of >= n full arity-16 nodes run their linear layers on the INT8 tensor cores (0 = never)"""
         self.check(self.L.smw_ctx_set_tc_min_nodes(self.h, int(n)))

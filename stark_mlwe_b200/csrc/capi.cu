@@ -1278,6 +1278,13 @@ int32_t smw_ntt_cyclic_to_chunks(smw_ctx* c, smw_comm* m, void* in_dev, void* ou
     return launch_dft_strided(c, (uint32_t*)out_dev, log_g, M / G, M / G, d_wpow);             // length-G DFT across the received pieces
 }
 uint64_t smw_ctx_collective_count(const smw_ctx* c) { return c ? c->collectives : 0; }
+int32_t smw_diag_tc_node_counts(const smw_ctx* c, const smw_params* p, uint64_t* out6) {
+    if (!c || !p || !out6) return SMW_ERR_INVALID_ARG;
+    for (int i = 0; i < 6; i++) out6[i] = 0;
+    out6[5] = c->tc_min_nodes;
+    if (p->t == 17 && c->use_f52 && p->d_tables52) smw::tc::node_counts(p->t, p->rp, out6);
+    return SMW_OK;
+}
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* c, uint64_t n) { if (!c) return SMW_ERR_INVALID_ARG; c->tc_min_nodes = n ? n : ~0ull; return SMW_OK; }
 
 // root of the tree whose DS-level-`level` children are `nodes` (level 0: the leaves / leaf digests themselves)

@@ -153,6 +153,28 @@ template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageAr
     return SMW_OK;
 }
 
+// What one arity-16 node (two permutations) costs on this path, counted from the launch sequence below:
+// out[0] = FP64-pipe instructions (DFMA.RZ + DADD: 75 per general limb product block, 45 per squaring, 85 per Montgomery
+// reduction, 5 per byte packing), out[1] = int8 multiply-accumulates the tensor cores execute (Toeplitz zeros included),
+// out[2] = word products (row x word, 32 x 64 byte MACs each), out[3] = kernel launches per batch, out[4] = group size.
+void node_counts(int t, int rp, uint64_t out[5]) {
+    const uint64_t G = (uint64_t)group_size(), NG = (uint64_t)rp / G, T = (uint64_t)t;
+    const uint64_t RED = 85, MUL = 75, SQR = 45, PACK = 5, SBOX = 2 * (SQR + RED) + (MUL + RED);
+    uint64_t fp = 0, wp = 0, launches = 1;
+    fp += T * (SBOX + RED + PACK) + 4 * MUL;                                          // head: 17 lanes (4 DS products), ARK, S-box
+    for (int perm = 0; perm < 2; perm++) {
+        fp += 6 * T * (RED + SBOX + PACK); wp += 6 * T * T; launches += 6;            // full rounds 1-3, 5-7: stage + S-box epilogue
+        fp += (T + G) * RED + T * PACK; wp += (T + G) * T; launches += 1;             // round 3 -> state and first dots
+        fp += NG * (G * (RED + SBOX + PACK) + (G * (G - 1) / 2) * MUL); launches += NG;            // chains
+        fp += (NG - 1) * ((T + G) * RED + T * PACK); wp += (NG - 1) * (T + G) * (T + G); launches += NG - 1;   // group stages
+        fp += T * (RED + SBOX + PACK); wp += T * (T + G); launches += 1;              // last group stage -> round 4 S-boxes
+        if (perm == 0) { fp += T * (RED + SBOX + PACK); wp += T * T; }                // round 7 + second rate block + round 0 S-boxes
+        else { fp += RED + MUL + RED; wp += T; }                                      // round 7, lane 0 only, external form
+        launches += 1;
+    }
+    out[0] = fp; out[1] = wp * 32 * WCOLS; out[2] = wp; out[3] = launches; out[4] = G;
+}
+
 // Hashes the nodes of `B` (every node with exactly 16 children) with the tensor-core pipeline.  The caller has checked the shape.
 int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
     if (!p->tc) { Tables* T = nullptr; int rc = build_tables(c, p, group_size(), &T); if (rc) return rc; p->tc = T; p->tc_free = free_tables; }
