@@ -184,6 +184,14 @@ int32_t smw_merkle_root_from_level(smw_ctx* ctx, smw_params* p, int32_t arity, u
 
 /* ---- Merkle-folded sum-check commit loop (channel/src/lib.rs:406-416, 592-598, 600-657) ---- */
 int32_t smw_sumcheck_round_coeffs(smw_ctx* ctx, const void* layer, size_t n, void* c0_host, void* c1_host, int32_t mem);
+/* NO COUNTERPART IN THE REFERENCE.  smw_sumcheck_round_coeffs for callers that may
+ * not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): `layer_dev` (n elements, n even,
+ * 0 < n <= 2^26) and `c0c1_out_dev` (64 bytes: c0 then c1) are DEVICE pointers; the per-block partial sums live in a fixed 64 KiB
+ * device array inside the library (held by every GPU that loads it until the process exits).  Calls no cudaMalloc / cudaFree;
+ * enqueues two kernels on the context's stream and returns without synchronising.  Larger n is rejected with SMW_ERR_INVALID_ARG.
+ * Every call on a device shares the array: calls that overlap on the GPU race.  The first call per device looks the array's address
+ * up (cudaGetSymbolAddress): make it once before capturing a graph. */
+int32_t smw_sumcheck_round_coeffs_noalloc(smw_ctx* ctx, const void* layer_dev, size_t n, void* c0c1_out_dev);
 int32_t smw_mf_round_challenge_from_root(smw_ctx* ctx, uint64_t round_idx, const void* prev_root_host, smw_params* tr_params_or_null, void* out_fr_host);
 int32_t smw_mf_fold(smw_ctx* ctx, const void* cur, size_t n, const void* r_fr_host, void* next, int32_t mem);
 int32_t smw_mf_commit_phase(smw_ctx* ctx, uint64_t ds_tag, const void* table, size_t n, int32_t mem, void* roots_out_host /* k+1 */, void* r_out_host /* k */, void* final_out_host);

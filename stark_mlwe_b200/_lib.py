@@ -49,7 +49,7 @@ def load():
         "smw_verify_many_legacy": [vp, vp, i32, vp, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
         "smw_verify_pairs_legacy": [vp, vp, i32, vp, vp, vp, vp, sz, vp, sz, i32, vp, vp, vp, vp, vp],
         "smw_comm_unique_id": [vp], "smw_comm_init": [vp, vp, i32, i32, vp], "smw_comm_rank": [vp], "smw_comm_world": [vp], "smw_comm_free": [vp],
-        "smw_comm_all_gather": [vp, vp, vp, sz], "smw_ctx_collective_count": [vp], "smw_ctx_set_tc_min_nodes": [vp, u64], "smw_diag_tc_node_counts": [vp, vp, vp],
+        "smw_comm_all_gather": [vp, vp, vp, sz], "smw_ctx_collective_count": [vp], "smw_ctx_set_tc_min_nodes": [vp, u64], "smw_diag_tc_node_counts": [vp, vp, vp], "smw_sumcheck_round_coeffs_noalloc": [vp, vp, sz, vp],
         "smw_fri_roots_sharded": [vp, vp, vp, sz, i32, vp, sz, vp, i32, u64, i32, vp],
         "smw_ntt_cyclic_to_chunks": [vp, vp, vp, vp, i32],
         "smw_mf_commit_phase_sharded": [vp, vp, u64, vp, sz, i32, vp, vp, vp],

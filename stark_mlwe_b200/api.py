@@ -847,6 +847,16 @@ def sumcheck_round_coeffs(ctx, layer):
     return c0[0], c1[0]
 
 
+def sumcheck_round_coeffs_noalloc(ctx, layer_dev, out_dev):
+    """smw_sumcheck_round_coeffs_noalloc: no allocation anywhere (fixed 64 KiB scratch inside the library, n <= 2^26).  `layer_dev` is a
+    CUDA tensor of n elements (n, 4) int64/uint64, `out_dev` a CUDA tensor of 8 x 8 bytes that receives c0 then c1; asynchronous on the
+    context's stream.  No counterpart in the reference."""
+    assert layer_dev.is_cuda and out_dev.is_cuda and layer_dev.is_contiguous() and out_dev.is_contiguous()
+    assert out_dev.numel() * out_dev.element_size() >= 64
+    n = layer_dev.numel() * layer_dev.element_size() // 32
+    ctx.check(ctx.L.smw_sumcheck_round_coeffs_noalloc(ctx.h, C.c_void_p(layer_dev.data_ptr()), n, C.c_void_p(out_dev.data_ptr())))
+
+
 def mf_round_challenge_from_root(ctx, round_idx, prev_root, tr_params=None):
     """channel/src/lib.rs:592-598"""
     r = _fr1(prev_root)

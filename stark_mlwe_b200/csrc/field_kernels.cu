@@ -365,4 +365,50 @@ int launch_diag_rate_ex(smw_ctx* c, int fp64, double* mac_per_s, double* winstr,
     return SMW_OK;
 }
 
+// ---------------------------------------------------------------------------------------- allocation-free round coefficients
+// smw_sumcheck_round_coeffs for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.  Same two launches as
+// launch_mf_coeffs above, but the per-block partial sums live in a file-scope device array instead of a cudaMalloc'ed buffer:
+//   * SMW_NOALLOC_MAX_BLOCKS x 2 x 32 B = 64 KiB, held by every GPU that loads the library until the process exits;
+//   * every call on a device shares it: calls that overlap on the GPU (different streams / contexts) race;
+//   * nothing in it has to start at zero — the first launch overwrites exactly the `blocks` entries the second one reads, so
+//     what an earlier (possibly larger) call left behind is never read.
+// In host code `g_noalloc_partials` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+constexpr unsigned SMW_NOALLOC_MAX_BLOCKS = 1024;
+constexpr size_t SMW_NOALLOC_MAX_N = (size_t)1 << 26;          // elements per call (2 GiB of input): BASELINE's largest layer
+static __device__ __align__(256) uint32_t g_noalloc_partials[SMW_NOALLOC_MAX_BLOCKS * 2 * 8];
+
+static int noalloc_partials_ptr(smw_ctx* c, uint32_t** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static uint32_t* ptr[MAX_DEV] = {};
+    if (c->device < 0 || c->device >= MAX_DEV) return set_err(c, SMW_ERR_INVALID_ARG, "smw_sumcheck_round_coeffs_noalloc: device index beyond 63");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[c->device]) {
+        void* p = nullptr;
+        SMW_CUDA(c, cudaGetSymbolAddress(&p, g_noalloc_partials));          // the device selected by the caller (cudaSetDevice) is current
+        ptr[c->device] = (uint32_t*)p;
+    }
+    *out = ptr[c->device];
+    return SMW_OK;
+}
+
 } // namespace smw
+
+int32_t smw_sumcheck_round_coeffs_noalloc(smw_ctx* c, const void* layer_dev, size_t n, void* c0c1_out_dev) {
+    using namespace smw;
+    if (!c) return SMW_ERR_INVALID_ARG;
+    if (!layer_dev || !c0c1_out_dev || n == 0 || (n & 1)) return set_err(c, SMW_ERR_INVALID_ARG, "smw_sumcheck_round_coeffs_noalloc: device pointers and an even, non-zero length are required");
+    if (n > SMW_NOALLOC_MAX_N) return set_err(c, SMW_ERR_INVALID_ARG, "smw_sumcheck_round_coeffs_noalloc: n exceeds the fixed scratch's limit of 2^26 elements (use smw_sumcheck_round_coeffs)");
+    SMW_CUDA(c, cudaSetDevice(c->device));
+    uint32_t* d_part = nullptr;
+    int rc = noalloc_partials_ptr(c, &d_part); if (rc) return rc;
+    const size_t pairs = n / 2;
+    unsigned blocks = (unsigned)std::min<size_t>((pairs + 255) / 256, SMW_NOALLOC_MAX_BLOCKS); if (blocks == 0) blocks = 1;
+    k_mf_coeffs<<<blocks, 256, 0, c->stream>>>((const uint32_t*)layer_dev, pairs, d_part, 0);
+    k_mf_coeffs<<<1, 256, 0, c->stream>>>(d_part, blocks, (uint32_t*)c0c1_out_dev, 1);
+    c->launches += 2;
+    SMW_CUDA(c, cudaGetLastError());
+    return SMW_OK;
+}
