@@ -49,20 +49,23 @@ Mat matmul(const Mat& A, const Mat& B) {
 }
 
 size_t core_pos(int rows, int row, int k) { return (size_t)(k / 16) * rows * 16 + (size_t)(row / 8) * 128 + (size_t)(row % 8) * 16 + (size_t)(k % 16); }
-// Toeplitz byte blocks [chunk][k-step] of W (nw x kw words; entries converted to the canonical 2^260-form integers the state uses)
-std::vector<uint8_t> toeplitz_blocks(const Mat& W, const U256& c260) {
+// Byte blocks [chunk][k-step] of W (nw x kw field elements, external form): row (w, c) of k-step j holds byte_c((W[w][j] * 2^(8a)) mod p)
+// at k = a — the reduced constants of poseidon_tc.cuh, in the UMMA K-major core-matrix layout
+std::vector<uint8_t> reduced_blocks(const Mat& W) {
     const int nw = (int)W.size(), kw = (int)W[0].size(), n_chunks = (nw + CHUNK_WORDS - 1) / CHUNK_WORDS;
     std::vector<uint8_t> out((size_t)n_chunks * kw * B_BLOCK_MAX, 0);
+    U256 shift[32];
+    for (int a = 0; a < 32; a++) { shift[a] = ZERO; shift[a].v[a / 8] = 1ull << (8 * (a % 8)); }       // the plain integer 2^(8a) < p
     for (int c = 0; c < n_chunks; c++) {
         const int words = std::min(CHUNK_WORDS, nw - c * CHUNK_WORDS), n_rows = words * WCOLS;
         for (int j = 0; j < kw; j++) {
             uint8_t* blk = out.data() + (size_t)c * kw * B_BLOCK_MAX + (size_t)j * n_rows * 32;
-            for (int w = 0; w < words; w++) {
-                const U256 e = mont_mul(W[c * CHUNK_WORDS + w][j], c260);
-                uint8_t byte[32]; memcpy(byte, e.v, 32);
-                for (int col = 0; col < WCOLS; col++)
-                    for (int a = 0; a < 32; a++) { const int d = col - a; if (d >= 0 && d < 32) blk[core_pos(n_rows, w * WCOLS + col, a)] = byte[d]; }
-            }
+            for (int w = 0; w < words; w++)
+                for (int a = 0; a < 32; a++) {
+                    const U256 e = mont_mul(W[c * CHUNK_WORDS + w][j], shift[a]);      // (W 2^256) (2^(8a)) / 2^256 = W 2^(8a) mod p, canonical
+                    uint8_t byte[32]; memcpy(byte, e.v, 32);
+                    for (int col = 0; col < WCOLS; col++) blk[core_pos(n_rows, w * WCOLS + col, a)] = byte[col];
+                }
         }
     }
     return out;
@@ -116,11 +119,11 @@ static int build_tables(smw_ctx* c, smw_params* p, int G, Tables** out) {
     Mat Bgrp = Wv; for (int k = 0; k < G; k++) Bgrp.push_back(Wd[k]);
     Mat Bfin(1, M[0]);
     Tables* T = new Tables; T->G = G;
-    int rc = upload(c, toeplitz_blocks(M, c260), &T->b_full);
-    if (!rc) rc = upload(c, toeplitz_blocks(Br3, c260), &T->b_r3);
-    if (!rc) rc = upload(c, toeplitz_blocks(Bgrp, c260), &T->b_grp);
-    if (!rc) rc = upload(c, toeplitz_blocks(Wv, c260), &T->b_last);
-    if (!rc) rc = upload(c, toeplitz_blocks(Bfin, c260), &T->b_final);
+    int rc = upload(c, reduced_blocks(M), &T->b_full);
+    if (!rc) rc = upload(c, reduced_blocks(Br3), &T->b_r3);
+    if (!rc) rc = upload(c, reduced_blocks(Bgrp), &T->b_grp);
+    if (!rc) rc = upload(c, reduced_blocks(Wv), &T->b_last);
+    if (!rc) rc = upload(c, reduced_blocks(Bfin), &T->b_final);
     if (!rc) {
         std::vector<double> gm((size_t)G * 5);
         for (int d = 0; d < G; d++) {
@@ -155,21 +158,21 @@ template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageAr
 
 // What one arity-16 node (two permutations) costs on this path, counted from the launch sequence below:
 // out[0] = FP64-pipe instructions (DFMA.RZ + DADD: 75 per general limb product block, 45 per squaring, 85 per Montgomery
-// reduction, 5 per byte packing), out[1] = int8 multiply-accumulates the tensor cores execute (Toeplitz zeros included),
-// out[2] = word products (row x word, 32 x 64 byte MACs each), out[3] = kernel launches per batch, out[4] = group size.
+// reduction, 15 per stage output (limb conversions of the fold), 5 per byte packing), out[1] = int8 multiply-accumulates the tensor
+// cores execute, out[2] = word products (row x word, 32 x 32 byte MACs each), out[3] = kernel launches per batch, out[4] = group size.
 void node_counts(int t, int rp, uint64_t out[5]) {
     const uint64_t G = (uint64_t)group_size(), NG = (uint64_t)rp / G, T = (uint64_t)t;
-    const uint64_t RED = 85, MUL = 75, SQR = 45, PACK = 5, SBOX = 2 * (SQR + RED) + (MUL + RED);
+    const uint64_t RED = 85, MUL = 75, SQR = 45, PACK = 5, FOLD = 15, SBOX = 2 * (SQR + RED) + (MUL + RED);
     uint64_t fp = 0, wp = 0, launches = 1;
     fp += T * (SBOX + RED + PACK) + 4 * MUL;                                          // head: 17 lanes (4 DS products), ARK, S-box
     for (int perm = 0; perm < 2; perm++) {
-        fp += 6 * T * (RED + SBOX + PACK); wp += 6 * T * T; launches += 6;            // full rounds 1-3, 5-7: stage + S-box epilogue
-        fp += (T + G) * RED + T * PACK; wp += (T + G) * T; launches += 1;             // round 3 -> state and first dots
+        fp += 6 * T * (FOLD + SBOX + PACK); wp += 6 * T * T; launches += 6;           // full rounds 1-3, 5-7: stage + S-box epilogue
+        fp += (T + G) * FOLD + T * PACK; wp += (T + G) * T; launches += 1;            // round 3 -> state and first dots
         fp += NG * (G * (RED + SBOX + PACK) + (G * (G - 1) / 2) * MUL); launches += NG;            // chains
-        fp += (NG - 1) * ((T + G) * RED + T * PACK); wp += (NG - 1) * (T + G) * (T + G); launches += NG - 1;   // group stages
-        fp += T * (RED + SBOX + PACK); wp += T * (T + G); launches += 1;              // last group stage -> round 4 S-boxes
-        if (perm == 0) { fp += T * (RED + SBOX + PACK); wp += T * T; }                // round 7 + second rate block + round 0 S-boxes
-        else { fp += RED + MUL + RED; wp += T; }                                      // round 7, lane 0 only, external form
+        fp += (NG - 1) * ((T + G) * FOLD + T * PACK); wp += (NG - 1) * (T + G) * (T + G); launches += NG - 1;   // group stages
+        fp += T * (FOLD + SBOX + PACK); wp += T * (T + G); launches += 1;             // last group stage -> round 4 S-boxes
+        if (perm == 0) { fp += T * (FOLD + SBOX + PACK); wp += T * T; }               // round 7 + second rate block + round 0 S-boxes
+        else { fp += FOLD + MUL + RED; wp += T; }                                     // round 7, lane 0 only, external form
         launches += 1;
     }
     out[0] = fp; out[1] = wp * 32 * WCOLS; out[2] = wp; out[3] = launches; out[4] = G;

@@ -1,20 +1,25 @@
 // poseidon_tc.cuh — the Poseidon permutation of the arity-16 Merkle node hash (t = 17) with every linear layer on the INT8 tensor
 // cores (tcgen05.mma kind::i8, accumulators in TMEM) and only the S-boxes and Montgomery reductions on the FP64 pipe.
 //
-// Why it is exact.  A state word is an integer < 2^256 (the 2^260-Montgomery form of fr52.cuh), written as 32 unsigned bytes; a
-// constant matrix W (n_out x n_in words, canonical entries) is Toeplitz-expanded over its bytes, B[(i, c)][(j, a)] =
-// byte_{c - a}(W[i][j]), so that the int32 accumulator column (i, c) is column c (weight 2^(8c)) of the exact integer row product
-// sum_j W[i][j] x[j]: a sum of <= 25 * 32 byte products < 2^16, < 2^26.  The epilogue packs the 63 columns of a word into ten 52-bit
-// limb columns and runs the SAME Montgomery reduction as the batch interpreter (fr52.cuh acc52_reduce_add2), so the values agree
-// mod p with poseidon/src/lib.rs:219-272 and the emitted digests are bit-identical (tests/test_gpu_poseidon_tc.py).
+// Why it is exact.  A state word is an integer < 2^256 (a lazily reduced representative in the 2^260-Montgomery form of fr52.cuh),
+// written as 32 unsigned bytes.  For a constant matrix W (n_out x n_in field elements) the B operand holds REDUCED constants:
+//      B[(i, c)][(j, a)] = byte_c( (W[i][j] * 2^(8a)) mod p ),   c, a = 0..31
+// so that the int32 accumulator column (i, c) = sum_j sum_a byte_a(x_j) * byte_c(W_ij 2^(8a) mod p) and
+//      y_i = sum_c column(i, c) * 2^(8c)  <  2^274,     y_i = sum_j W_ij x_j  (mod p)
+// — 32 columns per output word (a plain Toeplitz expansion of the 512-bit product needs 63 and is half zeros: twice the MMA work,
+// twice the TMEM reads).  A column is a sum of <= 25 * 32 byte products < 2^16, < 2^26: exact in int32.  The epilogue packs the 32
+// columns into 52-bit limbs and folds the 20 bits above 2^254 back with p = 2^254 + c:  y = low + p - top * c  in [0, 2^255) — integer
+// instructions only, no Montgomery reduction (the constants carry no Montgomery factor: the map is linear in the representatives).
+// S-boxes stay Montgomery products of fr52.cuh, so the values agree mod p with poseidon/src/lib.rs:219-272 and the emitted
+// digests are bit-identical (tests/test_gpu_poseidon_tc.py).
 //
-// Round structure (scratch/tc_model.py is the big-integer model; checked against the oracle's permutation):
+// Round structure (tools/tc_model.py is the big-integer model of all of this; checked against the oracle's permutation):
 //   full rounds     x = sbox(v + rc);  v' = M x                 -> one stage per round: GEMM 17 -> 17 words, epilogue reduce + rc' + x^5
 //   partial rounds  v' = Mh v + m0 sbox(v_0 + c_k),  Mh = M with column 0 zeroed, m0 = column 0 of M.  G rounds form a group:
 //                   the S-box inputs of a group are  s_k = e0^T Mh^k v + sum_{m<k} gamma_{k-1-m} x_m + c_k   (gamma_d = e0^T Mh^d m0)
 //                   so a group is: [chain kernel] G dependent S-boxes per permutation, each with a <= G-1 term correction, from the
 //                   G "dots" e0^T Mh^k v;  [stage] GEMM (17 + G) -> (17 + G) words giving the next group's v and dots.
-// Every GEMM input is an S-box output (< 2^254.3) or a stage output (< 2^255.3), so 32 bytes per word always suffice; the lazily
+// Every GEMM input is an S-box output (< 2^254.3) or a stage output (< 2^255), so 32 bytes per word always suffice; the lazily
 // reduced S-box inputs (< 2^260) never enter a GEMM.
 //
 // Data: "byte tiles" of 128 permutations, one 4 KB k-step per word in the UMMA no-swizzle K-major core-matrix layout
@@ -28,13 +33,10 @@ namespace tc {
 
 constexpr int TILE_M = 128;               // permutations per tile = TMEM lanes
 constexpr int KSTEP_BYTES = TILE_M * 32;  // one word of every permutation of a tile
-constexpr int WCOLS = 64;                 // accumulator columns per output word (63 used)
-#ifndef SMW_TC_PAIR
-#define SMW_TC_PAIR 1
-#endif
-constexpr int PAIR = SMW_TC_PAIR;         // tiles that share every B block (PAIR MMAs per block)
-constexpr int CHUNK_WORDS = 4 / PAIR;     // output words per MMA (N = 256 / PAIR columns)
-constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // bytes of one k-step of one chunk
+constexpr int WCOLS = 32;                 // accumulator columns per output word
+constexpr int PAIR = 1;                   // one tile per CTA at a time (two tiles sharing every B block measured slower: profiles/r02u_tc_variants.txt)
+constexpr int CHUNK_WORDS = 8;            // output words per MMA (N = 256 columns)
+constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // 8192 bytes: one k-step of one chunk
 constexpr int MAX_KW = 25;                // k-steps (input words) per tile: 17 state words + a group of up to 8 S-box outputs
 #ifndef SMW_TC_KSUB
 #define SMW_TC_KSUB 4
@@ -43,11 +45,12 @@ constexpr int KSUB = SMW_TC_KSUB;         // k-steps per ring stage: one bulk co
 #ifdef SMW_TC_NSTAGE
 constexpr int NSTAGE = SMW_TC_NSTAGE;
 #else
-constexpr int NSTAGE = (PAIR == 1 ? 112 : 24) * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words
+constexpr int NSTAGE = 112 * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words
 #endif
-constexpr int EPI_WARPS = 16;             // 4 TMEM lane quarters x (words of a chunk x tiles = 4)
+constexpr int EPI_SLOTS = 4;              // word slots per TMEM lane quarter: slot s owns words s and s + 4 of every chunk
+constexpr int EPI_WARPS = 4 * EPI_SLOTS;
 constexpr int STAGE_THREADS = 64 + 32 * EPI_WARPS;
-constexpr int ACC_COLS = PAIR * CHUNK_WORDS * WCOLS;      // 256 TMEM columns per accumulator stage: [tile][word][64]
+constexpr int ACC_COLS = CHUNK_WORDS * WCOLS;             // 256 TMEM columns per accumulator stage: [word][32]
 
 struct StageSmem {
     alignas(1024) uint8_t a[PAIR][MAX_KW * KSTEP_BYTES];  // 100 KB per tile: its input words
@@ -107,15 +110,16 @@ SMW_DEV void tmem_ld16(uint32_t taddr, uint32_t* r) {
 }
 SMW_DEV void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// 16 int32 columns k0 .. k0+15 (weights 2^(8k), each < 2^26) added into the ten lazily carried 52-bit limb columns (each stays < 2^60).
-// Column 63 is structurally zero.  A column lands at bit sh = 8k mod 52 of limb 8k / 52: for sh < 32 that is ONE multiply-add on the
-// FMA pipe (IMAD.WIDE.U32 c, 2^sh, acc: shift and 64-bit accumulation in one instruction — the ALU pipe is the busiest pipe of the
-// epilogue); for sh >= 32 the part below bit 52 goes into the high word of the limb and the rest into the next limb.
+// p = 2^254 + c, c in 26-bit pieces (126 bits): top * c_k < 2^47 is one IMAD.WIDE
+constexpr uint32_t PC26_0 = 0x0000001u, PC26_1 = 0x1bac840u, PC26_2 = 0x28dd8c4u, PC26_3 = 0x3f02652u, PC26_4 = 0x0224698u;
+// 16 int32 columns k0 .. k0+15 (weights 2^(8k), each < 2^26) added into lazily carried 52-bit limb columns (each stays < 2^60).
+// A column lands at bit sh = 8k mod 52 of limb 8k / 52: for sh < 32 that is ONE multiply-add on the FMA pipe (IMAD.WIDE.U32 c, 2^sh,
+// acc: shift and 64-bit accumulation in one instruction — the ALU pipe is the busiest pipe of the epilogue); for sh >= 32 the part
+// below bit 52 goes into the high word of the limb and the rest into the next limb.
 template <int K0> SMW_DEV void columns_to_limbs16(const uint32_t* c, uint64_t* acc) {
 #pragma unroll
     for (int i = 0; i < 16; i++) {
         const int k = K0 + i;
-        if (k >= 63) continue;
         const int bit = 8 * k, l = bit / 52, sh = bit % 52;
         if (sh < 32) acc[l] += (uint64_t)c[i] * (uint64_t)(1u << sh);
         else {
@@ -124,6 +128,28 @@ template <int K0> SMW_DEV void columns_to_limbs16(const uint32_t* c, uint64_t* a
             acc[l + 1] += (uint64_t)(c[i] >> (52 - sh));
         }
     }
+}
+// six limb columns of y < 2^274 (+ the limbs of two addends a, b given as exact doubles < 2^52 each) -> limbs of
+//      low254(y) + p - top(y) * c + a + b,    top = y >> 254 < 2^21
+// carried to limbs < 2^52 (the top limb takes what is left).  Integer instructions only.
+SMW_DEV F52 fold_top_add2(uint64_t* acc, const F52& a, const F52& b) {
+#pragma unroll
+    for (int i = 0; i < 5; i++) { acc[i + 1] += acc[i] >> 52; acc[i] &= M52; }
+    const uint32_t top = (uint32_t)((acc[4] >> 46) | (acc[5] << 6));
+    const uint64_t t0 = (uint64_t)top * PC26_0, t1 = (uint64_t)top * PC26_1, t2 = (uint64_t)top * PC26_2, t3 = (uint64_t)top * PC26_3, t4 = (uint64_t)top * PC26_4;
+    int64_t r[5];
+    r[0] = (int64_t)(acc[0] + P52_0) - (int64_t)(t0 + ((t1 & 0x3ffffffull) << 26));
+    r[1] = (int64_t)(acc[1] + P52_1) - (int64_t)((t1 >> 26) + t2 + ((t3 & 0x3ffffffull) << 26));
+    r[2] = (int64_t)(acc[2] + P52_2) - (int64_t)((t3 >> 26) + t4);
+    r[3] = (int64_t)acc[3];
+    r[4] = (int64_t)((acc[4] & ((1ull << 46) - 1ull)) + P52_4);
+#pragma unroll
+    for (int i = 0; i < 5; i++) r[i] += (int64_t)double_to_u52(a.v[i]) + (int64_t)double_to_u52(b.v[i]);
+    F52 out;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { r[i + 1] += r[i] >> 52; out.v[i] = u52_to_double((uint64_t)r[i] & M52); }      // arithmetic shift: borrows travel up
+    out.v[4] = u52_to_double((uint64_t)r[4]);
+    return out;
 }
 
 // byte-tile address of word `kstep` of row `row` (first 16-byte half; the second half is 2048 bytes further)
@@ -266,48 +292,53 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
             __syncwarp();
         }
     } else if (warp >= 2) {
-        // ---------------- epilogue: warp (quarter q, word slot wg, tile tl) owns word CHUNK_WORDS * c + wg of every chunk for the 32 permutations of its TMEM lane quarter
-        const int q = warp & 3, wg = ((warp - 2) >> 2) % CHUNK_WORDS, tl = ((warp - 2) >> 2) / CHUNK_WORDS, row = 32 * q + lane;
+        // ---------------- epilogue: warp (quarter q, slot) owns words slot and slot + 4 of every chunk for the 32 permutations of its TMEM lane quarter
+        const int q = warp & 3, slot = (warp - 2) >> 2, row = 32 * q + lane;
         uint32_t accit = 0; bool bad = false;
         for (uint64_t it = 0; it < my_pairs && !bad; it++) {
-            const uint64_t tile = (blockIdx.x + it * gridDim.x) * PAIR + tl;
-            const bool have_tile = tile < g.n_tiles;
+            const uint64_t tile = blockIdx.x + it * gridDim.x;
             const uint64_t perm = tile * TILE_M + row;
+            uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+            NodeSeg ns; uint64_t nq = 0; bool valid = true;
+            if (MODE == EPI_ABSORB_SBOX || MODE == EPI_EMIT) valid = resolve_node(g.B, g.node0 + perm, ns, nq);
             for (int c = 0; c < n_chunks; c++, accit++) {
-                const int as = accit & 1, word = have_tile ? c * CHUNK_WORDS + wg : g.nw;
+                const int as = accit & 1;
                 bool ok = true;
                 if (lane == 0) ok = mbar_wait(&S.acc_full[as], (accit >> 1) & 1);      // one lane waits, the warp follows
                 ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
                 if (!ok) { if (lane == 0) atomicExch(g.err, 6); bad = true; break; }
                 tc_fence_after();
-                if (word < g.nw) {
-                    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * ACC_COLS + (uint32_t)(tl * CHUNK_WORDS + wg) * WCOLS;
-                    Acc52 A;
+                const int w0 = c * CHUNK_WORDS + slot, w1 = w0 + EPI_SLOTS;
+                const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * ACC_COLS + (uint32_t)slot * WCOLS;
+                uint64_t acc0[6], acc1[6];
 #pragma unroll
-                    for (int i = 0; i < 10; i++) A.c[i] = 0;
-                    { uint32_t col[32];
-                      tmem_ld16(taddr, col); tmem_ld16(taddr + 16, col + 16); tmem_ld_wait();
-                      columns_to_limbs16<0>(col, A.c); columns_to_limbs16<16>(col + 16, A.c);
-                      tmem_ld16(taddr + 32, col); tmem_ld16(taddr + 48, col + 16); tmem_ld_wait();
-                      columns_to_limbs16<32>(col, A.c); columns_to_limbs16<48>(col + 16, A.c); }
-                    // the accumulator stage may be reused as soon as every warp has read its columns
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&S.acc_empty[as]);
-                    F52 rc = f52_zero();
+                for (int i = 0; i < 6; i++) { acc0[i] = 0; acc1[i] = 0; }
+                if (w0 < g.nw) {
+                    uint32_t col[32];
+                    tmem_ld16(taddr, col); tmem_ld16(taddr + 16, col + 16); tmem_ld_wait();
+                    columns_to_limbs16<0>(col, acc0); columns_to_limbs16<16>(col + 16, acc0);
+                }
+                if (w1 < g.nw) {
+                    uint32_t col[32];
+                    tmem_ld16(taddr + EPI_SLOTS * WCOLS, col); tmem_ld16(taddr + EPI_SLOTS * WCOLS + 16, col + 16); tmem_ld_wait();
+                    columns_to_limbs16<0>(col, acc1); columns_to_limbs16<16>(col + 16, acc1);
+                }
+                // the accumulator stage may be reused as soon as every warp has read its columns
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.acc_empty[as]);
+#pragma unroll 1
+                for (int h = 0; h < 2; h++) {
+                    const int word = h ? w1 : w0;
+                    if (word >= g.nw) break;
+                    F52 rc = f52_zero(), add = f52_zero();
                     if (g.rc_idx >= 0) rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + word));
-                    F52 add = f52_zero();
-                    NodeSeg ns; uint64_t nq = 0; bool valid = true;
-                    if (MODE == EPI_ABSORB_SBOX || MODE == EPI_EMIT) valid = resolve_node(g.B, g.node0 + perm, ns, nq);
-                    if (MODE == EPI_ABSORB_SBOX && valid) {
+                    if (MODE == EPI_ABSORB_SBOX && valid && word < 16) {
                         const int e = g.absorb_first + word - 4;                       // input index of this lane (4 DS fields precede the children)
-                        if (word < 16) {
-                            if (e < (int)ns.arity) add = ext_times16(ns.children + (nq * ns.arity + (uint64_t)e) * 8);
-                            else if (e == (int)ns.arity) add = f52_const(C_KONE52);    // the padding one: 2^260 mod p
-                        }
+                        if (e < (int)ns.arity) add = ext_times16(ns.children + (nq * ns.arity + (uint64_t)e) * 8);
+                        else if (e == (int)ns.arity) add = f52_const(C_KONE52);        // the padding one: 2^260 mod p
                     }
-                    F52 r = acc52_reduce_add2(A, 0, rc, add);
-                    uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+                    const F52 r = fold_top_add2(h ? acc1 : acc0, rc, add);
                     if (MODE == EPI_WORDS) {
                         if (word < g.nbytes) store_word_bytes(out_tile, g.out_koff + word, row, r);
                         else {
@@ -323,10 +354,6 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
                             emit_ext52(acc52_reduce_add2(Q, 1, f52_zero(), f52_zero()), ns.parents + nq * 8);
                         }
                     }
-                } else {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&S.acc_empty[as]);
                 }
             }
         }
