@@ -63,7 +63,11 @@ SMW_DEV uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_sh
 SMW_DEV void mbar_init(uint64_t* b, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(b)), "r"(count)); }
 SMW_DEV void mbar_expect_tx(uint64_t* b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(b)), "r"(bytes) : "memory"); }
 SMW_DEV void mbar_arrive(uint64_t* b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(b)) : "memory"); }
-// bounded wait: mbarrier.try_wait suspends the thread in hardware (no polling traffic); ~2 s of wall time without the phase
+#ifndef SMW_TC_WAIT_HINT_NS
+#define SMW_TC_WAIT_HINT_NS 20000u
+#endif
+// bounded wait: mbarrier.try_wait suspends the thread in hardware for up to the hinted time (the producer and MMA warps wait most of
+// the time: without the hint their polling loop took ~12 % of the issue slots of two schedulers, profiles/r03b); ~2 s of wall time without the phase
 // completing is a protocol error that ends the kernel with a flag instead of hanging the GPU
 SMW_DEV bool mbar_wait(uint64_t* b, uint32_t parity) {
     const uint32_t addr = smem_u32(b);
@@ -71,7 +75,7 @@ SMW_DEV bool mbar_wait(uint64_t* b, uint32_t parity) {
 #pragma unroll 1
     for (uint32_t spin = 0; ; spin++) {
         uint32_t ok;
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(addr), "r"(parity), "r"(SMW_TC_WAIT_HINT_NS) : "memory");
         if (ok) return true;
         if ((spin & 63) == 63) {
             uint64_t now; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));

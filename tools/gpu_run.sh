@@ -58,6 +58,7 @@ PYEOF
     ncu_tc)     SMW_TC_MIN=4096 timeout 900 $NCU_FULL -k regex:k_tc_stage -s 1 -c 2 -o $OUT/${TAG}_ncu_tc_stage -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_tc.out 2>&1
                 ncu -i $OUT/${TAG}_ncu_tc_stage.ncu-rep --page details --csv > $OUT/${TAG}_ncu_tc_stage_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_tc.out ;;
     tc_bench)   SMW_TC_MIN=${TCMIN:-16384} timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('TC', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_bench.txt ;;
+    tc_group)   for v in 8 4 2; do SMW_TC_GROUP=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_GROUP=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_group.txt; done ;;
     umma)       timeout 120 tools/_bin/umma_i8 ${UMMA_TILES:-16} $OUT/${TAG}_umma_dump.bin > $OUT/${TAG}_umma_i8.json 2> $OUT/${TAG}_umma_i8.err; echo "exit $?"; cat $OUT/${TAG}_umma_i8.json; tail -3 $OUT/${TAG}_umma_i8.err
                 timeout 120 python tools/umma_i8_check.py $OUT/${TAG}_umma_dump.bin | tee $OUT/${TAG}_umma_check.json; rm -f $OUT/${TAG}_umma_dump.bin ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
