@@ -35,7 +35,15 @@ constexpr int TILE_M = 128;               // permutations per tile = TMEM lanes
 constexpr int KSTEP_BYTES = TILE_M * 32;  // one word of every permutation of a tile
 constexpr int WCOLS = 32;                 // accumulator columns per output word
 constexpr int PAIR = 1;                   // one tile per CTA at a time (two tiles sharing every B block measured slower: profiles/r02u_tc_variants.txt)
-constexpr int CHUNK_WORDS = 8;            // output words per MMA (N = 256 columns)
+#ifndef SMW_TC_SLOTS
+#define SMW_TC_SLOTS 6
+#endif
+#ifndef SMW_TC_WPS
+#define SMW_TC_WPS 1
+#endif
+constexpr int EPI_SLOTS = SMW_TC_SLOTS;   // word slots per TMEM lane quarter (one epilogue warp each)
+constexpr int WPS = SMW_TC_WPS;           // words per slot and chunk: slot s owns words s, s + EPI_SLOTS, ... of every chunk
+constexpr int CHUNK_WORDS = EPI_SLOTS * WPS;              // output words per MMA (N = 32 x that <= 256 columns)
 constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // 8192 bytes: one k-step of one chunk
 constexpr int MAX_KW = 25;                // k-steps (input words) per tile: 17 state words + a group of up to 8 S-box outputs
 #ifndef SMW_TC_KSUB
@@ -47,10 +55,10 @@ constexpr int NSTAGE = SMW_TC_NSTAGE;
 #else
 constexpr int NSTAGE = 112 * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words
 #endif
-constexpr int EPI_SLOTS = 4;              // word slots per TMEM lane quarter: slot s owns words s and s + 4 of every chunk
 constexpr int EPI_WARPS = 4 * EPI_SLOTS;
 constexpr int STAGE_THREADS = 64 + 32 * EPI_WARPS;
-constexpr int ACC_COLS = CHUNK_WORDS * WCOLS;             // 256 TMEM columns per accumulator stage: [word][32]
+constexpr int ACC_COLS = CHUNK_WORDS * WCOLS;             // <= 256 TMEM columns per accumulator stage: [word][32]
+static_assert(ACC_COLS <= 256 && ACC_COLS % 16 == 0 && STAGE_THREADS <= 1024, "stage shape");
 
 struct StageSmem {
     alignas(1024) uint8_t a[PAIR][MAX_KW * KSTEP_BYTES];  // 100 KB per tile: its input words
@@ -296,7 +304,7 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
             __syncwarp();
         }
     } else if (warp >= 2) {
-        // ---------------- epilogue: warp (quarter q, slot) owns words slot and slot + 4 of every chunk for the 32 permutations of its TMEM lane quarter
+        // ---------------- epilogue: warp (quarter q, slot) owns words slot, slot + EPI_SLOTS, .. of every chunk for the 32 permutations of its TMEM lane quarter
         const int q = warp & 3, slot = (warp - 2) >> 2, row = 32 * q + lane;
         uint32_t accit = 0; bool bad = false;
         for (uint64_t it = 0; it < my_pairs && !bad; it++) {
@@ -312,28 +320,26 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
                 ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, 0) != 0;
                 if (!ok) { if (lane == 0) atomicExch(g.err, 6); bad = true; break; }
                 tc_fence_after();
-                const int w0 = c * CHUNK_WORDS + slot, w1 = w0 + EPI_SLOTS;
+                const int w0 = c * CHUNK_WORDS + slot;
                 const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)as * ACC_COLS + (uint32_t)slot * WCOLS;
-                uint64_t acc0[6], acc1[6];
+                uint64_t acc[WPS][6];
 #pragma unroll
-                for (int i = 0; i < 6; i++) { acc0[i] = 0; acc1[i] = 0; }
-                if (w0 < g.nw) {
-                    uint32_t col[32];
-                    tmem_ld16(taddr, col); tmem_ld16(taddr + 16, col + 16); tmem_ld_wait();
-                    columns_to_limbs16<0>(col, acc0); columns_to_limbs16<16>(col + 16, acc0);
-                }
-                if (w1 < g.nw) {
-                    uint32_t col[32];
-                    tmem_ld16(taddr + EPI_SLOTS * WCOLS, col); tmem_ld16(taddr + EPI_SLOTS * WCOLS + 16, col + 16); tmem_ld_wait();
-                    columns_to_limbs16<0>(col, acc1); columns_to_limbs16<16>(col + 16, acc1);
+                for (int h = 0; h < WPS; h++) {
+#pragma unroll
+                    for (int i = 0; i < 6; i++) acc[h][i] = 0;
+                    if (w0 + h * EPI_SLOTS < g.nw) {
+                        uint32_t col[32];
+                        tmem_ld16(taddr + h * EPI_SLOTS * WCOLS, col); tmem_ld16(taddr + h * EPI_SLOTS * WCOLS + 16, col + 16); tmem_ld_wait();
+                        columns_to_limbs16<0>(col, acc[h]); columns_to_limbs16<16>(col + 16, acc[h]);
+                    }
                 }
                 // the accumulator stage may be reused as soon as every warp has read its columns
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&S.acc_empty[as]);
-#pragma unroll 1
-                for (int h = 0; h < 2; h++) {
-                    const int word = h ? w1 : w0;
+#pragma unroll
+                for (int h = 0; h < WPS; h++) {
+                    const int word = w0 + h * EPI_SLOTS;
                     if (word >= g.nw) break;
                     F52 rc = f52_zero(), add = f52_zero();
                     if (g.rc_idx >= 0) rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + word));
@@ -342,7 +348,7 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
                         if (e < (int)ns.arity) add = ext_times16(ns.children + (nq * ns.arity + (uint64_t)e) * 8);
                         else if (e == (int)ns.arity) add = f52_const(C_KONE52);        // the padding one: 2^260 mod p
                     }
-                    const F52 r = fold_top_add2(h ? acc1 : acc0, rc, add);
+                    const F52 r = fold_top_add2(acc[h], rc, add);
                     if (MODE == EPI_WORDS) {
                         if (word < g.nbytes) store_word_bytes(out_tile, g.out_koff + word, row, r);
                         else {

@@ -54,7 +54,7 @@ tot = sum(v[1] for v in d.values())
 for k, v in sorted(d.items(), key=lambda kv: -kv[1][1]): print("%-60s n=%4d  %9.3f ms  %5.1f%%" % (k[:60], v[0], v[1], 100 * v[1] / tot))
 PYEOF
                 ;;
-    tc_var)     for lib in libsmw.so libsmw_k4.so libsmw_pair2.so; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_MIN=16384 timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_variants.txt; done ;;
+    tc_var)     for lib in libsmw.so libsmw_s6w1.so libsmw_s5w1.so; do SMW_LIB=$PWD/stark_mlwe_b200/$lib timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_variants.txt; done ;;
     ncu_tc)     SMW_TC_MIN=4096 timeout 900 $NCU_FULL -k regex:k_tc_stage -s 1 -c 2 -o $OUT/${TAG}_ncu_tc_stage -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_tc.out 2>&1
                 ncu -i $OUT/${TAG}_ncu_tc_stage.ncu-rep --page details --csv > $OUT/${TAG}_ncu_tc_stage_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_tc.out ;;
     tc_bench)   SMW_TC_MIN=${TCMIN:-16384} timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('TC', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_bench.txt ;;
