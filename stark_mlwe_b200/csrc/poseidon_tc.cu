@@ -145,13 +145,13 @@ static int build_tables(smw_ctx* c, smw_params* p, int G, Tables** out) {
 static int group_size() { static int g = -1; if (g < 0) { const char* e = getenv("SMW_TC_GROUP"); g = e ? atoi(e) : 8; if (g < 1 || g > MAX_G) g = 8; } return g; }
 static uint64_t batch_nodes() { static long v = -1; if (v < 0) { const char* e = getenv("SMW_TC_BATCH"); v = e ? atol(e) : (1L << 20); if (v < TILE_M) v = 1L << 20; } return (uint64_t)v; }
 
-template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageArgs a) {
+template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageArgs a, int kclass) {
     const size_t sm = sizeof(StageSmem) + 1024;
     static bool attr_set = false;
     if (!attr_set) { SMW_CUDA(c, cudaFuncSetAttribute(k_tc_stage<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); attr_set = true; }
     a.err = T->d_err;
-    const unsigned grid = (unsigned)std::min<uint64_t>((a.n_tiles + PAIR - 1) / PAIR, (uint64_t)T->n_sm);
-    { LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_stage<MODE><<<grid, STAGE_THREADS, sm, c->stream>>>(a); }
+    const unsigned grid = (unsigned)std::min<uint64_t>(a.n_tiles, (uint64_t)T->n_sm);
+    { LaunchScope ls(c, kclass); k_tc_stage<MODE><<<grid, STAGE_THREADS, sm, c->stream>>>(a); }
     SMW_CUDA(c, cudaGetLastError());
     return SMW_OK;
 }
@@ -178,13 +178,23 @@ void node_counts(int t, int rp, uint64_t out[5]) {
     out[0] = fp; out[1] = wp * 32 * WCOLS; out[2] = wp; out[3] = launches; out[4] = G;
 }
 
-// Hashes the nodes of `B` (every node with exactly 16 children) with the tensor-core pipeline.  The caller has checked the shape.
-int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
+// What a run of the pipeline hashes: Merkle nodes of full arity 16 (two permutations: the sponge absorbs 4 DS fields + 16 children + the
+// padding one in two rate blocks) or one-permutation leaves (FRI hashed leaves / pair leaves).
+struct Job {
+    int kind;                      // 0: nodes of B; 1: FRI hashed leaves (template); 2: pair leaves
+    LevelBatch B; LeafRuns R; const uint32_t* tmpl; int lane_f, lane_s;
+    uint64_t total; int kclass;
+};
+static int ensure(smw_ctx* c, smw_params* p, Tables** out) {
     if (!p->tc) { Tables* T = nullptr; int rc = build_tables(c, p, group_size(), &T); if (rc) return rc; p->tc = T; p->tc_free = free_tables; }
-    Tables* T = (Tables*)p->tc;
-    const int t = p->t, G = T->G, NG = p->rp / G;
+    *out = (Tables*)p->tc;
+    return SMW_OK;
+}
+static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
+    Tables* T; int rc0 = ensure(c, p, &T); if (rc0) return rc0;
+    const int t = p->t, G = T->G, NG = p->rp / G, n_perms = J.kind == 0 ? 2 : 1;
     const TableLayout& L = p->layout;
-    const uint64_t batch = std::min<uint64_t>(batch_nodes(), (B.total + TILE_M - 1) / TILE_M * TILE_M);
+    const uint64_t batch = std::min<uint64_t>(batch_nodes(), (J.total + TILE_M - 1) / TILE_M * TILE_M);
     if (T->cap_nodes < batch) {
         cudaFree(T->buf_p); cudaFree(T->buf_q); cudaFree(T->dots); T->buf_p = T->buf_q = nullptr; T->dots = nullptr; T->cap_nodes = 0;
         const size_t tiles = (size_t)(batch / TILE_M);
@@ -193,38 +203,44 @@ int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
         T->cap_nodes = batch;
     }
     const size_t tile_stride = (size_t)MAX_KW * KSTEP_BYTES;
-    for (uint64_t node0 = 0; node0 < B.total; node0 += batch) {
-        const uint64_t n = std::min<uint64_t>(batch, B.total - node0), n_tiles = (n + TILE_M - 1) / TILE_M;
+    for (uint64_t node0 = 0; node0 < J.total; node0 += batch) {
+        const uint64_t n = std::min<uint64_t>(batch, J.total - node0), n_tiles = (n + TILE_M - 1) / TILE_M;
         uint8_t *P = T->buf_p, *Q = T->buf_q;
         StageArgs base{}; base.in_tile_stride = tile_stride; base.out_tile_stride = tile_stride; base.tbl = p->d_tables52; base.rc_idx = -1; base.n_tiles = n_tiles;
-        base.B = B; base.node0 = node0; base.dots = T->dots; base.dots_stride = T->cap_nodes; base.nbytes = t;
+        base.B = J.B; base.leaves = J.R; base.node0 = node0; base.dots = T->dots; base.dots_stride = T->cap_nodes; base.nbytes = t;
         auto full_round = [&](int round_next) -> int {          // P: x of a full round -> Q: x of the next one
             StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_full; a.nw = t; a.out = Q; a.rc_idx = (int)(L.rc_full + (uint32_t)round_next * t);
-            int rc = launch_stage<EPI_SBOX>(c, T, a); std::swap(P, Q); return rc;
+            int rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); std::swap(P, Q); return rc;
         };
-        { HeadArgs h{B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
-          LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h); }
+        if (J.kind == 0) {
+            HeadArgs h{J.B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
+            LaunchScope ls(c, J.kclass); k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+        } else {
+            HeadLeafArgs h{J.R, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full, J.kind == 1 ? 0 : 1, J.tmpl, J.lane_f, J.lane_s};
+            LaunchScope ls(c, J.kclass); k_tc_head_leaf<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+        }
         SMW_CUDA(c, cudaGetLastError());
-        for (int perm = 0; perm < 2; perm++) {
+        for (int perm = 0; perm < n_perms; perm++) {
             int rc = 0;
             for (int r = 1; r <= 3 && !rc; r++) rc = full_round(r);
             if (rc) return rc;
-            { StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_r3; a.nw = t + G; a.out = Q; rc = launch_stage<EPI_WORDS>(c, T, a); std::swap(P, Q); if (rc) return rc; }
+            { StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_r3; a.nw = t + G; a.out = Q; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); std::swap(P, Q); if (rc) return rc; }
             for (int g = 0; g < NG; g++) {
                 { ChainArgs ch{T->dots, (size_t)T->cap_nodes, n, P, tile_stride, t, G, T->gamma, p->d_tables52, (int)(L.rc_part + (uint32_t)g * G)};
-                  LaunchScope ls(c, KC_MERKLE_LEVEL); k_tc_chain<<<(unsigned)((n + CHAIN_THREADS - 1) / CHAIN_THREADS), CHAIN_THREADS, 0, c->stream>>>(ch); }
+                  LaunchScope ls(c, J.kclass); k_tc_chain<<<(unsigned)((n + CHAIN_THREADS - 1) / CHAIN_THREADS), CHAIN_THREADS, 0, c->stream>>>(ch); }
                 SMW_CUDA(c, cudaGetLastError());
                 StageArgs a = base; a.in = P; a.kw = t + G; a.out = Q;
-                if (g + 1 < NG) { a.bmat = T->b_grp; a.nw = t + G; rc = launch_stage<EPI_WORDS>(c, T, a); }
-                else { a.bmat = T->b_last; a.nw = t; a.rc_idx = (int)(L.rc_full + 4u * t); rc = launch_stage<EPI_SBOX>(c, T, a); }
+                if (g + 1 < NG) { a.bmat = T->b_grp; a.nw = t + G; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); }
+                else { a.bmat = T->b_last; a.nw = t; a.rc_idx = (int)(L.rc_full + 4u * t); rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); }
                 std::swap(P, Q);
                 if (rc) return rc;
             }
             for (int r = 5; r <= 7 && !rc; r++) rc = full_round(r);
             if (rc) return rc;
             StageArgs a = base; a.in = P; a.kw = t; a.out = Q;
-            if (perm == 0) { a.bmat = T->b_full; a.nw = t; a.rc_idx = (int)L.rc_full; a.absorb_first = t - 1; rc = launch_stage<EPI_ABSORB_SBOX>(c, T, a); std::swap(P, Q); }
-            else { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT>(c, T, a); }
+            if (perm + 1 < n_perms) { a.bmat = T->b_full; a.nw = t; a.rc_idx = (int)L.rc_full; a.absorb_first = t - 1; rc = launch_stage<EPI_ABSORB_SBOX>(c, T, a, J.kclass); std::swap(P, Q); }
+            else if (J.kind == 0) { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT>(c, T, a, J.kclass); }
+            else { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT_LEAF>(c, T, a, J.kclass); }
             if (rc) return rc;
         }
     }
@@ -233,6 +249,22 @@ int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));
     if (err) { cudaMemsetAsync(T->d_err, 0, 4, c->stream); return set_err(c, SMW_ERR_CUDA, "tensor-core stage: mbarrier protocol timeout"); }
     return SMW_OK;
+}
+
+// Hashes the nodes of `B` (every node with exactly 16 children) with the tensor-core pipeline.  The caller has checked the shape.
+int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
+    Job J{}; J.kind = 0; J.B = B; J.total = B.total; J.kclass = KC_MERKLE_LEVEL;
+    return run_job(c, p, J);
+}
+// FRI hashed leaves (deep_ali/src/fri.rs:38-44), one permutation each: d_segs == nullptr takes the single run `u`
+int fri_leaves_tc(smw_ctx* c, smw_params* p, const uint32_t* d_tmpl, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total) {
+    Job J{}; J.kind = 1; J.R = LeafRuns{d_segs, n_segs, u, total}; J.tmpl = d_tmpl; J.lane_f = lane_f; J.lane_s = lane_s; J.total = total; J.kclass = KC_FRI_LEAF;
+    return run_job(c, p, J);
+}
+// pair leaves of arity-16 trees (merkle/src/lib.rs:382-400), one permutation each
+int pair_leaves_tc(smw_ctx* c, smw_params* p, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total) {
+    Job J{}; J.kind = 2; J.R = LeafRuns{d_segs, n_segs, u, total}; J.total = total; J.kclass = KC_PAIR_LEAVES;
+    return run_job(c, p, J);
 }
 
 } // namespace tc

@@ -194,8 +194,17 @@ SMW_DEV F52 ext_times16(const uint32_t* src) {
     return f52_from_limbs(l);
 }
 
+// leaves of one or several FRI layers hashed by one launch: explicit runs (device array) or a single run `u`
+struct LeafRuns { const LeafSeg* segs; int n_segs; LeafSeg u; uint64_t total; };
+SMW_DEV bool resolve_leaf(const LeafRuns& R, uint64_t g, LeafSeg& ls, uint64_t& i) {
+    if (g >= R.total) return false;
+    if (R.segs) { ls = R.segs[find_seg(g, &R.segs[0].first, sizeof(LeafSeg) / 8, R.n_segs)]; i = g - ls.first; }
+    else { ls = R.u; i = g; }
+    return true;
+}
+
 // ------------------------------------------------------------------ the GEMM stage
-enum { EPI_WORDS = 0, EPI_SBOX = 1, EPI_ABSORB_SBOX = 2, EPI_EMIT = 3 };
+enum { EPI_WORDS = 0, EPI_SBOX = 1, EPI_ABSORB_SBOX = 2, EPI_EMIT = 3, EPI_EMIT_LEAF = 4 };
 struct StageArgs {
     const uint8_t* in; size_t in_tile_stride; int kw;            // input byte tiles: kw k-steps are read from each
     const uint8_t* bmat; int nw;                                 // Toeplitz blocks [chunk][k-step] of the stage's matrix, nw output words
@@ -205,6 +214,7 @@ struct StageArgs {
     const uint32_t* tbl; int rc_idx;                             // tbl52 table and element index of the constant added to word 0 (rc_idx + w for word w); < 0: none
     uint64_t n_tiles;
     LevelBatch B; uint64_t node0;                                // EPI_ABSORB_SBOX / EPI_EMIT: the nodes of this batch are node0 .. of the level launch
+    LeafRuns leaves;                                             // EPI_EMIT_LEAF: the items are leaves node0 .. of these runs (digest -> run.out + 32 i)
     int absorb_first;                                            // EPI_ABSORB_SBOX: sponge element index of lane 0 in this rate block (16 for the second block)
     int* err;
 };
@@ -363,6 +373,12 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
                             Acc52 Q; acc52_mul(Q, r, f52_const(C_KOUT52));
                             emit_ext52(acc52_reduce_add2(Q, 1, f52_zero(), f52_zero()), ns.parents + nq * 8);
                         }
+                    } else if (MODE == EPI_EMIT_LEAF) {
+                        LeafSeg ls; uint64_t li = 0;
+                        if (word == 0 && resolve_leaf(g.leaves, g.node0 + perm, ls, li)) {
+                            Acc52 Q; acc52_mul(Q, r, f52_const(C_KOUT52));
+                            emit_ext52(acc52_reduce_add2(Q, 1, f52_zero(), f52_zero()), ls.out + li * 8);
+                        }
                     }
                 }
             }
@@ -400,6 +416,46 @@ template <int T> __global__ void __launch_bounds__(512) k_tc_head(const HeadArgs
                 else if (e == (int)ns.arity) add = f52_const(C_KONE52);
                 acc52_zero(A);
                 s = acc52_reduce_add2(A, 0, rc, add);          // rc + add with the carries normalised (limbs < 2^52)
+            }
+        }
+        store_word_bytes(out_tile, l, row, sbox52(s));
+    }
+}
+
+// head of a one-permutation leaf hash.  kind 0: FRI hashed leaf (deep_ali/src/fri.rs:38-44): a fixed 17-lane pre-image template (tags and
+// label words as 256-bit little-endian integers) with f_i and s_{i / cp_div} dropped into lanes lane_f, lane_s.  kind 1: pair leaf
+// (merkle/src/lib.rs:382-400): [arity, u32::MAX, i + pos_offset, label, f_i, cp_{i / cp_div}, 1, 0 ..].  x_l = (lane + rc_full[0][l])^5.
+struct HeadLeafArgs { LeafRuns R; uint64_t item0, n_items; uint8_t* out; size_t out_tile_stride; const uint32_t* tbl; int rc_idx;
+                      int kind; const uint32_t* tmpl; int lane_f, lane_s; };
+template <int T> __global__ void __launch_bounds__(512) k_tc_head_leaf(const HeadLeafArgs g) {
+    const int row = threadIdx.x;
+    const uint64_t tile = blockIdx.x, perm = tile * TILE_M + row;
+    LeafSeg ls; uint64_t i = 0;
+    const bool valid = perm < g.n_items && resolve_leaf(g.R, g.item0 + perm, ls, i);
+    uint8_t* out_tile = g.out + tile * g.out_tile_stride;
+    const F52 k_rr = f52_const(C_KRR52);
+    const int lane_f = g.kind == 0 ? g.lane_f : 4, lane_s = g.kind == 0 ? g.lane_s : 5;
+#pragma unroll 1
+    for (int l = threadIdx.y; l < T; l += blockDim.y) {
+        const F52 rc = tbl52_load(g.tbl, (uint32_t)(g.rc_idx + l));
+        F52 s = rc;
+        if (valid) {
+            Acc52 A;
+            if (l == lane_f || l == lane_s) {
+                F52 add = f52_zero();
+                if (l == lane_f) add = ext_times16(ls.f + i * 8);
+                else if (ls.cp) add = ext_times16(ls.cp + (i / ls.cp_div) * 8);
+                acc52_zero(A);
+                s = acc52_reduce_add2(A, 0, rc, add);
+            } else if (g.kind == 0) {                  // a template lane: integer * 2^520 / 2^260
+                acc52_mul(A, raw_ext52(g.tmpl + (size_t)l * 8), k_rr);
+                s = acc52_reduce_add2(A, 1, rc, f52_zero());
+            } else if (l < 4) {
+                acc52_mul(A, f52_from_u64(l == 0 ? (uint64_t)ls.arity : l == 1 ? 0xffffffffull : l == 2 ? i + ls.pos_offset : ls.label), k_rr);
+                s = acc52_reduce_add2(A, 1, rc, f52_zero());
+            } else if (l == 6) {
+                acc52_zero(A);
+                s = acc52_reduce_add2(A, 0, rc, f52_const(C_KONE52));
             }
         }
         store_word_bytes(out_tile, l, row, sbox52(s));

@@ -215,7 +215,11 @@ template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32
                                    uint32_t* d_out, size_t cp_div);
 template <int T> int hash_groups_T(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                                    size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
-namespace tc { int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B); void node_counts(int t, int rp, uint64_t out[5]); }     // poseidon_tc.cu
+namespace tc {
+int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B); void node_counts(int t, int rp, uint64_t out[5]);
+int fri_leaves_tc(smw_ctx* c, smw_params* p, const uint32_t* d_tmpl, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total);
+int pair_leaves_tc(smw_ctx* c, smw_params* p, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total);
+}     // poseidon_tc.cu
 template <int T> int merkle_level_multi_T(smw_ctx* c, const smw_params* p, const NodeSeg* d_segs, int n_segs, uint64_t total_nodes, int arity, bool all_full);
 template <int T> int pair_leaves_multi_T(smw_ctx* c, const smw_params* p, const LeafSeg* d_segs, int n_segs, uint64_t total);
 template <int T> int hash_ds_single_T(smw_ctx* c, const smw_params* p, const uint32_t* d_ds, int nds, const uint32_t* d_in, size_t n, uint32_t* d_out);

@@ -51,3 +51,34 @@ def test_same_digests_as_the_interpreter(ctx, smw, rnd):
     finally:
         ctx.set_tc_min_nodes(16384)
     assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("n", [1, 127, 129, 5000])
+def test_hashed_leaves_match_oracle(tc_ctx, smw, O, rnd, n):
+    """hash_leaf_pair (deep_ali/src/fri.rs:38-44): one transcript-parameter permutation per leaf, head kernel from the 17-lane template"""
+    f, s = rnd(600 + n, n), rnd(700 + n, n)
+    f[0] = 0
+    got = smw.hash_leaf_pair(tc_ctx, f, s)
+    want = O.hash_leaf_pair(f, s)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("n", [16 * 40, 16 * 300 + 7])
+def test_pair_leaf_tree_arity16_matches_oracle(tc_ctx, smw, O, rnd, n):
+    """MerkleTree::new_pairs with arity 16 (merkle/src/lib.rs:382-400): pair leaves and (full) node levels on the staged pipeline"""
+    f, cp = rnd(800 + n, n), rnd(900 + n, n)
+    cfg = smw.MerkleChannelCfg.new(tc_ctx, 16).with_tree_label(5)
+    got = smw.MerkleTree.new_pairs(f, cp, cfg)
+    want = O.MerkleTree.new_pairs(f, cp, 16, 5)
+    for l in range(want.nlevels()):
+        assert np.array_equal(got.level(l), want.level(l)), "level %d" % l
+
+
+def test_fri_paper_schedule_matches_oracle_with_tc_everywhere(tc_ctx, smw, O, rnd):
+    """fri_build_transcript (deep_ali/src/fri.rs:231-312) on [16, 16, 8]: hashed leaves, pair leaves and tree levels of every layer"""
+    n0 = 1 << 12
+    f0 = rnd(4242, n0)
+    st = smw.fri_build_transcript(tc_ctx, f0, smw.FriProverParams([16, 16, 8], 0xDEEFBAAD))
+    assert np.array_equal(st.roots(), O.FriProverState(f0, [16, 16, 8], 0xDEEFBAAD).roots())
+    sharded = smw.fri_roots_sharded(tc_ctx, None, f0.reshape(4, n0 // 4, 4), [i * (n0 // 4) for i in range(4)], n0, smw.FriProverParams([16, 16, 8], 0xDEEFBAAD))
+    assert np.array_equal(sharded, st.roots())
