@@ -47,6 +47,10 @@ MAC_PER_MM = 136             # 32x32->64 multiply-accumulates per 8-limb CIOS Mo
 # a profile constant, not something this run measured; the JSON says so.
 TRAFFIC_NCU = {"bytes": 136450048 + 6638592, "source": "profiles/r01ac_ncu_full_merkle_level52_details.csv (level 0, 16 columns x 2^18 leaves)",
                "algorithmic_bytes_of_that_launch": 142606336}
+# the same for ONE k_tc_stage<1> launch (one full round of 262 144 permutations = 2 048 byte tiles: 17 words x 4 KB read and written per
+# tile = 2 x 142 606 336 B; the capture saw 142.94 MB read and 96.71 MB written, the rest of the output still in L2 when the kernel ended)
+TRAFFIC_NCU_TC = {"bytes": 142940416 + 96708864, "source": "profiles/r04a_ncu_tc_stage_summary.txt (k_tc_stage<1>, level 0 of 16 columns x 2^18 leaves)",
+                  "algorithmic_bytes_of_that_launch": 2 * 142606336}
 
 
 def splitmix64(x):
@@ -523,7 +527,7 @@ def roofline_record(ctx, smw, prof, args, nc, N, interp=None):
     large enough, else k_merkle_level52<17>.  Two pipes carry the work, so two fractions are reported, both from counts of what the
     kernels EXECUTE (never the reference's dense count): `frac` = FP64-pipe instructions (S-boxes, Montgomery reductions) / kernel time /
     the DFMA rate measured live in this run; `tensor.frac` = int8 MACs of the linear layers / kernel time / the dense INT8 rate.  The
-    epilogues are bound by instruction issue across the ALU and FP64 pipes (profiles/r03*_ncu_tc_stage*), so neither reaches 1."""
+    epilogues are bound by instruction issue across the ALU and FP64 pipes (profiles/r04a_ncu_tc_stage_summary.txt), so neither reaches 1."""
     ml_ms, ml_launches = prof["merkle_level"]
     perms = nc * tree_perms(N, 16, 16)
     ml_s = ml_ms * 1e-3 / args.steps
@@ -538,7 +542,7 @@ def roofline_record(ctx, smw, prof, args, nc, N, interp=None):
     rec = {"kernel": name, "kernel_ms_per_step": ml_ms / args.steps, "kernel_launches_per_step": ml_launches / args.steps,
            "permutations_per_step": perms, "permutations_per_s": perms / ml_s,
            "hbm": {"achieved": alg_bytes / ml_s / 1e9, "peak": peak_hbm(), "unit": "GB/s", "frac": alg_bytes / ml_s / 1e9 / peak_hbm()},
-           "traffic": TRAFFIC_NCU["bytes"], "traffic_source": TRAFFIC_NCU,
+           "traffic": (TRAFFIC_NCU_TC if tc_nodes else TRAFFIC_NCU)["bytes"], "traffic_source": TRAFFIC_NCU_TC if tc_nodes else TRAFFIC_NCU,
            "step_share_ms": {k: v[0] / args.steps for k, v in prof.items() if v[1]}}
     if fp_perm:
         fp_exec = tc_nodes * cnt["fp64_instr"] + other_perms * fp_perm

@@ -239,10 +239,11 @@ int32_t smw_ntt_cyclic_to_chunks(smw_ctx* ctx, smw_comm* comm_or_null, void* in_
 int32_t smw_mf_commit_phase_sharded(smw_ctx* ctx, smw_comm* comm_or_null, uint64_t ds_tag, const void* table_slice, size_t n_local, int32_t mem,
                                     void* roots_out_host, void* r_out_host, void* final_out_host);
 uint64_t smw_ctx_collective_count(const smw_ctx* ctx);   /* NCCL collectives issued through this context */
-/* Tuning: Merkle levels of at least `n` full arity-16 nodes (t = 17) run their linear layers on the INT8 tensor cores
- * (csrc/poseidon_tc.cuh; same digests).  0 = never.  Default 16384, or SMW_TC_MIN from the environment. */
+/* Tuning: launches of at least `n` hashes of one shape -- full arity-16 nodes (t = 17), full arity-2 nodes (t = 9), pair leaves
+ * (t = 9, 17) or FRI hashed leaves (t = 17) -- run their linear layers on the INT8 tensor cores (csrc/poseidon_tc.cuh; same
+ * digests).  0 = never.  Default 16384, or SMW_TC_MIN from the environment. */
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* ctx, uint64_t n);
-/* What one arity-16 node costs on that path: out6 = {FP64-pipe instructions, int8 MACs on the tensor cores, word products,
+/* What one node (t = 17: arity 16, two permutations; t = 9: arity 2, one) costs on that path: out6 = {FP64-pipe instructions, int8 MACs on the tensor cores, word products,
  * kernel launches per batch, partial-round group size, the context's current threshold}; zeros 0..4 when the path is unavailable. */
 int32_t smw_diag_tc_node_counts(const smw_ctx* ctx, const smw_params* params, uint64_t* out6);
 

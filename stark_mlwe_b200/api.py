@@ -597,7 +597,10 @@ def lde_commit(ctx, cols, log_blowup, shift, label0=0):
     sh = _fr1(shift)
     if _is_torch(cols):
         n_cols, n = cols.shape[0], cols.shape[1]
-        p, mem, keep = C.c_void_p(cols.data_ptr()), DEVICE, cols
+        assert cols.is_contiguous() and cols.element_size() == 8 and cols.shape[-1] == 4
+        # a (pinned) CPU tensor is a HOST buffer: the library stages it with double-buffered copies under the kernels.  (Passed as a device
+        # pointer, pinned memory still worked through unified addressing, but the first kernel then read all of it over PCIe: 47 ms per cfg2 step.)
+        p, mem, keep = C.c_void_p(cols.data_ptr()), (DEVICE if cols.is_cuda else HOST), cols
     else:
         keep = np.ascontiguousarray(cols, dtype=np.uint64)
         n_cols, n = keep.shape[0], keep.shape[1]

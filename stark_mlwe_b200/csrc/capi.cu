@@ -649,9 +649,13 @@ int32_t smw_lde_commit(smw_ctx* c, const void* cols, int32_t log_n, int32_t log_
     // a short first range (1/16 of the columns) lets the kernels start after a small copy instead of after the whole input.
     std::vector<std::pair<int, int>> ranges;      // (first column, count)
     for (int c0 = 0; c0 < n_cols; c0 += chunk) ranges.push_back({c0, std::min(chunk, n_cols - c0)});
+    // The split is geometric (1/16, 3/16, the rest): the copy of a range must fit under the compute of the one before it, and
+    // with a single 15/16 remainder it did not when the host link delivers less than ~40 GB/s (e2e 50 ms behind `value` on cfg2).
     if (host && n_cols >= 16 && ranges[0].second > n_cols / 16) {
-        const int head = n_cols / 16, rest = ranges[0].second - head;
-        ranges[0] = {head, rest}; ranges.insert(ranges.begin(), {0, head});
+        const int first = ranges[0].second, head = n_cols / 16, mid = std::min(first - head, 3 * head), rest = first - head - mid;
+        std::vector<std::pair<int, int>> split = {{0, head}, {head, mid}};
+        if (rest > 0) split.push_back({head + mid, rest});
+        ranges.erase(ranges.begin()); ranges.insert(ranges.begin(), split.begin(), split.end());
     }
     const int n_chunks = (int)ranges.size();
     uint32_t* d_ext = nullptr; uint32_t* d_in[2] = {nullptr, nullptr};
@@ -1282,7 +1286,7 @@ int32_t smw_diag_tc_node_counts(const smw_ctx* c, const smw_params* p, uint64_t*
     if (!c || !p || !out6) return SMW_ERR_INVALID_ARG;
     for (int i = 0; i < 6; i++) out6[i] = 0;
     out6[5] = c->tc_min_nodes;
-    if (p->t == 17 && c->use_f52 && p->d_tables52) smw::tc::node_counts(p->t, p->rp, out6);
+    if ((p->t == 17 || p->t == 9) && c->use_f52 && p->d_tables52) smw::tc::node_counts(p->t, p->rp, out6);
     return SMW_OK;
 }
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* c, uint64_t n) { if (!c) return SMW_ERR_INVALID_ARG; c->tc_min_nodes = n ? n : ~0ull; return SMW_OK; }

@@ -89,9 +89,9 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     Segs sg; int rc = get_sponge_segs(c, p, 4, arity, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, p, &out_first); if (rc) return rc;
     PoseidonDev P = dev_view(p);
-#if SMW_T == 17
-    // full arity-16 levels above the threshold: linear layers on the INT8 tensor cores (poseidon_tc.cuh)
-    if (c->use_f52 && p->d_tables52 && arity == 16 && n_children == n_parents * 16 && (uint64_t)n_parents * (uint64_t)n_cols >= c->tc_min_nodes) {
+#if SMW_T == 17 || SMW_T == 9
+    // full arity-16 (t = 17) / arity-2 (t = 9) levels above the threshold: linear layers on the INT8 tensor cores (poseidon_tc.cuh)
+    if (c->use_f52 && p->d_tables52 && arity == (T == 17 ? 16 : 2) && n_children == n_parents * (size_t)arity && (uint64_t)n_parents * (uint64_t)n_cols >= c->tc_min_nodes) {
         LevelBatch B{}; B.segs = nullptr; B.n_segs = 0; B.n_cols = n_cols; B.label_stride = label_stride; B.child_col_stride = child_col_stride; B.parent_col_stride = parent_col_stride;
         B.u = NodeSeg{d_children, d_parents, (uint64_t)n_children, (uint64_t)n_parents, label0, pos_offset, level, (uint32_t)arity, 0};
         B.total = (uint64_t)n_parents * (uint64_t)n_cols;
@@ -131,8 +131,8 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
 template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const NodeSeg* d_segs, int n_segs, uint64_t total, int arity, bool all_full) {
     smw_params* p = const_cast<smw_params*>(cp);
     if (n_segs <= 0 || total == 0) return SMW_OK;
-#if SMW_T == 17
-    if (c->use_f52 && p->d_tables52 && arity == 16 && all_full && total >= c->tc_min_nodes) {
+#if SMW_T == 17 || SMW_T == 9
+    if (c->use_f52 && p->d_tables52 && arity == (T == 17 ? 16 : 2) && all_full && total >= c->tc_min_nodes) {
         LevelBatch B{}; B.segs = d_segs; B.n_segs = n_segs; B.total = total;
         return tc::merkle_level_tc(c, p, B);
     }
@@ -158,7 +158,7 @@ template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const 
 template <> int pair_leaves_multi_T<T>(smw_ctx* c, const smw_params* cp, const LeafSeg* d_segs, int n_segs, uint64_t total) {
     smw_params* p = const_cast<smw_params*>(cp);
     if (n_segs <= 0 || total == 0) return SMW_OK;
-#if SMW_T == 17
+#if SMW_T == 17 || SMW_T == 9
     if (c->use_f52 && p->d_tables52 && total >= c->tc_min_nodes) return tc::pair_leaves_tc(c, p, d_segs, n_segs, LeafSeg{}, total);
 #endif
 #if SMW_T == 9 || SMW_T == 17
@@ -191,7 +191,7 @@ template <> int hash_groups_T<T>(smw_ctx* c, const smw_params* cp, const uint32_
 template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_t* d_f, const uint32_t* d_cp, size_t n, int arity, uint64_t label, uint64_t pos_offset,
                                  uint32_t* d_out, size_t cp_div) {
     smw_params* p = const_cast<smw_params*>(cp);
-#if SMW_T == 17
+#if SMW_T == 17 || SMW_T == 9
     if (c->use_f52 && p->d_tables52 && (uint64_t)n >= c->tc_min_nodes) {      // linear layers on the tensor cores (poseidon_tc.cuh)
         LeafSeg u{d_f, d_cp, d_out, (uint64_t)n, label, pos_offset, (uint64_t)(cp_div ? cp_div : 1), (uint32_t)arity, 0, 0};
         return tc::pair_leaves_tc(c, p, nullptr, 0, u, (uint64_t)n);

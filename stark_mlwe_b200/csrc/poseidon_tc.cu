@@ -93,7 +93,7 @@ static int upload(smw_ctx* c, const std::vector<uint8_t>& h, uint8_t** d) {
 }
 static int build_tables(smw_ctx* c, smw_params* p, int G, Tables** out) {
     const int t = p->t, rp = p->rp;
-    if (t != 17 || G < 1 || G > MAX_G || rp % G) return set_err(c, SMW_ERR_INVALID_ARG, "tensor-core node hash: t = 17 and a group size dividing rp only");
+    if ((t != 17 && t != 9) || G < 1 || G > MAX_G || rp % G || t + G > MAX_KW) return set_err(c, SMW_ERR_INVALID_ARG, "tensor-core hash: t = 9 or 17 and a group size dividing rp only");
     std::vector<uint64_t> ext((size_t)t * t * 4);
     SMW_CUDA(c, cudaMemcpyAsync(ext.data(), p->d_ext, ext.size() * 8, cudaMemcpyDeviceToHost, c->stream));
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -142,7 +142,13 @@ static int build_tables(smw_ctx* c, smw_params* p, int G, Tables** out) {
 }
 
 // ------------------------------------------------------------------ one Merkle level
-static int group_size() { static int g = -1; if (g < 0) { const char* e = getenv("SMW_TC_GROUP"); g = e ? atoi(e) : 8; if (g < 1 || g > MAX_G) g = 8; } return g; }
+// partial rounds per group: t = 17 (rp = 64): 8; t = 9 (rp = 60): 6, so that a group stage has 15 input and output words
+static int group_size(int t) {
+    static int g17 = -1, g9 = -1;
+    if (g17 < 0) { const char* e = getenv("SMW_TC_GROUP"); g17 = e ? atoi(e) : 8; if (g17 < 1 || g17 > MAX_G) g17 = 8; }
+    if (g9 < 0) { const char* e = getenv("SMW_TC_GROUP9"); g9 = e ? atoi(e) : 6; if (g9 < 1 || g9 > MAX_G) g9 = 6; }
+    return t == 9 ? g9 : g17;
+}
 static uint64_t batch_nodes() { static long v = -1; if (v < 0) { const char* e = getenv("SMW_TC_BATCH"); v = e ? atol(e) : (1L << 20); if (v < TILE_M) v = 1L << 20; } return (uint64_t)v; }
 
 template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageArgs a, int kclass) {
@@ -161,17 +167,18 @@ template <int MODE> static int launch_stage(smw_ctx* c, const Tables* T, StageAr
 // reduction, 15 per stage output (limb conversions of the fold), 5 per byte packing), out[1] = int8 multiply-accumulates the tensor
 // cores execute, out[2] = word products (row x word, 32 x 32 byte MACs each), out[3] = kernel launches per batch, out[4] = group size.
 void node_counts(int t, int rp, uint64_t out[5]) {
-    const uint64_t G = (uint64_t)group_size(), NG = (uint64_t)rp / G, T = (uint64_t)t;
+    const uint64_t G = (uint64_t)group_size(t), NG = (uint64_t)rp / G, T = (uint64_t)t;
+    const int n_perms = t == 17 ? 2 : 1;              // an arity-16 node absorbs two rate blocks; a t = 9 node or any pair / hashed leaf one
     const uint64_t RED = 85, MUL = 75, SQR = 45, PACK = 5, FOLD = 15, SBOX = 2 * (SQR + RED) + (MUL + RED);
     uint64_t fp = 0, wp = 0, launches = 1;
     fp += T * (SBOX + RED + PACK) + 4 * MUL;                                          // head: 17 lanes (4 DS products), ARK, S-box
-    for (int perm = 0; perm < 2; perm++) {
+    for (int perm = 0; perm < n_perms; perm++) {
         fp += 6 * T * (FOLD + SBOX + PACK); wp += 6 * T * T; launches += 6;           // full rounds 1-3, 5-7: stage + S-box epilogue
         fp += (T + G) * FOLD + T * PACK; wp += (T + G) * T; launches += 1;            // round 3 -> state and first dots
         fp += NG * (G * (RED + SBOX + PACK) + (G * (G - 1) / 2) * MUL); launches += NG;            // chains
         fp += (NG - 1) * ((T + G) * FOLD + T * PACK); wp += (NG - 1) * (T + G) * (T + G); launches += NG - 1;   // group stages
         fp += T * (FOLD + SBOX + PACK); wp += T * (T + G); launches += 1;             // last group stage -> round 4 S-boxes
-        if (perm == 0) { fp += T * (FOLD + SBOX + PACK); wp += T * T; }               // round 7 + second rate block + round 0 S-boxes
+        if (perm + 1 < n_perms) { fp += T * (FOLD + SBOX + PACK); wp += T * T; }      // round 7 + second rate block + round 0 S-boxes
         else { fp += FOLD + MUL + RED; wp += T; }                                     // round 7, lane 0 only, external form
         launches += 1;
     }
@@ -181,18 +188,18 @@ void node_counts(int t, int rp, uint64_t out[5]) {
 // What a run of the pipeline hashes: Merkle nodes of full arity 16 (two permutations: the sponge absorbs 4 DS fields + 16 children + the
 // padding one in two rate blocks) or one-permutation leaves (FRI hashed leaves / pair leaves).
 struct Job {
-    int kind;                      // 0: nodes of B; 1: FRI hashed leaves (template); 2: pair leaves
+    int kind;                      // 0: nodes of B (t = 17: full arity 16, two permutations; t = 9: full arity 2, one); 1: FRI hashed leaves (template); 2: pair leaves
     LevelBatch B; LeafRuns R; const uint32_t* tmpl; int lane_f, lane_s;
     uint64_t total; int kclass;
 };
 static int ensure(smw_ctx* c, smw_params* p, Tables** out) {
-    if (!p->tc) { Tables* T = nullptr; int rc = build_tables(c, p, group_size(), &T); if (rc) return rc; p->tc = T; p->tc_free = free_tables; }
+    if (!p->tc) { Tables* T = nullptr; int rc = build_tables(c, p, group_size(p->t), &T); if (rc) return rc; p->tc = T; p->tc_free = free_tables; }
     *out = (Tables*)p->tc;
     return SMW_OK;
 }
 static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
     Tables* T; int rc0 = ensure(c, p, &T); if (rc0) return rc0;
-    const int t = p->t, G = T->G, NG = p->rp / G, n_perms = J.kind == 0 ? 2 : 1;
+    const int t = p->t, G = T->G, NG = p->rp / G, n_perms = (J.kind == 0 && t == 17) ? 2 : 1;
     const TableLayout& L = p->layout;
     const uint64_t batch = std::min<uint64_t>(batch_nodes(), (J.total + TILE_M - 1) / TILE_M * TILE_M);
     if (T->cap_nodes < batch) {
@@ -214,10 +221,14 @@ static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
         };
         if (J.kind == 0) {
             HeadArgs h{J.B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
-            LaunchScope ls(c, J.kclass); k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+            LaunchScope ls(c, J.kclass);
+            if (t == 17) k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+            else k_tc_head<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
         } else {
             HeadLeafArgs h{J.R, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full, J.kind == 1 ? 0 : 1, J.tmpl, J.lane_f, J.lane_s};
-            LaunchScope ls(c, J.kclass); k_tc_head_leaf<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+            LaunchScope ls(c, J.kclass);
+            if (t == 17) k_tc_head_leaf<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+            else k_tc_head_leaf<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
         }
         SMW_CUDA(c, cudaGetLastError());
         for (int perm = 0; perm < n_perms; perm++) {
@@ -251,7 +262,8 @@ static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
     return SMW_OK;
 }
 
-// Hashes the nodes of `B` (every node with exactly 16 children) with the tensor-core pipeline.  The caller has checked the shape.
+// Hashes the nodes of `B` with the tensor-core pipeline: t = 17, every node with exactly 16 children (two rate blocks), or t = 9, every
+// node with exactly 2 children (4 DS fields + 2 children + the padding one = 7 of the 8 rate lanes: one permutation).  The caller has checked the shape.
 int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {
     Job J{}; J.kind = 0; J.B = B; J.total = B.total; J.kclass = KC_MERKLE_LEVEL;
     return run_job(c, p, J);

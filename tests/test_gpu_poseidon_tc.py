@@ -82,3 +82,55 @@ def test_fri_paper_schedule_matches_oracle_with_tc_everywhere(tc_ctx, smw, O, rn
     assert np.array_equal(st.roots(), O.FriProverState(f0, [16, 16, 8], 0xDEEFBAAD).roots())
     sharded = smw.fri_roots_sharded(tc_ctx, None, f0.reshape(4, n0 // 4, 4), [i * (n0 // 4) for i in range(4)], n0, smw.FriProverParams([16, 16, 8], 0xDEEFBAAD))
     assert np.array_equal(sharded, st.roots())
+
+
+# ---- t = 9 (arity-2 trees: the fold-2 FRI layers of BASELINE configs[2] and the Merkle-folded sum-check) on the same pipeline
+@pytest.mark.parametrize("n,label", [(2, 0), (2 * 129, 3), (600, 7), (1 << 13, 11)])
+def test_arity2_tree_levels_match_oracle(tc_ctx, smw, O, rnd, n, label):
+    """MerkleTree::new with arity 2 (merkle/src/lib.rs:164-179): one t = 9 permutation per node (4 DS fields + 2 children + padding one)"""
+    leaves = rnd(5000 + n, n)
+    leaves[0] = 0
+    leaves[1] = O.ints_to_limbs([(O.P - 1) * O.R % O.P])[0]
+    cfg = smw.MerkleChannelCfg.new(tc_ctx, 2).with_tree_label(label)
+    launches0 = tc_ctx.launch_count()
+    got = smw.MerkleTree.new(leaves, cfg)
+    assert tc_ctx.launch_count() - launches0 >= 29         # the staged pipeline ran: 29 launches per batch of one-permutation t = 9 hashes
+    want = O.MerkleTree.new(leaves, 2, label)
+    assert got.height() + 1 == want.nlevels()
+    for l in range(1, want.nlevels()):
+        assert np.array_equal(got.level(l), want.level(l)), "level %d" % l
+
+
+@pytest.mark.parametrize("n", [2 * 64, 2 * 300 + 1, 1 << 12])
+def test_pair_leaf_tree_arity2_matches_oracle(tc_ctx, smw, O, rnd, n):
+    """MerkleTree::new_pairs with arity 2 (merkle/src/lib.rs:382-400): t = 9 pair leaves and node levels on the staged pipeline"""
+    f, cp = rnd(1800 + n, n), rnd(1900 + n, n)
+    cfg = smw.MerkleChannelCfg.new(tc_ctx, 2).with_tree_label(6)
+    got = smw.MerkleTree.new_pairs(f, cp, cfg)
+    want = O.MerkleTree.new_pairs(f, cp, 2, 6)
+    for l in range(want.nlevels()):
+        assert np.array_equal(got.level(l), want.level(l)), "level %d" % l
+
+
+def test_arity2_same_digests_as_the_interpreter(ctx, smw, rnd):
+    leaves = rnd(6, 1 << 12)
+    cfg = smw.MerkleChannelCfg.new(ctx, 2)
+    try:
+        ctx.set_tc_min_nodes(0)
+        a = smw.MerkleTree.new(leaves, cfg).root()
+        ctx.set_tc_min_nodes(1)
+        b = smw.MerkleTree.new(leaves, cfg).root()
+    finally:
+        ctx.set_tc_min_nodes(16384)
+    assert np.array_equal(a, b)
+
+
+def test_fri_fold2_schedule_matches_oracle_with_tc_everywhere(tc_ctx, smw, O, rnd):
+    """fri_build_transcript (deep_ali/src/fri.rs:231-312) with fold factor 2 down to one element: every layer an arity-2 pair-leaf tree"""
+    n0 = 1 << 11
+    f0 = rnd(4343, n0)
+    sched = [2] * 11
+    st = smw.fri_build_transcript(tc_ctx, f0, smw.FriProverParams(sched, 0xDEEFBAAD))
+    assert np.array_equal(st.roots(), O.FriProverState(f0, sched, 0xDEEFBAAD).roots())
+    sharded = smw.fri_roots_sharded(tc_ctx, None, f0.reshape(4, n0 // 4, 4), [i * (n0 // 4) for i in range(4)], n0, smw.FriProverParams(sched, 0xDEEFBAAD))
+    assert np.array_equal(sharded, st.roots())
