@@ -297,12 +297,15 @@ def fri_leg(ctx, smw, comm, T, rank, world, torch, steps):
     # executed-op roofline of the t = 9 kernels that carry the fold-2 phase (pair leaves + arity-2 levels: one permutation each)
     if rank == 0:
         p9 = smw.poseidon_params_for_width(ctx, 9)
-        fp = p9.executed_fp64_ops()
+        fp_interp = p9.executed_fp64_ops()
+        cnt9 = ctx.tc_node_counts(p9)                    # one-permutation hashes on the tensor-core pipeline (launches >= min_nodes), else the interpreter
+        fp = cnt9["fp64_instr"] or fp_interp
         r = out["fold2"]
         perms = (2 * n0 - 1) + (2 * n0 - 2 - log_n0)     # leaves: 2 n0 - 1 over all layers; arity-2 nodes: sum over layers of (n_l - 1)
         kms = sum(v for kk, v in r["kernel_ms"].items() if kk in ("pair_leaves", "merkle_level"))
-        out["fold2_t9_kernels"] = {"permutations_per_proof": perms, "fp64_ops_per_permutation": fp, "kernel_ms": kms,
-                                   "share_of_proof_time": kms / r["ms"], "permutations_per_s_all_ranks": perms / (kms * 1e-3) if kms else None}
+        out["fold2_t9_kernels"] = {"permutations_per_proof": perms, "fp64_ops_per_permutation": fp, "fp64_ops_per_permutation_interpreter": fp_interp,
+                                   "int8_mac_per_permutation": cnt9["int8_mac"], "path": "tensor-core pipeline (k_tc_stage / k_tc_chain / k_tc_head, t = 9, groups of %d partial rounds) for launches of >= %d hashes" % (cnt9["group"], cnt9["min_nodes"]) if cnt9["fp64_instr"] else "thread-per-permutation FP64 interpreter",
+                                   "kernel_ms": kms, "share_of_proof_time": kms / r["ms"], "permutations_per_s_all_ranks": perms / (kms * 1e-3) if kms else None}
     return out
 
 
