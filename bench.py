@@ -281,15 +281,21 @@ def fri_leg(ctx, smw, comm, T, rank, world, torch, steps):
         fn(); fn()
         ctx.profile(True)
         c0 = ctx.collective_count()
-        secs, roots = T.run(fn, steps)
+        reps = []                                        # every proof timed on its own: the record is the MEDIAN (a proof is 0.1-0.2 s, so one host
+        for _ in range(max(steps, 3)):                   # hiccup - a slow cudaFree of the arenas, say - would otherwise decide the mean); all reps are listed
+            t1, roots = T.run(fn, 1)
+            reps.append(t1)
+        n_reps = len(reps)
+        secs = sorted(reps)[n_reps // 2]
         prof = ctx.profile_read(); ctx.profile(False)
+        prof = {kk: (v[0] / n_reps, v[1] // n_reps) for kk, v in prof.items()}
         committed, n = 0, n0
         for m in sched + [1]:
             committed += n
             n //= m if m > 1 else 1
-        rec = {"ms": secs * 1e3 / steps, "n0_per_s": n0 * steps / secs, "committed_leaves": committed, "committed_leaves_per_s": committed * steps / secs,
-               "kernel_ms": {kk: v[0] / steps for kk, v in prof.items() if v[1]}, "launches": {kk: v[1] // steps for kk, v in prof.items() if v[1]},
-               "collectives_per_proof": (ctx.collective_count() - c0) // steps}
+        rec = {"ms": secs * 1e3, "ms_reps": [round(t * 1e3, 3) for t in reps], "n0_per_s": n0 / secs, "committed_leaves": committed, "committed_leaves_per_s": committed / secs,
+               "kernel_ms": {kk: v[0] for kk, v in prof.items() if v[1]}, "launches": {kk: v[1] for kk, v in prof.items() if v[1]},
+               "collectives_per_proof": (ctx.collective_count() - c0) // n_reps}
         if gsec in gold:
             hexes = ["0x%064x" % ((int(r[0]) | int(r[1]) << 64 | int(r[2]) << 128 | int(r[3]) << 192) * rinv % P) for r in roots]
             rec["roots_equal_oracle_golden"] = hexes == gold[gsec]["roots"]

@@ -1286,7 +1286,7 @@ int32_t smw_diag_tc_node_counts(const smw_ctx* c, const smw_params* p, uint64_t*
     if (!c || !p || !out6) return SMW_ERR_INVALID_ARG;
     for (int i = 0; i < 6; i++) out6[i] = 0;
     out6[5] = c->tc_min_nodes;
-    if ((p->t == 17 || p->t == 9) && c->use_f52 && p->d_tables52) smw::tc::node_counts(p->t, p->rp, out6);
+    if (c->use_f52 && smw::tc::usable(p)) smw::tc::node_counts(p->t, p->rp, out6);
     return SMW_OK;
 }
 int32_t smw_ctx_set_tc_min_nodes(smw_ctx* c, uint64_t n) { if (!c) return SMW_ERR_INVALID_ARG; c->tc_min_nodes = n ? n : ~0ull; return SMW_OK; }

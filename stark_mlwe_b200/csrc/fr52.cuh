@@ -132,6 +132,64 @@ SMW_DEV F52 acc52_reduce_add2(Acc52& A, uint32_t n_terms, const F52& s, const F5
     }
     return r;
 }
+// ---- one product, no addends: the form the S-boxes of the tensor-core epilogues use (poseidon_tc.cuh) -------------------------
+// The exponent bits that ONE product's patterns and the five reduction steps will add to each column are known at compile time, so the
+// accumulator STARTS at minus that amount (a constant folded into the first addition) instead of having it subtracted from the high
+// word of every column before the reduction; with no addends on top, the 3-input additions of two 2^52-biased zeros go as well.
+// ~60 ALU-pipe instructions less per x^5 (the ALU pipe is the busiest pipe of those epilogues, profiles/r04a_ncu_tc_stage_summary.txt).
+SMW_DEV void acc52_init_biased(Acc52& A) {
+    constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
+    constexpr uint32_t rlo[10] = {1, 2, 3, 3, 3, 2, 1, 0, 0, 0}, rhi[10] = {0, 1, 2, 3, 3, 3, 2, 1, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 10; k++) {
+        const uint32_t bias = ((nlo[k] + rlo[k]) * 0x433u + (nhi[k] + rhi[k]) * 0x467u) << 20;
+        A.c[k] = (uint64_t)(0u - bias) << 32;
+    }
+}
+SMW_DEV void acc52_mul_b(Acc52& A, const F52& a, const F52& b) { acc52_init_biased(A); acc52_mac(A, a, b); }
+SMW_DEV void acc52_sqr_b(Acc52& A, const F52& a) {
+    acc52_init_biased(A);
+#pragma unroll
+    for (int i = 0; i < 5; i++)
+#pragma unroll
+        for (int j = i; j < 5; j++) {
+            const double hi = __fma_rz(a.v[i], a.v[j], 0x1p104);
+            const double lo = __fma_rz(a.v[i], a.v[j], (0x1p104 + 0x1p52) - hi);
+            const uint64_t h = (uint64_t)__double_as_longlong(hi), l = (uint64_t)__double_as_longlong(lo);
+            if (i == j) { A.c[i + j + 1] += h; A.c[i + j] += l; }
+            else { A.c[i + j + 1] += h + h; A.c[i + j] += l + l; }
+        }
+}
+// (A + M p) / 2^260 for an accumulator started by acc52_init_biased and holding one product; limbs < 2^52
+SMW_DEV F52 acc52_reduce_b(Acc52& A) {
+    const double p0 = (double)P52_0, p1 = (double)P52_1, p2 = (double)P52_2, pinv = (double)PINV52;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        const double tl = u52_to_double(A.c[i] & M52);
+        const double mh = __fma_rz(tl, pinv, 0x1p104);
+        const double ml = __fma_rz(tl, pinv, (0x1p104 + 0x1p52) - mh);
+        const uint64_t m = (uint64_t)__double_as_longlong(ml) & M52;
+        const double md = ml - 0x1p52;
+        const double h0 = __fma_rz(md, p0, 0x1p104), l0 = __fma_rz(md, p0, (0x1p104 + 0x1p52) - h0);
+        const double h1 = __fma_rz(md, p1, 0x1p104), l1 = __fma_rz(md, p1, (0x1p104 + 0x1p52) - h1);
+        const double h2 = __fma_rz(md, p2, 0x1p104), l2 = __fma_rz(md, p2, (0x1p104 + 0x1p52) - h2);
+        A.c[i] += (uint64_t)__double_as_longlong(l0);
+        A.c[i + 1] += (uint64_t)__double_as_longlong(h0) + (uint64_t)__double_as_longlong(l1) + (A.c[i] >> 52);
+        A.c[i + 2] += (uint64_t)__double_as_longlong(h1) + (uint64_t)__double_as_longlong(l2);
+        A.c[i + 3] += (uint64_t)__double_as_longlong(h2);
+        A.c[i + 4] += (m & 63ull) << 46;
+        A.c[i + 5] += m >> 6;
+    }
+    F52 r; uint64_t carry = 0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const uint64_t v = A.c[5 + k] + carry;
+        r.v[k] = u52_to_double(k < 4 ? (v & M52) : v);
+        carry = v >> 52;
+    }
+    return r;
+}
+
 // The same reduction with a SHORTER DEPENDENCY CHAIN, for the cooperative (latency-bound, one lone warp) kernels: the quotient
 // digit m = -c_i / p mod 2^52 and the low halves of m * p_j come from 64-bit integer multiplies (IMAD.WIDE + 2 IMAD, ~5 cycles each,
 // running beside the FP64 pipe), only the high halves floor(m p_j / 2^52) stay on DFMA.RZ.  Per step the chain to the next column is

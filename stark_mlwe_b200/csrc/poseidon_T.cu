@@ -91,7 +91,7 @@ template <> int merkle_level_T<T>(smw_ctx* c, const smw_params* cp, const uint32
     PoseidonDev P = dev_view(p);
 #if SMW_T == 17 || SMW_T == 9
     // full arity-16 (t = 17) / arity-2 (t = 9) levels above the threshold: linear layers on the INT8 tensor cores (poseidon_tc.cuh)
-    if (c->use_f52 && p->d_tables52 && arity == (T == 17 ? 16 : 2) && n_children == n_parents * (size_t)arity && (uint64_t)n_parents * (uint64_t)n_cols >= c->tc_min_nodes) {
+    if (c->use_f52 && tc::usable(p) && arity == (T == 17 ? 16 : 2) && n_children == n_parents * (size_t)arity && (uint64_t)n_parents * (uint64_t)n_cols >= c->tc_min_nodes) {
         LevelBatch B{}; B.segs = nullptr; B.n_segs = 0; B.n_cols = n_cols; B.label_stride = label_stride; B.child_col_stride = child_col_stride; B.parent_col_stride = parent_col_stride;
         B.u = NodeSeg{d_children, d_parents, (uint64_t)n_children, (uint64_t)n_parents, label0, pos_offset, level, (uint32_t)arity, 0};
         B.total = (uint64_t)n_parents * (uint64_t)n_cols;
@@ -132,7 +132,7 @@ template <> int merkle_level_multi_T<T>(smw_ctx* c, const smw_params* cp, const 
     smw_params* p = const_cast<smw_params*>(cp);
     if (n_segs <= 0 || total == 0) return SMW_OK;
 #if SMW_T == 17 || SMW_T == 9
-    if (c->use_f52 && p->d_tables52 && arity == (T == 17 ? 16 : 2) && all_full && total >= c->tc_min_nodes) {
+    if (c->use_f52 && tc::usable(p) && arity == (T == 17 ? 16 : 2) && all_full && total >= c->tc_min_nodes) {
         LevelBatch B{}; B.segs = d_segs; B.n_segs = n_segs; B.total = total;
         return tc::merkle_level_tc(c, p, B);
     }
@@ -159,7 +159,7 @@ template <> int pair_leaves_multi_T<T>(smw_ctx* c, const smw_params* cp, const L
     smw_params* p = const_cast<smw_params*>(cp);
     if (n_segs <= 0 || total == 0) return SMW_OK;
 #if SMW_T == 17 || SMW_T == 9
-    if (c->use_f52 && p->d_tables52 && total >= c->tc_min_nodes) return tc::pair_leaves_tc(c, p, d_segs, n_segs, LeafSeg{}, total);
+    if (c->use_f52 && tc::usable(p) && total >= c->tc_min_nodes) return tc::pair_leaves_tc(c, p, d_segs, n_segs, LeafSeg{}, total);
 #endif
 #if SMW_T == 9 || SMW_T == 17
     if (c->use_f52 && p->d_tables52) {
@@ -192,7 +192,7 @@ template <> int pair_leaves_T<T>(smw_ctx* c, const smw_params* cp, const uint32_
                                  uint32_t* d_out, size_t cp_div) {
     smw_params* p = const_cast<smw_params*>(cp);
 #if SMW_T == 17 || SMW_T == 9
-    if (c->use_f52 && p->d_tables52 && (uint64_t)n >= c->tc_min_nodes) {      // linear layers on the tensor cores (poseidon_tc.cuh)
+    if (c->use_f52 && tc::usable(p) && (uint64_t)n >= c->tc_min_nodes) {      // linear layers on the tensor cores (poseidon_tc.cuh)
         LeafSeg u{d_f, d_cp, d_out, (uint64_t)n, label, pos_offset, (uint64_t)(cp_div ? cp_div : 1), (uint32_t)arity, 0, 0};
         return tc::pair_leaves_tc(c, p, nullptr, 0, u, (uint64_t)n);
     }
@@ -472,7 +472,7 @@ int launch_fri_leaf_hashed(smw_ctx* c, const smw_params* ctrp, const uint32_t* d
                            const uint32_t* d_f, const uint32_t* d_s, size_t s_div, size_t n, uint32_t* d_out) {
     if (n == 0) return SMW_OK;
     smw_params* trp = const_cast<smw_params*>(ctrp);
-    if (c->use_f52 && trp->d_tables52 && trp->t == 17 && (uint64_t)n >= c->tc_min_nodes) {      // linear layers on the tensor cores (poseidon_tc.cuh)
+    if (c->use_f52 && trp->t == 17 && tc::usable(trp) && (uint64_t)n >= c->tc_min_nodes) {      // linear layers on the tensor cores (poseidon_tc.cuh)
         LeafSeg u{d_f, d_s, d_out, (uint64_t)n, 0, 0, (uint64_t)(s_div ? s_div : 1), 0, 0, 0};
         return tc::fri_leaves_tc(c, trp, d_tmpl, lane_f, lane_s, nullptr, 0, u, (uint64_t)n);
     }
@@ -497,7 +497,7 @@ int launch_fri_leaf_hashed_multi(smw_ctx* c, const smw_params* ctrp, const uint3
     if (n_segs <= 0 || total == 0) return SMW_OK;
     smw_params* trp = const_cast<smw_params*>(ctrp);
     if (!(c->use_f52 && trp->d_tables52)) return set_err(c, SMW_ERR_UNSUPPORTED_WIDTH, "multi-run leaf launch needs the FP64-pipe tables");
-    if (trp->t == 17 && total >= c->tc_min_nodes) return tc::fri_leaves_tc(c, trp, d_tmpl, lane_f, lane_s, d_segs, n_segs, LeafSeg{}, total);
+    if (c->use_f52 && trp->t == 17 && tc::usable(trp) && total >= c->tc_min_nodes) return tc::fri_leaves_tc(c, trp, d_tmpl, lane_f, lane_s, d_segs, n_segs, LeafSeg{}, total);
     Segs sg; int rc = get_sponge_segs(c, trp, -2, lane_f * 256 + lane_s, &sg); if (rc) return rc;
     int out_first; rc = out_first_op(c, trp, &out_first); if (rc) return rc;
     const int nt = launch_threads(Cfg52<17>::RUN, Cfg52<17>::NT, "SMW_NT52"); size_t sm = state_smem_bytes52<17>(nt);

@@ -262,6 +262,13 @@ static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
     return SMW_OK;
 }
 
+// Whether this parameter set can take the pipeline at all: FP64-pipe tables present, width 9 or 17, and the partial rounds divisible into
+// groups (custom parameter sets with another rp — smw_params_from_seed / from_tables — stay on the interpreter instead of failing)
+bool usable(const smw_params* p) {
+    if (!p || !p->d_tables52 || (p->t != 17 && p->t != 9)) return false;
+    const int G = group_size(p->t);
+    return p->rp > 0 && p->rp % G == 0 && p->t + G <= MAX_KW;
+}
 // Hashes the nodes of `B` with the tensor-core pipeline: t = 17, every node with exactly 16 children (two rate blocks), or t = 9, every
 // node with exactly 2 children (4 DS fields + 2 children + the padding one = 7 of the 8 rate lanes: one permutation).  The caller has checked the shape.
 int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B) {

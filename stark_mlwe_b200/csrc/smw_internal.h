@@ -216,7 +216,7 @@ template <int T> int pair_leaves_T(smw_ctx* c, const smw_params* p, const uint32
 template <int T> int hash_groups_T(smw_ctx* c, const smw_params* p, const uint32_t* d_pool, const uint64_t* d_child_idx, const uint8_t* d_cnt, const uint64_t* d_pos,
                                    size_t n_groups, int arity, int row, uint32_t level, uint64_t label, uint32_t* d_out);
 namespace tc {
-int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B); void node_counts(int t, int rp, uint64_t out[5]);
+int merkle_level_tc(smw_ctx* c, smw_params* p, const LevelBatch& B); void node_counts(int t, int rp, uint64_t out[5]); bool usable(const smw_params* p);
 int fri_leaves_tc(smw_ctx* c, smw_params* p, const uint32_t* d_tmpl, int lane_f, int lane_s, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total);
 int pair_leaves_tc(smw_ctx* c, smw_params* p, const LeafSeg* d_segs, int n_segs, const LeafSeg& u, uint64_t total);
 }     // poseidon_tc.cu

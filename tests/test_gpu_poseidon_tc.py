@@ -134,3 +134,16 @@ def test_fri_fold2_schedule_matches_oracle_with_tc_everywhere(tc_ctx, smw, O, rn
     assert np.array_equal(st.roots(), O.FriProverState(f0, sched, 0xDEEFBAAD).roots())
     sharded = smw.fri_roots_sharded(tc_ctx, None, f0.reshape(4, n0 // 4, 4), [i * (n0 // 4) for i in range(4)], n0, smw.FriProverParams(sched, 0xDEEFBAAD))
     assert np.array_equal(sharded, st.roots())
+
+
+def test_custom_round_count_stays_on_the_interpreter(tc_ctx, smw, O, rnd):
+    """a parameter set whose rp is not a multiple of the group size (here t = 17, rp = 60; groups of 8) cannot take the staged pipeline: the level
+    launches fall back to the thread-per-node kernels instead of failing, and the roots still equal the oracle's"""
+    n, n_cols = 16 * 64, 2
+    cols = rnd(91, n * n_cols).reshape(n_cols, n, 4)
+    p = smw.params_from_seed(tc_ctx, b"TC-FALLBACK-SEED", 17, 60)
+    assert tc_ctx.tc_node_counts(p)["fp64_instr"] == 0
+    roots = smw.merkle_commit_columns(tc_ctx, cols, 16, p, label0=2, label_stride=1)
+    po = O.Params.from_seed(b"TC-FALLBACK-SEED", 17, 60)
+    for c in range(n_cols):
+        assert np.array_equal(roots[c], O.MerkleTree.new(cols[c], 16, 2 + c, po).root())
