@@ -343,7 +343,7 @@ int32_t smw_ctx_profile_read(smw_ctx* c, double* ms_out, uint64_t* launches_out,
     for (int i = 0; i < n_classes; i++) { if (ms_out) ms_out[i] = 0; if (launches_out) launches_out[i] = 0; }
     for (auto& r : c->prof) {
         float ms = 0; cudaEventElapsedTime(&ms, r.a, r.b);
-        if (r.cls < n_classes) { if (ms_out) ms_out[r.cls] += ms; if (launches_out) launches_out[r.cls]++; }
+        if (r.cls < n_classes) { if (ms_out) ms_out[r.cls] += ms; if (launches_out) launches_out[r.cls] += r.n; }
         c->prof_pool.push_back(r.a); c->prof_pool.push_back(r.b);
     }
     c->prof.clear();

@@ -2,6 +2,8 @@
 // the host from the parameter set's external-form tables (small modular arithmetic, once per parameter set), their Toeplitz
 // byte expansion in the UMMA block layout, and the launch sequence of one Merkle level.
 #include "poseidon_tc.cuh"
+#include <algorithm>
+#include <memory>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -197,12 +199,80 @@ static int ensure(smw_ctx* c, smw_params* p, Tables** out) {
     *out = (Tables*)p->tc;
     return SMW_OK;
 }
-static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
-    Tables* T; int rc0 = ensure(c, p, &T); if (rc0) return rc0;
+// Two halves of a batch on two streams (the default; SMW_TC_STREAMS=1 keeps one): each half runs the whole launch sequence in order on its own stream, so a chain
+// kernel of one half (FP64 / ALU pipes, small CTAs) can share the SMs with a group stage of the other half (tensor pipe, paced by the
+// matrix stream from L2) whenever the two meet, and the tail of every persistent stage kernel is covered by the other half.  The halves use
+// disjoint tile ranges of the same work buffers.  Measured on cfg2 (profiles/r04g, r04h): 755.4 -> 743.9 ms, with the chain kernel held to
+// 80 registers (six CTAs per SM) 748.2 -> 725.9 ms; a three-stage ring that would leave shared memory for a resident chain CTA: slower.
+static int n_streams() { static int v = -1; if (v < 0) { const char* e = getenv("SMW_TC_STREAMS"); v = e ? atoi(e) : 2; if (v < 1 || v > 2) v = 2; } return v; }
+struct SideStream {
+    smw_ctx* c; cudaStream_t main; bool used = false;
+    explicit SideStream(smw_ctx* ctx) : c(ctx), main(ctx->stream) {
+        if (c->side.empty()) {
+            cudaStream_t s; cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking); c->side.push_back(s);
+            cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming); c->side_ev.push_back(e);
+        }
+        if (!c->fan_ev) cudaEventCreateWithFlags(&c->fan_ev, cudaEventDisableTiming);
+    }
+    void enter() { cudaEventRecord(c->fan_ev, main); cudaStreamWaitEvent(c->side[0], c->fan_ev, 0); c->stream = c->side[0]; used = true; }
+    void leave() { c->stream = main; cudaEventRecord(c->side_ev[0], c->side[0]); cudaStreamWaitEvent(main, c->side_ev[0], 0); }
+    ~SideStream() { c->stream = main; }
+};
+
+// the launch sequence of `n` items (first one: item `node0` of the job) whose byte tiles start at P / Q and whose dots start at `dots`
+static int run_sequence(smw_ctx* c, smw_params* p, Tables* T, const Job& J, uint64_t node0, uint64_t n, uint8_t* P, uint8_t* Q, double* dots) {
     const int t = p->t, G = T->G, NG = p->rp / G, n_perms = (J.kind == 0 && t == 17) ? 2 : 1;
     const TableLayout& L = p->layout;
+    const size_t tile_stride = (size_t)MAX_KW * KSTEP_BYTES;
+    const uint64_t n_tiles = (n + TILE_M - 1) / TILE_M;
+    StageArgs base{}; base.in_tile_stride = tile_stride; base.out_tile_stride = tile_stride; base.tbl = p->d_tables52; base.rc_idx = -1; base.n_tiles = n_tiles;
+    base.B = J.B; base.leaves = J.R; base.node0 = node0; base.dots = dots; base.dots_stride = T->cap_nodes; base.nbytes = t;
+    auto full_round = [&](int round_next) -> int {          // P: x of a full round -> Q: x of the next one
+        StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_full; a.nw = t; a.out = Q; a.rc_idx = (int)(L.rc_full + (uint32_t)round_next * t);
+        int rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); std::swap(P, Q); return rc;
+    };
+    if (J.kind == 0) {
+        HeadArgs h{J.B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
+        LaunchScope ls(c, J.kclass);
+        if (t == 17) k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+        else k_tc_head<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
+    } else {
+        HeadLeafArgs h{J.R, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full, J.kind == 1 ? 0 : 1, J.tmpl, J.lane_f, J.lane_s};
+        LaunchScope ls(c, J.kclass);
+        if (t == 17) k_tc_head_leaf<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
+        else k_tc_head_leaf<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
+    }
+    SMW_CUDA(c, cudaGetLastError());
+    for (int perm = 0; perm < n_perms; perm++) {
+        int rc = 0;
+        for (int r = 1; r <= 3 && !rc; r++) rc = full_round(r);
+        if (rc) return rc;
+        { StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_r3; a.nw = t + G; a.out = Q; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); std::swap(P, Q); if (rc) return rc; }
+        for (int g = 0; g < NG; g++) {
+            { ChainArgs ch{dots, (size_t)T->cap_nodes, n, P, tile_stride, t, G, T->gamma, p->d_tables52, (int)(L.rc_part + (uint32_t)g * G)};
+              LaunchScope ls(c, J.kclass); k_tc_chain<<<(unsigned)((n + CHAIN_THREADS - 1) / CHAIN_THREADS), CHAIN_THREADS, 0, c->stream>>>(ch); }
+            SMW_CUDA(c, cudaGetLastError());
+            StageArgs a = base; a.in = P; a.kw = t + G; a.out = Q;
+            if (g + 1 < NG) { a.bmat = T->b_grp; a.nw = t + G; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); }
+            else { a.bmat = T->b_last; a.nw = t; a.rc_idx = (int)(L.rc_full + 4u * t); rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); }
+            std::swap(P, Q);
+            if (rc) return rc;
+        }
+        for (int r = 5; r <= 7 && !rc; r++) rc = full_round(r);
+        if (rc) return rc;
+        StageArgs a = base; a.in = P; a.kw = t; a.out = Q;
+        if (perm + 1 < n_perms) { a.bmat = T->b_full; a.nw = t; a.rc_idx = (int)L.rc_full; a.absorb_first = t - 1; rc = launch_stage<EPI_ABSORB_SBOX>(c, T, a, J.kclass); std::swap(P, Q); }
+        else if (J.kind == 0) { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT>(c, T, a, J.kclass); }
+        else { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT_LEAF>(c, T, a, J.kclass); }
+        if (rc) return rc;
+    }
+    return SMW_OK;
+}
+static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
+    Tables* T; int rc0 = ensure(c, p, &T); if (rc0) return rc0;
     const uint64_t batch = std::min<uint64_t>(batch_nodes(), (J.total + TILE_M - 1) / TILE_M * TILE_M);
     if (T->cap_nodes < batch) {
+        cudaStreamSynchronize(c->stream);
         cudaFree(T->buf_p); cudaFree(T->buf_q); cudaFree(T->dots); T->buf_p = T->buf_q = nullptr; T->dots = nullptr; T->cap_nodes = 0;
         const size_t tiles = (size_t)(batch / TILE_M);
         SMW_CUDA(c, cudaMalloc(&T->buf_p, tiles * MAX_KW * KSTEP_BYTES)); SMW_CUDA(c, cudaMalloc(&T->buf_q, tiles * MAX_KW * KSTEP_BYTES));
@@ -210,50 +280,23 @@ static int run_job(smw_ctx* c, smw_params* p, const Job& J) {
         T->cap_nodes = batch;
     }
     const size_t tile_stride = (size_t)MAX_KW * KSTEP_BYTES;
+    SideStream side(c);
     for (uint64_t node0 = 0; node0 < J.total; node0 += batch) {
         const uint64_t n = std::min<uint64_t>(batch, J.total - node0), n_tiles = (n + TILE_M - 1) / TILE_M;
-        uint8_t *P = T->buf_p, *Q = T->buf_q;
-        StageArgs base{}; base.in_tile_stride = tile_stride; base.out_tile_stride = tile_stride; base.tbl = p->d_tables52; base.rc_idx = -1; base.n_tiles = n_tiles;
-        base.B = J.B; base.leaves = J.R; base.node0 = node0; base.dots = T->dots; base.dots_stride = T->cap_nodes; base.nbytes = t;
-        auto full_round = [&](int round_next) -> int {          // P: x of a full round -> Q: x of the next one
-            StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_full; a.nw = t; a.out = Q; a.rc_idx = (int)(L.rc_full + (uint32_t)round_next * t);
-            int rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); std::swap(P, Q); return rc;
-        };
-        if (J.kind == 0) {
-            HeadArgs h{J.B, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full};
-            LaunchScope ls(c, J.kclass);
-            if (t == 17) k_tc_head<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
-            else k_tc_head<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
-        } else {
-            HeadLeafArgs h{J.R, node0, n, P, tile_stride, p->d_tables52, (int)L.rc_full, J.kind == 1 ? 0 : 1, J.tmpl, J.lane_f, J.lane_s};
-            LaunchScope ls(c, J.kclass);
-            if (t == 17) k_tc_head_leaf<17><<<(unsigned)n_tiles, dim3(TILE_M, 4), 0, c->stream>>>(h);
-            else k_tc_head_leaf<9><<<(unsigned)n_tiles, dim3(TILE_M, 3), 0, c->stream>>>(h);
+        const bool split = n_streams() == 2 && n_tiles >= 8ull * (uint64_t)T->n_sm && std::find(c->side.begin(), c->side.end(), c->stream) == c->side.end();   // not inside another fan-out
+        const uint64_t tiles0 = split ? (n_tiles + 1) / 2 : n_tiles, n0 = std::min<uint64_t>(n, tiles0 * TILE_M);
+        int rc = SMW_OK;
+        std::unique_ptr<ProfSpan> span;   // kernels of the two halves overlap: the profile gets ONE record for the batch (both events on the main stream)
+        if (split) span.reset(new ProfSpan(c, J.kclass, c->stream));
+        if (split) {                      // the second half first: it is enqueued on the side stream while the main stream is still empty
+            side.enter();
+            rc = run_sequence(c, p, T, J, node0 + n0, n - n0, T->buf_p + tiles0 * tile_stride, T->buf_q + tiles0 * tile_stride, T->dots + n0);
+            c->stream = side.main;
         }
-        SMW_CUDA(c, cudaGetLastError());
-        for (int perm = 0; perm < n_perms; perm++) {
-            int rc = 0;
-            for (int r = 1; r <= 3 && !rc; r++) rc = full_round(r);
-            if (rc) return rc;
-            { StageArgs a = base; a.in = P; a.kw = t; a.bmat = T->b_r3; a.nw = t + G; a.out = Q; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); std::swap(P, Q); if (rc) return rc; }
-            for (int g = 0; g < NG; g++) {
-                { ChainArgs ch{T->dots, (size_t)T->cap_nodes, n, P, tile_stride, t, G, T->gamma, p->d_tables52, (int)(L.rc_part + (uint32_t)g * G)};
-                  LaunchScope ls(c, J.kclass); k_tc_chain<<<(unsigned)((n + CHAIN_THREADS - 1) / CHAIN_THREADS), CHAIN_THREADS, 0, c->stream>>>(ch); }
-                SMW_CUDA(c, cudaGetLastError());
-                StageArgs a = base; a.in = P; a.kw = t + G; a.out = Q;
-                if (g + 1 < NG) { a.bmat = T->b_grp; a.nw = t + G; rc = launch_stage<EPI_WORDS>(c, T, a, J.kclass); }
-                else { a.bmat = T->b_last; a.nw = t; a.rc_idx = (int)(L.rc_full + 4u * t); rc = launch_stage<EPI_SBOX>(c, T, a, J.kclass); }
-                std::swap(P, Q);
-                if (rc) return rc;
-            }
-            for (int r = 5; r <= 7 && !rc; r++) rc = full_round(r);
-            if (rc) return rc;
-            StageArgs a = base; a.in = P; a.kw = t; a.out = Q;
-            if (perm + 1 < n_perms) { a.bmat = T->b_full; a.nw = t; a.rc_idx = (int)L.rc_full; a.absorb_first = t - 1; rc = launch_stage<EPI_ABSORB_SBOX>(c, T, a, J.kclass); std::swap(P, Q); }
-            else if (J.kind == 0) { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT>(c, T, a, J.kclass); }
-            else { a.bmat = T->b_final; a.nw = 1; rc = launch_stage<EPI_EMIT_LEAF>(c, T, a, J.kclass); }
-            if (rc) return rc;
-        }
+        if (!rc) rc = run_sequence(c, p, T, J, node0, n0, T->buf_p, T->buf_q, T->dots);
+        if (split) side.leave();
+        span.reset();
+        if (rc) return rc;
     }
     int err = 0;
     SMW_CUDA(c, cudaMemcpyAsync(&err, T->d_err, 4, cudaMemcpyDeviceToHost, c->stream));

@@ -465,10 +465,16 @@ template <int T> __global__ void __launch_bounds__(512) k_tc_head_leaf(const Hea
 // ------------------------------------------------------------------ chain: the G dependent S-boxes of one group of partial rounds
 // s_k = dot_k + sum_{m<k} gamma[k-1-m] x_m + rc_part[round0 + k],  x_k = s_k^5;  x_k -> k-step koff + k of the permutation's tile.
 // One thread per permutation; the group's x values stay in shared memory ([k][limb][thread], conflict-free).
-constexpr int CHAIN_THREADS = 128, MAX_G = 8;
+#ifndef SMW_TC_CHAIN_THREADS
+#define SMW_TC_CHAIN_THREADS 128
+#endif
+#ifndef SMW_TC_CHAIN_MINB
+#define SMW_TC_CHAIN_MINB 6      // 78 registers instead of 90, no spills: cfg2 755.4 -> 748.2 ms (profiles/r04h_tc_streams.txt)
+#endif
+constexpr int CHAIN_THREADS = SMW_TC_CHAIN_THREADS, MAX_G = 8;
 struct ChainArgs { const double* dots; size_t dots_stride; uint64_t n_perm; uint8_t* out; size_t out_tile_stride; int koff; int G;
                    const double* gamma; const uint32_t* tbl; int rc_idx; };
-__global__ void __launch_bounds__(CHAIN_THREADS) k_tc_chain(const ChainArgs g) {
+__global__ void __launch_bounds__(CHAIN_THREADS, SMW_TC_CHAIN_MINB) k_tc_chain(const ChainArgs g) {
     __shared__ double xs[MAX_G * 5 * CHAIN_THREADS];
     const uint64_t perm = (uint64_t)blockIdx.x * CHAIN_THREADS + threadIdx.x;
     if (perm >= g.n_perm) return;

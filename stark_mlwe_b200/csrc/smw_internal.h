@@ -70,7 +70,10 @@ struct smw_ctx {
     uint64_t collectives = 0;                    // NCCL collectives / grouped exchanges issued through this context
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
     bool prof_on = false;
-    struct ProfRec { int cls; cudaEvent_t a, b; };
+    // prof_span: launches inside a span are counted into it instead of being timed one by one (kernels of two streams overlap: their
+    // individual durations would add up to more than the wall time); n = launches the record stands for
+    int prof_span = -1;
+    struct ProfRec { int cls; cudaEvent_t a, b; uint64_t n = 1; };
     std::vector<ProfRec> prof;
     std::vector<cudaEvent_t> prof_pool;
 };
@@ -136,6 +139,7 @@ struct LaunchScope {
         c->launches++;
         nvtxRangePushA(KC_NAMES[cls < 8 ? cls : 7]);
         if (!c->prof_on) return;
+        if (c->prof_span >= 0) { c->prof[(size_t)c->prof_span].n++; return; }
         cudaEvent_t a;
         if (c->prof_pool.size() >= 2) { a = c->prof_pool.back(); c->prof_pool.pop_back(); b = c->prof_pool.back(); c->prof_pool.pop_back(); }
         else { cudaEventCreate(&a); cudaEventCreate(&b); }
@@ -143,6 +147,21 @@ struct LaunchScope {
         c->prof.push_back({cls, a, b});
     }
     ~LaunchScope() { if (b) cudaEventRecord(b, c->stream); nvtxRangePop(); }
+};
+// One timed record for a whole group of launches that run on several streams: both events go to `main` (the first before the streams
+// fork, the second after they have been joined), the launches in between are only counted.  No-op unless profiling is on.
+struct ProfSpan {
+    smw_ctx* c; cudaStream_t main; bool on = false;
+    ProfSpan(smw_ctx* ctx, int cls, cudaStream_t main_stream) : c(ctx), main(main_stream) {
+        if (!c->prof_on || c->prof_span >= 0) return;
+        cudaEvent_t a, b;
+        if (c->prof_pool.size() >= 2) { a = c->prof_pool.back(); c->prof_pool.pop_back(); b = c->prof_pool.back(); c->prof_pool.pop_back(); }
+        else { cudaEventCreate(&a); cudaEventCreate(&b); }
+        cudaEventRecord(a, main);
+        smw_ctx::ProfRec r; r.cls = cls; r.a = a; r.b = b; r.n = 0;
+        c->prof.push_back(r); c->prof_span = (int)c->prof.size() - 1; on = true;
+    }
+    ~ProfSpan() { if (on) { cudaEventRecord(c->prof[(size_t)c->prof_span].b, main); c->prof_span = -1; } }
 };
 
 // returns a device buffer of at least `bytes` for `slot` (valid until the next request for the same slot on this context)
