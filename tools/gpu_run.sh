@@ -65,7 +65,7 @@ PYEOF
     bench_short) timeout 600 python bench.py --no-fri --no-cpu --no-interp > $OUT/${TAG}_bench_short.json 2> $OUT/${TAG}_bench_short.err; python -c "import sys,json; d=json.loads(open('$OUT/${TAG}_bench_short.json').read().strip().splitlines()[-1]); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e'])" ;;
     fri_diag)   SMW_TRACE=1 timeout 300 python tools/fri_diag.py > $OUT/${TAG}_fri_diag.json 2> $OUT/${TAG}_fri_diag.err; cat $OUT/${TAG}_fri_diag.json; grep -v "^\[smw\] \(build_forest\|fri_free\)" $OUT/${TAG}_fri_diag.err | tail -60 ;;
     tc_streams) for lib in ${TCLIBS:-libsmw.so libsmw_ns3.so}; do for v in 1 2; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_STREAMS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib SMW_TC_STREAMS=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_streams.txt; done; done
-                SMW_TC_STREAMS=2 timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py tests/test_gpu_full_size.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_streams_tests.log 2>&1; tail -4 $OUT/${TAG}_tc_streams_tests.log ;;
+                SMW_LIB=$PWD/stark_mlwe_b200/${TESTLIB:-libsmw.so} timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py tests/test_gpu_full_size.py tests/test_gpu_fri_transcript.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_streams_tests.log 2>&1; tail -4 $OUT/${TAG}_tc_streams_tests.log ;;
     umma)       timeout 120 tools/_bin/umma_i8 ${UMMA_TILES:-16} $OUT/${TAG}_umma_dump.bin > $OUT/${TAG}_umma_i8.json 2> $OUT/${TAG}_umma_i8.err; echo "exit $?"; cat $OUT/${TAG}_umma_i8.json; tail -3 $OUT/${TAG}_umma_i8.err
                 timeout 120 python tools/umma_i8_check.py $OUT/${TAG}_umma_dump.bin | tee $OUT/${TAG}_umma_check.json; rm -f $OUT/${TAG}_umma_dump.bin ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
