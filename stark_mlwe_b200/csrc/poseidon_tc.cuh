@@ -91,6 +91,13 @@ SMW_DEV bool mbar_wait(uint64_t* b, uint32_t parity) {
         }
     }
 }
+#ifndef SMW_TC_PREFETCH
+#define SMW_TC_PREFETCH 1
+#endif
+// asks L2 for a contiguous global range ahead of the bulk copy that will bring it into shared memory
+SMW_DEV void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(src), "r"(bytes) : "memory");
+}
 SMW_DEV void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
@@ -248,6 +255,11 @@ __global__ void __launch_bounds__(STAGE_THREADS, 1) k_tc_stage(const StageArgs g
         for (uint64_t it = 0; it < my_pairs; it++) {
             const uint64_t tile0 = (blockIdx.x + it * gridDim.x) * PAIR;
             const int nt = (int)min((uint64_t)PAIR, g.n_tiles - tile0);
+            // The input words of a tile are resident for ALL of its chunks, so the copy of the next tile can only start when the last MMA of this
+            // one has retired, and the tile comes from HBM (the batch's tiles are far larger than L2): ~2-3 of the ~14 us a group-stage tile takes
+            // were exposed load time (profiles/r04k: tensor pipe 42 % active, L2 28 %).  The next tile is therefore requested into L2 one tile ahead.
+            if (SMW_TC_PREFETCH && it + 1 < my_pairs)
+                bulk_prefetch_l2(g.in + (blockIdx.x + (it + 1) * gridDim.x) * PAIR * g.in_tile_stride, (uint32_t)g.kw * KSTEP_BYTES);
             if (!mbar_wait(&S.a_empty, (uint32_t)(it & 1) ^ 1)) { atomicExch(g.err, 1); break; }
             mbar_expect_tx(&S.a_full, (uint32_t)(nt * g.kw) * KSTEP_BYTES);
             for (int tl = 0; tl < nt; tl++) bulk_g2s(S.a[tl], g.in + (tile0 + tl) * g.in_tile_stride, (uint32_t)g.kw * KSTEP_BYTES, &S.a_full);

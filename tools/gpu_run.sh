@@ -66,6 +66,11 @@ PYEOF
     fri_diag)   SMW_TRACE=1 timeout 300 python tools/fri_diag.py > $OUT/${TAG}_fri_diag.json 2> $OUT/${TAG}_fri_diag.err; cat $OUT/${TAG}_fri_diag.json; grep -v "^\[smw\] \(build_forest\|fri_free\)" $OUT/${TAG}_fri_diag.err | tail -60 ;;
     tc_streams) for lib in ${TCLIBS:-libsmw.so libsmw_ns3.so}; do for v in 1 2; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_STREAMS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib SMW_TC_STREAMS=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_streams.txt; done; done
                 SMW_LIB=$PWD/stark_mlwe_b200/${TESTLIB:-libsmw.so} timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py tests/test_gpu_full_size.py tests/test_gpu_fri_transcript.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_streams_tests.log 2>&1; tail -4 $OUT/${TAG}_tc_streams_tests.log ;;
+    ncu_tc2)    for kn in k_tc_chain k_tc_stageILi0; do
+                  SMW_TC_MIN=4096 SMW_TC_STREAMS=1 timeout 600 $NCU_FULL --kernel-name-base mangled -k regex:$kn -s 3 -c 1 -o $OUT/${TAG}_ncu_$kn -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri --no-interp > $OUT/${TAG}_ncu_$kn.out 2>&1
+                  ncu -i $OUT/${TAG}_ncu_$kn.ncu-rep --page details --csv > $OUT/${TAG}_ncu_${kn}_details.csv 2>/dev/null
+                  ncu -i $OUT/${TAG}_ncu_$kn.ncu-rep --page raw --csv > $OUT/${TAG}_ncu_${kn}_raw.csv 2>/dev/null; tail -2 $OUT/${TAG}_ncu_$kn.out | cut -c1-200
+                done ;;
     umma)       timeout 120 tools/_bin/umma_i8 ${UMMA_TILES:-16} $OUT/${TAG}_umma_dump.bin > $OUT/${TAG}_umma_i8.json 2> $OUT/${TAG}_umma_i8.err; echo "exit $?"; cat $OUT/${TAG}_umma_i8.json; tail -3 $OUT/${TAG}_umma_i8.err
                 timeout 120 python tools/umma_i8_check.py $OUT/${TAG}_umma_dump.bin | tee $OUT/${TAG}_umma_check.json; rm -f $OUT/${TAG}_umma_dump.bin ;;
     diag26)     timeout 1200 python tools/diag_2p26.py 24 25 26 > $OUT/${TAG}_diag_2p26.json 2> $OUT/${TAG}_diag_2p26.err; cat $OUT/${TAG}_diag_2p26.json; tail -5 $OUT/${TAG}_diag_2p26.err ;;
