@@ -47,14 +47,18 @@ constexpr int CHUNK_WORDS = EPI_SLOTS * WPS;              // output words per MM
 constexpr int B_BLOCK_MAX = CHUNK_WORDS * WCOLS * 32;     // 8192 bytes: one k-step of one chunk
 constexpr int MAX_KW = 25;                // k-steps (input words) per tile: 17 state words + a group of up to 8 S-box outputs
 #ifndef SMW_TC_KSUB
-#define SMW_TC_KSUB 4
+#define SMW_TC_KSUB 9
 #endif
-constexpr int KSUB = SMW_TC_KSUB;         // k-steps per ring stage: one bulk copy and one commit for KSUB MMAs (the issue loop, not the L2 stream, paced the kernel at KSUB = 1)
+// k-steps per ring stage: one bulk copy, one wait and one commit for KSUB MMAs.  The hand-over of a stage (mbarrier wait, fence, commit), not the L2
+// stream or the bytes in flight, paces the stages without S-boxes: cfg2 per step 799.8 ms at KSUB = 2 (ten stages), 733.0 at 4 (four stages; five stages: 741.6),
+// 731.1 at 5, 729.5 at 6, 725.5 at 9 (two stages of 54 KB: a chunk's 25 k-steps in three hand-overs) - profiles/r04m_tc_ring_variants.txt, r04n_tc_ring_stage_size.txt
+constexpr int KSUB = SMW_TC_KSUB;
 #ifdef SMW_TC_NSTAGE
 constexpr int NSTAGE = SMW_TC_NSTAGE;
 #else
-constexpr int NSTAGE = 112 * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words
+constexpr int NSTAGE = 112 * 1024 / (KSUB * B_BLOCK_MAX);   // ring stages: what 227 KB leave beside the resident input words (KSUB = 9: two)
 #endif
+static_assert(NSTAGE >= 2, "the matrix ring needs two stages");
 constexpr int EPI_WARPS = 4 * EPI_SLOTS;
 constexpr int STAGE_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int ACC_COLS = CHUNK_WORDS * WCOLS;             // <= 256 TMEM columns per accumulator stage: [word][32]

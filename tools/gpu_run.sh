@@ -64,7 +64,7 @@ PYEOF
                 SMW_TC_MIN=0 timeout 300 python tools/fri_bench.py 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_MIN=0 (interpreter)', {k: (round(x['ms'], 2), x['class_ms']) for k, x in d.items()})" | tee -a $OUT/${TAG}_fri_g9.txt ;;
     bench_short) timeout 600 python bench.py --no-fri --no-cpu --no-interp > $OUT/${TAG}_bench_short.json 2> $OUT/${TAG}_bench_short.err; python -c "import sys,json; d=json.loads(open('$OUT/${TAG}_bench_short.json').read().strip().splitlines()[-1]); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e'])" ;;
     fri_diag)   SMW_TRACE=1 timeout 300 python tools/fri_diag.py > $OUT/${TAG}_fri_diag.json 2> $OUT/${TAG}_fri_diag.err; cat $OUT/${TAG}_fri_diag.json; grep -v "^\[smw\] \(build_forest\|fri_free\)" $OUT/${TAG}_fri_diag.err | tail -60 ;;
-    tc_streams) for lib in ${TCLIBS:-libsmw.so libsmw_ns3.so}; do for v in 1 2; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_STREAMS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib SMW_TC_STREAMS=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_streams.txt; done; done
+    tc_streams) for lib in ${TCLIBS:-libsmw.so}; do for v in ${TCSTREAMS:-1 2}; do SMW_LIB=$PWD/stark_mlwe_b200/$lib SMW_TC_STREAMS=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib SMW_TC_STREAMS=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_streams.txt; done; done
                 SMW_LIB=$PWD/stark_mlwe_b200/${TESTLIB:-libsmw.so} timeout 600 python -m pytest tests/test_gpu_poseidon_tc.py tests/test_gpu_full_size.py tests/test_gpu_fri_transcript.py -m gpu -q -x --tb=short > $OUT/${TAG}_tc_streams_tests.log 2>&1; tail -4 $OUT/${TAG}_tc_streams_tests.log ;;
     ncu_tc2)    for kn in k_tc_chain k_tc_stageILi0; do
                   SMW_TC_MIN=4096 SMW_TC_STREAMS=1 timeout 600 $NCU_FULL --kernel-name-base mangled -k regex:$kn -s 3 -c 1 -o $OUT/${TAG}_ncu_$kn -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri --no-interp > $OUT/${TAG}_ncu_$kn.out 2>&1
