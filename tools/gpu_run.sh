@@ -2,7 +2,8 @@
 # One parameterised runner for a GPU lease (replaces the per-lease scripts of round 1):
 #   gpurun --timeout 1500 -- 'bash tools/gpu_run.sh <tag> <stage> [<stage> ...]'
 # Every stage writes gpurun_out/<tag>_<stage>.* ; a failing stage does not stop the later ones.
-# Stages: tests | tests_fast | smoke | bench | bench_ref | fri | kat | mf | launches | ncu_merkle | ncu_coop | ncu_ntt | sanitizer | umma | mgpu<N> | scale<N>
+# Stages: tests | tests_fast | smoke | bench | bench_short | bench_ref | fri | fri_g9 | fri_diag | kat | mf | e2e<K> | launches | launches_tc | ncu_merkle | ncu_coop | ncu_ntt |
+#         ncu_tc | ncu_tc2 | tc | tc_ab | tc_bench | tc_group | tc_batch | tc_streams (TCLIBS = tuning builds made with SMW_BUILD_SO / SMW_EXTRA_FLAGS) | sanitizer | umma | mgpu<N> | scale<N>
 set -u
 TAG=${1:?tag}; shift
 OUT=gpurun_out; mkdir -p $OUT
@@ -54,12 +55,11 @@ tot = sum(v[1] for v in d.values())
 for k, v in sorted(d.items(), key=lambda kv: -kv[1][1]): print("%-60s n=%4d  %9.3f ms  %5.1f%%" % (k[:60], v[0], v[1], 100 * v[1] / tot))
 PYEOF
                 ;;
-    tc_var)     for lib in libsmw.so libsmw_s6w1.so libsmw_s5w1.so; do SMW_LIB=$PWD/stark_mlwe_b200/$lib timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$lib', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_variants.txt; done ;;
     ncu_tc)     SMW_TC_MIN=4096 timeout 900 $NCU_FULL -k regex:k_tc_stage -s 1 -c 2 -o $OUT/${TAG}_ncu_tc_stage -f python bench.py --steps 1 --warmup 0 --log-n 16 --cols 16 --no-cpu --no-e2e --no-fri > $OUT/${TAG}_ncu_tc.out 2>&1
                 ncu -i $OUT/${TAG}_ncu_tc_stage.ncu-rep --page details --csv > $OUT/${TAG}_ncu_tc_stage_details.csv 2>/dev/null; tail -3 $OUT/${TAG}_ncu_tc.out ;;
     tc_bench)   SMW_TC_MIN=${TCMIN:-16384} timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('TC', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_bench.txt ;;
     tc_group)   for v in 8 4 2; do SMW_TC_GROUP=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_GROUP=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_group.txt; done ;;
-    tc_batch)   for v in 1048576 524288 262144 131072; do SMW_TC_BATCH=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_BATCH=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_batch.txt; done ;;
+    tc_batch)   for v in ${TCBATCHES:-1048576 524288 262144 131072}; do SMW_TC_BATCH=$v timeout 300 python bench.py --steps 2 --warmup 1 --no-fri --no-cpu --no-e2e --no-interp 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_BATCH=$v', 'value', d['value'], 'ms', d['ms_per_step'], d['roofline']['step_share_ms'])" | tee -a $OUT/${TAG}_tc_batch.txt; done ;;
     fri_g9)     for v in 6 5 4; do SMW_TC_GROUP9=$v timeout 300 python tools/fri_bench.py 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_GROUP9=$v', {k: (round(x['ms'], 2), x['class_ms']) for k, x in d.items()})" | tee -a $OUT/${TAG}_fri_g9.txt; done
                 SMW_TC_MIN=0 timeout 300 python tools/fri_bench.py 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('SMW_TC_MIN=0 (interpreter)', {k: (round(x['ms'], 2), x['class_ms']) for k, x in d.items()})" | tee -a $OUT/${TAG}_fri_g9.txt ;;
     bench_short) timeout 600 python bench.py --no-fri --no-cpu --no-interp > $OUT/${TAG}_bench_short.json 2> $OUT/${TAG}_bench_short.err; python -c "import sys,json; d=json.loads(open('$OUT/${TAG}_bench_short.json').read().strip().splitlines()[-1]); print('value', d['value'], 'ms', d['ms_per_step'], 'e2e', d['e2e'])" ;;
