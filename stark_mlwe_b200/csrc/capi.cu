@@ -30,6 +30,40 @@ int ctx_scratch(smw_ctx* c, int slot, size_t bytes, void** out) {
     *out = c->slot_ptr[slot];
     return SMW_OK;
 }
+// ---- arena pool (smw_internal.h) ----
+static constexpr size_t POOL_MIN = (size_t)1 << 20, POOL_MAX_FREE_BYTES = (size_t)24 << 30, POOL_MAX_FREE_BLOCKS = 16;
+void pool_release(smw_ctx* c) {
+    for (auto& b : c->pool_freelist) { c->pool_owned.erase(b.first); cudaFree(b.first); }
+    c->pool_freelist.clear(); c->pool_free_bytes = 0;
+}
+cudaError_t pool_malloc(smw_ctx* c, void** out, size_t bytes) {
+    *out = nullptr;
+    if (bytes < POOL_MIN) return cudaMalloc(out, bytes ? bytes : 1);
+    int best = -1;                                             // the smallest returned block that fits without wasting more than half of itself
+    for (int i = 0; i < (int)c->pool_freelist.size(); i++) {
+        const size_t cap = c->pool_freelist[i].second;
+        if (cap >= bytes && cap <= 2 * bytes && (best < 0 || cap < c->pool_freelist[best].second)) best = i;
+    }
+    if (best >= 0) {
+        *out = c->pool_freelist[best].first; c->pool_free_bytes -= c->pool_freelist[best].second;
+        c->pool_freelist.erase(c->pool_freelist.begin() + best);
+        return cudaSuccess;
+    }
+    cudaError_t e = cudaMalloc(out, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); pool_release(c); e = cudaMalloc(out, bytes); }      // give the pooled blocks back and try once more
+    if (e == cudaSuccess) c->pool_owned[*out] = bytes;
+    return e;
+}
+void pool_free(smw_ctx* c, void* p) {
+    if (!p) return;
+    auto it = c->pool_owned.find(p);
+    if (it == c->pool_owned.end()) { cudaFree(p); return; }
+    c->pool_freelist.push_back({p, it->second}); c->pool_free_bytes += it->second;
+    while (c->pool_freelist.size() > POOL_MAX_FREE_BLOCKS || c->pool_free_bytes > POOL_MAX_FREE_BYTES) {      // oldest first
+        auto b = c->pool_freelist.front(); c->pool_freelist.erase(c->pool_freelist.begin());
+        c->pool_free_bytes -= b.second; c->pool_owned.erase(b.first); cudaFree(b.first);
+    }
+}
 } // namespace smw
 
 namespace {
@@ -69,7 +103,8 @@ struct Out {
     }
     ~Out() { if (owned && d) { cudaStreamSynchronize(c->stream); cudaFree(d); } }
 };
-struct DevFree { std::vector<void*> v; cudaStream_t st; ~DevFree() { cudaStreamSynchronize(st); for (void* p : v) if (p) cudaFree(p); } };
+struct DevFree { std::vector<void*> v; cudaStream_t st; smw_ctx* pool = nullptr;      // pool != nullptr: blocks go back to the context's arena pool
+                 ~DevFree() { cudaStreamSynchronize(st); for (void* p : v) if (p) { if (pool) smw::pool_free(pool, p); else cudaFree(p); } } };
 int d2h(smw_ctx* c, void* host, const void* dev, size_t bytes) {
     SMW_CUDA(c, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
     SMW_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -213,7 +248,7 @@ int build_forest(smw_ctx* c, std::vector<ForestTree>& trees, uint32_t** arena_ou
         max_levels = std::max(max_levels, t.len.size());
     }
     uint32_t* arena = nullptr;
-    if (total) SMW_CUDA(c, cudaMalloc(&arena, total * FR));
+    if (total) SMW_CUDA(c, pool_malloc(c, (void**)&arena, total * FR));
     *arena_out = arena;
     { size_t off = 0; for (auto& t : trees) { t.lv.assign(1, t.leaves); for (size_t j = 1; j < t.len.size(); j++) { t.lv.push_back(arena + off * 8); off += t.len[j]; } } }
     struct Launch { smw_params* p; int arity; size_t seg0; int n; uint64_t total; };
@@ -277,7 +312,7 @@ int build_tree(smw_ctx* c, smw_params* p, int arity, uint64_t label, uint32_t* d
     uint32_t* arena = nullptr; std::vector<void*> defer;
     int rc = build_forest(c, f, &arena, defer);
     if (!defer.empty()) { cudaStreamSynchronize(c->stream); for (void* q : defer) cudaFree(q); }
-    if (rc) { cudaStreamSynchronize(c->stream); cudaFree(arena); if (own0) cudaFree(d_level0); return rc; }
+    if (rc) { cudaStreamSynchronize(c->stream); pool_free(c, arena); if (own0) cudaFree(d_level0); return rc; }
     smw_tree* t = tree_handle(c, f[0], own0); t->arena = arena;
     *out = t;
     return SMW_OK;
@@ -315,6 +350,7 @@ void smw_ctx_destroy(smw_ctx* c) {
     for (auto& kv : c->by_width) free_params_internal(kv.second);
     for (auto& r : c->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     for (auto e : c->prof_pool) cudaEventDestroy(e);
+    smw::pool_release(c); for (auto& kv : c->pool_owned) cudaFree(kv.first); c->pool_owned.clear();
     cudaFree(c->d_twiddles); for (int i = 0; i < smw_ctx::N_SLOTS; i++) cudaFree(c->slot_ptr[i]);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (auto st : c->side) cudaStreamDestroy(st);
@@ -555,7 +591,7 @@ void smw_tree_free(smw_tree* t) {
     if (!t) return;
     cudaSetDevice(t->ctx->device); cudaStreamSynchronize(t->ctx->stream);
     for (size_t i = 0; i < t->lv.size(); i++) if (t->owned[i]) cudaFree(t->lv[i]);
-    cudaFree(t->arena);
+    smw::pool_free(t->ctx, t->arena);
     delete t;
 }
 int32_t smw_merkle_commit_columns(smw_ctx* c, smw_params* p, int32_t arity, uint64_t label0, uint64_t label_stride,
@@ -927,7 +963,7 @@ void smw_fri_free(smw_fri* s) {
     Range rg("fri_free");
     cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
     for (auto* t : s->tree) smw_tree_free(t);
-    cudaFree(s->arena_f); cudaFree(s->arena_leaves); cudaFree(s->arena_levels);
+    smw::pool_free(s->ctx, s->arena_f); smw::pool_free(s->ctx, s->arena_leaves); smw::pool_free(s->ctx, s->arena_levels);
     cudaFree(s->d_z);
     delete s;
 }
@@ -948,7 +984,7 @@ int fri_commit_entries(smw_ctx* c, const std::vector<LayerEntry>& E, uint64_t le
     Range rg("fri.leaves+forest");
     smw_params* trp; int rc = smw_params_transcript_default(c, &trp); if (rc) return rc;
     size_t total = 0; for (auto& e : E) total += e.n_loc;
-    SMW_CUDA(c, cudaMalloc(&out.arena_leaves, total * FR));
+    SMW_CUDA(c, pool_malloc(c, (void**)&out.arena_leaves, total * FR));
     uint32_t* d_tmpl = nullptr; int lf = 0, ls = 0;
     std::vector<LeafSeg> hashed_segs, pair_segs; uint64_t hashed_total = 0, pair_total = 0; smw_params* pair_p = nullptr; bool pair_uniform = true;
     size_t off = 0;
@@ -1015,7 +1051,7 @@ int32_t smw_fri_build_transcript_from(smw_ctx* c, const void* f0, size_t n0, con
     std::vector<void*> defer;
     auto fail = [&](int code) { cudaStreamSynchronize(c->stream); for (void* q : defer) cudaFree(q); smw_fri_free(s.release()); return code; };
     { size_t total = 0; for (int l = 0; l <= L; l++) total += n[l];
-      cudaError_t e = cudaMalloc(&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri layers)"));
+      cudaError_t e = pool_malloc(c, (void**)&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri layers)"));
       size_t off = 0; for (int l = 0; l <= L; l++) { s->f[l] = s->arena_f + off * 8; off += n[l]; } }
     { cudaError_t e = cudaMalloc(&s->d_z, (size_t)(L + 1) * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc")); }
     { cudaError_t e = cudaMemcpyAsync(s->f[0], f0, n0 * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream); if (e != cudaSuccess) return fail(cuda_err(c, e, "copy f0")); }
@@ -1102,7 +1138,7 @@ struct smw_fri_shard {
 void smw_fri_shard_free(smw_fri_shard* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream);
-    cudaFree(s->arena_f); cudaFree(s->arena_leaves); cudaFree(s->arena_levels);
+    smw::pool_free(s->ctx, s->arena_f); smw::pool_free(s->ctx, s->arena_leaves); smw::pool_free(s->ctx, s->arena_levels);
     delete s;
 }
 int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, size_t n0, size_t first_index, const uint64_t* schedule, int32_t L,
@@ -1121,7 +1157,7 @@ int32_t smw_fri_shard_build(smw_ctx* c, const void* f0_slice, size_t n_local, si
     const int n_f = (K <= L) ? K + 1 : K;         // local slices of f_0 .. f_K (f_K only when K <= L)
     std::vector<uint32_t*> f(L + 2, nullptr); std::vector<size_t> n_loc(L + 1, 0); std::vector<uint64_t> first(L + 1, 0);
     { size_t total = 0; for (int l = 0; l < n_f; l++) total += n[l] / G;
-      cudaError_t e = cudaMalloc(&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri slices)"));
+      cudaError_t e = pool_malloc(c, (void**)&s->arena_f, total * FR); if (e != cudaSuccess) return fail(cuda_err(c, e, "cudaMalloc(fri slices)"));
       size_t off = 0; for (int l = 0; l < n_f; l++) { f[l] = s->arena_f + off * 8; off += n[l] / G; } }
     for (int l = 0; l <= L; l++) { n_loc[l] = n[l] / G; first[l] = (uint64_t)(first_index / (n0 / n[l])); }     // slice of layer l: [first_l, first_l + n_l / G)
     { cudaError_t e = cudaMemcpyAsync(f[0], f0_slice, n_local * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream);
@@ -1181,13 +1217,13 @@ int32_t smw_fri_roots_sharded(smw_ctx* c, smw_comm* m, const void* chunks, size_
     while (K <= L && n[K] % V == 0 && (K == L || (n[K] / V) % mm[K] == 0)) K++;
     const int n_f = (K <= L) ? K + 1 : K;
     std::vector<size_t> n_loc(L + 1, 0); for (int l = 0; l <= L; l++) n_loc[l] = n[l] / V;
-    DevFree fr{{}, c->stream};
+    DevFree fr{{}, c->stream, c};
     std::vector<void*> defer; struct DeferFree { std::vector<void*>& v; cudaStream_t st; ~DeferFree() { cudaStreamSynchronize(st); for (void* q : v) cudaFree(q); } } dfree{defer, c->stream};
     // local slices: layer l holds the C slices back to back, so ONE fold launch per layer covers them all (a slice of a local
     // layer is a whole number of fold blocks)
     std::vector<uint32_t*> f(L + 2, nullptr);
     { size_t total = 0; for (int l = 0; l < n_f; l++) total += (size_t)C * n_loc[l];
-      uint32_t* arena; SMW_CUDA(c, cudaMalloc(&arena, total * FR)); fr.v.push_back(arena);
+      uint32_t* arena; SMW_CUDA(c, pool_malloc(c, (void**)&arena, total * FR)); fr.v.push_back(arena);
       size_t off = 0; for (int l = 0; l < n_f; l++) { f[l] = arena + off * 8; off += (size_t)C * n_loc[l]; } }
     SMW_CUDA(c, cudaMemcpyAsync(f[0], chunks, (size_t)C * n_chunk * FR, mem == SMW_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
     uint32_t* d_z = nullptr; SMW_CUDA(c, cudaMalloc(&d_z, (size_t)(L + 1) * FR)); fr.v.push_back(d_z);
@@ -1210,8 +1246,8 @@ int32_t smw_fri_roots_sharded(smw_ctx* c, smw_comm* m, const void* chunks, size_
     const size_t off_tail = send_n, tail_n = (K <= L) ? n_loc[K] : 0;
     send_n += (size_t)C * tail_n;
     uint32_t *d_send, *d_recv;
-    SMW_CUDA(c, cudaMalloc(&d_send, send_n * FR)); fr.v.push_back(d_send);
-    SMW_CUDA(c, cudaMalloc(&d_recv, send_n * (size_t)world * FR)); fr.v.push_back(d_recv);
+    SMW_CUDA(c, pool_malloc(c, (void**)&d_send, send_n * FR)); fr.v.push_back(d_send);
+    SMW_CUDA(c, pool_malloc(c, (void**)&d_recv, send_n * (size_t)world * FR)); fr.v.push_back(d_recv);
     { std::vector<uint64_t> hdr((size_t)C * 4, 0); for (int q = 0; q < C; q++) hdr[(size_t)q * 4] = first_indices[q];
       SMW_CUDA(c, cudaMemcpyAsync(d_send, hdr.data(), (size_t)C * FR, cudaMemcpyHostToDevice, c->stream)); }
     for (int l = 0; l < K; l++) for (int q = 0; q < C; q++)
@@ -1238,7 +1274,7 @@ int32_t smw_fri_roots_sharded(smw_ctx* c, smw_comm* m, const void* chunks, size_
     uint64_t* d_idx = nullptr; uint32_t* d_tops = nullptr;
     if (tops_n) {
         SMW_CUDA(c, cudaMalloc(&d_idx, tops_n * 8)); fr.v.push_back(d_idx);
-        SMW_CUDA(c, cudaMalloc(&d_tops, tops_n * FR)); fr.v.push_back(d_tops);
+        SMW_CUDA(c, pool_malloc(c, (void**)&d_tops, tops_n * FR)); fr.v.push_back(d_tops);
         SMW_CUDA(c, cudaMemcpyAsync(d_idx, idx.data(), tops_n * 8, cudaMemcpyHostToDevice, c->stream));
         rc = launch_gather(c, d_recv, d_idx, tops_n, d_tops); if (rc) return rc;
     }

@@ -69,6 +69,13 @@ struct smw_ctx {
     uint64_t launches = 0;                       // kernels launched through this context (bench.py's gpu_launches)
     uint64_t collectives = 0;                    // NCCL collectives / grouped exchanges issued through this context
     // optional per-kernel-class device timing (CUDA events on this context's stream), for bench.py's roofline
+    // Arena pool: the large temporaries of the fold-and-recommit entry points (FRI layers, leaf digests, tree levels, exchange buffers) are
+    // handed back here instead of to cudaFree and reused by the next call of a similar size.  cudaMalloc / cudaFree of GB-sized blocks cost
+    // 10-200 ms each and varied from call to call (cfg5 FRI at 2^26: 1.51-1.77 s on one GPU, 649 ms on four where the kernels need ~400).
+    // Blocks are only returned after the stream has drained (every owner synchronises before freeing), so reuse is stream-safe.
+    std::map<void*, size_t> pool_owned;                       // every live block that came from pool_malloc: capacity in bytes
+    std::vector<std::pair<void*, size_t>> pool_freelist;      // returned blocks, oldest first
+    size_t pool_free_bytes = 0;
     bool prof_on = false;
     // prof_span: launches inside a span are counted into it instead of being timed one by one (kernels of two streams overlap: their
     // individual durations would add up to more than the wall time); n = launches the record stands for
@@ -166,6 +173,12 @@ struct ProfSpan {
 
 // returns a device buffer of at least `bytes` for `slot` (valid until the next request for the same slot on this context)
 int ctx_scratch(smw_ctx* c, int slot, size_t bytes, void** out);
+cudaError_t pool_malloc(smw_ctx* c, void** out, size_t bytes);   // blocks >= 1 MiB are pooled, smaller ones are plain cudaMalloc
+void pool_free(smw_ctx* c, void* p);                              // the caller has synchronised the stream(s) that used p; unknown pointers go to cudaFree
+void pool_release(smw_ctx* c);                                     // cudaFree every returned block
+cudaError_t pool_malloc(smw_ctx* c, void** out, size_t bytes);   // blocks >= 1 MiB are pooled, smaller ones are plain cudaMalloc
+void pool_free(smw_ctx* c, void* p);                              // the caller has synchronised the stream(s) that used p; unknown pointers go to cudaFree
+void pool_release(smw_ctx* c);                                     // cudaFree every returned block
 
 // NCCL entry points, bound by dlopen (comm.cu)
 struct NcclApi {
