@@ -4,7 +4,8 @@ oracle's permutation.  Test infrastructure (imports oracle/): run `python tools/
  2. byte GEMM with REDUCED constants: column c of output word i = sum_j sum_a byte_a(x_j) * byte_c((W_ij * 2^(8a)) mod p), 32 columns per
     word, value < 2^274, congruent to (W x)_i mod p; cheap reduction: y = low254 + p - top * (p - 2^254)  in [0, 2^255)."""
 import sys
-sys.path.insert(0, "/root/repo")
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import oracle as O
 
 P = 0x40000000000000000000000000000000224698fc0994a8dd8c46eb2100000001
