@@ -60,6 +60,10 @@ int32_t smw_ctx_create(int32_t device, smw_ctx** out);
 int32_t smw_ctx_create_on_stream(int32_t device, void* cuda_stream, smw_ctx** out);
 void smw_ctx_destroy(smw_ctx* ctx);
 int32_t smw_ctx_sync(smw_ctx* ctx);
+/* The context keeps the large device temporaries of the fold-and-recommit entry points (FRI layers, leaf digests, tree levels, exchange
+ * buffers: up to 16 blocks / 24 GiB) for the next call instead of returning them to the driver after every call.  This gives all idle
+ * blocks back now; smw_ctx_destroy does the same.  Not in the reference (it has no device). */
+int32_t smw_ctx_release_cached(smw_ctx* ctx);
 const char* smw_last_error(const smw_ctx* ctx);
 uint64_t smw_ctx_launch_count(const smw_ctx* ctx);   /* kernels launched so far through this context */
 void* smw_ctx_stream(const smw_ctx* ctx);

@@ -53,7 +53,7 @@ def load():
         "smw_fri_roots_sharded": [vp, vp, vp, sz, i32, vp, sz, vp, i32, u64, i32, vp],
         "smw_ntt_cyclic_to_chunks": [vp, vp, vp, vp, i32],
         "smw_mf_commit_phase_sharded": [vp, vp, u64, vp, sz, i32, vp, vp, vp],
-        "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp],
+        "smw_ctx_create": [i32, vp], "smw_ctx_create_on_stream": [i32, vp, vp], "smw_ctx_destroy": [vp], "smw_ctx_sync": [vp], "smw_ctx_release_cached": [vp],
         "smw_last_error": [vp], "smw_ctx_launch_count": [vp], "smw_ctx_stream": [vp],
         "smw_ctx_profile_enable": [vp, i32], "smw_ctx_profile_read": [vp, vp, vp, i32], "smw_diag_mac_rate": [vp, vp, vp], "smw_diag_fp64_rate": [vp, vp, vp], "smw_diag_pipe_rate": [vp, i32, vp], "smw_diag_perm_fp64_ops": [vp, vp], "smw_diag_f52_dot": [vp, vp, vp, sz, i32, vp, i32], "smw_index_from_seed": [vp, vp, sz, u64, vp, i32], "smw_ali_sample_z_beta": [vp, vp, vp, u64, vp, vp], "smw_scale_powers": [vp, vp, sz, vp, i32], "smw_dft_strided": [vp, vp, i32, sz, sz, i32],
         "smw_fri_build_transcript_from": [vp, vp, sz, vp, i32, u64, u64, i32, vp],

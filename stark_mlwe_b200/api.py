@@ -76,6 +76,10 @@ class Context:
     def sync(self):
         self.check(self.L.smw_ctx_sync(self.h))
 
+    def release_cached(self):
+        """give the idle blocks of the context's arena pool (large temporaries kept between calls) back to the driver"""
+        self.check(self.L.smw_ctx_release_cached(self.h))
+
     def launch_count(self):
         return int(self.L.smw_ctx_launch_count(self.h))
 

@@ -360,6 +360,7 @@ void smw_ctx_destroy(smw_ctx* c) {
     delete c;
 }
 int32_t smw_ctx_sync(smw_ctx* c) { if (!c) return SMW_ERR_INVALID_ARG; SMW_CUDA(c, cudaStreamSynchronize(c->stream)); return SMW_OK; }
+int32_t smw_ctx_release_cached(smw_ctx* c) { if (!c) return SMW_ERR_INVALID_ARG; cudaSetDevice(c->device); SMW_CUDA(c, cudaStreamSynchronize(c->stream)); smw::pool_release(c); return SMW_OK; }
 const char* smw_last_error(const smw_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
 uint64_t smw_ctx_launch_count(const smw_ctx* c) { return c ? c->launches : 0; }
 void* smw_ctx_stream(const smw_ctx* c) { return c ? (void*)c->stream : nullptr; }

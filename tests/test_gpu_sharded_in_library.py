@@ -67,6 +67,28 @@ def test_single_rank_forms_equal_the_plain_calls(ctx, smw, O, rnd):
     assert np.array_equal(out.cpu().numpy().view(np.uint64)[0], O.ntt(x))
 
 
+def test_arena_pool_reuse_and_release(ctx, smw, O, rnd):
+    """the large temporaries of the commit phase come from the context's arena pool: a second call reuses the blocks of the first, a call after
+    smw_ctx_release_cached allocates afresh, a differently sized call in between takes other blocks - the roots never change"""
+    n0, sched = 1 << 16, [16, 16, 8]           # 2 MiB layers: above the pool's 1 MiB threshold
+    f0 = rnd(31337, n0)
+    prm = smw.FriProverParams(sched, 0xDEEFBAAD)
+    want = O.FriProverState(f0, sched, 0xDEEFBAAD).roots()
+    chunks = f0.reshape(4, n0 // 4, 4)
+    firsts = [i * (n0 // 4) for i in range(4)]
+    for step in range(4):
+        got = smw.fri_roots_sharded(ctx, None, chunks, firsts, n0, prm)
+        assert np.array_equal(got, want), "call %d" % step
+        if step == 1:
+            ctx.release_cached()
+        if step == 2:                           # another size in between
+            g0 = rnd(4141, 1 << 15)
+            st = smw.fri_build_transcript(ctx, g0, smw.FriProverParams([2] * 15, 7))
+            assert np.array_equal(st.roots(), O.FriProverState(g0, [2] * 15, 7).roots())
+            del st
+    ctx.release_cached()
+
+
 def test_multi_gpu_data_plane_under_torchrun():
     """>= 2 GPUs on the box: the NCCL path itself (all-gather of caps, all-to-all of the four-step NTT, per-round cap gathers of
     the sum-check) against the single-GPU results, two ranks"""
