@@ -137,6 +137,14 @@ SMW_DEV F52 acc52_reduce_add2(Acc52& A, uint32_t n_terms, const F52& s, const F5
 // accumulator STARTS at minus that amount (a constant folded into the first addition) instead of having it subtracted from the high
 // word of every column before the reduction; with no addends on top, the 3-input additions of two 2^52-biased zeros go as well.
 // ~60 ALU-pipe instructions less per x^5 (the ALU pipe is the busiest pipe of those epilogues, profiles/r04a_ncu_tc_stage_summary.txt).
+// (low 52 bits of x) as an exact double.  ptxas has no three-input logic instruction with TWO immediates, so `(hi & 0xfffff) | 0x43300000` written with
+// constants compiles to two LOP3 on the ALU pipe (the busiest pipe of the S-box epilogues).  The exponent word is therefore read from a device variable
+// the compiler cannot fold: one LOP3 (a & imm | register).  ~30 ALU instructions less per x^5.
+static __device__ uint32_t g_exp52_hi = 0x43300000u;
+SMW_DEV double u52_to_double_m(uint64_t x, uint32_t exp_hi) {
+    const uint32_t hi = ((uint32_t)(x >> 32) & 0xfffffu) | exp_hi;
+    return __longlong_as_double((long long)(((uint64_t)hi << 32) | (x & 0xffffffffull))) - 0x1p52;
+}
 SMW_DEV void acc52_init_biased(Acc52& A) {
     constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
     constexpr uint32_t rlo[10] = {1, 2, 3, 3, 3, 2, 1, 0, 0, 0}, rhi[10] = {0, 1, 2, 3, 3, 3, 2, 1, 0, 0};
@@ -161,11 +169,11 @@ SMW_DEV void acc52_sqr_b(Acc52& A, const F52& a) {
         }
 }
 // (A + M p) / 2^260 for an accumulator started by acc52_init_biased and holding one product; limbs < 2^52
-SMW_DEV F52 acc52_reduce_b(Acc52& A) {
+SMW_DEV F52 acc52_reduce_b(Acc52& A, uint32_t exp_hi) {
     const double p0 = (double)P52_0, p1 = (double)P52_1, p2 = (double)P52_2, pinv = (double)PINV52;
 #pragma unroll
     for (int i = 0; i < 5; i++) {
-        const double tl = u52_to_double(A.c[i] & M52);
+        const double tl = u52_to_double_m(A.c[i], exp_hi);
         const double mh = __fma_rz(tl, pinv, 0x1p104);
         const double ml = __fma_rz(tl, pinv, (0x1p104 + 0x1p52) - mh);
         const uint64_t m = (uint64_t)__double_as_longlong(ml) & M52;
@@ -184,7 +192,7 @@ SMW_DEV F52 acc52_reduce_b(Acc52& A) {
 #pragma unroll
     for (int k = 0; k < 5; k++) {
         const uint64_t v = A.c[5 + k] + carry;
-        r.v[k] = u52_to_double(k < 4 ? (v & M52) : v);
+        r.v[k] = k < 4 ? u52_to_double_m(v, exp_hi) : u52_to_double(v);
         carry = v >> 52;
     }
     return r;

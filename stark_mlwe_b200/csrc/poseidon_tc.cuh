@@ -190,9 +190,10 @@ SMW_DEV void store_word_bytes(uint8_t* tile, int kstep, int row, const F52& x) {
 // x^5 (poseidon/src/lib.rs:24-29): two squarings with 15 limb products each and one general product
 SMW_DEV F52 sbox52(const F52& s) {
     Acc52 A;
-    acc52_sqr_b(A, s); const F52 x2 = acc52_reduce_b(A);
-    acc52_sqr_b(A, x2); const F52 x4 = acc52_reduce_b(A);
-    acc52_mul_b(A, x4, s); return acc52_reduce_b(A);
+    const uint32_t exp_hi = g_exp52_hi;
+    acc52_sqr_b(A, s); const F52 x2 = acc52_reduce_b(A, exp_hi);
+    acc52_sqr_b(A, x2); const F52 x4 = acc52_reduce_b(A, exp_hi);
+    acc52_mul_b(A, x4, s); return acc52_reduce_b(A, exp_hi);
 }
 // a canonical external-form element (x * 2^256 mod p, < p) -> limbs of 16 * that (= x * 2^260 mod p up to a multiple of p, < 2^259)
 SMW_DEV F52 ext_times16(const uint32_t* src) {
