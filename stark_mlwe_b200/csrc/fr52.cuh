@@ -145,9 +145,19 @@ SMW_DEV double u52_to_double_m(uint64_t x, uint32_t exp_hi) {
     const uint32_t hi = ((uint32_t)(x >> 32) & 0xfffffu) | exp_hi;
     return __longlong_as_double((long long)(((uint64_t)hi << 32) | (x & 0xffffffffull))) - 0x1p52;
 }
+#ifndef SMW_SBOX_M46_FP
+#define SMW_SBOX_M46_FP 0
+#endif
+// the top limb of a reduced value: its column can still carry exponent bits above bit 52 only if the bookkeeping is wrong, so it is taken as is
+SMW_DEV double u52_to_double_top(uint64_t v) { return u52_to_double(v); }
 SMW_DEV void acc52_init_biased(Acc52& A) {
     constexpr uint32_t nlo[10] = {1, 2, 3, 4, 5, 4, 3, 2, 1, 0}, nhi[10] = {0, 1, 2, 3, 4, 5, 4, 3, 2, 1};
+#if SMW_SBOX_M46_FP
+    // the 2^46 limb of p is split on the FP64 pipe like the others: one more low pattern in columns 4..8, one more high pattern in columns 5..9
+    constexpr uint32_t rlo[10] = {1, 2, 3, 3, 4, 3, 2, 1, 1, 0}, rhi[10] = {0, 1, 2, 3, 3, 4, 3, 2, 1, 1};
+#else
     constexpr uint32_t rlo[10] = {1, 2, 3, 3, 3, 2, 1, 0, 0, 0}, rhi[10] = {0, 1, 2, 3, 3, 3, 2, 1, 0, 0};
+#endif
 #pragma unroll
     for (int k = 0; k < 10; k++) {
         const uint32_t bias = ((nlo[k] + rlo[k]) * 0x433u + (nhi[k] + rhi[k]) * 0x467u) << 20;
@@ -176,7 +186,6 @@ SMW_DEV F52 acc52_reduce_b(Acc52& A, uint32_t exp_hi) {
         const double tl = u52_to_double_m(A.c[i], exp_hi);
         const double mh = __fma_rz(tl, pinv, 0x1p104);
         const double ml = __fma_rz(tl, pinv, (0x1p104 + 0x1p52) - mh);
-        const uint64_t m = (uint64_t)__double_as_longlong(ml) & M52;
         const double md = ml - 0x1p52;
         const double h0 = __fma_rz(md, p0, 0x1p104), l0 = __fma_rz(md, p0, (0x1p104 + 0x1p52) - h0);
         const double h1 = __fma_rz(md, p1, 0x1p104), l1 = __fma_rz(md, p1, (0x1p104 + 0x1p52) - h1);
@@ -185,14 +194,21 @@ SMW_DEV F52 acc52_reduce_b(Acc52& A, uint32_t exp_hi) {
         A.c[i + 1] += (uint64_t)__double_as_longlong(h0) + (uint64_t)__double_as_longlong(l1) + (A.c[i] >> 52);
         A.c[i + 2] += (uint64_t)__double_as_longlong(h1) + (uint64_t)__double_as_longlong(l2);
         A.c[i + 3] += (uint64_t)__double_as_longlong(h2);
+#if SMW_SBOX_M46_FP
+        const double h4 = __fma_rz(md, 0x1p46, 0x1p104), l4 = __fma_rz(md, 0x1p46, (0x1p104 + 0x1p52) - h4);      // m 2^46 = (m >> 6) 2^52 + (m & 63) 2^46
+        A.c[i + 4] += (uint64_t)__double_as_longlong(l4);
+        A.c[i + 5] += (uint64_t)__double_as_longlong(h4);
+#else
+        const uint64_t m = (uint64_t)__double_as_longlong(ml) & M52;
         A.c[i + 4] += (m & 63ull) << 46;
         A.c[i + 5] += m >> 6;
+#endif
     }
     F52 r; uint64_t carry = 0;
 #pragma unroll
     for (int k = 0; k < 5; k++) {
         const uint64_t v = A.c[5 + k] + carry;
-        r.v[k] = k < 4 ? u52_to_double_m(v, exp_hi) : u52_to_double(v);
+        r.v[k] = k < 4 ? u52_to_double_m(v, exp_hi) : u52_to_double_top(v);
         carry = v >> 52;
     }
     return r;
