@@ -229,3 +229,35 @@ def fri_roots_sharded_chunks(backend, chunks, first_indices, n0, world, schedule
         assert f_k.shape[0] == sizes[K]
         roots.extend(list(backend.build_from(f_k, list(schedule[K:]), seed_z, K)))
     return np.stack([np.asarray(r, dtype=np.uint64).reshape(4) for r in roots])
+
+
+# ----------------------------------------------------------------------------- Merkle-folded sum-check over a range-sharded table
+def mf_commit_phase_sharded_host(backend, table_slice, ds_tag, rank, world, gather=all_gather_rows):
+    """Backend-agnostic mirror of the slice logic of smw_mf_commit_phase_sharded (csrc/capi.cu; the product runs it inside the library over NCCL):
+    the commit loop of SumCheckMFProver (channel/src/lib.rs:600-657) for a table of world * len(table_slice) evaluations held as contiguous
+    slices.  Round i: every rank hashes its slice up to the last level made of whole sibling groups (DS positions offset by the slice start,
+    merkle/src/lib.rs:168-173), ONE all-gather of those cap nodes, every rank finishes the top, so root_i and r_i = H(i, root_i)
+    (channel/src/lib.rs:592-598) exist everywhere without a broadcast; the fold pairs (2j, 2j + 1) never straddle slices.  With one element
+    per rank left the layer is gathered and the remaining rounds run replicated.  Returns (roots (k + 1, 4), r (k, 4), final (4,))."""
+    cur = np.ascontiguousarray(table_slice, dtype=np.uint64).reshape(-1, 4)
+    n_local = len(cur)
+    assert n_local and n_local & (n_local - 1) == 0 and world & (world - 1) == 0, "power-of-two slices on a power-of-two number of ranks"
+    k = (n_local * world).bit_length() - 1
+    roots, rs = [], []
+    while world > 1 and len(cur) >= 2:
+        nodes, level = backend.cap(cur, ds_tag, rank * len(cur))
+        root = backend.root_from_level(gather(nodes), level, ds_tag)
+        r = backend.challenge(len(rs), root)
+        roots.append(root); rs.append(r)
+        cur = backend.fold(cur, r)
+    if world > 1:
+        cur = gather(cur[:1])                                   # one element per rank, in rank order = global order
+    while True:
+        roots.append(backend.root_from_level(cur, 0, ds_tag))
+        if len(cur) == 1:
+            break
+        r = backend.challenge(len(rs), roots[-1])
+        rs.append(r)
+        cur = backend.fold(cur, r)
+    assert len(roots) == k + 1 and len(rs) == k
+    return np.stack(roots), (np.stack(rs) if rs else np.zeros((0, 4), np.uint64)), cur[0].copy()

@@ -112,3 +112,24 @@ class OracleNttBackend:
                 acc = O.fr_add(acc, O.fr_mul(a[q * stride:q * stride + count], np.tile(wp[(q * k) % G].reshape(1, 4), (count, 1))))
             out[k * stride:k * stride + count] = acc
         return out
+
+
+class OracleMfBackend:
+    """one rank's work in the range-sharded Merkle-folded sum-check (shard.mf_commit_phase_sharded_host): arity-16 trees with the commitment
+    default parameters and tree_label = ds_tag (commitment/src/lib.rs:85-90), r_i from (i, root_i), the pairwise fold"""
+
+    def __init__(self):
+        self.params = O.Params.commitment_default()
+
+    def cap(self, cur, ds_tag, first):
+        return _levels_up(self.params, 16, ds_tag, cur, 0, first, True)
+
+    def root_from_level(self, nodes, level, ds_tag):
+        top, _ = _levels_up(self.params, 16, ds_tag, nodes, level, 0, False)
+        return top[0]
+
+    def challenge(self, i, root):
+        return O.mf_round_challenge_from_root(i, root)
+
+    def fold(self, cur, r):
+        return O.mf_fold(cur, r)

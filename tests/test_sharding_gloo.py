@@ -154,3 +154,44 @@ def test_distributed_ntt_then_sharded_fri(O, world, log_n, schedule):
             lo = M * k1 + r * (M // world)
             assert np.array_equal(got[r][0][k1], X[lo:lo + M // world]), "rank %d chunk %d" % (r, k1)
         assert np.array_equal(got[r][1], want_roots)
+
+
+# ----------------------------------------------------------------------------- Merkle-folded sum-check over a range-sharded table
+def _mf_worker(rank, world, port, k, ds_tag, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle import oracle as O
+    from oracle_shard_backend import OracleMfBackend
+    O.lib(); O.set_threads(1)
+    n = 1 << k
+    table = O.StdRng.seed_from_u64(7000 + k).fr_rand(n)         # every rank derives the same table, keeps its slice only
+    m = n // world
+    out = shard.mf_commit_phase_sharded_host(OracleMfBackend(), table[rank * m:(rank + 1) * m], ds_tag, rank, world)
+    q.put((rank, out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,k", [(2, 1), (2, 6), (4, 9), (2, 10)])
+def test_range_sharded_mf_commit_phase_matches_single_process(O, world, k):
+    """roots of every folded layer, every r_i and the final evaluation equal the single-process commit loop (channel/src/lib.rs:600-657) on
+    every rank; slices of 1 (k = 1 on two ranks), of fewer than 16 leaves, of whole subtrees (k = 9 on four ranks: 128 leaves per rank) and mixed"""
+    ds_tag = 0x5EED
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_mf_worker, args=(r, world, port, k, ds_tag, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    roots, rs, fin = O.mf_commit_phase(O.StdRng.seed_from_u64(7000 + k).fr_rand(1 << k), ds_tag)
+    for r in range(world):
+        g_roots, g_rs, g_fin = got[r]
+        assert np.array_equal(g_roots, roots), "roots, rank %d" % r
+        assert np.array_equal(g_rs, rs), "challenges, rank %d" % r
+        assert np.array_equal(g_fin, fin), "final evaluation, rank %d" % r
